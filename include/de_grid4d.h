@@ -1,0 +1,171 @@
+/*
+ * de_grid4d.h -- C ABI of libde_grid4d.so, the B200 (sm_100a) implementation of
+ * DeepEarth's Grid4D multi-resolution hash-grid spacetime encoder.
+ *
+ * The reference has no FFI for this path: its boundary is two Python nn.Modules
+ * (SURVEY.md section 8b).  Every entry point below therefore names the reference
+ * Python symbol whose work it replaces; deepearth_b200/{hash_encoding,encoders,
+ * geo2xyz}.py bind them through ctypes (see INTEGRATION.md for the stub a
+ * reference maintainer would add).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless the
+ *     argument name ends in _host (level descriptors are read on the host and
+ *     travel to the kernels as launch parameters -- no device allocation, no
+ *     global state, re-entrant);
+ *   - `stream` is a cudaStream_t / CUstream passed as void*; nothing synchronises;
+ *   - return value: 0 on success, a negative DE_E* code for argument errors,
+ *     a positive cudaError_t for launch errors; de_last_error() gives the text
+ *     for the calling thread;
+ *   - there is no CPU implementation behind any of these.
+ */
+#ifndef DE_GRID4D_H
+#define DE_GRID4D_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DE_ABI_VERSION 1
+
+/* status codes (negative = caller error) */
+#define DE_OK 0
+#define DE_EINVAL (-1)      /* bad argument value                                  */
+#define DE_EUNSUPPORTED (-2) /* combination the kernels are not instantiated for   */
+#define DE_EALIGN (-3)      /* pointer / stride alignment requirement violated     */
+
+/* element types */
+#define DE_F32 0
+#define DE_F16 1
+#define DE_F64 2
+
+/* flags */
+#define DE_INTERP_NEAREST 0u /* floor cell only: models/hash_encoding.py:57-72     */
+#define DE_INTERP_LINEAR 1u  /* 2^D-corner multilinear (decomposed Grid4D mode)    */
+#define DE_INTERP_MASK 1u
+
+#define DE_MAX_DIMS 4
+#define DE_MAX_LEVELS_PER_CALL 256
+
+/*
+ * One resolution level of one grid.  A "grid" is a D-dimensional hash grid over a
+ * subset of the coordinate columns (xyz -> dim={0,1,2}; xyt -> {0,1,3}; yzt ->
+ * {1,2,3}; xzt -> {0,2,3}; the reference's temporal encoder -> D=1, dim={3}).
+ * Replaces one iteration of the level loop at models/hash_encoding.py:87-93 and
+ * the nn.Embedding it indexes (:38-41).
+ */
+typedef struct de_level_desc {
+    const void* table;   /* (table_size, F) row-major entries, dtype = table_dtype  */
+    float* grad_table;   /* (table_size, F) fp32 accumulators; backward only        */
+    uint32_t table_size; /* T                                                       */
+    uint32_t resolution; /* integer R; coords are scaled by (float)R in fp32        */
+    uint32_t out_col;    /* first column of this level in the feature row           */
+    uint8_t n_dims;      /* D in 1..4                                               */
+    uint8_t dim[DE_MAX_DIMS]; /* coordinate column feeding each grid dimension      */
+    uint8_t dense;       /* 1: index = sum cell_d*(R+1)^d (requires (R+1)^D <= T)   */
+    uint8_t mask_id;     /* 0 none, 1 mask_a (spatial), 2 mask_b (temporal)         */
+    uint8_t reserved;
+} de_level_desc;
+
+int de_abi_version(void);
+const char* de_last_error(void);
+
+/* Number of interpolation corners per level for the given flags and D. */
+int de_corners(uint32_t flags, int n_dims);
+
+/*
+ * Hash / dense cell indices -- replaces MultiResolutionHashEncoding.hash_coords
+ * (models/hash_encoding.py:47-74) for every level in one launch.
+ * indices layout: [level][corner][point] int64, corner count = de_corners().
+ * All levels must share n_dims.
+ */
+int de_grid4d_hash_indices(const de_level_desc* levels_host, int n_levels,
+                           const float* coords, int64_t n_points, int coord_stride,
+                           uint32_t flags, int64_t* indices, void* stream);
+
+/*
+ * Forward encode -- replaces MultiResolutionHashEncoding.forward
+ * (models/hash_encoding.py:76-96) and, with levels from several grids plus the two
+ * row masks, the feature half of Grid4DEncoder.forward (models/encoders.py:68-82).
+ *   out[p, out_col + f] = mask(p) * out_scale * sum_k w_k(p) * table[idx_k(p)][f]
+ * coords: (n_points, coord_stride) fp32; out: rows of out_stride floats.
+ * mask_a / mask_b: optional (n_points,) bytes, 0 zeroes the level's features
+ * (models/encoders.py:73-79); pass NULL for none.
+ * levels_per_group: how many consecutive levels one CTA handles (0 = auto); the
+ * launch walks groups in order so a group's tables stay L2 resident.
+ */
+int de_grid4d_forward(const de_level_desc* levels_host, int n_levels,
+                      const float* coords, int64_t n_points, int coord_stride,
+                      int table_dtype, int n_features, float out_scale,
+                      const uint8_t* mask_a, const uint8_t* mask_b,
+                      float* out, int64_t out_stride,
+                      uint32_t flags, int levels_per_group, void* stream);
+
+/*
+ * Backward -- replaces autograd's aten::embedding_dense_backward for the tables
+ * (SURVEY.md section 3.2): grad_table[idx_k(p)][f] += mask(p) * w_k(p) *
+ * grad_out[p, out_col + f], accumulated with vector fp32 reductions.  grad_table
+ * buffers must be zeroed (or hold the running sum) by the caller.  Coordinates
+ * receive no gradient, as in the reference (graph cut at hash_encoding.py:61).
+ */
+int de_grid4d_backward(const de_level_desc* levels_host, int n_levels,
+                       const float* coords, int64_t n_points, int coord_stride,
+                       int n_features,
+                       const uint8_t* mask_a, const uint8_t* mask_b,
+                       const float* grad_out, int64_t grad_stride,
+                       uint32_t flags, int levels_per_group, void* stream);
+
+/*
+ * fp32 master tables -> fp16 working tables, dst = half(src * scale), one launch
+ * for all levels (level i: src = levels_host[i].table (fp32), dst =
+ * dst_tables[i]).  dst_tables_host: host array of n_levels device pointers.
+ */
+int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_features,
+                     void* const* dst_tables_host, float scale, void* stream);
+
+/*
+ * Geodetic prologue -- replaces GeospatialConverter.geodetic_to_xyz position
+ * branch (geospatial/geo2xyz.py:146-160) + xyz_to_norm with a pre-fitted bounding
+ * box (:327-332, utils.py:54-77) + the spec's time normalisation
+ * (SPECIFICATIONS.MD:765), fused into one pass.
+ *   geo: (n,3) [lat deg, lon deg, alt m] fp64 or fp32 (geo_dtype)
+ *   t:   (n,) fp64 or fp32 (t_dtype) or NULL (t column written as 0)
+ *   bbox_min_host/bbox_span_host: 3 doubles each; t_range_host: {t_min, t_max}
+ *   xyzt: (n,4) fp32 out; ecef: optional (n,3) fp64 out (NULL to skip)
+ */
+int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t_dtype,
+                     const double* bbox_min_host, const double* bbox_span_host,
+                     const double* t_range_host,
+                     float* xyzt, double* ecef, int64_t n_points, void* stream);
+
+/*
+ * Bounding box of ECEF positions of a geodetic batch -- replaces
+ * GeospatialConverter.update_bbox / BoundingBox.from_points
+ * (geo2xyz.py:305-320, data_structures.py:95-100).  minmax: 6 doubles on the
+ * device {min_x,min_y,min_z,max_x,max_y,max_z}; the caller initialises them to
+ * +inf/-inf (or a running box) -- the kernel folds the batch in with atomics.
+ */
+int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n_points,
+                void* stream);
+
+/* fp64 sum of an fp32 buffer into *result (device, caller-zeroed): bench/e2e checksum. */
+int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
+
+/*
+ * Gather / reduction peak probes used to define the "gather roofline"
+ * (SURVEY.md section 8d).  table: working set of n_entries entries of entry_bytes
+ * (4, 8 or 16); each of n_threads threads issues `per_thread` independent random
+ * accesses (xorshift addresses, optional x-pair pattern).  mode 0 = load,
+ * 1 = red.add.f32 vector.  sink: >= 4 bytes.
+ */
+int de_probe_gather(void* table, int64_t n_entries, int entry_bytes, int mode,
+                    int64_t n_threads, int per_thread, int pair_pattern,
+                    void* sink, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DE_GRID4D_H */

@@ -1,0 +1,244 @@
+/*
+ * grid4d_oracle.c -- CPU ORACLE (test infrastructure, NOT product code).
+ *
+ * A plain-C restatement of the reference algorithm for the Grid4D hash-grid
+ * encoder path.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline
+ * leg may load this; nothing under deepearth_b200/ may.
+ *
+ * Parity status
+ *   - NEAREST mode ("Mode R") restates /root/reference/models/hash_encoding.py
+ *     line by line and is PINNED: tests/test_oracle_golden.py checks it against
+ *     fixtures produced by running the unmodified reference classes
+ *     (tests/golden/make_golden.py).
+ *   - LINEAR mode ("Mode G", decomposed xyz/xyt/yzt/xzt grids with multilinear
+ *     interpolation and dense-index fallback) has NO implementation under
+ *     /root/reference (spec text only, SPECIFICATIONS.MD:1068-1200; the upstream
+ *     JiaweiXu8/Grid4D + torch-ngp gridencoder is un-vendored and un-pinned), so
+ *     its interpolation arithmetic is "PARITY UNPINNED": it is checked against the
+ *     math stated below, with the per-corner hash pinned to the reference's
+ *     hash_coords and the nearest-corner collapse pinned to Mode R.
+ *   - geo2xyz restates geospatial/geo2xyz.py and is PINNED against fixtures from
+ *     the reference GeospatialConverter.
+ *
+ * Stated math for one level (resolution R, table size T, grid dims d=0..D-1 fed by
+ * coordinate columns dim[d]):
+ *     s_d   = fl32(c[dim[d]] * fl32(R))                 hash_encoding.py:58
+ *     g_d   = (int64) floorf(s_d)                        hash_encoding.py:61
+ *     w_d   = fl32(s_d - floorf(s_d))                    (LINEAR only; exact)
+ *   corner k (bit d of k = offset o_d in {0,1}); NEAREST has the single corner o=0:
+ *     cell_d = g_d + o_d
+ *     hashed:  h = XOR_d (cell_d * prime_d)  in wrapping int64,
+ *              primes = {1, 2654435761, 805459861, 3674653429}  hash_encoding.py:64-69
+ *     dense:   h = SUM_d cell_d * (R+1)^d    (allowed only if (R+1)^D <= T)
+ *     idx    = h mod T, Python floor-mod, in [0,T)           hash_encoding.py:72
+ *     wk     = fl32(...fl32(u_0 * u_1) * ... u_{D-1}),  u_d = o_d ? w_d : fl32(1 - w_d)
+ *   feature f:  acc = 0; for k ascending: acc = fmaf(wk, table[idx_k][f], acc)
+ *               out[p][out_col+f] = fl32(fl32(acc * out_scale) * mask)
+ *   NEAREST:    out = table[idx_0][f] * out_scale * mask  (pure gather, :92)
+ *   backward:   grad[idx_k][f] += mask * wk * grad_out[p][out_col+f]
+ *               (embedding_dense_backward for NEAREST; accumulated here in fp64)
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define ORC_F32 0
+#define ORC_F16 1
+
+typedef struct orc_level {
+    int64_t table_off; /* offset of this level's table, in entries, from the base */
+    int32_t T;
+    int32_t R;
+    int32_t out_col;
+    int32_t D;
+    int32_t dim[4];
+    int32_t dense;
+    int32_t mask_id; /* 0 none, 1 mask_a, 2 mask_b */
+} orc_level;
+
+static const uint64_t ORC_PRIMES[4] = {1ull, 2654435761ull, 805459861ull, 3674653429ull};
+
+static inline int64_t floor_mod(int64_t h, int64_t T) {
+    int64_t r = h % T;
+    return r < 0 ? r + T : r;
+}
+
+static inline float half_to_float(uint16_t h) {
+    uint32_t sign = (uint32_t)(h & 0x8000u) << 16;
+    uint32_t exp = (h >> 10) & 0x1fu;
+    uint32_t man = h & 0x3ffu;
+    uint32_t bits;
+    if (exp == 0) {
+        if (man == 0) {
+            bits = sign;
+        } else { /* subnormal: value = man * 2^-24 */
+            float v = (float)man * 5.9604644775390625e-8f;
+            memcpy(&bits, &v, 4);
+            bits |= sign;
+        }
+    } else if (exp == 31) {
+        bits = sign | 0x7f800000u | (man << 13);
+    } else {
+        bits = sign | ((exp + 112u) << 23) | (man << 13);
+    }
+    float f;
+    memcpy(&f, &bits, 4);
+    return f;
+}
+
+/* cell coordinates g_d and fractional weights w_d of one point at one level */
+static inline void cell_of(const orc_level* lv, const float* c, int64_t g[4], float w[4]) {
+    const float Rf = (float)lv->R;
+    for (int d = 0; d < lv->D; ++d) {
+        float s = c[lv->dim[d]] * Rf; /* hash_encoding.py:58 (fp32 multiply) */
+        float fl = floorf(s);         /* :61 */
+        g[d] = (int64_t)fl;
+        w[d] = s - fl;
+    }
+}
+
+static inline int64_t index_of(const orc_level* lv, const int64_t g[4], int corner) {
+    int64_t h = 0;
+    if (lv->dense) {
+        int64_t stride = 1;
+        for (int d = 0; d < lv->D; ++d) {
+            int64_t cell = g[d] + ((corner >> d) & 1);
+            h += cell * stride;
+            stride *= (int64_t)lv->R + 1;
+        }
+    } else {
+        for (int d = 0; d < lv->D; ++d) { /* hash_encoding.py:66-69 */
+            uint64_t cell = (uint64_t)(g[d] + ((corner >> d) & 1));
+            h ^= (int64_t)(cell * ORC_PRIMES[d]);
+        }
+    }
+    return floor_mod(h, (int64_t)lv->T); /* :72 */
+}
+
+static inline float weight_of(const orc_level* lv, const float w[4], int corner) {
+    float wk = 1.0f;
+    for (int d = 0; d < lv->D; ++d) {
+        float u = ((corner >> d) & 1) ? w[d] : (1.0f - w[d]);
+        wk = (d == 0) ? u : wk * u;
+    }
+    return wk;
+}
+
+static inline float mask_of(const orc_level* lv, const uint8_t* ma, const uint8_t* mb, int64_t p) {
+    if (lv->mask_id == 1 && ma) return ma[p] ? 1.0f : 0.0f;
+    if (lv->mask_id == 2 && mb) return mb[p] ? 1.0f : 0.0f;
+    return 1.0f;
+}
+
+int orc_corners(int linear, int D) { return linear ? (1 << D) : 1; }
+
+/* indices[level][corner][point] */
+void orc_hash_indices(const orc_level* lv, int n_levels, const float* coords, int64_t n,
+                      int stride, int linear, int64_t* indices) {
+    for (int l = 0; l < n_levels; ++l) {
+        const int C = orc_corners(linear, lv[l].D);
+        int64_t base = 0;
+        for (int j = 0; j < l; ++j) base += (int64_t)orc_corners(linear, lv[j].D) * n;
+#pragma omp parallel for schedule(static)
+        for (int64_t p = 0; p < n; ++p) {
+            int64_t g[4];
+            float w[4];
+            cell_of(&lv[l], coords + p * stride, g, w);
+            for (int k = 0; k < C; ++k) indices[base + (int64_t)k * n + p] = index_of(&lv[l], g, k);
+        }
+    }
+}
+
+void orc_forward(const orc_level* lv, int n_levels, const float* coords, int64_t n, int stride,
+                 const void* tables, int table_dtype, int F, float out_scale,
+                 const uint8_t* mask_a, const uint8_t* mask_b, float* out, int64_t out_stride,
+                 int linear) {
+#pragma omp parallel for schedule(static)
+    for (int64_t p = 0; p < n; ++p) {
+        for (int l = 0; l < n_levels; ++l) {
+            const orc_level* L = &lv[l];
+            int64_t g[4];
+            float w[4];
+            cell_of(L, coords + p * stride, g, w);
+            const float m = mask_of(L, mask_a, mask_b, p);
+            const int C = orc_corners(linear, L->D);
+            for (int f = 0; f < F; ++f) {
+                float acc = 0.0f;
+                for (int k = 0; k < C; ++k) {
+                    int64_t e = (L->table_off + index_of(L, g, k)) * F + f;
+                    float v = table_dtype == ORC_F16 ? half_to_float(((const uint16_t*)tables)[e])
+                                                     : ((const float*)tables)[e];
+                    if (linear)
+                        acc = fmaf(weight_of(L, w, k), v, acc);
+                    else
+                        acc = v;
+                }
+                float o = acc;
+                if (out_scale != 1.0f) o = o * out_scale;
+                out[p * out_stride + L->out_col + f] = o * m; /* encoders.py:73-79 */
+            }
+        }
+    }
+}
+
+/* grad_tables: fp64 accumulators, same entry layout as tables (table_off, F). */
+void orc_backward(const orc_level* lv, int n_levels, const float* coords, int64_t n, int stride,
+                  int F, const uint8_t* mask_a, const uint8_t* mask_b, const float* grad_out,
+                  int64_t grad_stride, double* grad_tables, int linear) {
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int l = 0; l < n_levels; ++l) { /* levels own disjoint tables: race free */
+        const orc_level* L = &lv[l];
+        const int C = orc_corners(linear, L->D);
+        for (int64_t p = 0; p < n; ++p) {
+            int64_t g[4];
+            float w[4];
+            cell_of(L, coords + p * stride, g, w);
+            const float m = mask_of(L, mask_a, mask_b, p);
+            for (int k = 0; k < C; ++k) {
+                const int64_t e = (L->table_off + index_of(L, g, k)) * F;
+                const float wk = linear ? weight_of(L, w, k) : 1.0f;
+                for (int f = 0; f < F; ++f) {
+                    float go = grad_out[p * grad_stride + L->out_col + f] * m;
+                    grad_tables[e + f] += (double)wk * (double)go;
+                }
+            }
+        }
+    }
+}
+
+/*
+ * Geodetic prologue: geospatial/geo2xyz.py:146-160 (WGS-84 geodetic -> ECEF, fp64),
+ * :327-332 + utils.py:54-77 (bbox normalisation with 0.5 for degenerate spans),
+ * SPECIFICATIONS.MD:765 (time normalisation).  geo is fp64 (n,3); t fp64 (n,) or NULL.
+ */
+void orc_geo2xyzt_norm(const double* geo, const double* t, const double bbox_min[3],
+                       const double bbox_span[3], const double t_range[2], float* xyzt,
+                       double* ecef, int64_t n) {
+    const double A = 6378137.0;                  /* geo2xyz.py:98  */
+    const double Fl = 1.0 / 298.257223563;       /* :99            */
+    const double E2 = 2.0 * Fl - Fl * Fl;        /* :100           */
+    const double D2R = 0.017453292519943295769236907684886; /* torch.deg2rad constant */
+#pragma omp parallel for schedule(static)
+    for (int64_t p = 0; p < n; ++p) {
+        const double lat = geo[3 * p + 0] * D2R, lon = geo[3 * p + 1] * D2R, alt = geo[3 * p + 2];
+        const double sl = sin(lat), cl = cos(lat), so = sin(lon), co = cos(lon);
+        const double N = A / sqrt(1.0 - E2 * (sl * sl)); /* :153 */
+        double xyz[3];
+        xyz[0] = ((N + alt) * cl) * co;                  /* :157 */
+        xyz[1] = ((N + alt) * cl) * so;                  /* :158 */
+        xyz[2] = (N * (1.0 - E2) + alt) * sl;            /* :159 */
+        for (int d = 0; d < 3; ++d) {
+            if (ecef) ecef[3 * p + d] = xyz[d];
+            const double span = bbox_span[d];
+            double v = fabs(span) < 1e-9 ? 0.5 : (xyz[d] - bbox_min[d]) / span; /* utils.py:54-77 */
+            xyzt[4 * p + d] = (float)v;
+        }
+        double tv = 0.0;
+        if (t) {
+            const double tspan = t_range[1] - t_range[0];
+            tv = fabs(tspan) < 1e-9 ? 0.5 : (t[p] - t_range[0]) / tspan;
+        }
+        xyzt[4 * p + 3] = (float)tv;
+    }
+}
