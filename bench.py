@@ -1,0 +1,438 @@
+#!/usr/bin/env python
+"""bench.py -- Grid4D hash-encode forward+backward throughput (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c1r] [--impl reference]
+
+A "step" is one pass of the hot path over one batch of synthetic points: zero the table-gradient
+buffer, forward encode (de_grid4d_forward), backward scatter (de_grid4d_backward) and -- at N>1 -- the
+NCCL all-reduce of the flat gradient buffer.  Per-GPU work is fixed as N grows (weak scaling): points
+shard across ranks, tables are replicated.
+
+Workloads (BASELINE.json configs):
+  c2  (default) decomposed xyz/xyt/yzt/xzt x 16 levels x 2 feat, T=2^19, 2^22 uniform points per GPU,
+      fp16 working tables, fp32 output and gradients                       [configs[1]]
+  c3  same grids with T=2^22 (HBM-resident tables), 2^24 Florida-clustered points run through the
+      geo2xyz prologue first                                               [configs[2]]
+  c1r the reference's own Grid4DEncoder geometry (xyz 16 levels T=2^19 + t 8 levels T=2^17, nearest,
+      fp32 tables), 2^22 points                                            [configs[0] geometry on GPU]
+
+One JSON line on stdout (rank 0).  `value` times the C-ABI calls with device-resident inputs;
+`e2e` times the public nn.Module API with pinned-host coordinates copied in and a scalar read back.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "grid4d_hash_encode_fwd_bwd_mpoints_per_s"
+UNIT = "Mpoints/s"
+
+WORKLOADS = {
+    # name: (mode, T, log2 points/GPU, coords, table dtype)
+    "c2": dict(mode="decomposed", T=2 ** 19, log2_points=22, coords="uniform", table_dtype="float16",
+               desc="configs[1]: 4 grids (xyz/xyt/yzt/xzt) x 16 levels x 2 feat, T=2^19/level, 2^22 points/GPU, fp16 tables, fp32 grads"),
+    "c3": dict(mode="decomposed", T=2 ** 22, log2_points=24, coords="florida", table_dtype="float16",
+               desc="configs[2]: 4 grids x 16 levels x 2 feat, T=2^22/level (HBM resident), 2^24 Florida-clustered points/GPU"),
+    "c1r": dict(mode="reference", T=2 ** 19, log2_points=22, coords="uniform", table_dtype="float32",
+                desc="reference Grid4DEncoder geometry (xyz L16 T=2^19 + t L8 T=2^17, nearest, fp32 tables), 2^22 points/GPU"),
+}
+
+
+def algorithmic_bytes_per_point(n_level_rows: int, corners: int, F: int, table_bytes: int):
+    """fwd = 16 + G*L*(C*F*s_t + F*4); bwd = 16 + G*L*(F*4 + C*F*4)."""
+    fwd = 16 + n_level_rows * (corners * F * table_bytes + F * 4)
+    bwd = 16 + n_level_rows * (F * 4 + corners * F * 4)
+    return fwd, bwd
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            parts = [p.strip() for p in r.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                smax.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# workload construction
+# ---------------------------------------------------------------------------------------------------
+def build_config(wl):
+    import deepearth_b200 as de
+    res = [2 ** i for i in range(4, 20)]
+    if wl["mode"] == "decomposed":
+        return de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=wl["T"],
+                                  n_spatial_levels=16, n_temporal_levels=16, spatial_resolutions=res,
+                                  temporal_resolutions=res, grid4d_mode="decomposed",
+                                  grid4d_table_dtype=wl["table_dtype"])
+    return de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=wl["T"])
+
+
+def make_coords(wl, n, device, seed):
+    g = torch.Generator(device=device).manual_seed(seed)
+    if wl["coords"] == "uniform":
+        return torch.rand((n, 4), device=device, generator=g)
+    # Florida-clustered geodetic points pushed through the geo2xyz prologue kernel
+    import deepearth_b200 as de
+    from _synth import FLORIDA_BBOX_GEO as B, FLORIDA_T_RANGE
+    K = 64
+    cu = torch.rand((K, 2), device=device, generator=g, dtype=torch.float64)
+    clat = B["south"] + (B["north"] - B["south"]) * cu[:, 0]
+    clon = B["west"] + (B["east"] - B["west"]) * cu[:, 1]
+    w = 1.0 / torch.arange(1, K + 1, device=device, dtype=torch.float64)
+    which = torch.multinomial(w / w.sum(), n, replacement=True, generator=g)
+    lat = clat[which] + 0.1 * torch.randn(n, device=device, generator=g, dtype=torch.float64)
+    lon = clon[which] + 0.1 * torch.randn(n, device=device, generator=g, dtype=torch.float64)
+    alt = 50.0 * torch.rand(n, device=device, generator=g, dtype=torch.float64)
+    t = FLORIDA_T_RANGE[0] + (FLORIDA_T_RANGE[1] - FLORIDA_T_RANGE[0]) * torch.rand(n, device=device, generator=g, dtype=torch.float64)
+    geo = torch.stack([lat, lon, alt], 1)
+    # bbox = the Central-Florida box at alt 0..50 m, fitted once from its 8 corners (+ edge midpoints)
+    conv = de.GeospatialConverter(device=str(device), t_range=FLORIDA_T_RANGE)
+    lats = torch.linspace(B["south"], B["north"], 9, dtype=torch.float64, device=device)
+    lons = torch.linspace(B["west"], B["east"], 9, dtype=torch.float64, device=device)
+    alts = torch.tensor([B["alt_min"], B["alt_max"]], dtype=torch.float64, device=device)
+    conv.update_bbox(torch.cartesian_prod(lats, lons, alts))
+    return conv.geodetic_to_xyzt_norm(geo, t)
+
+
+class Job:
+    """Device-resident state of one rank: module, flat gradient buffer, inputs, level plan."""
+
+    def __init__(self, wl, device, seed, n_points):
+        import deepearth_b200 as de
+        self.de = de
+        self.wl = wl
+        self.device = device
+        self.n = n_points
+        torch.manual_seed(1234)                       # identical (replicated) tables on every rank
+        self.enc = de.Grid4DEncoder(build_config(wl)).to(device)
+        self.plan = self.enc._plan()
+        self.weights = [w for e in self.enc._encoders for w in e.weights()]
+        self.F = self.plan.n_features
+        self.linear = self.plan.linear
+        if self.plan.table_dtype == torch.float16:
+            self.table_ptrs = [p for e in self.enc._encoders for p in e.working_ptrs()]
+        else:
+            self.table_ptrs = [w.data_ptr() for w in self.weights]
+        self.flat_grad = torch.zeros(self.plan.grad_numel, dtype=torch.float32, device=device)
+        self.grad_ptrs = [self.flat_grad.data_ptr() + 4 * o for o in self.plan.grad_offsets]
+        self.coords = make_coords(wl, n_points, device, seed)
+        g = torch.Generator(device=device).manual_seed(seed + 1)
+        self.gout = torch.randn((n_points, self.plan.out_cols), device=device, generator=g)
+        self.out = torch.empty((n_points, self.plan.out_cols), dtype=torch.float32, device=device)
+        corners = 8 if self.linear else 1
+        tb = 2 if self.plan.table_dtype == torch.float16 else 4
+        self.bytes_fwd, self.bytes_bwd = algorithmic_bytes_per_point(len(self.plan.specs), corners, self.F, tb)
+        self.out_scale = 1.0 / self.plan.table_scale if self.plan.table_scale != 1.0 else 1.0
+
+    def forward(self):
+        from deepearth_b200 import functional as Fn
+        Fn.encode_forward(self.plan.specs, self.coords, self.table_ptrs, self.plan.table_dtype, self.F,
+                          self.plan.out_cols, self.linear, self.out_scale, out=self.out,
+                          levels_per_group=self.plan.levels_per_group)
+
+    def backward(self):
+        from deepearth_b200 import functional as Fn
+        Fn.encode_backward(self.plan.specs, self.coords, self.gout, self.grad_ptrs, self.F, self.linear,
+                           levels_per_group=self.plan.bwd_levels_per_group)
+
+    def n_launches_per_step(self):
+        # one launch per run of equal-D levels (<= 64) for forward and for backward
+        runs, prev = 0, None
+        cnt = 0
+        for s in self.plan.specs:
+            if len(s.dims) != prev or cnt == 64:
+                runs += 1
+                prev, cnt = len(s.dims), 0
+            cnt += 1
+        return 2 * runs
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU baseline (the reference is PyTorch eager on CPU; oracle/grid4d_torch.py issues the same ATen ops)
+# ---------------------------------------------------------------------------------------------------
+def cpu_baseline_run(wl, log2_sample, steps, warmup):
+    from oracle.grid4d_torch import RefGrid4DFeatures, grid4d_forward
+    n = 2 ** log2_sample
+    torch.manual_seed(1234)
+    threads = torch.get_num_threads()
+    g = torch.Generator().manual_seed(99)
+    xyzt = torch.rand((n, 4), generator=g)
+    res = [2 ** i for i in range(4, 20)]
+    if wl["mode"] == "decomposed":
+        T = wl["T"]
+        dims_list = [(0, 1, 2), (0, 1, 3), (1, 2, 3), (0, 2, 3)]
+        specs = [(d, R, T, (R + 1) ** 3 <= T) for d in dims_list for R in res]
+        tabs = [torch.nn.Parameter((torch.rand((T, 2), generator=g) * 2e-4 - 1e-4)) for _ in specs]
+        gout = torch.randn((n, 128), generator=g)
+
+        def step():
+            for t in tabs:
+                t.grad = None
+            out = grid4d_forward(xyzt, tabs, specs, linear=True)
+            out.backward(gout)
+    else:
+        model = RefGrid4DFeatures(hash_table_size=wl["T"])
+        gout = torch.randn((n, 48), generator=g)
+
+        def step():
+            model.zero_grad(set_to_none=True)
+            model(xyzt).backward(gout)
+    for _ in range(warmup):
+        step()
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        step()
+        times.append(time.perf_counter() - t0)
+    sec = float(np.mean(times))
+    return {"value": n / sec / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{steps} fwd+bwd steps of 2^{log2_sample} uniform points, same grids/levels/T as the GPU arm, "
+                      f"fp32 tables, PyTorch eager CPU ops (oracle/grid4d_torch.py), {threads} threads",
+            "ms_per_step": sec * 1e3}
+
+
+def run_reference_arm(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    log2_sample = 16 if wl["mode"] == "decomposed" else 18
+    if wl["T"] > 2 ** 20:
+        log2_sample = 15
+    cb = cpu_baseline_run(wl, log2_sample, max(1, args.steps), max(1, args.warmup))
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "description": wl["desc"], "sample": cb["sample"]},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+def run_gpu_arm(args, wl):
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU port)")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    from deepearth_b200 import functional as Fn
+
+    n = 2 ** (args.log2_points if args.log2_points else wl["log2_points"])
+    job = Job(wl, device, seed=1234 + rank, n_points=n)
+    if args.levels_per_group:
+        job.plan.levels_per_group = args.levels_per_group
+    if args.bwd_levels_per_group:
+        job.plan.bwd_levels_per_group = args.bwd_levels_per_group
+
+    def step(ev=None):
+        job.flat_grad.zero_()
+        if ev:
+            ev[0].record()
+        job.forward()
+        if ev:
+            ev[1].record()
+        job.backward()
+        if ev:
+            ev[2].record()
+        if world > 1:
+            dist.all_reduce(job.flat_grad)
+            if ev:
+                ev[3].record()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_start.record()
+    for k in range(args.steps):
+        step(evs[k])
+    t_end.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    total_ms = t_start.elapsed_time(t_end)
+    fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+    bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
+    ar_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in evs])) if world > 1 else 0.0
+    if world > 1:
+        t = torch.tensor([total_ms], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t)
+    ms_per_step = total_ms / args.steps
+    value = world * n / (ms_per_step * 1e-3) / 1e6
+
+    # ---- end to end through the public nn.Module API, pinned-host coordinates in, scalar out --------
+    host = job.coords.cpu().pin_memory()
+    params = job.weights
+    del job.out      # the module allocates its own output
+    torch.cuda.empty_cache()
+
+    def e2e_step():
+        for p in params:
+            p.grad = None
+        xyzt = host.to(device, non_blocking=True)
+        feats = job.enc.encode_features(xyzt)
+        feats.backward(job.gout)
+        if world > 1:
+            from deepearth_b200.distributed import allreduce_table_grads
+            allreduce_table_grads(params, average=True)
+        chk = Fn.sum_f32(feats.detach())
+        return float(chk.item())          # device -> host read of the step's result
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        checksum = e2e_step()
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([e2e_ms], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t)
+    e2e_value = world * n / (e2e_ms / args.steps * 1e-3) / 1e6
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        dom = "backward" if bwd_ms >= fwd_ms else "forward"
+        dom_ms = max(bwd_ms, fwd_ms)
+        dom_bytes = (job.bytes_bwd if dom == "backward" else job.bytes_fwd) * n
+        achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                traffic = json.load(f).get(args.workload, {}).get(dom)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16 tables / f32 accumulate" if wl["table_dtype"] == "float16" else "f32",
+            "data": "synthetic",
+            "config": {"workload": args.workload, "description": wl["desc"], "points_per_gpu": n,
+                       "coords": wl["coords"], "levels": len(job.plan.specs), "features_per_level": job.F,
+                       "table_size": wl["T"], "interpolation": "linear" if job.linear else "nearest",
+                       "l2_policy": "inputs larger than L2 (coords+grad_out+out > 4 GiB per step); no flush",
+                       "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"},
+            "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms},
+            "roofline": {"bound": "hbm", "kernel": f"grid4d_{dom}_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_point": {"forward": job.bytes_fwd, "backward": job.bytes_bwd}},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(host.numel() * 4 * world),
+                    "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps, "checksum": checksum,
+                    "api": "Grid4DEncoder.encode_features + autograd backward, pinned host xyzt -> device each step"},
+            "gpu_launches": job.n_launches_per_step() * args.steps,
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            log2_sample = 16 if wl["mode"] == "decomposed" else 18
+            if wl["T"] > 2 ** 20:
+                log2_sample = 15
+            cb = cpu_baseline_run(wl, log2_sample, 3, 1)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--log2-points", type=int, default=0, help="override points per GPU (power of two)")
+    ap.add_argument("--levels-per-group", type=int, default=0)
+    ap.add_argument("--bwd-levels-per-group", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+    else:
+        run_gpu_arm(args, wl)
+
+
+if __name__ == "__main__":
+    main()

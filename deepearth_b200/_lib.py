@@ -1,0 +1,98 @@
+"""ctypes binding of libde_grid4d.so (the C ABI declared in include/de_grid4d.h).
+
+There is deliberately no fallback: if the shared library is missing or a call fails, an
+exception is raised.  Build it with ``python -m deepearth_b200.build`` (nvcc, sm_100a).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libde_grid4d.so")
+
+DE_OK = 0
+DE_F32, DE_F16, DE_F64 = 0, 1, 2
+DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
+DE_MAX_LEVELS_PER_CALL = 256
+
+c_void_p = ctypes.c_void_p
+c_int = ctypes.c_int
+c_i64 = ctypes.c_int64
+c_u32 = ctypes.c_uint32
+c_float = ctypes.c_float
+
+
+class DeLevelDesc(ctypes.Structure):
+    """Mirror of ``de_level_desc`` (include/de_grid4d.h)."""
+    _fields_ = [
+        ("table", c_void_p),
+        ("grad_table", c_void_p),
+        ("table_size", c_u32),
+        ("resolution", c_u32),
+        ("out_col", c_u32),
+        ("n_dims", ctypes.c_uint8),
+        ("dim", ctypes.c_uint8 * 4),
+        ("dense", ctypes.c_uint8),
+        ("mask_id", ctypes.c_uint8),
+        ("reserved", ctypes.c_uint8),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/de_grid4d.h declares
+SIGNATURES = {
+    "de_abi_version": (c_int, []),
+    "de_last_error": (ctypes.c_char_p, []),
+    "de_corners": (c_int, [c_u32, c_int]),
+    "de_grid4d_hash_indices": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_void_p, c_i64, c_int, c_u32,
+                                       c_void_p, c_void_p]),
+    "de_grid4d_forward": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_void_p, c_i64, c_int, c_int, c_int,
+                                  c_float, c_void_p, c_void_p, c_void_p, c_i64, c_u32, c_int, c_void_p]),
+    "de_grid4d_backward": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_void_p, c_i64, c_int, c_int,
+                                   c_void_p, c_void_p, c_void_p, c_i64, c_u32, c_int, c_void_p]),
+    "de_tables_to_f16": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_int, ctypes.POINTER(c_void_p), c_float,
+                                 c_void_p]),
+    "de_geo2xyzt_norm": (c_int, [c_void_p, c_int, c_void_p, c_int, ctypes.POINTER(ctypes.c_double),
+                                 ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), c_void_p,
+                                 c_void_p, c_i64, c_void_p]),
+    "de_geo_bbox": (c_int, [c_void_p, c_int, c_void_p, c_i64, c_void_p]),
+    "de_sum_f32": (c_int, [c_void_p, c_i64, c_void_p, c_void_p]),
+    "de_probe_gather": (c_int, [c_void_p, c_i64, c_int, c_int, c_i64, c_int, c_int, c_void_p, c_void_p]),
+}
+
+_lock = threading.Lock()
+_lib = None
+
+
+class DeepEarthB200Error(RuntimeError):
+    pass
+
+
+def load() -> ctypes.CDLL:
+    """Load the shared library once; raise loudly if it is not there."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise DeepEarthB200Error(
+                f"{LIB_PATH} is missing: the CUDA library has not been built. Run "
+                "`python -m deepearth_b200.build` (needs nvcc; targets sm_100a). There is no CPU fallback.")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)   # AttributeError here = header / library mismatch
+            fn.restype = res
+            fn.argtypes = args
+        if lib.de_abi_version() != 1:
+            raise DeepEarthB200Error(f"ABI version {lib.de_abi_version()} != 1")
+        _lib = lib
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != DE_OK:
+        msg = load().de_last_error().decode("utf-8", "replace")
+        raise DeepEarthB200Error(f"{what} failed (code {rc}): {msg}")

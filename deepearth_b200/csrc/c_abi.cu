@@ -1,0 +1,306 @@
+// c_abi.cu -- the extern "C" surface of libde_grid4d.so (declared in include/de_grid4d.h).
+// Host-only logic: argument validation, segmentation of the level list into launches, group / tile
+// geometry.  No torch types, no device allocation, no global mutable state (the last-error text is
+// thread local), nothing synchronises.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/de_grid4d.h"
+#include "grid4d_common.cuh"
+#include "launch.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    return static_cast<int>(e);
+}
+
+bool is_pow2(uint32_t v) { return v && !(v & (v - 1)); }
+
+int floor_pow2(int v) {
+    int p = 1;
+    while (p * 2 <= v) p *= 2;
+    return p;
+}
+
+struct CallArgs {
+    const de_level_desc* levels;
+    int n_levels;
+    const float* coords;
+    int64_t n_points;
+    int coord_stride;
+    int table_dtype;
+    int n_features;
+    uint32_t flags;
+    int levels_per_group;
+    bool need_tables, need_grads;
+};
+
+int validate(const CallArgs& a) {
+    if (!a.levels || a.n_levels <= 0 || a.n_levels > DE_MAX_LEVELS_PER_CALL)
+        return fail(DE_EINVAL, "n_levels=%d outside 1..%d", a.n_levels, DE_MAX_LEVELS_PER_CALL);
+    if (a.n_points < 0) return fail(DE_EINVAL, "n_points=%lld < 0", (long long)a.n_points);
+    if (a.n_points > 0 && !a.coords) return fail(DE_EINVAL, "coords is NULL");
+    if (a.coord_stride < 1) return fail(DE_EINVAL, "coord_stride=%d < 1", a.coord_stride);
+    if (a.n_features < 1 || a.n_features > 64) return fail(DE_EUNSUPPORTED, "n_features=%d outside 1..64", a.n_features);
+    if (a.table_dtype != DE_F32 && a.table_dtype != DE_F16) return fail(DE_EUNSUPPORTED, "table_dtype=%d", a.table_dtype);
+    if (a.flags & ~DE_INTERP_MASK) return fail(DE_EINVAL, "unknown flags 0x%x", a.flags);
+    if (a.levels_per_group < 0 || a.levels_per_group > de::kMaxGroup)
+        return fail(DE_EINVAL, "levels_per_group=%d outside 0..%d", a.levels_per_group, de::kMaxGroup);
+    for (int i = 0; i < a.n_levels; ++i) {
+        const de_level_desc& L = a.levels[i];
+        if (L.n_dims < 1 || L.n_dims > DE_MAX_DIMS) return fail(DE_EUNSUPPORTED, "level %d: n_dims=%d outside 1..4", i, L.n_dims);
+        if (L.table_size == 0) return fail(DE_EINVAL, "level %d: table_size=0", i);
+        if (L.resolution > (1u << 30)) return fail(DE_EUNSUPPORTED, "level %d: resolution %u > 2^30", i, L.resolution);
+        for (int d = 0; d < L.n_dims; ++d)
+            if (L.dim[d] >= a.coord_stride) return fail(DE_EINVAL, "level %d: dim[%d]=%d >= coord_stride=%d", i, d, L.dim[d], a.coord_stride);
+        if (L.dense) {
+            unsigned long long cells = 1;
+            for (int d = 0; d < L.n_dims; ++d) cells *= (unsigned long long)L.resolution + 1ull;
+            if (cells > L.table_size) return fail(DE_EINVAL, "level %d: dense index needs (R+1)^D=%llu <= T=%u", i, cells, L.table_size);
+        }
+        if (L.mask_id > 2) return fail(DE_EINVAL, "level %d: mask_id=%d", i, L.mask_id);
+        if (a.need_tables && !L.table) return fail(DE_EINVAL, "level %d: table is NULL", i);
+        if (a.need_grads && !L.grad_table) return fail(DE_EINVAL, "level %d: grad_table is NULL", i);
+        const size_t entry = (size_t)a.n_features * (a.table_dtype == DE_F16 ? 2 : 4);
+        const size_t align = (a.n_features == 1 || a.n_features == 2 || a.n_features == 4 || a.n_features == 8) ? (entry > 16 ? 16 : entry) : 1;
+        if (a.need_tables && (reinterpret_cast<uintptr_t>(L.table) % align)) return fail(DE_EALIGN, "level %d: table not %zu-byte aligned", i, align);
+        const size_t galign = (a.n_features == 2) ? 8 : ((a.n_features == 4 || a.n_features == 8) ? 16 : 4);
+        if (a.need_grads && (reinterpret_cast<uintptr_t>(L.grad_table) % galign)) return fail(DE_EALIGN, "level %d: grad_table not %zu-byte aligned", i, galign);
+    }
+    return DE_OK;
+}
+
+void fill_level(const de_level_desc& L, de::LevelParams& o) {
+    o.table = L.table;
+    o.grad = L.grad_table;
+    o.T = L.table_size;
+    o.res_f = static_cast<float>(L.resolution);   // Python int -> fp32 scalar, round to nearest
+    o.res_p1 = L.resolution + 1u;
+    o.out_col = L.out_col;
+    for (int d = 0; d < 4; ++d) o.dim[d] = L.dim[d];
+    o.dense = L.dense ? 1 : 0;
+    o.pow2 = is_pow2(L.table_size) ? 1 : 0;
+    o.mask_id = L.mask_id;
+    o.pad = 0;
+}
+
+bool rows_vectorisable(const void* base, int64_t stride, const de_level_desc* levels, int n_levels, int F) {
+    if (!(F == 2 || F == 4 || F == 8)) return false;
+    const int unit = F == 2 ? 2 : 4;   // floats per vector access
+    if (reinterpret_cast<uintptr_t>(base) % (unit * 4)) return false;
+    if (stride % unit) return false;
+    for (int i = 0; i < n_levels; ++i)
+        if (levels[i].out_col % unit) return false;
+    return true;
+}
+
+enum class Op { Forward, Backward, Indices };
+
+// Cuts the level list into launches (runs of equal D, <= 64 levels) and starts them in order.
+int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
+    if (a.n_points == 0) return DE_OK;
+    const bool linear = (a.flags & DE_INTERP_MASK) == DE_INTERP_LINEAR;
+    int begin = 0;
+    while (begin < a.n_levels) {
+        const int D = a.levels[begin].n_dims;
+        int end = begin + 1;
+        while (end < a.n_levels && a.levels[end].n_dims == D && end - begin < de::kMaxLaunchLevels) ++end;
+        const int n = end - begin;
+
+        de::EncodeParams P = base;
+        P.n_levels = n;
+        for (int i = 0; i < n; ++i) fill_level(a.levels[begin + i], P.levels[i]);
+        int G = a.levels_per_group;
+        if (G == 0) {  // auto: make the G lanes of a point cover at least one 32 B sector of its row
+            G = 8 / a.n_features;
+            if (G < 1) G = 1;
+        }
+        G = floor_pow2(G > n ? n : G);
+        if (G > de::kMaxGroup) G = de::kMaxGroup;
+        P.group_size = G;
+        P.n_groups = (n + G - 1) / G;
+        const int iters = 4;
+        P.points_per_cta = (de::kThreads / G) * iters;
+        const long long tiles = (a.n_points + P.points_per_cta - 1) / P.points_per_cta;
+        if (tiles * P.n_groups >= (1ll << 31)) return fail(DE_EUNSUPPORTED, "n_points=%lld too large for one launch", (long long)a.n_points);
+        P.n_tiles = static_cast<int>(tiles);
+
+        cudaError_t e = cudaSuccess;
+        switch (op) {
+            case Op::Forward: e = de::launch_forward(P, D, linear, a.table_dtype == DE_F16, a.n_features, stream); break;
+            case Op::Backward: e = de::launch_backward(P, D, linear, a.n_features, stream); break;
+            case Op::Indices: {
+                // indices are laid out per call, so offset the level index by `begin`
+                const int C = linear ? (1 << D) : 1;
+                P.indices = base.indices + static_cast<long long>(begin) * C * a.n_points;
+                e = de::launch_indices(P, D, linear, stream);
+                break;
+            }
+        }
+        if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+        begin = end;
+    }
+    return DE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+DE_API int de_abi_version(void) { return DE_ABI_VERSION; }
+
+DE_API const char* de_last_error(void) { return g_err; }
+
+DE_API int de_corners(uint32_t flags, int n_dims) {
+    return ((flags & DE_INTERP_MASK) == DE_INTERP_LINEAR) ? (1 << n_dims) : 1;
+}
+
+DE_API int de_grid4d_hash_indices(const de_level_desc* levels_host, int n_levels, const float* coords,
+                           int64_t n_points, int coord_stride, uint32_t flags, int64_t* indices,
+                           void* stream) {
+    CallArgs a{levels_host, n_levels, coords, n_points, coord_stride, DE_F32, 1, flags, 0, false, false};
+    if (int rc = validate(a)) return rc;
+    for (int i = 1; i < n_levels; ++i)
+        if (levels_host[i].n_dims != levels_host[0].n_dims) return fail(DE_EINVAL, "hash_indices: all levels must share n_dims");
+    if (n_points > 0 && !indices) return fail(DE_EINVAL, "indices is NULL");
+    de::EncodeParams P{};
+    P.coords = coords;
+    P.indices = reinterpret_cast<long long*>(indices);
+    P.n_points = n_points;
+    P.coord_stride = coord_stride;
+    P.n_features = 1;
+    P.vec_coords = (coord_stride == 4 && reinterpret_cast<uintptr_t>(coords) % 16 == 0) ? 1 : 0;
+    P.out_scale = 1.0f;
+    return run(a, Op::Indices, P, static_cast<cudaStream_t>(stream));
+}
+
+DE_API int de_grid4d_forward(const de_level_desc* levels_host, int n_levels, const float* coords,
+                      int64_t n_points, int coord_stride, int table_dtype, int n_features,
+                      float out_scale, const uint8_t* mask_a, const uint8_t* mask_b, float* out,
+                      int64_t out_stride, uint32_t flags, int levels_per_group, void* stream) {
+    CallArgs a{levels_host, n_levels, coords, n_points, coord_stride, table_dtype, n_features, flags, levels_per_group, true, false};
+    if (int rc = validate(a)) return rc;
+    if (n_points > 0 && !out) return fail(DE_EINVAL, "out is NULL");
+    for (int i = 0; i < n_levels; ++i)
+        if ((int64_t)levels_host[i].out_col + n_features > out_stride)
+            return fail(DE_EINVAL, "level %d: out_col %u + F %d exceeds out_stride %lld", i, levels_host[i].out_col, n_features, (long long)out_stride);
+    de::EncodeParams P{};
+    P.coords = coords;
+    P.mask_a = mask_a;
+    P.mask_b = mask_b;
+    P.out = out;
+    P.n_points = n_points;
+    P.out_stride = out_stride;
+    P.coord_stride = coord_stride;
+    P.n_features = n_features;
+    P.vec_coords = (coord_stride == 4 && reinterpret_cast<uintptr_t>(coords) % 16 == 0) ? 1 : 0;
+    P.vec_rows = rows_vectorisable(out, out_stride, levels_host, n_levels, n_features) ? 1 : 0;
+    P.out_scale = out_scale;
+    return run(a, Op::Forward, P, static_cast<cudaStream_t>(stream));
+}
+
+DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels, const float* coords,
+                       int64_t n_points, int coord_stride, int n_features, const uint8_t* mask_a,
+                       const uint8_t* mask_b, const float* grad_out, int64_t grad_stride,
+                       uint32_t flags, int levels_per_group, void* stream) {
+    CallArgs a{levels_host, n_levels, coords, n_points, coord_stride, DE_F32, n_features, flags, levels_per_group, false, true};
+    if (int rc = validate(a)) return rc;
+    if (n_points > 0 && !grad_out) return fail(DE_EINVAL, "grad_out is NULL");
+    for (int i = 0; i < n_levels; ++i)
+        if ((int64_t)levels_host[i].out_col + n_features > grad_stride)
+            return fail(DE_EINVAL, "level %d: out_col %u + F %d exceeds grad_stride %lld", i, levels_host[i].out_col, n_features, (long long)grad_stride);
+    de::EncodeParams P{};
+    P.coords = coords;
+    P.mask_a = mask_a;
+    P.mask_b = mask_b;
+    P.grad_out = grad_out;
+    P.n_points = n_points;
+    P.out_stride = grad_stride;
+    P.coord_stride = coord_stride;
+    P.n_features = n_features;
+    P.vec_coords = (coord_stride == 4 && reinterpret_cast<uintptr_t>(coords) % 16 == 0) ? 1 : 0;
+    P.vec_rows = rows_vectorisable(grad_out, grad_stride, levels_host, n_levels, n_features) ? 1 : 0;
+    P.out_scale = 1.0f;
+    return run(a, Op::Backward, P, static_cast<cudaStream_t>(stream));
+}
+
+DE_API int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_features,
+                     void* const* dst_tables_host, float scale, void* stream) {
+    if (!levels_host || !dst_tables_host || n_levels <= 0) return fail(DE_EINVAL, "tables_to_f16: bad arguments");
+    if (n_features < 1) return fail(DE_EINVAL, "n_features=%d", n_features);
+    int begin = 0;
+    while (begin < n_levels) {
+        de::CastParams P{};
+        const int n = (n_levels - begin) < 64 ? (n_levels - begin) : 64;
+        for (int i = 0; i < n; ++i) {
+            if (!levels_host[begin + i].table || !dst_tables_host[begin + i]) return fail(DE_EINVAL, "tables_to_f16: level %d NULL pointer", begin + i);
+            P.src[i] = static_cast<const float*>(levels_host[begin + i].table);
+            P.dst[i] = dst_tables_host[begin + i];
+            P.n_elems[i] = static_cast<long long>(levels_host[begin + i].table_size) * n_features;
+        }
+        P.n_levels = n;
+        P.scale = scale;
+        cudaError_t e = de::launch_cast_f16(P, static_cast<cudaStream_t>(stream));
+        if (e != cudaSuccess) return cuda_fail(e, "tables_to_f16 launch");
+        begin += n;
+    }
+    return DE_OK;
+}
+
+DE_API int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t_dtype,
+                     const double* bbox_min_host, const double* bbox_span_host,
+                     const double* t_range_host, float* xyzt, double* ecef, int64_t n_points,
+                     void* stream) {
+    if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (n_points == 0) return DE_OK;
+    if (!geo || !xyzt || !bbox_min_host || !bbox_span_host) return fail(DE_EINVAL, "geo2xyzt: NULL pointer");
+    if (geo_dtype != DE_F64 && geo_dtype != DE_F32) return fail(DE_EUNSUPPORTED, "geo_dtype=%d", geo_dtype);
+    if (t && t_dtype != DE_F64 && t_dtype != DE_F32) return fail(DE_EUNSUPPORTED, "t_dtype=%d", t_dtype);
+    if (t && !t_range_host) return fail(DE_EINVAL, "t given without t_range");
+    if (reinterpret_cast<uintptr_t>(xyzt) % 16) return fail(DE_EALIGN, "xyzt not 16-byte aligned");
+    cudaError_t e = de::launch_geo2xyzt(geo, geo_dtype == DE_F64, t, t_dtype == DE_F64, bbox_min_host,
+                                        bbox_span_host, t_range_host, xyzt, ecef, n_points,
+                                        static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "geo2xyzt launch");
+}
+
+DE_API int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n_points, void* stream) {
+    if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (n_points == 0) return DE_OK;
+    if (!geo || !minmax) return fail(DE_EINVAL, "geo_bbox: NULL pointer");
+    if (geo_dtype != DE_F64 && geo_dtype != DE_F32) return fail(DE_EUNSUPPORTED, "geo_dtype=%d", geo_dtype);
+    cudaError_t e = de::launch_geo_bbox(geo, geo_dtype == DE_F64, minmax, n_points, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "geo_bbox launch");
+}
+
+DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream) {
+    if (n < 0 || (n > 0 && (!x || !result))) return fail(DE_EINVAL, "sum_f32: bad arguments");
+    cudaError_t e = de::launch_sum_f32(x, n, result, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "sum_f32 launch");
+}
+
+DE_API int de_probe_gather(void* table, int64_t n_entries, int entry_bytes, int mode, int64_t n_threads,
+                    int per_thread, int pair_pattern, void* sink, void* stream) {
+    if (!table || !sink) return fail(DE_EINVAL, "probe: NULL pointer");
+    if (n_entries <= 0 || (n_entries & (n_entries - 1)) || n_entries > (1ll << 32)) return fail(DE_EINVAL, "probe: n_entries must be a power of two <= 2^32");
+    if (entry_bytes != 4 && entry_bytes != 8 && entry_bytes != 16) return fail(DE_EUNSUPPORTED, "probe: entry_bytes=%d", entry_bytes);
+    if (mode != 0 && mode != 1) return fail(DE_EINVAL, "probe: mode=%d", mode);
+    if (n_threads <= 0 || per_thread <= 0 || per_thread % 8) return fail(DE_EINVAL, "probe: per_thread must be a positive multiple of 8");
+    cudaError_t e = de::launch_probe(table, n_entries, entry_bytes, mode, n_threads, per_thread, pair_pattern, sink, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "probe launch");
+}
+
+}  // extern "C"

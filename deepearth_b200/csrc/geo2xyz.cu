@@ -1,0 +1,148 @@
+// geo2xyz.cu -- fused geodetic prologue (sm_100a): WGS-84 geodetic -> ECEF (fp64) -> bounding-box
+// normalisation -> packed fp32 (x,y,z,t) rows, one pass, one thread per point.
+// Replaces ~20 ATen launches of GeospatialConverter.geodetic_to_xyz + xyz_to_norm
+// (/root/reference/geospatial/geo2xyz.py:146-160, :327-332; utils.py:54-77).
+// Compiled with -fmad=false so every fp64 operation rounds once, in the reference's order.
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "launch.h"
+
+namespace de {
+
+struct GeoParams {
+    const void* geo;
+    const void* t;
+    float* xyzt;
+    double* ecef;
+    double* minmax;
+    long long n;
+    double bbox_min[3];
+    double bbox_span[3];
+    double t_min, t_span;
+    int geo_f64, t_f64;
+};
+
+__device__ __forceinline__ void ecef_of(const GeoParams& P, long long p, double (&xyz)[3]) {
+    constexpr double A = 6378137.0;                       // geo2xyz.py:98
+    constexpr double FL = 1.0 / 298.257223563;            // :99
+    constexpr double E2 = 2.0 * FL - FL * FL;             // :100
+    constexpr double D2R = 0.017453292519943295769236907684886;  // torch.deg2rad
+    double lat, lon, alt;
+    if (P.geo_f64) {
+        const double* g = static_cast<const double*>(P.geo) + 3 * p;
+        lat = __ldg(g); lon = __ldg(g + 1); alt = __ldg(g + 2);
+    } else {
+        const float* g = static_cast<const float*>(P.geo) + 3 * p;
+        lat = __ldg(g); lon = __ldg(g + 1); alt = __ldg(g + 2);   // _as_fp64 (:147)
+    }
+    double sl, cl, so, co;
+    sincos(lat * D2R, &sl, &cl);
+    sincos(lon * D2R, &so, &co);
+    const double N = A / sqrt(1.0 - E2 * (sl * sl));      // :153
+    xyz[0] = ((N + alt) * cl) * co;                       // :157
+    xyz[1] = ((N + alt) * cl) * so;                       // :158
+    xyz[2] = (N * (1.0 - E2) + alt) * sl;                 // :159
+}
+
+__global__ void __launch_bounds__(256) geo2xyzt_kernel(const __grid_constant__ GeoParams P) {
+    const long long p = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (p >= P.n) return;
+    double xyz[3];
+    ecef_of(P, p, xyz);
+    float4 o;
+    float* of = reinterpret_cast<float*>(&o);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        if (P.ecef) P.ecef[3 * p + d] = xyz[d];
+        const double span = P.bbox_span[d];
+        // _safe_div: |span| < 1e-9 -> 0.5 (utils.py:54-77)
+        of[d] = static_cast<float>(fabs(span) < 1e-9 ? 0.5 : (xyz[d] - P.bbox_min[d]) / span);
+    }
+    double tv = 0.0;
+    if (P.t) {
+        const double tt = P.t_f64 ? __ldg(static_cast<const double*>(P.t) + p)
+                                  : static_cast<double>(__ldg(static_cast<const float*>(P.t) + p));
+        tv = fabs(P.t_span) < 1e-9 ? 0.5 : (tt - P.t_min) / P.t_span;   // SPECIFICATIONS.MD:765
+    }
+    o.w = static_cast<float>(tv);
+    reinterpret_cast<float4*>(P.xyzt)[p] = o;
+}
+
+__device__ __forceinline__ void atomic_min_f64(double* addr, double v) {
+    unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+    unsigned long long old = *a;
+    while (v < __longlong_as_double(old)) {
+        const unsigned long long seen = atomicCAS(a, old, __double_as_longlong(v));
+        if (seen == old) break;
+        old = seen;
+    }
+}
+__device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
+    unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+    unsigned long long old = *a;
+    while (v > __longlong_as_double(old)) {
+        const unsigned long long seen = atomicCAS(a, old, __double_as_longlong(v));
+        if (seen == old) break;
+        old = seen;
+    }
+}
+
+// BoundingBox.from_points (data_structures.py:95-100) folded into a running box (geo2xyz.py:305-320).
+__global__ void __launch_bounds__(256) geo_bbox_kernel(const __grid_constant__ GeoParams P) {
+    double lo[3] = {CUDART_INF, CUDART_INF, CUDART_INF};
+    double hi[3] = {-CUDART_INF, -CUDART_INF, -CUDART_INF};
+    for (long long p = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; p < P.n;
+         p += static_cast<long long>(gridDim.x) * blockDim.x) {
+        double xyz[3];
+        ecef_of(P, p, xyz);
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            lo[d] = fmin(lo[d], xyz[d]);
+            hi[d] = fmax(hi[d], xyz[d]);
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            lo[d] = fmin(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], off));
+            hi[d] = fmax(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], off));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            atomic_min_f64(P.minmax + d, lo[d]);
+            atomic_max_f64(P.minmax + 3 + d, hi[d]);
+        }
+    }
+}
+
+cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,
+                            const double* bbox_span, const double* t_range, float* xyzt, double* ecef,
+                            long long n, cudaStream_t s) {
+    GeoParams P{};
+    P.geo = geo; P.t = t; P.xyzt = xyzt; P.ecef = ecef; P.minmax = nullptr; P.n = n;
+    for (int d = 0; d < 3; ++d) { P.bbox_min[d] = bbox_min[d]; P.bbox_span[d] = bbox_span[d]; }
+    P.t_min = t_range ? t_range[0] : 0.0;
+    P.t_span = t_range ? t_range[1] - t_range[0] : 1.0;
+    P.geo_f64 = geo_f64; P.t_f64 = t_f64;
+    if (n == 0) return cudaSuccess;
+    const unsigned blocks = static_cast<unsigned>((n + 255) / 256);
+    geo2xyzt_kernel<<<blocks, 256, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_geo_bbox(const void* geo, bool geo_f64, double* minmax, long long n, cudaStream_t s) {
+    GeoParams P{};
+    P.geo = geo; P.minmax = minmax; P.n = n; P.geo_f64 = geo_f64;
+    if (n == 0) return cudaSuccess;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    geo_bbox_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
+}  // namespace de

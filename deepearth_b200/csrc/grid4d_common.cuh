@@ -1,0 +1,294 @@
+// grid4d_common.cuh -- device-side building blocks shared by the Grid4D kernels (sm_100a).
+//
+// Arithmetic contract (must match oracle/grid4d_oracle.c, which restates
+// /root/reference/models/hash_encoding.py:47-96):
+//   s_d = fl32(c_d * fl32(R));  g_d = (int64) floor(s_d);  w_d = s_d - floor(s_d)
+//   hashed: h = XOR_d (g_d + o_d) * prime_d  (wrapping int64), dense: h = SUM_d (g_d+o_d)*(R+1)^d
+//   idx = floor_mod(h, T)
+// Every fp32 operation that decides an index or a weight is a single IEEE operation written with
+// an explicit intrinsic (__fmul_rn / __fsub_rn / __fmaf_rn) so the compiler cannot contract it.
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace de {
+
+constexpr int kMaxLaunchLevels = 64;  // levels carried by one launch (kernel parameter space)
+constexpr int kMaxGroup = 32;         // levels handled by one CTA
+constexpr int kThreads = 256;
+
+// hash_encoding.py:64 -- the int64 primes; their low 32 bits are what a power-of-two table sees.
+__device__ __constant__ const uint32_t kPrime32[4] = {1u, 2654435761u, 805459861u, 3674653429u};
+__device__ __constant__ const uint64_t kPrime64[4] = {1ull, 2654435761ull, 805459861ull, 3674653429ull};
+
+struct LevelParams {
+    const void* table;  // (T,F) entries
+    float* grad;        // (T,F) fp32 accumulators (backward)
+    uint32_t T;
+    float res_f;        // (float)R
+    uint32_t res_p1;    // R+1: dense stride base
+    uint32_t out_col;
+    uint8_t dim[4];
+    uint8_t dense;
+    uint8_t pow2;       // T is a power of two: 32-bit hash fast path is bit-identical
+    uint8_t mask_id;
+    uint8_t pad;
+};
+
+struct EncodeParams {
+    const float* coords;
+    const uint8_t* mask_a;
+    const uint8_t* mask_b;
+    float* out;             // forward: features; hash_indices: unused
+    const float* grad_out;  // backward
+    long long* indices;     // hash_indices kernel
+    long long n_points;
+    long long out_stride;   // row stride of out / grad_out in floats
+    int coord_stride;
+    int n_levels;           // levels in this launch
+    int group_size;         // levels per CTA (power of two)
+    int n_groups;
+    int n_tiles;            // point tiles per group
+    int points_per_cta;
+    int n_features;         // runtime F (used when the template F is 0)
+    int vec_coords;         // coords are 16 B-aligned float4 rows
+    int vec_rows;           // feature / grad rows are aligned for F-wide vector access
+    float out_scale;
+    LevelParams levels[kMaxLaunchLevels];
+};
+
+__device__ __forceinline__ float pick4(const float4& v, int d) {
+    return d == 0 ? v.x : (d == 1 ? v.y : (d == 2 ? v.z : v.w));
+}
+
+// Per-(point, level) cell: integer cell coordinates (low 32 bits + full 64) and fractional weights.
+template <int D>
+struct Cell {
+    long long g[D];
+    float w[D];
+};
+
+template <int D>
+__device__ __forceinline__ void load_cell(const EncodeParams& P, const LevelParams& lv, long long p,
+                                          Cell<D>& c) {
+    float x[D];
+    if (P.vec_coords) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(P.coords) + p);
+#pragma unroll
+        for (int d = 0; d < D; ++d) x[d] = pick4(v, lv.dim[d]);
+    } else {
+        const float* row = P.coords + p * P.coord_stride;
+#pragma unroll
+        for (int d = 0; d < D; ++d) x[d] = __ldg(row + lv.dim[d]);
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const float s = __fmul_rn(x[d], lv.res_f);  // hash_encoding.py:58
+        const float fl = floorf(s);                 // :61
+        c.g[d] = __float2ll_rd(s);
+        c.w[d] = __fsub_rn(s, fl);
+    }
+}
+
+// Index of corner `k` (bit d = +1 offset along grid dim d).
+template <int D>
+__device__ __forceinline__ uint32_t corner_index(const LevelParams& lv, const Cell<D>& c, int k) {
+    if (lv.pow2) {
+        // T | 2^32, so arithmetic mod 2^32 followed by & (T-1) equals the int64 floor-mod.
+        uint32_t h = 0;
+        uint32_t stride = 1;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const uint32_t cell = static_cast<uint32_t>(c.g[d]) + ((k >> d) & 1);
+            if (lv.dense) {
+                h += cell * stride;
+                stride *= lv.res_p1;
+            } else {
+                h ^= cell * kPrime32[d];
+            }
+        }
+        return h & (lv.T - 1u);
+    }
+    long long h = 0;
+    long long stride = 1;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const long long cell = c.g[d] + ((k >> d) & 1);
+        if (lv.dense) {
+            h += cell * stride;
+            stride *= static_cast<long long>(lv.res_p1);
+        } else {
+            h ^= static_cast<long long>(static_cast<unsigned long long>(cell) * kPrime64[d]);
+        }
+    }
+    long long r = h % static_cast<long long>(lv.T);  // hash_encoding.py:72, Python floor-mod
+    if (r < 0) r += lv.T;
+    return static_cast<uint32_t>(r);
+}
+
+template <int D>
+__device__ __forceinline__ float corner_weight(const Cell<D>& c, int k) {
+    float wk = 1.0f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const float u = ((k >> d) & 1) ? c.w[d] : __fsub_rn(1.0f, c.w[d]);
+        wk = (d == 0) ? u : __fmul_rn(wk, u);
+    }
+    return wk;
+}
+
+__device__ __forceinline__ float row_mask(const EncodeParams& P, const LevelParams& lv, long long p,
+                                          bool& has_mask) {
+    has_mask = false;
+    if (lv.mask_id == 1 && P.mask_a) {
+        has_mask = true;
+        return __ldg(P.mask_a + p) ? 1.0f : 0.0f;
+    }
+    if (lv.mask_id == 2 && P.mask_b) {
+        has_mask = true;
+        return __ldg(P.mask_b + p) ? 1.0f : 0.0f;
+    }
+    return 1.0f;
+}
+
+// ---- table entry loads: one vector load per entry where the entry is 2/4/8/16/32 bytes ----------
+template <typename TT, int F>
+struct EntryLoader;
+
+template <>
+struct EntryLoader<float, 1> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[1]) {
+        v[0] = __ldg(static_cast<const float*>(t) + i);
+    }
+};
+template <>
+struct EntryLoader<float, 2> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[2]) {
+        const float2 x = __ldg(static_cast<const float2*>(t) + i);
+        v[0] = x.x; v[1] = x.y;
+    }
+};
+template <>
+struct EntryLoader<float, 4> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[4]) {
+        const float4 x = __ldg(static_cast<const float4*>(t) + i);
+        v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+    }
+};
+template <>
+struct EntryLoader<float, 8> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[8]) {
+        const float4 a = __ldg(static_cast<const float4*>(t) + 2ull * i);
+        const float4 b = __ldg(static_cast<const float4*>(t) + 2ull * i + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    }
+};
+template <>
+struct EntryLoader<__half, 1> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[1]) {
+        const unsigned short raw = __ldg(static_cast<const unsigned short*>(t) + i);
+        v[0] = __half2float(__ushort_as_half(raw));
+    }
+};
+template <>
+struct EntryLoader<__half, 2> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[2]) {
+        const unsigned int raw = __ldg(static_cast<const unsigned int*>(t) + i);
+        const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&raw));
+        v[0] = x.x; v[1] = x.y;
+    }
+};
+template <>
+struct EntryLoader<__half, 4> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[4]) {
+        const uint2 raw = __ldg(static_cast<const uint2*>(t) + i);
+        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+        const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+    }
+};
+template <>
+struct EntryLoader<__half, 8> {
+    static __device__ __forceinline__ void load(const void* t, uint32_t i, float (&v)[8]) {
+        const uint4 raw = __ldg(static_cast<const uint4*>(t) + i);
+        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+        const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+        const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&raw.z));
+        const float2 d = __half22float2(*reinterpret_cast<const __half2*>(&raw.w));
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+    }
+};
+
+template <typename TT>
+__device__ __forceinline__ float load_elem(const void* t, unsigned long long e) {
+    return __ldg(static_cast<const float*>(t) + e);
+}
+template <>
+__device__ __forceinline__ float load_elem<__half>(const void* t, unsigned long long e) {
+    return __half2float(__ushort_as_half(__ldg(static_cast<const unsigned short*>(t) + e)));
+}
+
+// ---- streaming row stores / loads of F consecutive floats ---------------------------------------
+template <int F>
+__device__ __forceinline__ void store_row(float* dst, const float (&v)[F], bool vec) {
+    if constexpr (F == 2) {
+        if (vec) { __stcs(reinterpret_cast<float2*>(dst), make_float2(v[0], v[1])); return; }
+    } else if constexpr (F == 4) {
+        if (vec) { __stcs(reinterpret_cast<float4*>(dst), make_float4(v[0], v[1], v[2], v[3])); return; }
+    } else if constexpr (F == 8) {
+        if (vec) {
+            __stcs(reinterpret_cast<float4*>(dst), make_float4(v[0], v[1], v[2], v[3]));
+            __stcs(reinterpret_cast<float4*>(dst) + 1, make_float4(v[4], v[5], v[6], v[7]));
+            return;
+        }
+    }
+#pragma unroll
+    for (int f = 0; f < F; ++f) __stcs(dst + f, v[f]);
+}
+
+template <int F>
+__device__ __forceinline__ void load_row(const float* src, float (&v)[F], bool vec) {
+    if constexpr (F == 2) {
+        if (vec) {
+            const float2 x = __ldcs(reinterpret_cast<const float2*>(src));
+            v[0] = x.x; v[1] = x.y;
+            return;
+        }
+    } else if constexpr (F == 4) {
+        if (vec) {
+            const float4 x = __ldcs(reinterpret_cast<const float4*>(src));
+            v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+            return;
+        }
+    } else if constexpr (F == 8) {
+        if (vec) {
+            const float4 a = __ldcs(reinterpret_cast<const float4*>(src));
+            const float4 b = __ldcs(reinterpret_cast<const float4*>(src) + 1);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+            return;
+        }
+    }
+#pragma unroll
+    for (int f = 0; f < F; ++f) v[f] = __ldcs(src + f);
+}
+
+// ---- vector fp32 reductions into the gradient table (REDG.E.ADD.F32x2 / F32x4 on sm_100a) -------
+template <int F>
+__device__ __forceinline__ void red_add_entry(float* grad, uint32_t idx, const float (&v)[F]) {
+    float* dst = grad + static_cast<unsigned long long>(idx) * F;
+    if constexpr (F == 2) {
+        atomicAdd(reinterpret_cast<float2*>(dst), make_float2(v[0], v[1]));
+    } else if constexpr (F == 4) {
+        atomicAdd(reinterpret_cast<float4*>(dst), make_float4(v[0], v[1], v[2], v[3]));
+    } else if constexpr (F == 8) {
+        atomicAdd(reinterpret_cast<float4*>(dst), make_float4(v[0], v[1], v[2], v[3]));
+        atomicAdd(reinterpret_cast<float4*>(dst) + 1, make_float4(v[4], v[5], v[6], v[7]));
+    } else {
+#pragma unroll
+        for (int f = 0; f < F; ++f) atomicAdd(dst + f, v[f]);
+    }
+}
+
+}  // namespace de

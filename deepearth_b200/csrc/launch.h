@@ -1,0 +1,31 @@
+// launch.h -- host-side launcher declarations shared by the translation units of libde_grid4d.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace de {
+
+struct EncodeParams;
+
+cudaError_t launch_forward(const EncodeParams& P, int D, bool linear, bool half_tables, int F, cudaStream_t s);
+cudaError_t launch_backward(const EncodeParams& P, int D, bool linear, int F, cudaStream_t s);
+cudaError_t launch_indices(const EncodeParams& P, int D, bool linear, cudaStream_t s);
+
+struct CastParams {
+    const float* src[64];
+    void* dst[64];
+    long long n_elems[64];
+    int n_levels;
+    float scale;
+};
+cudaError_t launch_cast_f16(const CastParams& P, cudaStream_t s);
+
+cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,
+                            const double* bbox_span, const double* t_range, float* xyzt, double* ecef,
+                            long long n, cudaStream_t s);
+cudaError_t launch_geo_bbox(const void* geo, bool geo_f64, double* minmax, long long n, cudaStream_t s);
+cudaError_t launch_sum_f32(const float* x, long long n, double* result, cudaStream_t s);
+cudaError_t launch_probe(void* table, long long n_entries, int entry_bytes, int mode, long long n_threads,
+                         int per_thread, int pair_pattern, void* sink, cudaStream_t s);
+
+}  // namespace de

@@ -1,0 +1,131 @@
+// misc.cu -- small helper kernels of libde_grid4d.so (sm_100a):
+//   * fp32 master tables -> scaled fp16 working tables, all levels in one launch;
+//   * fp64 checksum of an fp32 buffer (bench / e2e result read-back);
+//   * the random gather / vector-reduction probes that define the "gather roofline".
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "launch.h"
+
+namespace de {
+
+// ---- tables -> fp16 ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cast_f16_kernel(const __grid_constant__ CastParams P) {
+    const int level = blockIdx.y;
+    const long long n = P.n_elems[level];
+    const float* __restrict__ src = P.src[level];
+    __half* __restrict__ dst = static_cast<__half*>(P.dst[level]);
+    const long long n4 = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0) ? n / 4 : 0;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+        __half2 a = __floats2half2_rn(v.x * P.scale, v.y * P.scale);
+        __half2 b = __floats2half2_rn(v.z * P.scale, v.w * P.scale);
+        uint2 o;
+        o.x = *reinterpret_cast<unsigned int*>(&a);
+        o.y = *reinterpret_cast<unsigned int*>(&b);
+        reinterpret_cast<uint2*>(dst)[i] = o;
+    }
+    for (long long i = n4 * 4 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+        dst[i] = __float2half_rn(src[i] * P.scale);
+}
+
+cudaError_t launch_cast_f16(const CastParams& P, cudaStream_t s) {
+    if (P.n_levels == 0) return cudaSuccess;
+    long long max_n = 0;
+    for (int i = 0; i < P.n_levels; ++i) max_n = P.n_elems[i] > max_n ? P.n_elems[i] : max_n;
+    long long bx = (max_n / 4 + 255) / 256;
+    if (bx < 1) bx = 1;
+    if (bx > 148 * 4) bx = 148 * 4;
+    dim3 grid(static_cast<unsigned>(bx), static_cast<unsigned>(P.n_levels));
+    cast_f16_kernel<<<grid, 256, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
+// ---- fp64 sum of fp32 --------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sum_f32_kernel(const float* __restrict__ x, long long n, double* result) {
+    double acc = 0.0;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+        acc += static_cast<double>(__ldcs(x + i));
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    __shared__ double s_part[8];
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int w = 0; w < 8; ++w) tot += s_part[w];
+        atomicAdd(result, tot);
+    }
+}
+
+cudaError_t launch_sum_f32(const float* x, long long n, double* result, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    sum_f32_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(x, n, result);
+    return cudaGetLastError();
+}
+
+// ---- gather / reduction probes -----------------------------------------------------------------
+// Each thread walks `per_thread` pseudo-random entries of a power-of-two table.  pair_pattern mimics
+// a multilinear cell of the encoder: entries come as (i, i+1) neighbours -- the x-pair of a corner
+// set, which shares a 32 B sector most of the time because prime[0] = 1 (hash_encoding.py:64).
+__device__ __forceinline__ uint32_t xorshift32(uint32_t& s) {
+    s ^= s << 13; s ^= s >> 17; s ^= s << 5;
+    return s;
+}
+
+template <int BYTES, int MODE>
+__global__ void __launch_bounds__(256)
+probe_kernel(void* table, uint32_t mask, long long n_threads, int per_thread, int pair_pattern, float* sink) {
+    const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (tid >= n_threads) return;
+    uint32_t s = static_cast<uint32_t>(tid) * 2654435761u + 12345u;
+    s |= 1u;
+    float acc = 0.0f;
+    constexpr int U = 8;
+    for (int it = 0; it < per_thread; it += U) {
+        uint32_t idx[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (pair_pattern && (u & 1)) idx[u] = (idx[u - 1] + 1u) & mask;
+            else idx[u] = xorshift32(s) & mask;
+        }
+        if constexpr (MODE == 0) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if constexpr (BYTES == 4) acc += __uint_as_float(__ldg(static_cast<const unsigned int*>(table) + idx[u]));
+                else if constexpr (BYTES == 8) { const float2 v = __ldg(static_cast<const float2*>(table) + idx[u]); acc += v.x + v.y; }
+                else { const float4 v = __ldg(static_cast<const float4*>(table) + idx[u]); acc += v.x + v.y + v.z + v.w; }
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if constexpr (BYTES == 4) atomicAdd(static_cast<float*>(table) + idx[u], 1.0f);
+                else if constexpr (BYTES == 8) atomicAdd(static_cast<float2*>(table) + idx[u], make_float2(1.0f, 1.0f));
+                else atomicAdd(static_cast<float4*>(table) + idx[u], make_float4(1.0f, 1.0f, 1.0f, 1.0f));
+            }
+        }
+    }
+    if (acc == 123.456f) *sink = acc;   // keep the loads alive
+}
+
+cudaError_t launch_probe(void* table, long long n_entries, int entry_bytes, int mode, long long n_threads,
+                         int per_thread, int pair_pattern, void* sink, cudaStream_t s) {
+    const uint32_t mask = static_cast<uint32_t>(n_entries - 1);
+    const unsigned blocks = static_cast<unsigned>((n_threads + 255) / 256);
+    float* sk = static_cast<float*>(sink);
+#define DE_PROBE(B, M) probe_kernel<B, M><<<blocks, 256, 0, s>>>(table, mask, n_threads, per_thread, pair_pattern, sk)
+    if (mode == 0) {
+        if (entry_bytes == 4) DE_PROBE(4, 0); else if (entry_bytes == 8) DE_PROBE(8, 0); else DE_PROBE(16, 0);
+    } else {
+        if (entry_bytes == 4) DE_PROBE(4, 1); else if (entry_bytes == 8) DE_PROBE(8, 1); else DE_PROBE(16, 1);
+    }
+#undef DE_PROBE
+    return cudaGetLastError();
+}
+
+}  // namespace de

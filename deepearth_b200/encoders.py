@@ -1,0 +1,114 @@
+"""Grid4DEncoder -- B200 drop-in for /root/reference/models/encoders.py:12-85.
+
+Reference mode (default): ``spatial_encoder`` (xyz, D=3) + ``temporal_encoder`` (t, D=1, T//4), optional
+row masks that multiply the *features* (:73-79), concat to (B, 48) and the Linear-LayerNorm-GELU-Linear
+``projection`` (:47-52).  Same attribute names, parameter names and state-dict keys; the feature half
+is ONE fused launch over all 24 levels writing straight into the concatenated (B, 48) buffer.
+
+Decomposed mode (``config.grid4d_mode = "decomposed"``; SPECIFICATIONS.MD:1068-1200): four 3-D grids
+xyz / xyt / yzt / xzt with multilinear interpolation, dense-index fallback on coarse levels and optional
+fp16 working tables; masks zero the *coordinates* as the spec does (:1159-1164).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+from .functional import GRID_DIMS, EncodePlan, Grid4DFunction
+from .hash_encoding import MultiResolutionHashEncoding
+
+
+def _cfg(config, name, default):
+    v = getattr(config, name, default)
+    return default if v is None else v
+
+
+class Grid4DEncoder(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        self.config = config
+        self.mode = _cfg(config, "grid4d_mode", "reference")
+        F = config.n_features_per_level
+        table_dtype = _cfg(config, "grid4d_table_dtype", "float32")
+        table_scale = getattr(config, "grid4d_table_scale", None)
+
+        if self.mode == "reference":
+            interp = _cfg(config, "grid4d_interpolation", "nearest")
+            dense = bool(_cfg(config, "grid4d_dense_fallback", False))
+            self.spatial_encoder = MultiResolutionHashEncoding(
+                n_levels=config.n_spatial_levels, n_features_per_level=F,
+                resolutions=config.spatial_resolutions, hash_table_size=config.hash_table_size, coords_dim=3,
+                interpolation=interp, dense_fallback=dense, table_dtype=table_dtype, table_scale=table_scale,
+                dims=(0, 1, 2))
+            self.temporal_encoder = MultiResolutionHashEncoding(
+                n_levels=config.n_temporal_levels, n_features_per_level=F,
+                resolutions=config.temporal_resolutions, hash_table_size=config.hash_table_size // 4,
+                coords_dim=1, interpolation=interp, dense_fallback=dense, table_dtype=table_dtype,
+                table_scale=table_scale, dims=(3,))
+            self._encoders = [self.spatial_encoder, self.temporal_encoder]
+            self._mask_ids = [1, 2]
+        elif self.mode == "decomposed":
+            interp = _cfg(config, "grid4d_interpolation", "linear")
+            dense = bool(_cfg(config, "grid4d_dense_fallback", True))
+            st_res = _cfg(config, "spacetime_resolutions", config.temporal_resolutions)
+            kw = dict(n_features_per_level=F, hash_table_size=config.hash_table_size, coords_dim=3,
+                      interpolation=interp, dense_fallback=dense, table_dtype=table_dtype, table_scale=table_scale)
+            self.xyz_encoder = MultiResolutionHashEncoding(
+                n_levels=config.n_spatial_levels, resolutions=config.spatial_resolutions, dims=GRID_DIMS["xyz"], **kw)
+            self.xyt_encoder = MultiResolutionHashEncoding(
+                n_levels=config.n_temporal_levels, resolutions=st_res, dims=GRID_DIMS["xyt"], **kw)
+            self.yzt_encoder = MultiResolutionHashEncoding(
+                n_levels=config.n_temporal_levels, resolutions=st_res, dims=GRID_DIMS["yzt"], **kw)
+            self.xzt_encoder = MultiResolutionHashEncoding(
+                n_levels=config.n_temporal_levels, resolutions=st_res, dims=GRID_DIMS["xzt"], **kw)
+            self._encoders = [self.xyz_encoder, self.xyt_encoder, self.yzt_encoder, self.xzt_encoder]
+            self._mask_ids = [0, 0, 0, 0]
+        else:
+            raise ValueError(f"unknown grid4d_mode {self.mode!r}")
+
+        self.feature_dim = sum(e.output_dim for e in self._encoders)
+        self.projection = nn.Sequential(
+            nn.Linear(self.feature_dim, config.hidden_dim),
+            nn.LayerNorm(config.hidden_dim),
+            nn.GELU(),
+            nn.Linear(config.hidden_dim, config.hidden_dim),
+        )
+
+    # ---- fused feature path -------------------------------------------------------------------------
+    def _plan(self) -> EncodePlan:
+        specs, col = [], 0
+        for enc, mid in zip(self._encoders, self._mask_ids):
+            specs += enc.level_specs(out_col0=col, mask_id=mid)
+            col += enc.output_dim
+        e0 = self._encoders[0]
+        return EncodePlan(specs, e0.n_features_per_level, self.feature_dim, e0.interpolation == "linear",
+                          e0.table_dtype, e0.table_scale, e0.levels_per_group, e0.bwd_levels_per_group)
+
+    def encode_features(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,
+                        temporal_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """(B,4) -> (B, feature_dim): the concatenated hash features, before the projection."""
+        if xyzt.dim() != 2 or xyzt.shape[1] != 4:
+            raise ValueError(f"xyzt must be (B, 4), got {tuple(xyzt.shape)}")
+        Fn._require_cuda(xyzt, "xyzt")
+        weights: List[torch.Tensor] = []
+        ptrs: Optional[List[int]] = [] if self._encoders[0].table_dtype == torch.float16 else None
+        for enc in self._encoders:
+            weights += enc.weights()
+            if ptrs is not None:
+                ptrs += enc.working_ptrs()
+        Fn._require_cuda(weights[0], "hash table weights")
+        if self.mode == "decomposed" and (spatial_mask is not None or temporal_mask is not None):
+            xyzt = xyzt.clone()                       # SPECIFICATIONS.MD:1159-1164: mask coordinates
+            if spatial_mask is not None:
+                xyzt[~spatial_mask.bool(), :3] = 0
+            if temporal_mask is not None:
+                xyzt[~temporal_mask.bool(), 3] = 0
+            spatial_mask = temporal_mask = None
+        return Grid4DFunction.apply(xyzt, spatial_mask, temporal_mask, self._plan(), ptrs, *weights)
+
+    def forward(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,
+                temporal_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        return self.projection(self.encode_features(xyzt, spatial_mask, temporal_mask))

@@ -1,0 +1,147 @@
+"""Geodetic prologue -- host mirror of the reference GeospatialConverter's position path.
+
+Reference: /root/reference/geospatial/geo2xyz.py (``geodetic_to_xyz`` :128-160, ``update_bbox``
+:305-325, ``xyz_to_norm`` :327-332), utils.py ``_safe_div`` :54-77, data_structures.py ``BoundingBox``
+:46-100.  The reference runs ~20 fp64 ATen ops and a device->host bbox round trip per call; here one
+fused kernel (csrc/geo2xyz.cu) turns (lat, lon, alt[, t]) rows into packed fp32 (x, y, z, t) rows in
+[0,1], ready for the Grid4D encoder.  Orientation matrices / CSV I/O are camera-pose tooling outside
+this path and are not provided.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from .functional import _ptr, _require_cuda, _stream_ptr
+
+_DT = {torch.float64: _lib.DE_F64, torch.float32: _lib.DE_F32}
+
+
+@dataclass
+class BoundingBox:
+    """Axis-aligned ECEF box used for normalisation (data_structures.py:46-100)."""
+    min_x: float
+    min_y: float
+    min_z: float
+    max_x: float
+    max_y: float
+    max_z: float
+
+    @property
+    def min_point(self) -> Tuple[float, float, float]:
+        return (self.min_x, self.min_y, self.min_z)
+
+    @property
+    def max_point(self) -> Tuple[float, float, float]:
+        return (self.max_x, self.max_y, self.max_z)
+
+    @property
+    def span(self) -> Tuple[float, float, float]:
+        return (self.max_x - self.min_x, self.max_y - self.min_y, self.max_z - self.min_z)
+
+
+def _dbl3(v: Sequence[float]):
+    return (ctypes.c_double * len(v))(*[float(x) for x in v])
+
+
+def _geo_arg(geo: torch.Tensor) -> torch.Tensor:
+    _require_cuda(geo, "geo")
+    if geo.shape[-1] != 3:
+        raise ValueError("last dimension must be (lat, lon, alt)")   # geo2xyz.py:146
+    if geo.dtype not in _DT:
+        geo = geo.to(torch.float64)
+    return geo.reshape(-1, 3).contiguous()
+
+
+class GeospatialConverter:
+    """geodetic (lat deg, lon deg, alt m) -> normalised fp32 xyzt, with the reference's bbox semantics."""
+
+    def __init__(self, *, device: str = "cuda", bbox: Optional[BoundingBox] = None,
+                 t_range: Optional[Tuple[float, float]] = None) -> None:
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("deepearth_b200.GeospatialConverter runs on CUDA devices only")
+        self._bbox = bbox
+        self.t_range = t_range
+
+    @property
+    def bbox(self) -> Optional[BoundingBox]:
+        return self._bbox
+
+    def reset_bbox(self) -> None:
+        self._bbox = None
+
+    def update_bbox(self, geo: torch.Tensor) -> BoundingBox:
+        """Fold the ECEF extent of ``geo`` into the running box (geo2xyz.py:305-320)."""
+        g = _geo_arg(geo)
+        inf = float("inf")
+        b = self._bbox
+        init = [inf, inf, inf, -inf, -inf, -inf] if b is None else [*b.min_point, *b.max_point]
+        mm = torch.tensor(init, dtype=torch.float64, device=g.device)
+        with torch.cuda.device(g.device):
+            rc = _lib.load().de_geo_bbox(_ptr(g), _DT[g.dtype], _ptr(mm), g.shape[0], _stream_ptr(g.device))
+        _lib.check(rc, "de_geo_bbox")
+        v = mm.tolist()   # the one host read-back, as in the reference (BoundingBox holds Python floats)
+        self._bbox = BoundingBox(*v)
+        return self._bbox
+
+    def geodetic_to_xyzt_norm(self, geo: torch.Tensor, t: Optional[torch.Tensor] = None, *,
+                              update_bbox: bool = False, return_ecef: bool = False):
+        """(…,3) geodetic [+ (…,) time] -> (N,4) fp32 normalised rows (and optionally (N,3) fp64 ECEF).
+
+        With ``update_bbox=True`` this is the reference's ``xyz_to_norm(geodetic_to_xyz(geo))`` (the box
+        grows to include the batch first); otherwise the pre-fitted box is used, which is what a training
+        loop wants.
+        """
+        g = _geo_arg(geo)
+        if update_bbox or self._bbox is None:
+            self.update_bbox(g)
+        n = g.shape[0]
+        tt = None
+        t_range = None
+        if t is not None:
+            _require_cuda(t, "t")
+            tt = t.reshape(-1)
+            if tt.dtype not in _DT:
+                tt = tt.to(torch.float64)
+            tt = tt.contiguous()
+            if tt.shape[0] != n:
+                raise ValueError("t must have one value per point")
+            if self.t_range is None:
+                raise ValueError("t given but the converter has no t_range")
+            t_range = _dbl3(self.t_range)
+        xyzt = torch.empty((n, 4), dtype=torch.float32, device=g.device)
+        ecef = torch.empty((n, 3), dtype=torch.float64, device=g.device) if return_ecef else None
+        with torch.cuda.device(g.device):
+            rc = _lib.load().de_geo2xyzt_norm(_ptr(g), _DT[g.dtype], _ptr(tt), _DT[tt.dtype] if tt is not None else 0,
+                                              _dbl3(self._bbox.min_point), _dbl3(self._bbox.span), t_range,
+                                              _ptr(xyzt), _ptr(ecef), n, _stream_ptr(g.device))
+        _lib.check(rc, "de_geo2xyzt_norm")
+        return (xyzt, ecef) if return_ecef else xyzt
+
+    # reference-named conveniences --------------------------------------------------------------------
+    def geodetic_to_xyz(self, geo: torch.Tensor) -> torch.Tensor:
+        """(…,3) geodetic -> (…,3) fp64 ECEF metres (geo2xyz.py:146-160, position branch only)."""
+        g = _geo_arg(geo)
+        keep = self._bbox
+        if self._bbox is None:
+            self._bbox = BoundingBox(0, 0, 0, 1, 1, 1)
+        try:
+            _, ecef = self.geodetic_to_xyzt_norm(g, None, return_ecef=True)
+        finally:
+            self._bbox = keep
+        return ecef.reshape(*geo.shape[:-1], 3)
+
+
+def geo2xyz(lat, lon, alt, *, device="cuda"):
+    """``x, y, z = geo2xyz(lat, lon, elev)`` -- the function several reference callers import but the
+    reference never defines (core/plant_data_loader.py:144, florida_plants_deepearth.py:93).  Returns ECEF
+    metres (fp64 tensors) for scalars or tensors."""
+    lat, lon, alt = (torch.as_tensor(v, dtype=torch.float64, device=device) for v in (lat, lon, alt))
+    geo = torch.stack(torch.broadcast_tensors(lat, lon, alt), -1)
+    xyz = GeospatialConverter(device=device).geodetic_to_xyz(geo)
+    return xyz[..., 0], xyz[..., 1], xyz[..., 2]

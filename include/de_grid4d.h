@@ -29,6 +29,12 @@
 extern "C" {
 #endif
 
+#if defined(__GNUC__)
+#define DE_API __attribute__((visibility("default")))
+#else
+#define DE_API
+#endif
+
 #define DE_ABI_VERSION 1
 
 /* status codes (negative = caller error) */
@@ -70,11 +76,11 @@ typedef struct de_level_desc {
     uint8_t reserved;
 } de_level_desc;
 
-int de_abi_version(void);
-const char* de_last_error(void);
+DE_API int de_abi_version(void);
+DE_API const char* de_last_error(void);
 
 /* Number of interpolation corners per level for the given flags and D. */
-int de_corners(uint32_t flags, int n_dims);
+DE_API int de_corners(uint32_t flags, int n_dims);
 
 /*
  * Hash / dense cell indices -- replaces MultiResolutionHashEncoding.hash_coords
@@ -82,7 +88,7 @@ int de_corners(uint32_t flags, int n_dims);
  * indices layout: [level][corner][point] int64, corner count = de_corners().
  * All levels must share n_dims.
  */
-int de_grid4d_hash_indices(const de_level_desc* levels_host, int n_levels,
+DE_API int de_grid4d_hash_indices(const de_level_desc* levels_host, int n_levels,
                            const float* coords, int64_t n_points, int coord_stride,
                            uint32_t flags, int64_t* indices, void* stream);
 
@@ -97,7 +103,7 @@ int de_grid4d_hash_indices(const de_level_desc* levels_host, int n_levels,
  * levels_per_group: how many consecutive levels one CTA handles (0 = auto); the
  * launch walks groups in order so a group's tables stay L2 resident.
  */
-int de_grid4d_forward(const de_level_desc* levels_host, int n_levels,
+DE_API int de_grid4d_forward(const de_level_desc* levels_host, int n_levels,
                       const float* coords, int64_t n_points, int coord_stride,
                       int table_dtype, int n_features, float out_scale,
                       const uint8_t* mask_a, const uint8_t* mask_b,
@@ -111,7 +117,7 @@ int de_grid4d_forward(const de_level_desc* levels_host, int n_levels,
  * buffers must be zeroed (or hold the running sum) by the caller.  Coordinates
  * receive no gradient, as in the reference (graph cut at hash_encoding.py:61).
  */
-int de_grid4d_backward(const de_level_desc* levels_host, int n_levels,
+DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels,
                        const float* coords, int64_t n_points, int coord_stride,
                        int n_features,
                        const uint8_t* mask_a, const uint8_t* mask_b,
@@ -123,7 +129,7 @@ int de_grid4d_backward(const de_level_desc* levels_host, int n_levels,
  * for all levels (level i: src = levels_host[i].table (fp32), dst =
  * dst_tables[i]).  dst_tables_host: host array of n_levels device pointers.
  */
-int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_features,
+DE_API int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_features,
                      void* const* dst_tables_host, float scale, void* stream);
 
 /*
@@ -136,7 +142,7 @@ int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_featu
  *   bbox_min_host/bbox_span_host: 3 doubles each; t_range_host: {t_min, t_max}
  *   xyzt: (n,4) fp32 out; ecef: optional (n,3) fp64 out (NULL to skip)
  */
-int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t_dtype,
+DE_API int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t_dtype,
                      const double* bbox_min_host, const double* bbox_span_host,
                      const double* t_range_host,
                      float* xyzt, double* ecef, int64_t n_points, void* stream);
@@ -148,11 +154,11 @@ int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t_dtype,
  * device {min_x,min_y,min_z,max_x,max_y,max_z}; the caller initialises them to
  * +inf/-inf (or a running box) -- the kernel folds the batch in with atomics.
  */
-int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n_points,
+DE_API int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n_points,
                 void* stream);
 
 /* fp64 sum of an fp32 buffer into *result (device, caller-zeroed): bench/e2e checksum. */
-int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
+DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
 
 /*
  * Gather / reduction peak probes used to define the "gather roofline"
@@ -161,7 +167,7 @@ int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
  * accesses (xorshift addresses, optional x-pair pattern).  mode 0 = load,
  * 1 = red.add.f32 vector.  sink: >= 4 bytes.
  */
-int de_probe_gather(void* table, int64_t n_entries, int entry_bytes, int mode,
+DE_API int de_probe_gather(void* table, int64_t n_entries, int entry_bytes, int mode,
                     int64_t n_threads, int per_thread, int pair_pattern,
                     void* sink, void* stream);
 

@@ -1,0 +1,122 @@
+"""CPU-only checks of the C-ABI library: it loads, exports every symbol include/de_grid4d.h declares,
+and rejects bad arguments before touching a device (no kernel is launched here)."""
+import ctypes
+import os
+import re
+import shutil
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from deepearth_b200 import _lib, build
+    if shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc"):
+        build.build_library()
+    return _lib.load()
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "de_grid4d.h")).read()
+    return sorted(set(re.findall(r"DE_API\s+[\w\s\*]+?\b(de_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported(lib):
+    from deepearth_b200 import _lib
+    syms = declared_symbols()
+    assert len(syms) >= 11
+    for s in syms:
+        assert hasattr(lib, s), f"{s} declared in include/de_grid4d.h but not exported"
+        assert s in _lib.SIGNATURES, f"{s} has no ctypes signature in deepearth_b200/_lib.py"
+    assert lib.de_abi_version() == 1
+    assert lib.de_corners(1, 3) == 8 and lib.de_corners(0, 3) == 1 and lib.de_corners(1, 4) == 16
+
+
+def test_level_desc_layout_matches_header():
+    from deepearth_b200._lib import DeLevelDesc
+    assert ctypes.sizeof(DeLevelDesc) == 40
+    assert DeLevelDesc.table_size.offset == 16 and DeLevelDesc.out_col.offset == 24
+    assert DeLevelDesc.n_dims.offset == 28 and DeLevelDesc.dim.offset == 29 and DeLevelDesc.mask_id.offset == 34
+
+
+def test_argument_validation_no_device(lib):
+    from deepearth_b200._lib import DeLevelDesc
+    lv = (DeLevelDesc * 1)()
+    lv[0].table = 0x1000
+    lv[0].table_size = 1024
+    lv[0].resolution = 16
+    lv[0].n_dims = 3
+    lv[0].dim[0], lv[0].dim[1], lv[0].dim[2] = 0, 1, 2
+    fake = ctypes.c_void_p(0x10000)
+    args = dict(coords=fake, n=8, stride=4, dt=0, F=2, scale=1.0, out=fake, ostride=2)
+
+    def fwd(levels=lv, nl=1, **kw):
+        a = {**args, **kw}
+        return lib.de_grid4d_forward(levels, nl, a["coords"], a["n"], a["stride"], a["dt"], a["F"], a["scale"], None,
+                                     None, a["out"], a["ostride"], a.get("flags", 0), a.get("g", 0), None)
+
+    assert fwd(nl=0) == -1
+    assert fwd(coords=None) == -1 and b"coords" in lib.de_last_error()
+    assert fwd(n=-1) == -1
+    assert fwd(dt=7) == -2
+    assert fwd(F=0) == -2
+    assert fwd(flags=8) == -1
+    assert fwd(stride=2) == -1          # dim 2 >= coord_stride
+    assert fwd(ostride=1) == -1         # out_col + F > out_stride
+    lv[0].dense = 1                     # (16+1)^3 = 4913 > 1024
+    assert fwd() == -1 and b"dense" in lib.de_last_error()
+    lv[0].dense = 0
+    lv[0].n_dims = 5
+    assert fwd() == -2
+    lv[0].n_dims = 3
+    lv[0].table = 0x1002                # misaligned for 8-byte entries
+    assert fwd() == -3
+    lv[0].table = 0x1000
+    assert fwd(n=0) == 0                # empty batch: accepted, nothing launched
+    assert lib.de_probe_gather(fake, 1000, 4, 0, 32, 8, 0, fake, None) == -1   # not a power of two
+    assert lib.de_geo2xyzt_norm(None, 2, None, 0, None, None, None, None, None, 4, None) == -1
+
+
+def test_modules_refuse_cpu_tensors():
+    import torch
+    import deepearth_b200 as de
+    enc = de.MultiResolutionHashEncoding(4, 2, [16, 32, 64, 128], 2 ** 10, 3)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        enc(torch.rand(8, 3))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        enc.hash_coords(torch.rand(8, 3), 16)
+    g = de.Grid4DEncoder(de.DeepEarthConfig(hidden_dim=16, hash_table_size=2 ** 10))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        g(torch.rand(8, 4))
+    with pytest.raises(ValueError):
+        de.MultiResolutionHashEncoding(4, 2, [16, 32], 2 ** 10, 3)       # fewer resolutions than levels
+    with pytest.raises(ValueError):
+        de.MultiResolutionHashEncoding(1, 2, [16], 2 ** 10, 5)
+
+
+def test_state_dict_contract_matches_reference(golden_dir):
+    """Keys / shapes / dtypes of the reference Grid4DEncoder state dict."""
+    import numpy as np
+    import torch
+    import deepearth_b200 as de
+    want = [str(k) for k in np.load(os.path.join(golden_dir, "grid4d_encoder.npz"))["state_keys"]]
+    enc = de.Grid4DEncoder(de.DeepEarthConfig(hidden_dim=32, n_heads=4, n_layers=1, hash_table_size=2 ** 14))
+    sd = enc.state_dict()
+    assert list(sd.keys()) == want
+    assert sd["spatial_encoder.hash_tables.0.weight"].shape == (2 ** 14, 2)
+    assert sd["temporal_encoder.hash_tables.7.weight"].shape == (2 ** 12, 2)
+    assert all(v.dtype == torch.float32 for v in sd.values())
+    enc2 = de.Grid4DEncoder(de.DeepEarthConfig(hidden_dim=32, n_heads=4, n_layers=1, hash_table_size=2 ** 14))
+    enc2.load_state_dict(sd)
+    for k, v in enc2.state_dict().items():
+        assert torch.equal(v, sd[k])
+    # same seed -> same initial weights as the reference init order (hash_encoding.py:38-45)
+    torch.manual_seed(3)
+    a = de.MultiResolutionHashEncoding(2, 2, [16, 32], 64, 3)
+    torch.manual_seed(3)
+    ref = [torch.nn.Embedding(64, 2) for _ in range(2)]
+    for e in ref:
+        torch.nn.init.uniform_(e.weight, -1e-4, 1e-4)
+    assert all(torch.equal(x.weight, y.weight) for x, y in zip(a.hash_tables, ref))

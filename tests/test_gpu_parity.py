@@ -1,0 +1,410 @@
+"""Parity of the CUDA path (through the nn.Module / C-ABI boundary) against the CPU oracle and the
+reference's golden vectors.  Needs a GPU: run with ``-m gpu`` on the B200 box.
+
+Tolerances (BASELINE.json north_star): hash indices bit-exact; forward features 1e-5 relative with
+fp32 tables (nearest mode is a pure gather and must be bit-exact), 1e-2 with fp16 tables; table
+gradients 1e-4 relative (atomic ordering).  "Relative" is taken against max|reference| of the tensor
+compared, because individual interpolated features can cancel to ~0.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from _synth import coords_mixed, synth_table, uniform01
+
+pytestmark = pytest.mark.gpu
+
+FWD_TOL_F32 = 1e-5
+FWD_TOL_F16 = 1e-2
+GRAD_TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+def rel_err(got, want):
+    want = np.asarray(want, dtype=np.float64)
+    return float(np.abs(np.asarray(got, dtype=np.float64) - want).max() / max(np.abs(want).max(), 1e-30))
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"), allow_pickle=False)
+
+
+def make_encoder(de, L, F, res, T, D, seed, dev, **kw):
+    enc = de.MultiResolutionHashEncoding(L, F, list(res), T, D, **kw).to(dev)
+    tabs = [synth_table(T, F, 1000 * seed + l) for l in range(L)]
+    with torch.no_grad():
+        for emb, t in zip(enc.hash_tables, tabs):
+            emb.weight.copy_(torch.from_numpy(t))
+    return enc, np.concatenate(tabs, 0)
+
+
+def oracle_levels(enc, linear):
+    from oracle.grid4d_oracle import Level
+    T, F = enc.hash_table_size, enc.n_features_per_level
+    return [Level(T=s.table_size, R=s.resolution, dims=s.dims, out_col=s.out_col, table_off=l * T, dense=s.dense)
+            for l, s in enumerate(enc.level_specs())]
+
+
+ENC_CASES = ["enc_d3_l16_t19", "enc_d4_l16_t19", "enc_d1_l8_t17", "enc_d2_l5_f4_npow2",
+             "enc_d3_l3_f1_prime", "enc_d3_l4_f8", "enc_d3_l2_f3_b1"]
+
+
+# ---------------------------------------------------------------------------------------------------
+# reference mode (nearest) against golden vectors produced by the unmodified reference
+# ---------------------------------------------------------------------------------------------------
+def test_hash_known_answers(dev, golden_dir):
+    import deepearth_b200 as de
+    g = load(golden_dir, "hash_kat")
+    enc3 = de.MultiResolutionHashEncoding(1, 2, [16], 2 ** 19, 3).to(dev)
+    pts = torch.from_numpy(g["kat_pts"]).to(dev)
+    assert enc3.hash_coords(pts, 16).tolist() == [322876, 94504, 41480]          # SURVEY.md 8c probes
+    assert enc3.hash_coords(pts, 524288).tolist() == [22798, 262144, 262144]
+    enc4 = de.MultiResolutionHashEncoding(1, 2, [1024], 2 ** 19, 4).to(dev)
+    assert enc4.hash_coords(torch.from_numpy(g["kat4_pts"]).to(dev), 1024).tolist() == [427944, 70136]
+    for k in range(int(g["n_cases"][0])):
+        D, T, R = (int(v) for v in g[f"c{k}_meta"])
+        enc = de.MultiResolutionHashEncoding(1, 2, [R], T, D)
+        got = enc.hash_coords(torch.from_numpy(g[f"c{k}_coords"]).to(dev), R)
+        assert got.dtype == torch.int64
+        assert np.array_equal(got.cpu().numpy(), g[f"c{k}_idx"]), f"case {k}: D={D} T={T} R={R}"
+
+
+@pytest.mark.parametrize("name", ENC_CASES)
+def test_encoder_vs_reference_golden(dev, golden_dir, name):
+    import deepearth_b200 as de
+    g = load(golden_dir, name)
+    L, F, T, D, seed = (int(v) for v in g["meta"])
+    enc, _ = make_encoder(de, L, F, g["resolutions"], T, D, seed, dev)
+    coords = torch.from_numpy(g["coords"]).to(dev).requires_grad_(True)
+    for l, R in enumerate(g["resolutions"]):
+        assert np.array_equal(enc.hash_coords(coords.detach(), int(R)).cpu().numpy(), g["indices"][l])
+    out = enc(coords)
+    assert out.shape == (coords.shape[0], L * F) and out.dtype == torch.float32
+    assert np.array_equal(out.detach().cpu().numpy(), g["features"])            # pure gather: bit exact
+    out.backward(torch.from_numpy(g["grad_out"]).to(dev))
+    assert coords.grad is None                                                  # hash_encoding.py:61 cuts the graph
+    for l, emb in enumerate(enc.hash_tables):
+        want = np.zeros((T, F), dtype=np.float32)
+        want[g[f"grad_rows_{l}"]] = g[f"grad_vals_{l}"]
+        assert emb.weight.grad.shape == (T, F)
+        assert rel_err(emb.weight.grad.cpu().numpy(), want) <= GRAD_TOL
+
+
+def test_grid4d_encoder_vs_reference_golden(dev, golden_dir):
+    import deepearth_b200 as de
+    g = load(golden_dir, "grid4d_encoder")
+    cfg = de.DeepEarthConfig(hidden_dim=32, n_heads=4, n_layers=1, hash_table_size=2 ** 14)
+    enc = de.Grid4DEncoder(cfg).to(dev)
+    with torch.no_grad():
+        for l, e in enumerate(enc.spatial_encoder.hash_tables):
+            e.weight.copy_(torch.from_numpy(synth_table(2 ** 14, 2, 5000 + l)))
+        for l, e in enumerate(enc.temporal_encoder.hash_tables):
+            e.weight.copy_(torch.from_numpy(synth_table(2 ** 12, 2, 6000 + l)))
+        for i, p in enumerate(enc.projection.parameters()):
+            p.copy_(torch.from_numpy((uniform01(p.numel(), 900 + i).reshape(p.shape) * 0.4 - 0.2).astype(np.float32)))
+    xyzt = torch.from_numpy(g["xyzt"]).to(dev)
+    sm = torch.from_numpy(g["spatial_mask"]).to(dev)
+    tm = torch.from_numpy(g["temporal_mask"]).to(dev)
+    assert np.array_equal(enc.encode_features(xyzt).detach().cpu().numpy(), g["features_nomask"])
+    assert np.array_equal(enc.encode_features(xyzt, sm, tm).detach().cpu().numpy(), g["features"])
+    assert rel_err(enc(xyzt).detach().cpu().numpy(), g["embedding_nomask"]) <= 1e-5
+    emb = enc(xyzt, spatial_mask=sm, temporal_mask=tm)
+    assert rel_err(emb.detach().cpu().numpy(), g["embedding"]) <= 1e-5
+    emb.backward(torch.from_numpy(g["grad_out"]).to(dev))
+    for nm, sub, T in (("s", enc.spatial_encoder, 2 ** 14), ("t", enc.temporal_encoder, 2 ** 12)):
+        for l, e in enumerate(sub.hash_tables):
+            want = np.zeros((T, 2), dtype=np.float32)
+            want[g[f"grad_rows_{nm}{l}"]] = g[f"grad_vals_{nm}{l}"]
+            assert rel_err(e.weight.grad.cpu().numpy(), want) <= GRAD_TOL, (nm, l)
+    for i, p in enumerate(enc.projection.parameters()):
+        assert rel_err(p.grad.cpu().numpy(), g[f"proj_grad_{i}"]) <= 1e-4
+    # the stand-alone sub-encoders keep the reference call signature
+    s = enc.spatial_encoder(xyzt[:, :3])
+    t = enc.temporal_encoder(xyzt[:, 3:4])
+    assert np.array_equal(torch.cat([s, t], -1).detach().cpu().numpy(), g["features_nomask"])
+
+
+# ---------------------------------------------------------------------------------------------------
+# seeded inputs against the C oracle: both modes, both table dtypes
+# ---------------------------------------------------------------------------------------------------
+CFGS = [
+    # L, F, resolutions, T, D, n, linear, dense
+    (16, 2, [2 ** i for i in range(4, 20)], 2 ** 19, 3, 20000, False, False),
+    (16, 2, [2 ** i for i in range(4, 20)], 2 ** 19, 3, 20000, True, True),
+    (8, 2, [2 ** i for i in range(2, 10)], 2 ** 17, 1, 5000, True, True),
+    (6, 4, [5, 16, 47, 128, 500, 4096], 2 ** 12, 2, 7001, True, True),
+    (5, 2, [4, 8, 16, 32, 64], 2 ** 16, 4, 3000, True, True),
+    (5, 1, [3, 9, 27, 81, 243], 30011, 3, 4099, True, True),      # non power-of-two table: int64 path
+    (3, 8, [16, 64, 256], 2 ** 10, 3, 2500, True, False),
+    (2, 3, [16, 128], 1000, 3, 1025, True, True),                 # runtime-F path
+]
+
+
+@pytest.mark.parametrize("cfg", CFGS, ids=lambda c: f"L{c[0]}F{c[1]}T{c[3]}D{c[4]}{'lin' if c[6] else 'nn'}")
+def test_modes_vs_oracle_fp32(dev, oracle, cfg):
+    import deepearth_b200 as de
+    from deepearth_b200 import functional as Fn
+    L, F, res, T, D, n, linear, dense = cfg
+    enc, tables = make_encoder(de, L, F, res, T, D, 11, dev, interpolation="linear" if linear else "nearest",
+                               dense_fallback=dense)
+    levels = oracle_levels(enc, linear)
+    assert any(lv.dense for lv in levels) == (dense and (res[0] + 1) ** D <= T)
+    coords_np = coords_mixed(n, D, 5, res_hint=res[0])
+    coords = torch.from_numpy(coords_np).to(dev)
+    idx = Fn.hash_indices(enc.level_specs(), coords, linear).cpu().numpy()
+    want_idx = oracle.hash_indices(levels, coords_np, linear)
+    for l in range(L):
+        assert np.array_equal(idx[l], want_idx[l]), f"level {l}"            # bit exact, every corner
+    out = enc(coords)
+    want = oracle.forward(levels, coords_np, tables, F, linear)
+    err = rel_err(out.detach().cpu().numpy(), want)
+    assert err <= (FWD_TOL_F32 if linear else 0.0), err
+    gout_np = (uniform01(n * L * F, 99).reshape(n, L * F) * 2 - 1).astype(np.float32)
+    out.backward(torch.from_numpy(gout_np).to(dev))
+    want_g = oracle.backward(levels, coords_np, gout_np, L * T, F, linear)
+    for l, emb in enumerate(enc.hash_tables):
+        assert rel_err(emb.weight.grad.cpu().numpy(), want_g[l * T:(l + 1) * T]) <= GRAD_TOL, f"level {l}"
+
+
+def test_fp16_tables_vs_oracle(dev, oracle):
+    import deepearth_b200 as de
+    L, F, T, D, n = 16, 2, 2 ** 19, 3, 20000
+    res = [2 ** i for i in range(4, 20)]
+    enc, tables = make_encoder(de, L, F, res, T, D, 13, dev, interpolation="linear", dense_fallback=True,
+                               table_dtype="float16")
+    assert enc.table_scale == 4096.0
+    levels = oracle_levels(enc, True)
+    coords_np = coords_mixed(n, D, 6)
+    out = enc(torch.from_numpy(coords_np).to(dev)).detach().cpu().numpy()
+    half_tables = (tables * np.float32(enc.table_scale)).astype(np.float16)
+    assert np.array_equal(enc._work.cpu().numpy().reshape(-1, F), half_tables)   # cast kernel: exact
+    want_h = oracle.forward(levels, coords_np, half_tables, F, True, out_scale=1.0 / enc.table_scale)
+    assert rel_err(out, want_h) <= FWD_TOL_F32              # same fp16 tables: only accumulation order
+    want_f = oracle.forward(levels, coords_np, tables, F, True)
+    assert rel_err(out, want_f) <= FWD_TOL_F16              # vs fp32 tables: the stated fp16 tolerance
+    # unscaled fp16 storage of the 1e-4 init is subnormal -- show why the scale is there
+    enc1, _ = make_encoder(de, L, F, res, T, D, 13, dev, interpolation="linear", dense_fallback=True,
+                           table_dtype="float16", table_scale=1.0)
+    out1 = enc1(torch.from_numpy(coords_np).to(dev)).detach().cpu().numpy()
+    assert rel_err(out1, want_f) <= FWD_TOL_F16
+    assert rel_err(out, want_f) < rel_err(out1, want_f)
+
+
+def test_decomposed_encoder_vs_oracle(dev, oracle):
+    """BASELINE config 2 geometry at reduced size: xyz/xyt/yzt/xzt x 16 levels, fp16 tables, fp32 grads."""
+    import deepearth_b200 as de
+    from oracle.grid4d_oracle import GRID_DIMS, Level
+    T, F, L, n = 2 ** 16, 2, 16, 6000
+    res = [2 ** i for i in range(4, 20)]
+    cfg = de.DeepEarthConfig(hidden_dim=16, n_heads=4, n_layers=1, hash_table_size=T, n_temporal_levels=16,
+                             temporal_resolutions=res, grid4d_mode="decomposed", grid4d_table_dtype="float16")
+    enc = de.Grid4DEncoder(cfg).to(dev)
+    assert enc.feature_dim == 128
+    names = ["xyz", "xyt", "yzt", "xzt"]
+    levels, tabs = [], []
+    for gi, nm in enumerate(names):
+        sub = getattr(enc, f"{nm}_encoder")
+        for l in range(L):
+            t = synth_table(T, F, 7000 + 100 * gi + l)
+            tabs.append(t)
+            with torch.no_grad():
+                sub.hash_tables[l].weight.copy_(torch.from_numpy(t))
+            levels.append(Level(T=T, R=res[l], dims=GRID_DIMS[nm], out_col=(gi * L + l) * F,
+                                table_off=(gi * L + l) * T, dense=(res[l] + 1) ** 3 <= T))
+    tables = np.concatenate(tabs, 0)
+    xyzt_np = coords_mixed(n, 4, 21)
+    xyzt = torch.from_numpy(xyzt_np).to(dev)
+    feats = enc.encode_features(xyzt)
+    half = (tables * np.float32(4096.0)).astype(np.float16)
+    want = oracle.forward(levels, xyzt_np, half, F, True, out_scale=1.0 / 4096.0)
+    assert rel_err(feats.detach().cpu().numpy(), want) <= FWD_TOL_F32
+    assert rel_err(feats.detach().cpu().numpy(), oracle.forward(levels, xyzt_np, tables, F, True)) <= FWD_TOL_F16
+    gout_np = (uniform01(n * 128, 5).reshape(n, 128) * 2 - 1).astype(np.float32)
+    feats.backward(torch.from_numpy(gout_np).to(dev))
+    want_g = oracle.backward(levels, xyzt_np, gout_np, 4 * L * T, F, True)
+    k = 0
+    for nm in names:
+        for e in getattr(enc, f"{nm}_encoder").hash_tables:
+            assert e.weight.grad.dtype == torch.float32
+            assert rel_err(e.weight.grad.cpu().numpy(), want_g[k * T:(k + 1) * T]) <= GRAD_TOL, (nm, k)
+            k += 1
+    # spec masking: coordinates, not features, are zeroed (SPECIFICATIONS.MD:1159-1164)
+    sm = torch.from_numpy(uniform01(n, 8) > 0.5).to(dev)
+    masked = xyzt_np.copy()
+    masked[~sm.cpu().numpy(), :3] = 0
+    want_m = oracle.forward(levels, masked, half, F, True, out_scale=1.0 / 4096.0)
+    assert rel_err(enc.encode_features(xyzt, spatial_mask=sm).detach().cpu().numpy(), want_m) <= FWD_TOL_F32
+
+
+# ---------------------------------------------------------------------------------------------------
+# edge cases
+# ---------------------------------------------------------------------------------------------------
+def test_edge_shapes(dev, oracle):
+    import deepearth_b200 as de
+    enc, tables = make_encoder(de, 4, 2, [16, 32, 64, 128], 2 ** 12, 3, 3, dev, interpolation="linear")
+    empty = enc(torch.empty((0, 3), device=dev))
+    assert empty.shape == (0, 8)
+    one = enc(torch.tensor([[0.3, -0.2, 1.7]], device=dev))
+    assert one.shape == (1, 8)
+    # non-contiguous input: a column slice of an xyzt batch is consumed in place (row stride 4)
+    xyzt_np = coords_mixed(1000, 4, 9)
+    xyzt = torch.from_numpy(xyzt_np).to(dev)
+    a = enc(xyzt[:, :3])
+    b = enc(xyzt[:, :3].contiguous())
+    assert torch.equal(a, b)
+    t = xyzt.t().contiguous().t()[:, :3]          # column-major view: needs the copy path
+    assert torch.equal(enc(t), b)
+    with pytest.raises(TypeError):
+        enc(xyzt[:, :3].double())
+    with pytest.raises(ValueError):
+        enc(xyzt[:, :2])
+    # levels_per_group override gives identical results
+    enc.levels_per_group = 1
+    assert torch.equal(enc(xyzt[:, :3]), b)
+    enc.levels_per_group = 2
+    assert torch.equal(enc(xyzt[:, :3]), b)
+    # no_grad / eval and autocast keep fp32 features
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        c = enc(xyzt[:, :3])
+    assert c.dtype == torch.float32 and torch.equal(c, b)
+
+
+def test_frozen_tables_and_grad_accumulation(dev):
+    import deepearth_b200 as de
+    enc, _ = make_encoder(de, 3, 2, [16, 32, 64], 2 ** 10, 3, 4, dev)
+    enc.hash_tables[1].weight.requires_grad_(False)
+    x = torch.rand(500, 3, device=dev)
+    enc(x).sum().backward()
+    g0 = enc.hash_tables[0].weight.grad.clone()
+    assert enc.hash_tables[1].weight.grad is None
+    enc(x).sum().backward()                        # second backward accumulates
+    assert torch.allclose(enc.hash_tables[0].weight.grad, 2 * g0)
+    assert float(g0.sum()) == pytest.approx(500 * 2, rel=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE.json sizes: size-independent properties + the device-resident torch restatement
+# ---------------------------------------------------------------------------------------------------
+def test_full_size_properties(dev):
+    """Config 2 (4 grids x 16 levels x 2 feat, T=2^19, 2^22 points, fp16 tables): constant tables
+    interpolate to the constant, the encode is linear in the tables, and sum(grad_tables) equals
+    sum(grad_out) per feature column group (corner weights sum to 1)."""
+    import deepearth_b200 as de
+    T, L, F, n = 2 ** 19, 16, 2, 2 ** 22
+    res = [2 ** i for i in range(4, 20)]
+    cfg = de.DeepEarthConfig(hidden_dim=16, n_heads=4, n_layers=1, hash_table_size=T, n_temporal_levels=16,
+                             temporal_resolutions=res, grid4d_mode="decomposed", grid4d_table_dtype="float16",
+                             grid4d_table_scale=1.0)
+    enc = de.Grid4DEncoder(cfg).to(dev)
+    g = torch.Generator(device=dev).manual_seed(1234)
+    xyzt = torch.rand((n, 4), device=dev, generator=g)
+    tabs = [e.weight for sub in enc._encoders for e in sub.hash_tables]
+    assert len(tabs) == 64
+    with torch.no_grad():
+        for p in tabs:
+            p.fill_(0.25)
+    feats = enc.encode_features(xyzt)
+    assert float((feats - 0.25).abs().max()) <= 1e-6
+    del feats
+    with torch.no_grad():
+        for i, p in enumerate(tabs):
+            p.copy_((torch.rand(p.shape, device=dev, generator=g) * 2 - 1).half().float())   # exactly fp16
+    f1 = enc.encode_features(xyzt).detach()
+    with torch.no_grad():
+        for p in tabs:
+            p.mul_(0.5)                                  # exact in fp16
+    f2 = enc.encode_features(xyzt).detach()
+    assert torch.equal(f2, f1 * 0.5)                     # linear in the tables, exactly for a power of two
+    gout = torch.randn((n, 128), device=dev, generator=g)
+    feats = enc.encode_features(xyzt)
+    feats.backward(gout)
+    col_sums = gout.double().sum(0).view(64, F)
+    abs_sum = float(gout.abs().double().sum(0).max())
+    for k, p in enumerate(tabs):
+        got = p.grad.double().sum(0)
+        assert float((got - col_sums[k]).abs().max()) <= 1e-5 * abs_sum, k
+
+
+def test_large_vs_torch_restatement_on_device(dev):
+    """2^20 points against oracle/grid4d_torch.py running through ATen on the same GPU."""
+    import deepearth_b200 as de
+    from oracle.grid4d_torch import grid4d_forward
+    T, L, F, n = 2 ** 19, 16, 2, 2 ** 20
+    res = [2 ** i for i in range(4, 20)]
+    g = torch.Generator(device=dev).manual_seed(7)
+    for linear in (False, True):
+        enc = de.MultiResolutionHashEncoding(L, F, res, T, 3, interpolation="linear" if linear else "nearest",
+                                             dense_fallback=linear).to(dev)
+        with torch.no_grad():
+            for e in enc.hash_tables:
+                e.weight.copy_(torch.rand(e.weight.shape, device=dev, generator=g) * 2e-4 - 1e-4)
+        coords = torch.randn((n, 3), device=dev, generator=g) * 0.7
+        specs = [((0, 1, 2), s.resolution, T, s.dense) for s in enc.level_specs()]
+        tabs = [e.weight for e in enc.hash_tables]
+        out = enc(coords)
+        want = grid4d_forward(coords, tabs, specs, linear)
+        if linear:
+            assert float((out - want).abs().max() / want.abs().max()) <= FWD_TOL_F32
+        else:
+            assert torch.equal(out, want)
+        gout = torch.randn(out.shape, device=dev, generator=g)
+        out.backward(gout)
+        mine = [e.weight.grad.clone() for e in enc.hash_tables]
+        for e in enc.hash_tables:
+            e.weight.grad = None
+        want.backward(gout)
+        for l, e in enumerate(enc.hash_tables):
+            denom = float(e.weight.grad.abs().max())
+            assert float((mine[l] - e.weight.grad).abs().max()) <= GRAD_TOL * denom, l
+
+
+# ---------------------------------------------------------------------------------------------------
+# geodetic prologue
+# ---------------------------------------------------------------------------------------------------
+def test_geo2xyz_vs_reference_and_oracle(dev, oracle, golden_dir):
+    import deepearth_b200 as de
+    g = load(golden_dir, "geo2xyz")
+    for name in ("landmarks", "florida", "global"):
+        geo = torch.from_numpy(g[f"{name}_geo"]).to(dev)
+        conv = de.GeospatialConverter(device="cuda:0")
+        xyzt, ecef = conv.geodetic_to_xyzt_norm(geo, update_bbox=True, return_ecef=True)
+        assert np.abs(ecef.cpu().numpy() - g[f"{name}_ecef"]).max() <= 1e-6          # metres
+        assert np.allclose(np.array(conv.bbox.min_point), g[f"{name}_bbox_min"], rtol=0, atol=1e-6)
+        assert np.allclose(np.array(conv.bbox.span), g[f"{name}_bbox_span"], rtol=0, atol=1e-6)
+        want = g[f"{name}_norm"].astype(np.float32)
+        assert np.abs(xyzt[:, :3].cpu().numpy() - want).max() <= 1.2e-7
+        assert float(xyzt[:, 3].abs().max()) == 0.0
+        # pre-fitted box + oracle: fp32 outputs identical except where fp64 libm vs CUDA rounding differs
+        fixed = de.GeospatialConverter(device="cuda:0", bbox=de.BoundingBox(*g[f"{name}_bbox_min"],
+                                       *(g[f"{name}_bbox_min"] + g[f"{name}_bbox_span"])), t_range=(0.0, 10.0))
+        tt = torch.linspace(-1, 11, geo.shape[0], dtype=torch.float64, device=dev)
+        x2 = fixed.geodetic_to_xyzt_norm(geo, tt).cpu().numpy()
+        o2 = oracle.geo2xyzt_norm(g[f"{name}_geo"], tt.cpu().numpy(), g[f"{name}_bbox_min"],
+                                  np.array(fixed.bbox.span), (0.0, 10.0))
+        assert np.abs(x2 - o2).max() <= 1.2e-7
+        assert (x2 != o2).mean() <= 1e-3
+    same = torch.from_numpy(g["degenerate_geo"]).to(dev)
+    conv = de.GeospatialConverter(device="cuda:0")
+    assert np.array_equal(conv.geodetic_to_xyzt_norm(same, update_bbox=True)[:, :3].cpu().numpy(),
+                          g["degenerate_norm"].astype(np.float32))                    # all 0.5
+    # fp32 geodetic input is up-cast like _as_fp64 (geo2xyz.py:147)
+    geo32 = torch.from_numpy(g["florida_geo"]).float().to(dev)
+    a = de.GeospatialConverter(device="cuda:0").geodetic_to_xyz(geo32)
+    b = de.GeospatialConverter(device="cuda:0").geodetic_to_xyz(geo32.double())
+    assert torch.equal(a, b)
+    x, y, z = de.geo2xyz(28.5, -81.4, 25.0)
+    assert abs(float(x) - g["landmarks_ecef"][-1, 0]) < 1e-6
+
+
+def test_sum_and_probe_helpers(dev):
+    from deepearth_b200 import functional as Fn
+    x = torch.randn(1_000_003, device=dev)
+    assert float(Fn.sum_f32(x)) == pytest.approx(float(x.double().sum()), rel=1e-9, abs=1e-6)
