@@ -195,7 +195,8 @@ def test_fp16_tables_vs_oracle(dev, oracle):
                            table_dtype="float16", table_scale=1.0)
     out1 = enc1(torch.from_numpy(coords_np).to(dev)).detach().cpu().numpy()
     assert rel_err(out1, want_f) <= FWD_TOL_F16
-    assert rel_err(out, want_f) < rel_err(out1, want_f)
+    # max error can tie (both hit the same fp16-normal entry); the scale shows in the mean error
+    assert np.abs(out - want_f).mean() < np.abs(out1 - want_f).mean()
 
 
 def test_decomposed_encoder_vs_oracle(dev, oracle):
