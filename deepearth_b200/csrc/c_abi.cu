@@ -298,6 +298,7 @@ DE_API int de_probe_gather(void* table, int64_t n_entries, int entry_bytes, int 
     if (n_entries <= 0 || (n_entries & (n_entries - 1)) || n_entries > (1ll << 32)) return fail(DE_EINVAL, "probe: n_entries must be a power of two <= 2^32");
     if (entry_bytes != 4 && entry_bytes != 8 && entry_bytes != 16) return fail(DE_EUNSUPPORTED, "probe: entry_bytes=%d", entry_bytes);
     if (mode != 0 && mode != 1) return fail(DE_EINVAL, "probe: mode=%d", mode);
+    if (pair_pattern != 0 && pair_pattern != 1 && pair_pattern != 2 && pair_pattern != 4 && pair_pattern != 8) return fail(DE_EINVAL, "probe: pair_pattern=%d", pair_pattern);
     if (n_threads <= 0 || per_thread <= 0 || per_thread % 8) return fail(DE_EINVAL, "probe: per_thread must be a positive multiple of 8");
     cudaError_t e = de::launch_probe(table, n_entries, entry_bytes, mode, n_threads, per_thread, pair_pattern, sink, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "probe launch");

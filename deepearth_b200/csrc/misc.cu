@@ -71,8 +71,10 @@ cudaError_t launch_sum_f32(const float* x, long long n, double* result, cudaStre
 
 // ---- gather / reduction probes -----------------------------------------------------------------
 // Each thread walks `per_thread` pseudo-random entries of a power-of-two table.  pair_pattern mimics
-// a multilinear cell of the encoder: entries come as (i, i+1) neighbours -- the x-pair of a corner
-// set, which shares a 32 B sector most of the time because prime[0] = 1 (hash_encoding.py:64).
+// a multilinear cell of the encoder: pair_pattern = 1 -> entries come as (i, i+1) neighbours in CONSECUTIVE
+// instructions of one thread -- the x-pair of a corner set, which shares a 32 B sector most of the time
+// because prime[0] = 1 (hash_encoding.py:64); pair_pattern = 2/4/8 -> that many neighbouring LANES address
+// neighbouring entries in the same instruction.
 __device__ __forceinline__ uint32_t xorshift32(uint32_t& s) {
     s ^= s << 13; s ^= s >> 17; s ^= s << 5;
     return s;
@@ -91,8 +93,19 @@ probe_kernel(void* table, uint32_t mask, long long n_threads, int per_thread, in
         uint32_t idx[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            if (pair_pattern && (u & 1)) idx[u] = (idx[u - 1] + 1u) & mask;
+            if (pair_pattern == 1 && (u & 1)) idx[u] = (idx[u - 1] + 1u) & mask;
             else idx[u] = xorshift32(s) & mask;
+        }
+        if (pair_pattern >= 2) {
+            // lane-adjacent pattern: groups of `pair_pattern` neighbouring lanes address neighbouring
+            // entries in the SAME instruction (what a corner-per-lane layout would issue)
+            const int gl = pair_pattern;                    // 2, 4 or 8 lanes per group
+            const int lane = threadIdx.x & 31;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t base = __shfl_sync(0xffffffffu, idx[u], lane & ~(gl - 1));
+                idx[u] = ((base & ~static_cast<uint32_t>(gl - 1)) + (lane & (gl - 1))) & mask;
+            }
         }
         if constexpr (MODE == 0) {
 #pragma unroll
