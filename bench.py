@@ -285,6 +285,12 @@ def run_gpu_arm(args, wl):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     from deepearth_b200 import functional as Fn
+    from deepearth_b200 import _lib as _L
+    import ctypes as _ct
+    if args.l2_fetch:
+        _L.check(_L.load().de_set_l2_fetch_granularity(args.l2_fetch), "de_set_l2_fetch_granularity")
+    _gran = _ct.c_int(0)
+    _L.load().de_get_l2_fetch_granularity(_ct.byref(_gran))
 
     n = 2 ** (args.log2_points if args.log2_points else wl["log2_points"])
     job = Job(wl, device, seed=1234 + rank, n_points=n)
@@ -393,6 +399,7 @@ def run_gpu_arm(args, wl):
                        "coords": wl["coords"], "levels": len(job.plan.specs), "features_per_level": job.F,
                        "table_size": wl["T"], "interpolation": "linear" if job.linear else "nearest",
                        "l2_policy": "inputs larger than L2 (coords+grad_out+out > 4 GiB per step); no flush",
+                       "l2_fetch_granularity": _gran.value,
                        "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"},
             "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms},
             "roofline": {"bound": "hbm", "kernel": f"grid4d_{dom}_kernel", "achieved": achieved, "peak": peak,
@@ -426,6 +433,7 @@ def main():
     ap.add_argument("--levels-per-group", type=int, default=0)
     ap.add_argument("--bwd-levels-per-group", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--l2-fetch", type=int, default=0, help="set cudaLimitMaxL2FetchGranularity (32/64/128)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

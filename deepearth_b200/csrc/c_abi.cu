@@ -29,6 +29,9 @@ int cuda_fail(cudaError_t e, const char* what) {
 
 bool is_pow2(uint32_t v) { return v && !(v & (v - 1)); }
 
+// L2 working-set budget of one level group (B200 L2 ~126 MB, split over two dies)
+constexpr unsigned long long kL2BudgetBytes = 64ull << 20;
+
 int floor_pow2(int v) {
     int p = 1;
     while (p * 2 <= v) p *= 2;
@@ -95,6 +98,13 @@ void fill_level(const de_level_desc& L, de::LevelParams& o) {
     o.pow2 = is_pow2(L.table_size) ? 1 : 0;
     o.mask_id = L.mask_id;
     o.pad = 0;
+    static const uint32_t kPrimes[4] = {1u, 2654435761u, 805459861u, 3674653429u};   // hash_encoding.py:64
+    uint64_t stride = 1;
+    for (int d = 0; d < 4; ++d) {
+        o.mul[d] = L.dense ? static_cast<uint32_t>(stride) : kPrimes[d];
+        stride *= static_cast<uint64_t>(L.resolution) + 1ull;   // validate() bounds (R+1)^D <= T < 2^32 for dense
+        if (stride > 0xffffffffull) stride = 0;                  // never used: beyond n_dims of a valid dense level
+    }
 }
 
 bool rows_vectorisable(const void* base, int64_t stride, const de_level_desc* levels, int n_levels, int F) {
@@ -122,26 +132,54 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
 
         de::EncodeParams P = base;
         P.n_levels = n;
-        for (int i = 0; i < n; ++i) fill_level(a.levels[begin + i], P.levels[i]);
+        bool pow2_all = true;
+        unsigned long long max_level_bytes = 1;
+        for (int i = 0; i < n; ++i) {
+            const de_level_desc& L = a.levels[begin + i];
+            fill_level(L, P.levels[i]);
+            pow2_all = pow2_all && is_pow2(L.table_size);
+            unsigned long long live = L.table_size;
+            if (L.dense) {   // a dense level only ever touches its (R+1)^D cells
+                live = 1;
+                for (int d = 0; d < L.n_dims; ++d) live *= (unsigned long long)L.resolution + 1ull;
+            }
+            const unsigned long long eb = (unsigned long long)a.n_features * (op == Op::Backward ? 4u : (a.table_dtype == DE_F16 ? 2u : 4u));
+            if (live * eb > max_level_bytes) max_level_bytes = live * eb;
+        }
+        const bool pair = op != Op::Indices && de::pair_layout_supported(linear, a.n_features);
         int G = a.levels_per_group;
-        if (G == 0) {  // auto: make the G lanes of a point cover at least one 32 B sector of its row
-            G = 8 / a.n_features;
-            if (G < 1) G = 1;
+        if (G == 0) {
+            if (pair) {
+                // as many levels per CTA group as keep the group's (gradient) tables L2 resident, up to the
+                // 16 that make a point's slice of the feature row a full 128 B line (F = 2)
+                G = 16;
+                while (G > 1 && (unsigned long long)G * max_level_bytes > kL2BudgetBytes) G >>= 1;
+            } else {
+                G = 8 / a.n_features;   // the G lanes of a point cover at least one 32 B sector of its row
+                if (G < 1) G = 1;
+            }
         }
         G = floor_pow2(G > n ? n : G);
         if (G > de::kMaxGroup) G = de::kMaxGroup;
         P.group_size = G;
         P.n_groups = (n + G - 1) / G;
-        const int iters = 4;
-        P.points_per_cta = (de::kThreads / G) * iters;
+        const int lanes_per_point = pair ? 2 * G : G;
+        const int iters = pair ? 8 : 4;
+        P.points_per_cta = (de::kThreads / lanes_per_point) * iters;
         const long long tiles = (a.n_points + P.points_per_cta - 1) / P.points_per_cta;
         if (tiles * P.n_groups >= (1ll << 31)) return fail(DE_EUNSUPPORTED, "n_points=%lld too large for one launch", (long long)a.n_points);
         P.n_tiles = static_cast<int>(tiles);
 
         cudaError_t e = cudaSuccess;
         switch (op) {
-            case Op::Forward: e = de::launch_forward(P, D, linear, a.table_dtype == DE_F16, a.n_features, stream); break;
-            case Op::Backward: e = de::launch_backward(P, D, linear, a.n_features, stream); break;
+            case Op::Forward:
+                e = pair ? de::launch_forward_pair(P, D, a.table_dtype == DE_F16, a.n_features, pow2_all, stream)
+                         : de::launch_forward(P, D, linear, a.table_dtype == DE_F16, a.n_features, stream);
+                break;
+            case Op::Backward:
+                e = pair ? de::launch_backward_pair(P, D, a.n_features, pow2_all, stream)
+                         : de::launch_backward(P, D, linear, a.n_features, stream);
+                break;
             case Op::Indices: {
                 // indices are laid out per call, so offset the level index by `begin`
                 const int C = linear ? (1 << D) : 1;
@@ -284,6 +322,21 @@ DE_API int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n
     if (geo_dtype != DE_F64 && geo_dtype != DE_F32) return fail(DE_EUNSUPPORTED, "geo_dtype=%d", geo_dtype);
     cudaError_t e = de::launch_geo_bbox(geo, geo_dtype == DE_F64, minmax, n_points, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "geo_bbox launch");
+}
+
+DE_API int de_set_l2_fetch_granularity(int bytes) {
+    if (bytes != 32 && bytes != 64 && bytes != 128) return fail(DE_EINVAL, "l2 fetch granularity must be 32, 64 or 128, got %d", bytes);
+    cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, static_cast<size_t>(bytes));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "cudaDeviceSetLimit(MaxL2FetchGranularity)");
+}
+
+DE_API int de_get_l2_fetch_granularity(int* bytes) {
+    if (!bytes) return fail(DE_EINVAL, "bytes is NULL");
+    size_t v = 0;
+    cudaError_t e = cudaDeviceGetLimit(&v, cudaLimitMaxL2FetchGranularity);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetLimit(MaxL2FetchGranularity)");
+    *bytes = static_cast<int>(v);
+    return DE_OK;
 }
 
 DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream) {

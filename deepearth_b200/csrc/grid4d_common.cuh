@@ -35,6 +35,7 @@ struct LevelParams {
     uint8_t pow2;       // T is a power of two: 32-bit hash fast path is bit-identical
     uint8_t mask_id;
     uint8_t pad;
+    uint32_t mul[4];    // per-dimension index multiplier: prime_d (hashed) or (R+1)^d (dense); mul[0] == 1
 };
 
 struct EncodeParams {

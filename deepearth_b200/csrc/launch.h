@@ -11,6 +11,11 @@ cudaError_t launch_forward(const EncodeParams& P, int D, bool linear, bool half_
 cudaError_t launch_backward(const EncodeParams& P, int D, bool linear, int F, cudaStream_t s);
 cudaError_t launch_indices(const EncodeParams& P, int D, bool linear, cudaStream_t s);
 
+// lane-pair layout (grid4d_pair_kernels.cu): multilinear mode, F in {1,2,4,8}
+bool pair_layout_supported(bool linear, int F);
+cudaError_t launch_forward_pair(const EncodeParams& P, int D, bool half_tables, int F, bool pow2, cudaStream_t s);
+cudaError_t launch_backward_pair(const EncodeParams& P, int D, int F, bool pow2, cudaStream_t s);
+
 struct CastParams {
     const float* src[64];
     void* dst[64];

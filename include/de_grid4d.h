@@ -157,6 +157,15 @@ DE_API int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t
 DE_API int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n_points,
                 void* stream);
 
+/*
+ * Device-wide L2 fetch granularity hint (cudaLimitMaxL2FetchGranularity) of the current device: 32, 64 or
+ * 128 bytes.  The encoder reads gradient rows in pieces of G*F*4 bytes per level group; with the
+ * default 128 B granularity the L2 over-fetches the rest of each line from HBM.  Application-level
+ * knob (it affects every kernel of the process on that device); get returns the value in *bytes.
+ */
+DE_API int de_set_l2_fetch_granularity(int bytes);
+DE_API int de_get_l2_fetch_granularity(int* bytes);
+
 /* fp64 sum of an fp32 buffer into *result (device, caller-zeroed): bench/e2e checksum. */
 DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
 
