@@ -81,7 +81,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except OSError:
@@ -89,16 +89,25 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.perf_counter(), line.strip()))
 
-    def stop(self):
+    def mark(self):
+        """Host time stamp; samples are attributed to the window between two marks."""
+        return time.perf_counter()
+
+    def n_between(self, t0, t1):
+        return sum(1 for t, _ in self.rows if t0 <= t <= t1)
+
+    def stop(self, t0=None, t1=None):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.1)
         self.proc.terminate()
         sm, smax, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for t, r in self.rows:
+            if t0 is not None and not (t0 <= t <= t1):
+                continue
             parts = [p.strip() for p in r.split(",")]
             if len(parts) < 7:
                 continue
@@ -189,12 +198,12 @@ class Job:
         from deepearth_b200 import functional as Fn
         Fn.encode_forward(self.plan.specs, self.coords, self.table_ptrs, self.plan.table_dtype, self.F,
                           self.plan.out_cols, self.linear, self.out_scale, out=self.out,
-                          levels_per_group=self.plan.levels_per_group)
+                          levels_per_group=self.plan.levels_per_group, extra_flags=self.plan.extra_flags)
 
     def backward(self):
         from deepearth_b200 import functional as Fn
         Fn.encode_backward(self.plan.specs, self.coords, self.gout, self.grad_ptrs, self.F, self.linear,
-                           levels_per_group=self.plan.bwd_levels_per_group)
+                           levels_per_group=self.plan.bwd_levels_per_group, extra_flags=self.plan.extra_flags)
 
     def n_launches_per_step(self):
         # one launch per run of equal-D levels (<= 64) for forward and for backward
@@ -298,6 +307,7 @@ def run_gpu_arm(args, wl):
         job.plan.levels_per_group = args.levels_per_group
     if args.bwd_levels_per_group:
         job.plan.bwd_levels_per_group = args.bwd_levels_per_group
+    job.plan.extra_flags = args.flags
 
     def step(ev=None):
         job.flat_grad.zero_()
@@ -319,21 +329,41 @@ def run_gpu_arm(args, wl):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()                    # nvidia-smi takes ~0.5 s to deliver its first sample
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    w0 = sampler.mark()
     t_start.record()
     for k in range(args.steps):
         step(evs[k])
     t_end.record()
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    w1 = sampler.mark()
+    clock_window = "timed region"
+    # the timed region may be shorter than a few nvidia-smi periods: then every rank keeps the same load
+    # running (untimed) until rank 0 has enough samples, and the JSON line says so
+    extra = 0
+    if rank == 0 and sampler.proc is not None and sampler.n_between(w0, w1) < 4:
+        extra = max(1, int(1500.0 / max(t_start.elapsed_time(t_end) / args.steps, 0.05)))
+    if world > 1:
+        ex = torch.tensor([extra], device=device, dtype=torch.int64)
+        dist.broadcast(ex, 0)
+        extra = int(ex)
+    if extra:
+        clock_window = "timed region + identical untimed steps run straight after it"
+        for _ in range(extra):
+            step()
+        barrier()
+        w1 = sampler.mark()
+    clocks = sampler.stop(w0, w1) if rank == 0 else None
+    if clocks is not None:
+        clocks["window"] = clock_window
     total_ms = t_start.elapsed_time(t_end)
     fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
     bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
@@ -433,6 +463,7 @@ def main():
     ap.add_argument("--levels-per-group", type=int, default=0)
     ap.add_argument("--bwd-levels-per-group", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--flags", type=lambda v: int(v, 0), default=0, help="DE_FLAG_* opt-in paths (0x100 TMA-staged backward, 0x200 shared-memory coarse forward)")
     ap.add_argument("--l2-fetch", type=int, default=0, help="set cudaLimitMaxL2FetchGranularity (32/64/128)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

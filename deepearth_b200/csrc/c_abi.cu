@@ -4,6 +4,7 @@
 // thread local), nothing synchronises.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/de_grid4d.h"
@@ -59,7 +60,7 @@ int validate(const CallArgs& a) {
     if (a.coord_stride < 1) return fail(DE_EINVAL, "coord_stride=%d < 1", a.coord_stride);
     if (a.n_features < 1 || a.n_features > 64) return fail(DE_EUNSUPPORTED, "n_features=%d outside 1..64", a.n_features);
     if (a.table_dtype != DE_F32 && a.table_dtype != DE_F16) return fail(DE_EUNSUPPORTED, "table_dtype=%d", a.table_dtype);
-    if (a.flags & ~DE_INTERP_MASK) return fail(DE_EINVAL, "unknown flags 0x%x", a.flags);
+    if (a.flags & ~DE_FLAG_MASK) return fail(DE_EINVAL, "unknown flags 0x%x", a.flags);
     if (a.levels_per_group < 0 || a.levels_per_group > de::kMaxGroup)
         return fail(DE_EINVAL, "levels_per_group=%d outside 0..%d", a.levels_per_group, de::kMaxGroup);
     for (int i = 0; i < a.n_levels; ++i) {
@@ -119,6 +120,128 @@ bool rows_vectorisable(const void* base, int64_t stride, const de_level_desc* le
 
 enum class Op { Forward, Backward, Indices };
 
+// The TMA-staged backward needs float4 coordinate rows, every group's columns contiguous in the gradient
+// row, and each group's slice of every row 16-byte aligned with a multiple-of-16 length.
+bool staging_ok(const CallArgs& a, const de::EncodeParams& P, const int* idx, int n) {
+    if (!(a.flags & DE_FLAG_STAGED_BWD)) return false;
+    if (!P.vec_coords) return false;
+    if (reinterpret_cast<uintptr_t>(P.grad_out) % 16 || P.out_stride % 4) return false;
+    const int G = P.group_size, F = a.n_features;
+    for (int g0 = 0; g0 < n; g0 += G) {
+        const int n_in = (n - g0) < G ? (n - g0) : G;
+        const uint32_t col0 = a.levels[idx[g0]].out_col;
+        if (col0 % 4 || (n_in * F) % 4) return false;
+        for (int i = 1; i < n_in; ++i)
+            if (a.levels[idx[g0 + i]].out_col != col0 + static_cast<uint32_t>(i * F)) return false;
+    }
+    return true;
+}
+
+// Developer tuning knobs read from the environment per call (never required; defaults are the measured best).
+int tune_env(const char* name, int dflt, int lo, int hi) {
+    const char* v = getenv(name);
+    if (!v || !*v) return dflt;
+    const long x = strtol(v, nullptr, 0);
+    return (x < lo || x > hi) ? dflt : static_cast<int>(x);
+}
+
+// Ring geometry: ~64 points per stage (a whole number of CTA passes), 4 stages, long-lived CTAs.
+void plan_stages(const CallArgs& a, de::EncodeParams& P) {
+    const int p_step = de::kThreads / (2 * P.group_size);
+    int tp = tune_env("DE_BWD_STAGE_POINTS", 64, 8, 1024);
+    tp = ((tp + p_step - 1) / p_step) * p_step;
+    P.stage_points = tp;
+    P.n_stages = tune_env("DE_BWD_STAGES", 4, 2, 8);
+    while (P.n_stages > 2 && de::staged_smem_bytes(P, a.n_features) > 96 * 1024) --P.n_stages;
+    long long per_cta = (a.n_points + 148ll * 8 - 1) / (148ll * 8);      // >= 8 CTAs per SM and group
+    long long stages = (per_cta + tp - 1) / tp;
+    const int max_stages = tune_env("DE_BWD_CTA_STAGES", 32, 1, 4096);
+    if (stages < 1) stages = 1;
+    if (stages > max_stages) stages = max_stages;
+    P.points_per_cta = static_cast<int>(stages) * tp;
+    P.n_tiles = static_cast<int>((a.n_points + P.points_per_cta - 1) / P.points_per_cta);
+}
+
+constexpr unsigned long long kSmemTableBudget = 200ull << 10;   // of the 227 KB a CTA may own
+constexpr long long kSmemMinPoints = 1ll << 16;                 // below this the table staging does not amortise
+
+unsigned long long live_cells(const de_level_desc& L) {
+    unsigned long long live = 1;
+    for (int d = 0; d < L.n_dims; ++d) live *= (unsigned long long)L.resolution + 1ull;
+    return live;
+}
+
+// Forward only: picks the dense levels of [begin, end) whose live cells fit shared memory, packs them into
+// shared-memory groups and launches grid4d_forward_smem_kernel for them.  taken[i] marks the levels served.
+int run_smem_forward(const CallArgs& a, const de::EncodeParams& base, int begin, int end, bool* taken,
+                     cudaStream_t stream) {
+    const int n = end - begin;
+    for (int i = 0; i < n; ++i) taken[i] = false;
+    const bool linear = (a.flags & DE_INTERP_MASK) == DE_INTERP_LINEAR;
+    const bool half_tables = a.table_dtype == DE_F16;
+    if (!linear || !(a.flags & DE_FLAG_SMEM_COARSE) || a.n_points < kSmemMinPoints) return DE_OK;
+    if (!de::smem_layout_supported(half_tables, a.n_features)) return DE_OK;
+    const unsigned long long eb = (unsigned long long)a.n_features * (half_tables ? 2u : 4u);
+
+    de::EncodeParams P = base;
+    de::SmemPlan S{};
+    int n_lv = 0;
+    bool pow2_all = true;
+    unsigned long long used = 0;
+    for (int i = 0; i < n; ++i) {
+        const de_level_desc& L = a.levels[begin + i];
+        if (!L.dense) continue;
+        const unsigned long long bytes = (live_cells(L) * eb + 15ull) & ~15ull;
+        if (bytes > kSmemTableBudget) continue;
+        if (reinterpret_cast<uintptr_t>(L.table) % 4) continue;
+        int g = S.n_sgroups - 1;
+        // a group holds consecutive picks of ONE grid (same coordinate columns), <= 4 levels, <= budget
+        bool join = false;
+        if (g >= 0 && S.count[g] < de::kSmemGroupLevels && used + bytes <= kSmemTableBudget) {
+            // the group's first level sits at P.levels[S.first[g]]; compare its dims with L's
+            const de::LevelParams& f = P.levels[S.first[g]];
+            join = f.mask_id == L.mask_id;
+            for (int d = 0; d < L.n_dims && join; ++d) join = f.dim[d] == L.dim[d];
+        }
+        if (!join) {
+            if (S.n_sgroups == de::kMaxSmemGroups) break;
+            g = S.n_sgroups++;
+            S.first[g] = n_lv;
+            S.count[g] = 0;
+            used = 0;
+        }
+        fill_level(L, P.levels[n_lv]);
+        S.off[g][S.count[g]] = static_cast<uint32_t>(used);
+        S.live[g][S.count[g]] = static_cast<uint32_t>(live_cells(L));
+        ++S.count[g];
+        used += bytes;
+        if (used > S.smem_bytes) S.smem_bytes = static_cast<unsigned>(used);
+        pow2_all = pow2_all && is_pow2(L.table_size);
+        taken[i] = true;
+        ++n_lv;
+    }
+    if (n_lv == 0) return DE_OK;
+
+    int dev = 0, n_sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    int cta = 0;
+    for (int g = 0; g < S.n_sgroups; ++g) {
+        int gs = 1;
+        while (gs < S.count[g]) gs <<= 1;
+        S.gs[g] = gs;
+        int c = static_cast<int>(static_cast<long long>(n_sms) * S.count[g] / n_lv);   // one CTA per SM in total
+        if (c < 1) c = 1;
+        S.cta_begin[g] = cta;
+        S.cta_count[g] = c;
+        cta += c;
+    }
+    S.n_ctas = cta;
+    P.n_levels = n_lv;
+    cudaError_t e = de::launch_forward_smem(P, S, a.levels[begin].n_dims, half_tables, a.n_features, pow2_all, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "shared-memory forward launch");
+    return DE_OK;
+}
+
 // Cuts the level list into launches (runs of equal D, <= 64 levels) and starts them in order.
 int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
     if (a.n_points == 0) return DE_OK;
@@ -128,25 +251,29 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
         const int D = a.levels[begin].n_dims;
         int end = begin + 1;
         while (end < a.n_levels && a.levels[end].n_dims == D && end - begin < de::kMaxLaunchLevels) ++end;
-        const int n = end - begin;
+        const bool pair = op != Op::Indices && de::pair_layout_supported(linear, a.n_features);
+
+        bool taken[de::kMaxLaunchLevels] = {};
+        if (op == Op::Forward && pair)
+            if (int rc = run_smem_forward(a, base, begin, end, taken, stream)) return rc;
 
         de::EncodeParams P = base;
+        int idx[de::kMaxLaunchLevels];
+        int n = 0;
+        for (int i = begin; i < end; ++i)
+            if (!taken[i - begin]) idx[n++] = i;
+        if (n == 0) { begin = end; continue; }
         P.n_levels = n;
         bool pow2_all = true;
         unsigned long long max_level_bytes = 1;
         for (int i = 0; i < n; ++i) {
-            const de_level_desc& L = a.levels[begin + i];
+            const de_level_desc& L = a.levels[idx[i]];
             fill_level(L, P.levels[i]);
             pow2_all = pow2_all && is_pow2(L.table_size);
-            unsigned long long live = L.table_size;
-            if (L.dense) {   // a dense level only ever touches its (R+1)^D cells
-                live = 1;
-                for (int d = 0; d < L.n_dims; ++d) live *= (unsigned long long)L.resolution + 1ull;
-            }
+            const unsigned long long live = L.dense ? live_cells(L) : L.table_size;   // a dense level only touches (R+1)^D cells
             const unsigned long long eb = (unsigned long long)a.n_features * (op == Op::Backward ? 4u : (a.table_dtype == DE_F16 ? 2u : 4u));
             if (live * eb > max_level_bytes) max_level_bytes = live * eb;
         }
-        const bool pair = op != Op::Indices && de::pair_layout_supported(linear, a.n_features);
         int G = a.levels_per_group;
         if (G == 0) {
             if (pair) {
@@ -177,8 +304,13 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
                          : de::launch_forward(P, D, linear, a.table_dtype == DE_F16, a.n_features, stream);
                 break;
             case Op::Backward:
-                e = pair ? de::launch_backward_pair(P, D, a.n_features, pow2_all, stream)
-                         : de::launch_backward(P, D, linear, a.n_features, stream);
+                if (pair && staging_ok(a, P, idx, n)) {
+                    plan_stages(a, P);
+                    e = de::launch_backward_staged(P, D, a.n_features, pow2_all, stream);
+                } else {
+                    e = pair ? de::launch_backward_pair(P, D, a.n_features, pow2_all, stream)
+                             : de::launch_backward(P, D, linear, a.n_features, stream);
+                }
                 break;
             case Op::Indices: {
                 // indices are laid out per call, so offset the level index by `begin`

@@ -56,8 +56,28 @@ struct EncodeParams {
     int n_features;         // runtime F (used when the template F is 0)
     int vec_coords;         // coords are 16 B-aligned float4 rows
     int vec_rows;           // feature / grad rows are aligned for F-wide vector access
+    int n_stages;           // staged kernels: ring depth
+    int stage_points;       // staged kernels: points per stage (multiple of the points one CTA pass covers)
     float out_scale;
     LevelParams levels[kMaxLaunchLevels];
+};
+
+// ---- shared-memory coarse levels (grid4d_smem_kernels.cu) ---------------------------------------
+constexpr int kSmemThreads = 512;
+constexpr int kSmemGroupLevels = 4;   // levels one CTA keeps in shared memory
+constexpr int kMaxSmemGroups = 8;     // shared-memory groups per launch
+
+struct SmemPlan {
+    int n_sgroups;
+    int n_ctas;
+    unsigned smem_bytes;              // dynamic shared memory per CTA (largest group)
+    int first[kMaxSmemGroups];        // index of the group's first level in EncodeParams::levels
+    int count[kMaxSmemGroups];        // levels in the group (<= kSmemGroupLevels)
+    int gs[kMaxSmemGroups];           // power of two >= count: lanes per point = 2 * gs
+    int cta_begin[kMaxSmemGroups];    // first blockIdx.x of the group's CTAs
+    int cta_count[kMaxSmemGroups];
+    uint32_t off[kMaxSmemGroups][kSmemGroupLevels];    // byte offset of each staged table (16 B aligned)
+    uint32_t live[kMaxSmemGroups][kSmemGroupLevels];   // staged entries: (R+1)^D
 };
 
 __device__ __forceinline__ float pick4(const float4& v, int d) {
@@ -276,19 +296,33 @@ __device__ __forceinline__ void load_row(const float* src, float (&v)[F], bool v
 }
 
 // ---- vector fp32 reductions into the gradient table (REDG.E.ADD.F32x2 / F32x4 on sm_100a) -------
+// Written as red.global PTX on purpose: the gradient pointer travels through shared memory (LevelParams),
+// so the compiler cannot prove it is a global address and atomicAdd() becomes a GENERIC `ATOM ... RZ`
+// -- an atomic WITH return: a 32 B response per sector back to the SM (45 GB per C2 backward in
+// profiles/r01b_kernels_c2.txt) and a scoreboard wait.  REDG is fire-and-forget.
+__device__ __forceinline__ void red_add_f32(float* p, float a) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
+}
+__device__ __forceinline__ void red_add_v2(float* p, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 template <int F>
 __device__ __forceinline__ void red_add_entry(float* grad, uint32_t idx, const float (&v)[F]) {
     float* dst = grad + static_cast<unsigned long long>(idx) * F;
     if constexpr (F == 2) {
-        atomicAdd(reinterpret_cast<float2*>(dst), make_float2(v[0], v[1]));
+        red_add_v2(dst, v[0], v[1]);
     } else if constexpr (F == 4) {
-        atomicAdd(reinterpret_cast<float4*>(dst), make_float4(v[0], v[1], v[2], v[3]));
+        red_add_v4(dst, v[0], v[1], v[2], v[3]);
     } else if constexpr (F == 8) {
-        atomicAdd(reinterpret_cast<float4*>(dst), make_float4(v[0], v[1], v[2], v[3]));
-        atomicAdd(reinterpret_cast<float4*>(dst) + 1, make_float4(v[4], v[5], v[6], v[7]));
+        red_add_v4(dst, v[0], v[1], v[2], v[3]);
+        red_add_v4(dst + 4, v[4], v[5], v[6], v[7]);
     } else {
 #pragma unroll
-        for (int f = 0; f < F; ++f) atomicAdd(dst + f, v[f]);
+        for (int f = 0; f < F; ++f) red_add_f32(dst + f, v[f]);
     }
 }
 

@@ -151,7 +151,7 @@ grid4d_backward_kernel(const __grid_constant__ EncodeParams P) {
                 const uint32_t idx = corner_index<D>(lv, cell, k);
                 const float wk = LINEAR ? corner_weight<D>(cell, k) : 1.0f;
                 float* dst = lv.grad + static_cast<unsigned long long>(idx) * nf;
-                for (int f = 0; f < nf; ++f) atomicAdd(dst + f, LINEAR ? __fmul_rn(wk, __ldcs(src + f)) : __ldcs(src + f));
+                for (int f = 0; f < nf; ++f) red_add_f32(dst + f, LINEAR ? __fmul_rn(wk, __ldcs(src + f)) : __ldcs(src + f));
             }
         }
     }

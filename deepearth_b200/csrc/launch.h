@@ -6,6 +6,7 @@
 namespace de {
 
 struct EncodeParams;
+struct SmemPlan;
 
 cudaError_t launch_forward(const EncodeParams& P, int D, bool linear, bool half_tables, int F, cudaStream_t s);
 cudaError_t launch_backward(const EncodeParams& P, int D, bool linear, int F, cudaStream_t s);
@@ -15,6 +16,15 @@ cudaError_t launch_indices(const EncodeParams& P, int D, bool linear, cudaStream
 bool pair_layout_supported(bool linear, int F);
 cudaError_t launch_forward_pair(const EncodeParams& P, int D, bool half_tables, int F, bool pow2, cudaStream_t s);
 cudaError_t launch_backward_pair(const EncodeParams& P, int D, int F, bool pow2, cudaStream_t s);
+
+// TMA-staged backward (grid4d_staged_kernels.cu): group columns contiguous, rows 16 B aligned
+size_t staged_smem_bytes(const EncodeParams& P, int F);
+cudaError_t launch_backward_staged(const EncodeParams& P, int D, int F, bool pow2, cudaStream_t s);
+
+// dense coarse levels served from shared memory (grid4d_smem_kernels.cu)
+bool smem_layout_supported(bool half_tables, int F);
+cudaError_t launch_forward_smem(const EncodeParams& P, const SmemPlan& S, int D, bool half_tables, int F, bool pow2,
+                                cudaStream_t s);
 
 struct CastParams {
     const float* src[64];

@@ -85,7 +85,8 @@ class Grid4DEncoder(nn.Module):
             col += enc.output_dim
         e0 = self._encoders[0]
         return EncodePlan(specs, e0.n_features_per_level, self.feature_dim, e0.interpolation == "linear",
-                          e0.table_dtype, e0.table_scale, e0.levels_per_group, e0.bwd_levels_per_group)
+                          e0.table_dtype, e0.table_scale, e0.levels_per_group, e0.bwd_levels_per_group,
+                          e0.extra_flags)
 
     def encode_features(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,
                         temporal_mask: Optional[torch.Tensor] = None) -> torch.Tensor:

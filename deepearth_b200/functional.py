@@ -131,7 +131,7 @@ def encode_forward(specs: Sequence[LevelSpec], coords: torch.Tensor, table_ptrs:
                    table_dtype: torch.dtype, n_features: int, out_cols: int, linear: bool,
                    out_scale: float = 1.0, mask_a: Optional[torch.Tensor] = None,
                    mask_b: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                   levels_per_group: int = 0) -> torch.Tensor:
+                   levels_per_group: int = 0, extra_flags: int = 0) -> torch.Tensor:
     _require_cuda(coords, "coords")
     coords, stride = _coords_view(coords)
     n = coords.shape[0]
@@ -150,7 +150,7 @@ def encode_forward(specs: Sequence[LevelSpec], coords: torch.Tensor, table_ptrs:
     with torch.cuda.device(coords.device):
         rc = lib.de_grid4d_forward(pack_levels(specs, table_ptrs), len(specs), _ptr(coords), n, stride, dt,
                                    n_features, out_scale, _ptr(ma), _ptr(mb), _ptr(out), out.stride(0),
-                                   _lib.DE_INTERP_LINEAR if linear else _lib.DE_INTERP_NEAREST,
+                                   (_lib.DE_INTERP_LINEAR if linear else _lib.DE_INTERP_NEAREST) | extra_flags,
                                    levels_per_group, _stream_ptr(coords.device))
     _lib.check(rc, "de_grid4d_forward")
     return out
@@ -159,7 +159,7 @@ def encode_forward(specs: Sequence[LevelSpec], coords: torch.Tensor, table_ptrs:
 def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: torch.Tensor,
                     grad_ptrs: Sequence[int], n_features: int, linear: bool,
                     mask_a: Optional[torch.Tensor] = None, mask_b: Optional[torch.Tensor] = None,
-                    levels_per_group: int = 0) -> None:
+                    levels_per_group: int = 0, extra_flags: int = 0) -> None:
     """Accumulate table gradients into the fp32 buffers at ``grad_ptrs`` (caller zeroes them)."""
     _require_cuda(coords, "coords")
     _require_cuda(grad_out, "grad_out")
@@ -178,7 +178,7 @@ def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: 
         rc = lib.de_grid4d_backward(pack_levels(specs, None, grad_ptrs), len(specs), _ptr(coords), n, stride,
                                     n_features, _ptr(ma), _ptr(mb), _ptr(grad_out),
                                     grad_out.stride(0) if n > 1 else grad_out.shape[1],
-                                    _lib.DE_INTERP_LINEAR if linear else _lib.DE_INTERP_NEAREST,
+                                    (_lib.DE_INTERP_LINEAR if linear else _lib.DE_INTERP_NEAREST) | extra_flags,
                                     levels_per_group, _stream_ptr(coords.device))
     _lib.check(rc, "de_grid4d_backward")
 
@@ -209,8 +209,9 @@ class EncodePlan:
 
     def __init__(self, specs: Sequence[LevelSpec], n_features: int, out_cols: int, linear: bool,
                  table_dtype: torch.dtype = torch.float32, table_scale: float = 1.0,
-                 levels_per_group: int = 0, bwd_levels_per_group: int = 0):
+                 levels_per_group: int = 0, bwd_levels_per_group: int = 0, extra_flags: int = 0):
         self.specs = list(specs)
+        self.extra_flags = int(extra_flags)   # DE_FLAG_* A/B switches (include/de_grid4d.h)
         self.n_features = int(n_features)
         self.out_cols = int(out_cols)
         self.linear = bool(linear)
@@ -240,7 +241,7 @@ class Grid4DFunction(torch.autograd.Function):
         ptrs = working_ptrs if working_ptrs is not None else [w.data_ptr() for w in weights]
         out = encode_forward(plan.specs, coords, ptrs, plan.table_dtype, plan.n_features, plan.out_cols,
                              plan.linear, 1.0 / plan.table_scale if plan.table_scale != 1.0 else 1.0,
-                             mask_a, mask_b, levels_per_group=plan.levels_per_group)
+                             mask_a, mask_b, levels_per_group=plan.levels_per_group, extra_flags=plan.extra_flags)
         ctx.plan = plan
         ctx.weight_shapes = [tuple(w.shape) for w in weights]
         ctx.save_for_backward(coords, mask_a, mask_b)
@@ -259,7 +260,7 @@ class Grid4DFunction(torch.autograd.Function):
         base = flat.data_ptr()
         encode_backward(plan.specs, coords, grad_out, [base + 4 * o for o in plan.grad_offsets],
                         plan.n_features, plan.linear, mask_a, mask_b,
-                        levels_per_group=plan.bwd_levels_per_group)
+                        levels_per_group=plan.bwd_levels_per_group, extra_flags=plan.extra_flags)
         grads = []
         for i, shape in enumerate(ctx.weight_shapes):
             o = plan.grad_offsets[i]

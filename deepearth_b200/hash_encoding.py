@@ -62,6 +62,7 @@ class MultiResolutionHashEncoding(nn.Module):
             raise ValueError("dims must name coords_dim coordinate columns")
         self.levels_per_group = levels_per_group
         self.bwd_levels_per_group = bwd_levels_per_group
+        self.extra_flags = 0   # DE_FLAG_* A/B switches (include/de_grid4d.h); 0 = every optimisation on
 
         self.hash_tables = nn.ModuleList(
             [nn.Embedding(hash_table_size, n_features_per_level) for _ in range(n_levels)])
@@ -135,7 +136,7 @@ class MultiResolutionHashEncoding(nn.Module):
     def plan(self, dims: Optional[Sequence[int]] = None) -> EncodePlan:
         return EncodePlan(self.level_specs(dims), self.n_features_per_level, self.output_dim,
                           self.interpolation == "linear", self.table_dtype, self.table_scale,
-                          self.levels_per_group, self.bwd_levels_per_group)
+                          self.levels_per_group, self.bwd_levels_per_group, self.extra_flags)
 
     def forward(self, coords: torch.Tensor) -> torch.Tensor:
         if coords.dim() != 2 or coords.shape[1] < self.coords_dim:

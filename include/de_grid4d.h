@@ -52,6 +52,10 @@ extern "C" {
 #define DE_INTERP_NEAREST 0u /* floor cell only: models/hash_encoding.py:57-72     */
 #define DE_INTERP_LINEAR 1u  /* 2^D-corner multilinear (decomposed Grid4D mode)    */
 #define DE_INTERP_MASK 1u
+/* opt-in code paths that measured SLOWER than the default on B200 (profiles/r01c_ab_matrix.txt); kept for A/B runs */
+#define DE_FLAG_STAGED_BWD 0x100u  /* backward: stage coordinates + gradient rows through TMA bulk copies + shared memory */
+#define DE_FLAG_SMEM_COARSE 0x200u /* forward: serve dense coarse levels from shared-memory copies of their tables      */
+#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE)
 
 #define DE_MAX_DIMS 4
 #define DE_MAX_LEVELS_PER_CALL 256

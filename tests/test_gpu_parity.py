@@ -410,3 +410,54 @@ def test_sum_and_probe_helpers(dev):
     from deepearth_b200 import functional as Fn
     x = torch.randn(1_000_003, device=dev)
     assert float(Fn.sum_f32(x)) == pytest.approx(float(x.double().sum()), rel=1e-9, abs=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------
+# A/B switches: the opt-in paths must reproduce the default lane-pair path
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("table_dtype", ["float32", "float16"])
+def test_smem_coarse_and_staged_paths_match_plain_path(dev, oracle, table_dtype):
+    """Dense coarse levels served from shared memory (forward) and the TMA-staged backward against the
+    plain L2-path kernels (bit-identical forward: same corner order) and against the C oracle."""
+    import deepearth_b200 as de
+    from deepearth_b200 import _lib
+    from oracle.grid4d_oracle import Level
+    T, L, F, n = 2 ** 16, 6, 2, 2 ** 16 + 777
+    res = [4, 8, 16, 32, 64, 128]                      # (R+1)^3 <= T up to R=32: four dense levels, two hashed
+    g = torch.Generator(device=dev).manual_seed(11)
+    enc = de.MultiResolutionHashEncoding(L, F, res, T, 3, interpolation="linear", dense_fallback=True,
+                                         table_dtype=table_dtype).to(dev)
+    with torch.no_grad():
+        for e in enc.hash_tables:
+            e.weight.copy_(torch.round(torch.rand(e.weight.shape, device=dev, generator=g) * 2048 - 1024) / 2 ** 22)
+    coords = torch.rand((n, 3), device=dev, generator=g)
+    coords[:4096] = torch.randn((4096, 3), device=dev, generator=g) * 1.5     # out-of-range: index wraps past the live cells
+    gout = torch.randn((n, L * F), device=dev, generator=g)
+
+    def run(flags):
+        enc.extra_flags = flags
+        for e in enc.hash_tables:
+            e.weight.grad = None
+        out = enc(coords)
+        out.backward(gout)
+        return out.detach().clone(), torch.cat([e.weight.grad.reshape(-1) for e in enc.hash_tables])
+
+    out_opt, grad_opt = run(_lib.DE_FLAG_STAGED_BWD | _lib.DE_FLAG_SMEM_COARSE)
+    out_ref, grad_ref = run(0)
+    assert torch.equal(out_opt, out_ref)
+    denom = float(grad_ref.abs().max())
+    assert float((grad_opt - grad_ref).abs().max()) <= GRAD_TOL * denom
+
+    levels = [Level(T=T, R=R, dims=(0, 1, 2), out_col=l * F, table_off=l * T, dense=(R + 1) ** 3 <= T)
+              for l, R in enumerate(res)]
+    tables = np.concatenate([e.weight.detach().cpu().numpy() for e in enc.hash_tables], 0)
+    if table_dtype == "float16":
+        tables = (tables * np.float32(enc.table_scale)).astype(np.float16)
+        want = oracle.forward(levels, coords.cpu().numpy(), tables, F, True, out_scale=1.0 / enc.table_scale)
+    else:
+        want = oracle.forward(levels, coords.cpu().numpy(), tables, F, True)
+    err = np.abs(out_opt.cpu().numpy() - want).max() / np.abs(want).max()
+    assert err <= FWD_TOL_F32, err
+    want_g = oracle.backward(levels, coords.cpu().numpy(), gout.cpu().numpy(), L * T, F, True)
+    gerr = np.abs(grad_opt.cpu().numpy().reshape(-1, F) - want_g).max() / np.abs(want_g).max()
+    assert gerr <= GRAD_TOL, gerr
