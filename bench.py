@@ -193,6 +193,7 @@ class Job:
         tb = 2 if self.plan.table_dtype == torch.float16 else 4
         self.bytes_fwd, self.bytes_bwd = algorithmic_bytes_per_point(len(self.plan.specs), corners, self.F, tb)
         self.out_scale = 1.0 / self.plan.table_scale if self.plan.table_scale != 1.0 else 1.0
+        self.use_replicas = True
 
     def forward(self):
         from deepearth_b200 import functional as Fn
@@ -203,7 +204,8 @@ class Job:
     def backward(self):
         from deepearth_b200 import functional as Fn
         Fn.encode_backward(self.plan.specs, self.coords, self.gout, self.grad_ptrs, self.F, self.linear,
-                           levels_per_group=self.plan.bwd_levels_per_group, extra_flags=self.plan.extra_flags)
+                           levels_per_group=self.plan.bwd_levels_per_group, extra_flags=self.plan.extra_flags,
+                           use_replicas=self.use_replicas)
 
     def n_launches_per_step(self):
         # one launch per run of equal-D levels (<= 64) for forward and for backward
@@ -308,6 +310,7 @@ def run_gpu_arm(args, wl):
     if args.bwd_levels_per_group:
         job.plan.bwd_levels_per_group = args.bwd_levels_per_group
     job.plan.extra_flags = args.flags
+    job.use_replicas = not args.no_replicas
 
     def step(ev=None):
         job.flat_grad.zero_()
@@ -463,6 +466,7 @@ def main():
     ap.add_argument("--levels-per-group", type=int, default=0)
     ap.add_argument("--bwd-levels-per-group", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-replicas", action="store_true", help="backward without gradient replicas for contended coarse levels (A/B)")
     ap.add_argument("--flags", type=lambda v: int(v, 0), default=0, help="DE_FLAG_* opt-in paths (0x100 TMA-staged backward, 0x200 shared-memory coarse forward)")
     ap.add_argument("--l2-fetch", type=int, default=0, help="set cudaLimitMaxL2FetchGranularity (32/64/128)")
     args = ap.parse_args()

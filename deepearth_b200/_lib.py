@@ -13,6 +13,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libde_grid4d.so")
 
 DE_OK = 0
+ABI_VERSION = 2
 DE_F32, DE_F16, DE_F64 = 0, 1, 2
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE = 0x100, 0x200
@@ -51,12 +52,17 @@ SIGNATURES = {
     "de_grid4d_forward": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_void_p, c_i64, c_int, c_int, c_int,
                                   c_float, c_void_p, c_void_p, c_void_p, c_i64, c_u32, c_int, c_void_p]),
     "de_grid4d_backward": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_void_p, c_i64, c_int, c_int,
-                                   c_void_p, c_void_p, c_void_p, c_i64, c_u32, c_int, c_void_p]),
+                                   c_void_p, c_void_p, c_void_p, c_i64, c_u32, c_int, c_void_p, ctypes.c_size_t,
+                                   c_void_p]),
+    "de_grid4d_backward_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32]),
     "de_tables_to_f16": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_int, ctypes.POINTER(c_void_p), c_float,
                                  c_void_p]),
     "de_geo2xyzt_norm": (c_int, [c_void_p, c_int, c_void_p, c_int, ctypes.POINTER(ctypes.c_double),
                                  ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), c_void_p,
                                  c_void_p, c_i64, c_void_p]),
+    "de_mlp_head_supported": (c_int, [c_int, c_int, c_int]),
+    "de_mlp_head_forward": (c_int, [c_void_p, c_i64, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                    c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_i64, c_void_p]),
     "de_geo_bbox": (c_int, [c_void_p, c_int, c_void_p, c_i64, c_void_p]),
     "de_set_l2_fetch_granularity": (c_int, [c_int]),
     "de_get_l2_fetch_granularity": (c_int, [ctypes.POINTER(c_int)]),
@@ -89,8 +95,8 @@ def load() -> ctypes.CDLL:
             fn = getattr(lib, name)   # AttributeError here = header / library mismatch
             fn.restype = res
             fn.argtypes = args
-        if lib.de_abi_version() != 1:
-            raise DeepEarthB200Error(f"ABI version {lib.de_abi_version()} != 1")
+        if lib.de_abi_version() != ABI_VERSION:
+            raise DeepEarthB200Error(f"ABI version {lib.de_abi_version()} != {ABI_VERSION}: rebuild libde_grid4d.so")
         _lib = lib
     return _lib
 

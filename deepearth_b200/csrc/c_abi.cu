@@ -50,6 +50,8 @@ struct CallArgs {
     uint32_t flags;
     int levels_per_group;
     bool need_tables, need_grads;
+    void* workspace = nullptr;
+    size_t workspace_bytes = 0;
 };
 
 int validate(const CallArgs& a) {
@@ -99,6 +101,11 @@ void fill_level(const de_level_desc& L, de::LevelParams& o) {
     o.pow2 = is_pow2(L.table_size) ? 1 : 0;
     o.mask_id = L.mask_id;
     o.pad = 0;
+    o.rep_base = nullptr;
+    o.rep_count = 0;
+    o.rep_stride = 0;
+    o.rep_live = 0;
+    o.pad2 = 0;
     static const uint32_t kPrimes[4] = {1u, 2654435761u, 805459861u, 3674653429u};   // hash_encoding.py:64
     uint64_t stride = 1;
     for (int d = 0; d < 4; ++d) {
@@ -169,6 +176,52 @@ unsigned long long live_cells(const de_level_desc& L) {
     unsigned long long live = 1;
     for (int d = 0; d < L.n_dims; ++d) live *= (unsigned long long)L.resolution + 1ull;
     return live;
+}
+
+// ---- gradient replicas for contended coarse levels (backward) --------------------------------------
+// A level whose live entries are few receives thousands of reductions per entry; the L2 atomic units
+// serialise same-address updates (profiles/r01c_level_sweep_c3.json: R=16 costs 6x a fine level on
+// clustered points).  Such a level gets K copies of its live entries -- CTA tile t adds into copy t % K --
+// which are folded into the real table by one small kernel afterwards.
+constexpr unsigned long long kRepTargetBytes = 8ull << 20;   // replicas of one level stay within this much L2
+constexpr unsigned kRepMax = 64;
+constexpr unsigned long long kRepMinUpdatesPerEntry = 256;
+
+struct RepPlan {
+    unsigned count;      // replicas including the table itself (1 = none)
+    unsigned live;       // entries per replica
+    unsigned stride;     // floats between replicas
+};
+
+RepPlan plan_replicas(const de_level_desc& L, int n_features, int64_t n_points, bool linear) {
+    RepPlan r{1, 0, 0};
+    unsigned long long live = L.dense ? live_cells(L) : L.table_size;
+    if (!L.dense) {
+        // a hashed level touches min(T, (R+1)^D) entries scattered over the whole table -- except in 1-D,
+        // where prime[0] = 1 (hash_encoding.py:64) makes the index the cell number itself: entries 0..R
+        live = L.table_size;
+        if (L.n_dims == 1 && (unsigned long long)L.resolution + 1ull < live) live = (unsigned long long)L.resolution + 1ull;
+    }
+    const unsigned long long bytes = live * n_features * 4ull;
+    const unsigned long long corners = linear ? (1ull << L.n_dims) : 1ull;
+    if (bytes == 0 || bytes * 2 > kRepTargetBytes) return r;
+    if ((unsigned long long)n_points * corners < kRepMinUpdatesPerEntry * live) return r;
+    unsigned long long k = kRepTargetBytes / bytes;
+    if (k > kRepMax) k = kRepMax;
+    if (k < 2) return r;
+    r.count = static_cast<unsigned>(k);
+    r.live = static_cast<unsigned>(live);
+    r.stride = static_cast<unsigned>((live * n_features + 63ull) & ~63ull);
+    return r;
+}
+
+size_t replica_workspace_bytes(const de_level_desc* levels, int n_levels, int n_features, int64_t n_points, bool linear) {
+    size_t total = 0;
+    for (int i = 0; i < n_levels; ++i) {
+        const RepPlan r = plan_replicas(levels[i], n_features, n_points, linear);
+        if (r.count > 1) total += static_cast<size_t>(r.count - 1) * r.stride * 4;
+    }
+    return total;
 }
 
 // Forward only: picks the dense levels of [begin, end) whose live cells fit shared memory, packs them into
@@ -246,6 +299,14 @@ int run_smem_forward(const CallArgs& a, const de::EncodeParams& base, int begin,
 int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
     if (a.n_points == 0) return DE_OK;
     const bool linear = (a.flags & DE_INTERP_MASK) == DE_INTERP_LINEAR;
+    size_t ws_off = 0;
+    if (op == Op::Backward && a.workspace) {
+        const size_t used = replica_workspace_bytes(a.levels, a.n_levels, a.n_features, a.n_points, linear);
+        if (used > 0 && used <= a.workspace_bytes) {
+            cudaError_t e = cudaMemsetAsync(a.workspace, 0, used, stream);
+            if (e != cudaSuccess) return cuda_fail(e, "workspace memset");
+        }
+    }
     int begin = 0;
     while (begin < a.n_levels) {
         const int D = a.levels[begin].n_dims;
@@ -266,9 +327,31 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
         P.n_levels = n;
         bool pow2_all = true;
         unsigned long long max_level_bytes = 1;
+        de::ReplicaFoldParams fold{};
         for (int i = 0; i < n; ++i) {
             const de_level_desc& L = a.levels[idx[i]];
             fill_level(L, P.levels[i]);
+            if (op == Op::Backward && a.workspace) {
+                // same walk as replica_workspace_bytes(): ws_off advances over ALL levels of the call in order
+                const RepPlan r = plan_replicas(L, a.n_features, a.n_points, linear);
+                if (r.count > 1) {
+                    const size_t need = static_cast<size_t>(r.count - 1) * r.stride * 4;
+                    if (ws_off + need <= a.workspace_bytes) {
+                        de::LevelParams& lp = P.levels[i];
+                        lp.rep_base = reinterpret_cast<float*>(static_cast<char*>(a.workspace) + ws_off);
+                        lp.rep_count = r.count;
+                        lp.rep_stride = r.stride;
+                        lp.rep_live = r.live;
+                        fold.dst[fold.n] = L.grad_table;
+                        fold.rep[fold.n] = lp.rep_base;
+                        fold.n_floats[fold.n] = r.live * static_cast<unsigned>(a.n_features);
+                        fold.count[fold.n] = r.count - 1;
+                        fold.stride[fold.n] = r.stride;
+                        ++fold.n;
+                        ws_off += need;
+                    }
+                }
+            }
             pow2_all = pow2_all && is_pow2(L.table_size);
             const unsigned long long live = L.dense ? live_cells(L) : L.table_size;   // a dense level only touches (R+1)^D cells
             const unsigned long long eb = (unsigned long long)a.n_features * (op == Op::Backward ? 4u : (a.table_dtype == DE_F16 ? 2u : 4u));
@@ -321,6 +404,10 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
             }
         }
         if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+        if (fold.n) {
+            e = de::launch_replica_fold(fold, stream);
+            if (e != cudaSuccess) return cuda_fail(e, "replica fold launch");
+        }
         begin = end;
     }
     return DE_OK;
@@ -385,8 +472,12 @@ DE_API int de_grid4d_forward(const de_level_desc* levels_host, int n_levels, con
 DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels, const float* coords,
                        int64_t n_points, int coord_stride, int n_features, const uint8_t* mask_a,
                        const uint8_t* mask_b, const float* grad_out, int64_t grad_stride,
-                       uint32_t flags, int levels_per_group, void* stream) {
+                       uint32_t flags, int levels_per_group, void* workspace, size_t workspace_bytes,
+                       void* stream) {
     CallArgs a{levels_host, n_levels, coords, n_points, coord_stride, DE_F32, n_features, flags, levels_per_group, false, true};
+    a.workspace = workspace_bytes ? workspace : nullptr;
+    a.workspace_bytes = workspace_bytes;
+    if (a.workspace && reinterpret_cast<uintptr_t>(a.workspace) % 16) return fail(DE_EALIGN, "workspace not 16-byte aligned");
     if (int rc = validate(a)) return rc;
     if (n_points > 0 && !grad_out) return fail(DE_EINVAL, "grad_out is NULL");
     for (int i = 0; i < n_levels; ++i)
@@ -405,6 +496,12 @@ DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels, co
     P.vec_rows = rows_vectorisable(grad_out, grad_stride, levels_host, n_levels, n_features) ? 1 : 0;
     P.out_scale = 1.0f;
     return run(a, Op::Backward, P, static_cast<cudaStream_t>(stream));
+}
+
+DE_API size_t de_grid4d_backward_workspace_bytes(const de_level_desc* levels_host, int n_levels, int n_features,
+                                                 int64_t n_points, uint32_t flags) {
+    if (!levels_host || n_levels <= 0 || n_features < 1 || n_points <= 0) return 0;
+    return replica_workspace_bytes(levels_host, n_levels, n_features, n_points, (flags & DE_INTERP_MASK) == DE_INTERP_LINEAR);
 }
 
 DE_API int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_features,
@@ -454,6 +551,35 @@ DE_API int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n
     if (geo_dtype != DE_F64 && geo_dtype != DE_F32) return fail(DE_EUNSUPPORTED, "geo_dtype=%d", geo_dtype);
     cudaError_t e = de::launch_geo_bbox(geo, geo_dtype == DE_F64, minmax, n_points, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "geo_bbox launch");
+}
+
+DE_API int de_mlp_head_supported(int in_dim, int hidden, int out_dim) {
+    return de::mlp_head_supported(in_dim, hidden, out_dim) ? 1 : 0;
+}
+
+DE_API int de_mlp_head_forward(const float* x, int64_t n_points, int in_dim, int64_t x_stride,
+                        const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta,
+                        float ln_eps, int layernorm, int activation, const void* w2_bf16, const float* b2,
+                        int hidden, int out_dim, float* y, int64_t y_stride, void* stream) {
+    if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (n_points == 0) return DE_OK;
+    if (!x || !w1_bf16 || !w2_bf16 || !y) return fail(DE_EINVAL, "mlp_head: NULL pointer");
+    if (!de::mlp_head_supported(in_dim, hidden, out_dim))
+        return fail(DE_EUNSUPPORTED, "mlp_head: in_dim=%d hidden=%d out_dim=%d (built for in_dim in {32,48,64,96,128}, hidden = out = 64)", in_dim, hidden, out_dim);
+    if (activation < 0 || activation > 2) return fail(DE_EINVAL, "mlp_head: activation=%d", activation);
+    if (x_stride < in_dim || y_stride < out_dim) return fail(DE_EINVAL, "mlp_head: row stride shorter than the row");
+    if (reinterpret_cast<uintptr_t>(x) % 16 || x_stride % 4) return fail(DE_EALIGN, "mlp_head: x rows not 16-byte aligned");
+    if (reinterpret_cast<uintptr_t>(y) % 16 || y_stride % 4) return fail(DE_EALIGN, "mlp_head: y rows not 16-byte aligned");
+    if (reinterpret_cast<uintptr_t>(w1_bf16) % 16 || reinterpret_cast<uintptr_t>(w2_bf16) % 16) return fail(DE_EALIGN, "mlp_head: weights not 16-byte aligned");
+    de::MlpHeadParams P{};
+    P.x = x; P.n = n_points; P.x_stride = x_stride;
+    P.w1 = w1_bf16; P.b1 = b1; P.ln_gamma = ln_gamma; P.ln_beta = ln_beta; P.ln_eps = ln_eps;
+    P.layernorm = layernorm ? 1 : 0; P.activation = activation;
+    P.w2 = w2_bf16; P.b2 = b2; P.y = y; P.y_stride = y_stride;
+    int dev = 0, n_sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = de::launch_mlp_head(P, in_dim, n_sms, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "mlp_head launch");
 }
 
 DE_API int de_set_l2_fetch_granularity(int bytes) {

@@ -36,7 +36,31 @@ struct LevelParams {
     uint8_t mask_id;
     uint8_t pad;
     uint32_t mul[4];    // per-dimension index multiplier: prime_d (hashed) or (R+1)^d (dense); mul[0] == 1
+    // backward, contended coarse levels: CTA tile t accumulates into replica (t % rep_count); replica 0 is
+    // `grad` itself, replicas 1.. live in the caller's workspace and are folded into `grad` afterwards
+    float* rep_base;
+    uint32_t rep_count;   // 0 / 1 = not replicated
+    uint32_t rep_stride;  // floats between replicas
+    uint32_t rep_live;    // entries a replica holds (indices >= rep_live go to `grad`: out-of-range coordinates)
+    uint32_t pad2;
 };
+
+// Gradient table a CTA tile accumulates into, and the bound below which it applies.
+struct GradTarget {
+    float* base;
+    uint32_t live;
+};
+__device__ __forceinline__ GradTarget grad_target(const LevelParams& lv, int tile) {
+    GradTarget t{lv.grad, 0u};
+    if (lv.rep_count > 1) {
+        const uint32_t r = static_cast<uint32_t>(tile) % lv.rep_count;
+        if (r) {
+            t.base = lv.rep_base + static_cast<size_t>(r - 1) * lv.rep_stride;
+            t.live = lv.rep_live;
+        }
+    }
+    return t;
+}
 
 struct EncodeParams {
     const float* coords;

@@ -119,6 +119,7 @@ grid4d_backward_kernel(const __grid_constant__ EncodeParams P) {
     if (!setup_thread(P, s_lv, lane_level, p0, p_step, lv)) return;
     constexpr int C = Corners<D, LINEAR>::value;
     const long long p_end = min(P.n_points, (static_cast<long long>(blockIdx.x % P.n_tiles) + 1) * P.points_per_cta);
+    const GradTarget gt = grad_target(lv, blockIdx.x % P.n_tiles);
 
     for (long long p = p0; p < p_end; p += p_step) {
         bool has_mask;
@@ -142,7 +143,7 @@ grid4d_backward_kernel(const __grid_constant__ EncodeParams P) {
 #pragma unroll
                     for (int f = 0; f < F; ++f) val[f] = go[f];
                 }
-                red_add_entry<F>(lv.grad, idx, val);
+                red_add_entry<F>(idx < gt.live ? gt.base : lv.grad, idx, val);
             }
         } else {
             const int nf = P.n_features;
@@ -150,7 +151,7 @@ grid4d_backward_kernel(const __grid_constant__ EncodeParams P) {
             for (int k = 0; k < C; ++k) {
                 const uint32_t idx = corner_index<D>(lv, cell, k);
                 const float wk = LINEAR ? corner_weight<D>(cell, k) : 1.0f;
-                float* dst = lv.grad + static_cast<unsigned long long>(idx) * nf;
+                float* dst = (idx < gt.live ? gt.base : lv.grad) + static_cast<unsigned long long>(idx) * nf;
                 for (int f = 0; f < nf; ++f) red_add_f32(dst + f, LINEAR ? __fmul_rn(wk, __ldcs(src + f)) : __ldcs(src + f));
             }
         }

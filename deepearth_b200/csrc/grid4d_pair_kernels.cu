@@ -113,6 +113,7 @@ grid4d_backward_pair_kernel(const __grid_constant__ EncodeParams P) {
     if (!pair_setup(P, s_lv, t, lv)) return;
     constexpr int J = PairGeom<D>::kCombos;
     const bool vec = P.vec_rows != 0;
+    const GradTarget gt = grad_target(lv, blockIdx.x % P.n_tiles);
 
     float x_n[D], go_n[F];
     if (t.p0 < t.p_end) {
@@ -145,7 +146,7 @@ grid4d_backward_pair_kernel(const __grid_constant__ EncodeParams P) {
             float val[F];
 #pragma unroll
             for (int f = 0; f < F; ++f) val[f] = __fmul_rn(wk, go[f]);
-            red_add_entry<F>(lv.grad, idx, val);
+            red_add_entry<F>(idx < gt.live ? gt.base : lv.grad, idx, val);
         }
     }
 }

@@ -105,6 +105,7 @@ grid4d_backward_staged_kernel(const __grid_constant__ EncodeParams P) {
     const int slot0 = threadIdx.x / (2 * G);
     LevelParams lv = s_lv[active ? lane_level : 0];
     constexpr int J = PairGeom<D>::kCombos;
+    const GradTarget gt = grad_target(lv, tile);
 
     for (int k = 0; k < n_k; ++k) {
         // refill the stage consumed in iteration k-1 (every thread passed the __syncthreads below)
@@ -149,7 +150,7 @@ grid4d_backward_staged_kernel(const __grid_constant__ EncodeParams P) {
                     float val[F];
 #pragma unroll
                     for (int f = 0; f < F; ++f) val[f] = __fmul_rn(wk, go[f]);
-                    red_add_entry<F>(lv.grad, idx, val);
+                    red_add_entry<F>(idx < gt.live ? gt.base : lv.grad, idx, val);
                 }
             }
         }

@@ -35,6 +35,38 @@ struct CastParams {
 };
 cudaError_t launch_cast_f16(const CastParams& P, cudaStream_t s);
 
+// folds gradient replicas back into their tables: dst[i] += sum_r rep[r * stride + i]
+struct ReplicaFoldParams {
+    float* dst[64];
+    const float* rep[64];
+    unsigned n_floats[64];
+    unsigned count[64];    // replicas in the workspace (rep_count - 1)
+    unsigned stride[64];
+    int n;
+};
+cudaError_t launch_replica_fold(const ReplicaFoldParams& P, cudaStream_t s);
+
+// tensor-core MLP head (mlp_head.cu): y = W2 * act(LN(W1 * x + b1)) + b2, hidden = out = 64
+struct MlpHeadParams {
+    const float* x;               // (n, in_dim) fp32 features, rows x_stride floats apart (16 B aligned)
+    long long n;
+    long long x_stride;
+    const void* w1;               // (64, in_dim) bf16 row-major (nn.Linear.weight layout)
+    const float* b1;              // (64,) or NULL
+    const float* ln_gamma;        // (64,) or NULL
+    const float* ln_beta;         // (64,) or NULL
+    float ln_eps;
+    int layernorm;                // 0 / 1
+    int activation;               // 0 none, 1 ReLU, 2 GELU (erf)
+    const void* w2;               // (64, 64) bf16 row-major
+    const float* b2;              // (64,) or NULL
+    float* y;                     // (n, 64) fp32, rows y_stride floats apart (16 B aligned)
+    long long y_stride;
+    int n_tiles;
+};
+bool mlp_head_supported(int in_dim, int hidden, int out_dim);
+cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s);
+
 cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,
                             const double* bbox_span, const double* t_range, float* xyzt, double* ecef,
                             long long n, cudaStream_t s);

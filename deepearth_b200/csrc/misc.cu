@@ -43,6 +43,29 @@ cudaError_t launch_cast_f16(const CastParams& P, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// ---- gradient replicas -> table ---------------------------------------------------------------
+__global__ void __launch_bounds__(256) replica_fold_kernel(const __grid_constant__ ReplicaFoldParams P) {
+    const int e = blockIdx.y;
+    float* __restrict__ dst = P.dst[e];
+    const float* __restrict__ rep = P.rep[e];
+    const unsigned n = P.n_floats[e], cnt = P.count[e], stride = P.stride[e];
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float acc = dst[i];
+        for (unsigned r = 0; r < cnt; ++r) acc += __ldcs(rep + static_cast<size_t>(r) * stride + i);
+        dst[i] = acc;
+    }
+}
+
+cudaError_t launch_replica_fold(const ReplicaFoldParams& P, cudaStream_t s) {
+    if (P.n == 0) return cudaSuccess;
+    unsigned max_n = 0;
+    for (int i = 0; i < P.n; ++i) max_n = P.n_floats[i] > max_n ? P.n_floats[i] : max_n;
+    unsigned bx = (max_n + 255) / 256;
+    if (bx > 148 * 2) bx = 148 * 2;
+    replica_fold_kernel<<<dim3(bx, static_cast<unsigned>(P.n)), 256, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
 // ---- fp64 sum of fp32 --------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) sum_f32_kernel(const float* __restrict__ x, long long n, double* result) {
     double acc = 0.0;

@@ -1,0 +1,314 @@
+// mlp_head.cu -- the encoder's small MLP head on the 5th-generation tensor cores (sm_100a, tcgen05 + TMEM).
+//
+//   y = Linear2( act( LayerNorm( Linear1(x) ) ) )            x: (n, K1) fp32 features, hidden = out = 64
+//
+// This is the structure of Grid4DEncoder.projection (/root/reference/models/encoders.py:47-52:
+// Linear -> LayerNorm -> GELU -> Linear) at the 64-wide size BASELINE.json's configs[4] names; LayerNorm and
+// the activation are switchable so the plain "2-layer MLP" is the same kernel.  It is the only dense
+// contraction on the path, hence the only place tensor cores are used.
+//
+// One CTA = 128 threads = one 128-point tile at a time (persistent over tiles):
+//   1. the tile's features are read once (fp32, coalesced), rounded to bf16 and laid out in shared memory in
+//      the UMMA canonical K-major, no-swizzle layout (8-row x 16-byte core matrices);
+//   2. one elected thread issues K1/16 tcgen05.mma (M=128, N=64, K=16, bf16 x bf16 -> fp32) into TMEM;
+//      completion arrives on an mbarrier through tcgen05.commit;
+//   3. every thread owns one row: tcgen05.ld brings its 64 accumulators to registers, bias + LayerNorm +
+//      activation run in registers, the bf16 hidden row goes back to shared memory as the A operand of
+//   4. the second GEMM (4 tcgen05.mma), whose accumulators are read back, biased and streamed to HBM.
+// The hidden activations never leave the SM.  Weights are staged once per CTA.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "launch.h"
+
+namespace de {
+
+namespace {
+
+constexpr int kMlpThreads = 128;
+constexpr int kTileM = 128;
+constexpr int kH = 64;            // hidden width = output width
+constexpr int kTmemCols = 128;    // D1: columns [0,64), D2: columns [64,128)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+// ---- UMMA canonical layout, K-major, SWIZZLE_NONE ----------------------------------------------
+// core matrix = 8 rows x 16 bytes (8 bf16), stored as 128 contiguous bytes; core matrices adjacent along K are
+// 128 B apart (leading byte offset), 8-row groups are (Kt/8)*128 B apart (stride byte offset).
+__device__ __forceinline__ uint32_t canon_chunk_offset(int row, int k8, int kt) {
+    return static_cast<uint32_t>((row >> 3) * (kt >> 3) * 128 + k8 * 128 + (row & 7) * 16);
+}
+
+// shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFFu);             // [0,14)  start address >> 4
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;   // [16,30) leading byte offset >> 4
+    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;   // [32,46) stride byte offset >> 4
+    d |= 1ull << 46;                                                // [46,48) descriptor version 1 (Blackwell)
+    return d;                                                       // base offset 0, layout type 0 = no swizzle
+}
+
+// instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, bf16 A and B, both K-major, M=128
+__device__ __forceinline__ constexpr uint32_t umma_idesc(int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(kTileM >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    } while (!ok);
+}
+
+// 32 consecutive fp32 accumulator columns of this thread's TMEM lane (= tile row)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+}  // namespace
+
+// dynamic shared memory: A1 [128 x K1] | B1 [64 x K1] | A2 [128 x 64] | B2 [64 x 64] (all bf16, canonical layout)
+template <int K1>
+__global__ void __launch_bounds__(kMlpThreads)
+mlp_head_kernel(const __grid_constant__ MlpHeadParams P) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ float s_vec[4][kH];            // b1, ln gamma, ln beta, b2
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ uint32_t s_tmem;
+
+    unsigned char* sA1 = smem;
+    unsigned char* sB1 = sA1 + kTileM * K1 * 2;
+    unsigned char* sA2 = sB1 + kH * K1 * 2;
+    unsigned char* sB2 = sA2 + kTileM * kH * 2;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    // ---- one-time setup: weights -> canonical layout, vectors, mbarrier, TMEM ------------------
+    for (int c = tid; c < kH * (K1 / 8); c += kMlpThreads) {       // W1 is nn.Linear.weight: (64, K1) row-major = K-major
+        const int n = c / (K1 / 8), k8 = c % (K1 / 8);
+        const uint4 v = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(P.w1) + static_cast<size_t>(n) * K1 + k8 * 8);
+        *reinterpret_cast<uint4*>(sB1 + canon_chunk_offset(n, k8, K1)) = v;
+    }
+    for (int c = tid; c < kH * (kH / 8); c += kMlpThreads) {
+        const int n = c / (kH / 8), k8 = c % (kH / 8);
+        const uint4 v = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(P.w2) + static_cast<size_t>(n) * kH + k8 * 8);
+        *reinterpret_cast<uint4*>(sB2 + canon_chunk_offset(n, k8, kH)) = v;
+    }
+    if (tid < kH) {
+        s_vec[0][tid] = P.b1 ? P.b1[tid] : 0.0f;
+        s_vec[1][tid] = P.ln_gamma ? P.ln_gamma[tid] : 1.0f;
+        s_vec[2][tid] = P.ln_beta ? P.ln_beta[tid] : 0.0f;
+        s_vec[3][tid] = P.b2 ? P.b2[tid] : 0.0f;
+    }
+    if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+    const uint32_t tmem_row = tmem + (static_cast<uint32_t>(warp * 32) << 16);   // this warp's 32 TMEM lanes
+    constexpr uint32_t kIdesc = umma_idesc(kH);
+    uint32_t phase = 0;
+    const int row = tid;                                            // tile row owned in the epilogues
+
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+        const long long p0 = static_cast<long long>(tile) * kTileM;
+
+        // ---- 1. features -> bf16 A tile: 8 consecutive lanes take 8 consecutive rows of one 16-byte chunk
+        //         column (conflict-free shared stores), 4 chunk columns per request (128 B global segments)
+        // each warp fills its 32 rows: 4 groups of 8 rows x (K1/8) chunks; chunk c -> (row % 8 = c % 8, k8)
+#pragma unroll 2
+        for (int c = lane; c < 4 * K1; c += 32) {
+            const int rg = c / K1, rem = c % K1;
+            const int r = warp * 32 + rg * 8 + (rem & 7);
+            const int k8 = rem >> 3;
+            uint4 packed = make_uint4(0u, 0u, 0u, 0u);
+            if (p0 + r < P.n) {
+                const float4* src = reinterpret_cast<const float4*>(P.x + (p0 + r) * P.x_stride + k8 * 8);
+                const float4 a = __ldcs(src), b = __ldcs(src + 1);
+                packed = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w));
+            }
+            *reinterpret_cast<uint4*>(sA1 + canon_chunk_offset(r, k8, K1)) = packed;
+        }
+        fence_async_smem();          // generic-proxy writes -> visible to the tensor core's async proxy
+        tc_fence_before();           // orders this thread's earlier tcgen05.ld (previous tile) before the barrier
+        __syncthreads();
+
+        // ---- 2. GEMM 1: D1[128 x 64] = A1[128 x K1] * W1^T -------------------------------------
+        if (tid == 0) {
+            tc_fence_after();
+            const uint32_t a0 = smem_u32(sA1), b0 = smem_u32(sB1);
+#pragma unroll
+            for (int k = 0; k < K1 / 16; ++k)
+                umma_bf16(tmem, umma_desc(a0 + k * 256, 128, (K1 / 8) * 128), umma_desc(b0 + k * 256, 128, (K1 / 8) * 128),
+                          kIdesc, k > 0 ? 1u : 0u);
+            umma_commit(&s_bar);
+        }
+        mbar_wait(&s_bar, phase);
+        phase ^= 1u;
+        tc_fence_after();
+
+        // ---- 3. epilogue 1: bias + LayerNorm + activation, hidden row -> bf16 A2 ---------------
+        {
+            float h[kH];
+            {
+                float lo[32], hi[32];
+                tmem_ld32(tmem_row, lo);
+                tmem_ld32(tmem_row + 32, hi);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) { h[j] = lo[j] + s_vec[0][j]; h[32 + j] = hi[j] + s_vec[0][32 + j]; }
+            }
+            if (P.layernorm) {
+                float mean = 0.0f;
+#pragma unroll
+                for (int j = 0; j < kH; ++j) mean += h[j];
+                mean *= (1.0f / kH);
+                float var = 0.0f;
+#pragma unroll
+                for (int j = 0; j < kH; ++j) { const float d = h[j] - mean; var = fmaf(d, d, var); }
+                const float rstd = rsqrtf(var * (1.0f / kH) + P.ln_eps);
+#pragma unroll
+                for (int j = 0; j < kH; ++j) h[j] = fmaf((h[j] - mean) * rstd, s_vec[1][j], s_vec[2][j]);
+            }
+            if (P.activation == 1) {
+#pragma unroll
+                for (int j = 0; j < kH; ++j) h[j] = fmaxf(h[j], 0.0f);
+            } else if (P.activation == 2) {
+#pragma unroll
+                for (int j = 0; j < kH; ++j) h[j] = 0.5f * h[j] * (1.0f + erff(h[j] * 0.70710678118654752f));   // nn.GELU() (erf form)
+            }
+#pragma unroll
+            for (int k8 = 0; k8 < kH / 8; ++k8) {
+                const uint4 v = make_uint4(pack_bf16(h[8 * k8], h[8 * k8 + 1]), pack_bf16(h[8 * k8 + 2], h[8 * k8 + 3]),
+                                           pack_bf16(h[8 * k8 + 4], h[8 * k8 + 5]), pack_bf16(h[8 * k8 + 6], h[8 * k8 + 7]));
+                *reinterpret_cast<uint4*>(sA2 + canon_chunk_offset(row, k8, kH)) = v;
+            }
+        }
+        fence_async_smem();
+        tc_fence_before();
+        __syncthreads();
+
+        // ---- 4. GEMM 2: D2[128 x 64] = A2[128 x 64] * W2^T -------------------------------------
+        if (tid == 0) {
+            tc_fence_after();
+            const uint32_t a0 = smem_u32(sA2), b0 = smem_u32(sB2);
+#pragma unroll
+            for (int k = 0; k < kH / 16; ++k)
+                umma_bf16(tmem + kH, umma_desc(a0 + k * 256, 128, (kH / 8) * 128), umma_desc(b0 + k * 256, 128, (kH / 8) * 128),
+                          kIdesc, k > 0 ? 1u : 0u);
+            umma_commit(&s_bar);
+        }
+        mbar_wait(&s_bar, phase);
+        phase ^= 1u;
+        tc_fence_after();
+
+        // ---- 5. epilogue 2: bias, stream the output row ----------------------------------------
+        {
+            float lo[32], hi[32];
+            tmem_ld32(tmem_row + kH, lo);
+            tmem_ld32(tmem_row + kH + 32, hi);
+            if (p0 + row < P.n) {
+                float4* dst = reinterpret_cast<float4*>(P.y + (p0 + row) * P.y_stride);
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    __stcs(dst + q, make_float4(lo[4 * q] + s_vec[3][4 * q], lo[4 * q + 1] + s_vec[3][4 * q + 1],
+                                                lo[4 * q + 2] + s_vec[3][4 * q + 2], lo[4 * q + 3] + s_vec[3][4 * q + 3]));
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    __stcs(dst + 8 + q, make_float4(hi[4 * q] + s_vec[3][32 + 4 * q], hi[4 * q + 1] + s_vec[3][33 + 4 * q],
+                                                    hi[4 * q + 2] + s_vec[3][34 + 4 * q], hi[4 * q + 3] + s_vec[3][35 + 4 * q]));
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// host launcher
+// ------------------------------------------------------------------------------------------------
+template <int K1>
+static cudaError_t launch_k(const MlpHeadParams& P, int n_sms, cudaStream_t s) {
+    auto kernel = mlp_head_kernel<K1>;
+    const size_t smem = static_cast<size_t>(kTileM) * K1 * 2 + kH * K1 * 2 + kTileM * kH * 2 + kH * kH * 2;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    int per_sm = static_cast<int>((220 * 1024) / (smem + 2048));
+    if (per_sm > 4) per_sm = 4;                       // 4 x 128 TMEM columns = the SM's 512
+    if (per_sm < 1) per_sm = 1;
+    int grid = n_sms * per_sm;
+    if (grid > P.n_tiles) grid = P.n_tiles;
+    kernel<<<grid, kMlpThreads, smem, s>>>(P);
+    return cudaGetLastError();
+}
+
+bool mlp_head_supported(int in_dim, int hidden, int out_dim) {
+    return hidden == kH && out_dim == kH && (in_dim == 32 || in_dim == 48 || in_dim == 64 || in_dim == 96 || in_dim == 128);
+}
+
+cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s) {
+    P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
+    if (P.n_tiles == 0) return cudaSuccess;
+    switch (in_dim) {
+        case 32: return launch_k<32>(P, n_sms, s);
+        case 48: return launch_k<48>(P, n_sms, s);
+        case 64: return launch_k<64>(P, n_sms, s);
+        case 96: return launch_k<96>(P, n_sms, s);
+        case 128: return launch_k<128>(P, n_sms, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace de

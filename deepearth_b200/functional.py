@@ -159,7 +159,7 @@ def encode_forward(specs: Sequence[LevelSpec], coords: torch.Tensor, table_ptrs:
 def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: torch.Tensor,
                     grad_ptrs: Sequence[int], n_features: int, linear: bool,
                     mask_a: Optional[torch.Tensor] = None, mask_b: Optional[torch.Tensor] = None,
-                    levels_per_group: int = 0, extra_flags: int = 0) -> None:
+                    levels_per_group: int = 0, extra_flags: int = 0, use_replicas: bool = True) -> None:
     """Accumulate table gradients into the fp32 buffers at ``grad_ptrs`` (caller zeroes them)."""
     _require_cuda(coords, "coords")
     _require_cuda(grad_out, "grad_out")
@@ -174,12 +174,18 @@ def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: 
     ma = _mask_u8(mask_a, n, coords.device)
     mb = _mask_u8(mask_b, n, coords.device)
     lib = _lib.load()
+    flags = (_lib.DE_INTERP_LINEAR if linear else _lib.DE_INTERP_NEAREST) | extra_flags
+    levels = pack_levels(specs, None, grad_ptrs)
+    ws, ws_bytes = None, 0
+    if use_replicas:
+        ws_bytes = int(lib.de_grid4d_backward_workspace_bytes(levels, len(specs), n_features, n, flags))
+        if ws_bytes:
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=coords.device)   # caching allocator: no cudaMalloc in steady state
     with torch.cuda.device(coords.device):
-        rc = lib.de_grid4d_backward(pack_levels(specs, None, grad_ptrs), len(specs), _ptr(coords), n, stride,
+        rc = lib.de_grid4d_backward(levels, len(specs), _ptr(coords), n, stride,
                                     n_features, _ptr(ma), _ptr(mb), _ptr(grad_out),
                                     grad_out.stride(0) if n > 1 else grad_out.shape[1],
-                                    (_lib.DE_INTERP_LINEAR if linear else _lib.DE_INTERP_NEAREST) | extra_flags,
-                                    levels_per_group, _stream_ptr(coords.device))
+                                    flags, levels_per_group, _ptr(ws), ws_bytes, _stream_ptr(coords.device))
     _lib.check(rc, "de_grid4d_backward")
 
 

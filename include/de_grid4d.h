@@ -35,7 +35,7 @@ extern "C" {
 #define DE_API
 #endif
 
-#define DE_ABI_VERSION 1
+#define DE_ABI_VERSION 2
 
 /* status codes (negative = caller error) */
 #define DE_OK 0
@@ -120,13 +120,24 @@ DE_API int de_grid4d_forward(const de_level_desc* levels_host, int n_levels,
  * grad_out[p, out_col + f], accumulated with vector fp32 reductions.  grad_table
  * buffers must be zeroed (or hold the running sum) by the caller.  Coordinates
  * receive no gradient, as in the reference (graph cut at hash_encoding.py:61).
+ * workspace: device scratch of de_grid4d_backward_workspace_bytes() bytes, 16 B aligned, or NULL.
  */
 DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels,
                        const float* coords, int64_t n_points, int coord_stride,
                        int n_features,
                        const uint8_t* mask_a, const uint8_t* mask_b,
                        const float* grad_out, int64_t grad_stride,
-                       uint32_t flags, int levels_per_group, void* stream);
+                       uint32_t flags, int levels_per_group,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Scratch the backward wants for this call (0 = none).  Coarse levels with few live
+ * entries take thousands of reductions per entry; with a workspace the kernel spreads
+ * them over private copies ("replicas") that a small kernel folds into grad_table
+ * afterwards.  The call zeroes what it uses; pass NULL / 0 to run without replicas.
+ */
+DE_API size_t de_grid4d_backward_workspace_bytes(const de_level_desc* levels_host, int n_levels,
+                                                 int n_features, int64_t n_points, uint32_t flags);
 
 /*
  * fp32 master tables -> fp16 working tables, dst = half(src * scale), one launch
@@ -160,6 +171,22 @@ DE_API int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t
  */
 DE_API int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n_points,
                 void* stream);
+
+/*
+ * Tensor-core MLP head -- replaces Grid4DEncoder.projection (models/encoders.py:47-52:
+ * Linear -> LayerNorm -> GELU -> Linear) at the 64-wide size of BASELINE.json configs[4]:
+ *   y = W2 * act( LN( W1 * x + b1 ) ) + b2        hidden = out_dim = 64
+ * One kernel: bf16 tcgen05.mma with fp32 accumulators in tensor memory; the hidden row never
+ * leaves the SM.  x: (n, in_dim) fp32 features (the encoder's output), in_dim in {32,48,64,96,128};
+ * w1_bf16: (64, in_dim), w2_bf16: (64, 64) bf16 in nn.Linear.weight layout; biases / LayerNorm
+ * vectors fp32 or NULL; layernorm 0/1; activation 0 none, 1 ReLU, 2 GELU (erf form).
+ */
+DE_API int de_mlp_head_supported(int in_dim, int hidden, int out_dim);
+DE_API int de_mlp_head_forward(const float* x, int64_t n_points, int in_dim, int64_t x_stride,
+                        const void* w1_bf16, const float* b1,
+                        const float* ln_gamma, const float* ln_beta, float ln_eps, int layernorm,
+                        int activation, const void* w2_bf16, const float* b2,
+                        int hidden, int out_dim, float* y, int64_t y_stride, void* stream);
 
 /*
  * Device-wide L2 fetch granularity hint (cudaLimitMaxL2FetchGranularity) of the current device: 32, 64 or

@@ -444,6 +444,14 @@ def test_smem_coarse_and_staged_paths_match_plain_path(dev, oracle, table_dtype)
 
     out_opt, grad_opt = run(_lib.DE_FLAG_STAGED_BWD | _lib.DE_FLAG_SMEM_COARSE)
     out_ref, grad_ref = run(0)
+    # the default backward spreads the two coarsest levels over gradient replicas; without a workspace it must agree
+    from deepearth_b200 import functional as Fn
+    specs = enc.level_specs()
+    flat = torch.zeros(L * T * F, device=dev)
+    ptrs = [flat.data_ptr() + 4 * l * T * F for l in range(L)]
+    assert _lib.load().de_grid4d_backward_workspace_bytes(Fn.pack_levels(specs, None, ptrs), L, F, n, 1) > 0
+    Fn.encode_backward(specs, coords, gout, ptrs, F, True, use_replicas=False)
+    assert float((flat - grad_ref).abs().max()) <= GRAD_TOL * float(grad_ref.abs().max())
     assert torch.equal(out_opt, out_ref)
     denom = float(grad_ref.abs().max())
     assert float((grad_opt - grad_ref).abs().max()) <= GRAD_TOL * denom
