@@ -465,12 +465,16 @@ def main():
     ap.add_argument("--log2-points", type=int, default=0, help="override points per GPU (power of two)")
     ap.add_argument("--levels-per-group", type=int, default=0)
     ap.add_argument("--bwd-levels-per-group", type=int, default=0)
+    ap.add_argument("--coords", default="", choices=["", "uniform", "florida"], help="override the workload's coordinate distribution")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-replicas", action="store_true", help="backward without gradient replicas for contended coarse levels (A/B)")
     ap.add_argument("--flags", type=lambda v: int(v, 0), default=0, help="DE_FLAG_* opt-in paths (0x100 TMA-staged backward, 0x200 shared-memory coarse forward)")
     ap.add_argument("--l2-fetch", type=int, default=0, help="set cudaLimitMaxL2FetchGranularity (32/64/128)")
     args = ap.parse_args()
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.coords:
+        wl["coords"] = args.coords
+        wl["desc"] += f" [coords overridden: {args.coords}]"
     if args.impl == "reference":
         run_reference_arm(args, wl)
     else:

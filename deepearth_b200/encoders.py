@@ -19,6 +19,7 @@ import torch.nn as nn
 from . import functional as Fn
 from .functional import GRID_DIMS, EncodePlan, Grid4DFunction
 from .hash_encoding import MultiResolutionHashEncoding
+from .mlp_head import FusedProjection
 
 
 def _cfg(config, name, default):
@@ -70,6 +71,7 @@ class Grid4DEncoder(nn.Module):
             raise ValueError(f"unknown grid4d_mode {self.mode!r}")
 
         self.feature_dim = sum(e.output_dim for e in self._encoders)
+        self._fused_head = None   # FusedProjection | False, resolved on first forward
         self.projection = nn.Sequential(
             nn.Linear(self.feature_dim, config.hidden_dim),
             nn.LayerNorm(config.hidden_dim),
@@ -110,6 +112,19 @@ class Grid4DEncoder(nn.Module):
             spatial_mask = temporal_mask = None
         return Grid4DFunction.apply(xyzt, spatial_mask, temporal_mask, self._plan(), ptrs, *weights)
 
+    def _project(self, feats: torch.Tensor) -> torch.Tensor:
+        # opt-in (config.grid4d_fused_head = True): a hidden_dim = 64 head runs as one bf16 tcgen05 kernel
+        # (csrc/mlp_head.cu); the default and every other width is the reference's fp32 nn.Sequential (cuBLAS)
+        if not _cfg(self.config, "grid4d_fused_head", False) or torch.is_autocast_enabled():
+            return self.projection(feats)
+        if self._fused_head is None:
+            try:
+                fp = FusedProjection(self.projection)
+                self._fused_head = fp if fp.supported() else False
+            except TypeError:
+                self._fused_head = False
+        return self._fused_head(feats) if self._fused_head else self.projection(feats)
+
     def forward(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,
                 temporal_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
-        return self.projection(self.encode_features(xyzt, spatial_mask, temporal_mask))
+        return self._project(self.encode_features(xyzt, spatial_mask, temporal_mask))

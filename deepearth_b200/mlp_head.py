@@ -1,0 +1,132 @@
+"""Tensor-core MLP head: Linear -> LayerNorm -> GELU -> Linear at hidden = out = 64 in ONE kernel.
+
+Mirrors ``Grid4DEncoder.projection`` (/root/reference/models/encoders.py:47-52).  The parameters stay in an
+ordinary ``nn.Sequential`` (same state-dict keys as the reference: ``projection.0.weight`` ...); this module
+only changes how the forward is computed: ``de_mlp_head_forward`` (deepearth_b200/csrc/mlp_head.cu) runs both
+GEMMs as bf16 ``tcgen05.mma`` with fp32 accumulators in tensor memory, and the hidden row never leaves the SM.
+The backward pass recomputes through the fp32 PyTorch modules (cuBLAS): training keeps full-precision
+gradients, inference and the forward half of training use the fused kernel.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .functional import _ptr, _require_cuda, _stream_ptr
+
+_ACT = {"none": 0, "relu": 1, "gelu": 2}
+
+
+def mlp_head_supported(in_dim: int, hidden: int, out_dim: int) -> bool:
+    return bool(_lib.load().de_mlp_head_supported(int(in_dim), int(hidden), int(out_dim)))
+
+
+def mlp_head_forward(x: torch.Tensor, w1_bf16: torch.Tensor, b1: Optional[torch.Tensor],
+                     ln_gamma: Optional[torch.Tensor], ln_beta: Optional[torch.Tensor], ln_eps: float,
+                     layernorm: bool, activation: str, w2_bf16: torch.Tensor, b2: Optional[torch.Tensor],
+                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x (n, in_dim) fp32 CUDA -> (n, 64) fp32.  Weights are bf16 in nn.Linear.weight layout."""
+    _require_cuda(x, "x")
+    if x.dim() != 2 or x.dtype != torch.float32:
+        raise TypeError("x must be a 2-D float32 tensor")
+    if x.stride(1) != 1 or x.stride(0) % 4 or x.data_ptr() % 16:
+        x = x.contiguous()
+    n, in_dim = x.shape
+    hidden, out_dim = w1_bf16.shape[0], w2_bf16.shape[0]
+    if w1_bf16.dtype != torch.bfloat16 or w2_bf16.dtype != torch.bfloat16:
+        raise TypeError("weights must be bfloat16")
+    if w1_bf16.shape != (hidden, in_dim) or w2_bf16.shape != (out_dim, hidden):
+        raise ValueError("weight shapes do not chain")
+    if out is None:
+        out = torch.empty((n, out_dim), dtype=torch.float32, device=x.device)
+    if n == 0:
+        return out
+    lib = _lib.load()
+    with torch.cuda.device(x.device):
+        rc = lib.de_mlp_head_forward(_ptr(x), n, in_dim, x.stride(0), _ptr(w1_bf16.contiguous()), _ptr(b1),
+                                     _ptr(ln_gamma), _ptr(ln_beta), float(ln_eps), int(bool(layernorm)),
+                                     _ACT[activation], _ptr(w2_bf16.contiguous()), _ptr(b2), hidden, out_dim,
+                                     _ptr(out), out.stride(0), _stream_ptr(x.device))
+    _lib.check(rc, "de_mlp_head_forward")
+    return out
+
+
+class _HeadFunction(torch.autograd.Function):
+    """forward = fused tensor-core kernel; backward = recompute through the fp32 modules (cuBLAS)."""
+
+    @staticmethod
+    def forward(ctx, x, head, *params):
+        ctx.head = head
+        ctx.save_for_backward(x)
+        return head.fused(x)
+
+    @staticmethod
+    def backward(ctx, grad_y):
+        (x,) = ctx.saved_tensors
+        head = ctx.head
+        params = list(head.seq.parameters())
+        with torch.enable_grad():
+            xd = x.detach().requires_grad_(ctx.needs_input_grad[0])
+            y = head.seq(xd)
+            wanted = ([xd] if ctx.needs_input_grad[0] else []) + [p for i, p in enumerate(params) if ctx.needs_input_grad[2 + i]]
+            grads = list(torch.autograd.grad(y, wanted, grad_y, allow_unused=True))
+        gx = grads.pop(0) if ctx.needs_input_grad[0] else None
+        gp = [grads.pop(0) if ctx.needs_input_grad[2 + i] else None for i in range(len(params))]
+        return (gx, None, *gp)
+
+
+class FusedProjection:
+    """Computes an ``nn.Sequential(Linear, LayerNorm, GELU|ReLU, Linear)`` (or without the LayerNorm) with the
+    fused kernel.  Holds no parameters of its own: bf16 copies of the Linear weights are re-derived whenever the
+    fp32 parameters change."""
+
+    def __init__(self, seq: nn.Sequential):
+        mods = list(seq)
+        if not (isinstance(mods[0], nn.Linear) and isinstance(mods[-1], nn.Linear)):
+            raise TypeError("expected Linear ... Linear")
+        mid = mods[1:-1]
+        self.seq = seq
+        self.lin1, self.lin2 = mods[0], mods[-1]
+        self.norm = next((m for m in mid if isinstance(m, nn.LayerNorm)), None)
+        acts = [m for m in mid if not isinstance(m, nn.LayerNorm)]
+        if len(acts) > 1:
+            raise TypeError("at most one activation between the Linear layers")
+        if not acts:
+            self.activation = "none"
+        elif isinstance(acts[0], nn.GELU) and getattr(acts[0], "approximate", "none") == "none":
+            self.activation = "gelu"
+        elif isinstance(acts[0], nn.ReLU):
+            self.activation = "relu"
+        else:
+            raise TypeError(f"unsupported activation {acts[0]!r}")
+        self._key = None
+        self._w1 = self._w2 = None
+
+    def supported(self) -> bool:
+        return mlp_head_supported(self.lin1.in_features, self.lin1.out_features, self.lin2.out_features)
+
+    def _weights(self):
+        key = (self.lin1.weight._version, self.lin2.weight._version, self.lin1.weight.data_ptr(), self.lin2.weight.data_ptr())
+        if key != self._key:
+            with torch.no_grad():
+                self._w1 = self.lin1.weight.detach().to(torch.bfloat16).contiguous()
+                self._w2 = self.lin2.weight.detach().to(torch.bfloat16).contiguous()
+            self._key = key
+        return self._w1, self._w2
+
+    def fused(self, x: torch.Tensor) -> torch.Tensor:
+        w1, w2 = self._weights()
+        n = self.norm
+        return mlp_head_forward(x, w1, self.lin1.bias, n.weight if n is not None else None,
+                                n.bias if n is not None else None, n.eps if n is not None else 1e-5,
+                                n is not None, self.activation, w2, self.lin2.bias)
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        needs_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.seq.parameters()))
+        if needs_grad:
+            return _HeadFunction.apply(x, self, *self.seq.parameters())
+        return self.fused(x)

@@ -469,3 +469,74 @@ def test_smem_coarse_and_staged_paths_match_plain_path(dev, oracle, table_dtype)
     want_g = oracle.backward(levels, coords.cpu().numpy(), gout.cpu().numpy(), L * T, F, True)
     gerr = np.abs(grad_opt.cpu().numpy().reshape(-1, F) - want_g).max() / np.abs(want_g).max()
     assert gerr <= GRAD_TOL, gerr
+
+
+# ---------------------------------------------------------------------------------------------------
+# tensor-core MLP head (tcgen05): Linear -> LayerNorm -> GELU -> Linear, hidden = out = 64
+# ---------------------------------------------------------------------------------------------------
+def _head_reference(x, seq):
+    """fp32 PyTorch evaluation with the kernel's roundings: bf16 inputs / weights / hidden row, fp32 accumulate."""
+    mods = list(seq)
+    bf = lambda t: t.to(torch.bfloat16).to(torch.float32)
+    h = bf(x) @ bf(mods[0].weight).t() + mods[0].bias
+    for m in mods[1:-1]:
+        h = m(h)
+    return bf(h) @ bf(mods[-1].weight).t() + mods[-1].bias
+
+
+@pytest.mark.parametrize("in_dim,layernorm,act", [(128, True, "gelu"), (48, True, "gelu"), (64, False, "relu"),
+                                                  (32, False, "none"), (96, True, "relu")])
+def test_mlp_head_vs_torch(dev, in_dim, layernorm, act):
+    from deepearth_b200.mlp_head import FusedProjection
+    torch.manual_seed(3)
+    mods = [torch.nn.Linear(in_dim, 64)]
+    if layernorm:
+        mods.append(torch.nn.LayerNorm(64))
+    if act != "none":
+        mods.append(torch.nn.GELU() if act == "gelu" else torch.nn.ReLU())
+    mods.append(torch.nn.Linear(64, 64))
+    seq = torch.nn.Sequential(*mods).to(dev)
+    if layernorm:
+        with torch.no_grad():
+            seq[1].weight.uniform_(0.5, 1.5)
+            seq[1].bias.uniform_(-0.2, 0.2)
+    head = FusedProjection(seq)
+    assert head.supported()
+    g = torch.Generator(device=dev).manual_seed(5)
+    for n in (1, 127, 128, 129, 5000, 148 * 4 * 128 + 17):      # ragged tails and more tiles than resident CTAs
+        x = torch.randn((n, in_dim), device=dev, generator=g)
+        with torch.no_grad():
+            got = head(x)
+            want = _head_reference(x, seq)
+            full = seq(x)
+        scale = float(want.abs().max())
+        assert float((got - want).abs().max()) <= 2e-3 * scale, (n, float((got - want).abs().max()), scale)
+        assert float((got - full).abs().max()) <= 3e-2 * scale      # bf16 operands vs the fp32 module
+    # training: forward through the kernel, gradients through the fp32 recompute
+    x = torch.randn((777, in_dim), device=dev, generator=g, requires_grad=True)
+    y = head(x)
+    gy = torch.randn(y.shape, device=dev, generator=g)
+    y.backward(gy)
+    gx, gw = x.grad.clone(), seq[0].weight.grad.clone()
+    x.grad = None
+    seq.zero_grad()
+    seq(x).backward(gy)
+    assert torch.allclose(gx, x.grad, rtol=1e-5, atol=1e-6) and torch.allclose(gw, seq[0].weight.grad, rtol=1e-5, atol=1e-6)
+
+
+def test_grid4d_encoder_fused_head(dev):
+    import deepearth_b200 as de
+    cfg = de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=2 ** 14, grid4d_fused_head=True)
+    enc = de.Grid4DEncoder(cfg).to(dev)
+    with torch.no_grad():
+        for p in enc.parameters():
+            if p.dim() == 2 and p.shape[1] == 2:
+                p.uniform_(-1.0, 1.0)
+    xyzt = torch.rand((4096 + 5, 4), device=dev)
+    with torch.no_grad():
+        got = enc(xyzt)
+        want = enc.projection(enc.encode_features(xyzt))
+    assert enc._fused_head not in (None, False)
+    assert float((got - want).abs().max()) <= 3e-2 * float(want.abs().max())
+    enc(xyzt).sum().backward()
+    assert all(p.grad is not None for p in enc.parameters())
