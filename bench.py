@@ -46,6 +46,9 @@ WORKLOADS = {
                desc="configs[1]: 4 grids (xyz/xyt/yzt/xzt) x 16 levels x 2 feat, T=2^19/level, 2^22 points/GPU, fp16 tables, fp32 grads"),
     "c3": dict(mode="decomposed", T=2 ** 22, log2_points=24, coords="florida", table_dtype="float16",
                desc="configs[2]: 4 grids x 16 levels x 2 feat, T=2^22/level (HBM resident), 2^24 Florida-clustered points/GPU"),
+    "c5": dict(mode="decomposed", T=2 ** 22, log2_points=24, coords="florida", table_dtype="float16", head=True,
+               desc="configs[4]: geo2xyz prologue + 4 grids x 16 levels x 2 feat (T=2^22) + Linear-LayerNorm-GELU-Linear 64-wide head "
+                    "(tcgen05 kernel forward, cuBLAS recompute backward), 2^24 Florida-clustered geodetic points/GPU"),
     "c1r": dict(mode="reference", T=2 ** 19, log2_points=22, coords="uniform", table_dtype="float32",
                 desc="reference Grid4DEncoder geometry (xyz L16 T=2^19 + t L8 T=2^17, nearest, fp32 tables), 2^22 points/GPU"),
 }
@@ -133,17 +136,15 @@ def build_config(wl):
         return de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=wl["T"],
                                   n_spatial_levels=16, n_temporal_levels=16, spatial_resolutions=res,
                                   temporal_resolutions=res, grid4d_mode="decomposed",
-                                  grid4d_table_dtype=wl["table_dtype"])
+                                  grid4d_table_dtype=wl["table_dtype"], grid4d_fused_head=bool(wl.get("head")))
     return de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=wl["T"])
 
 
-def make_coords(wl, n, device, seed):
-    g = torch.Generator(device=device).manual_seed(seed)
-    if wl["coords"] == "uniform":
-        return torch.rand((n, 4), device=device, generator=g)
-    # Florida-clustered geodetic points pushed through the geo2xyz prologue kernel
+def make_geo(n, device, seed):
+    """Florida-clustered geodetic points: (geo (n,3) fp64, t (n,) fp64, converter with pre-fitted bbox)."""
     import deepearth_b200 as de
     from _synth import FLORIDA_BBOX_GEO as B, FLORIDA_T_RANGE
+    g = torch.Generator(device=device).manual_seed(seed)
     K = 64
     cu = torch.rand((K, 2), device=device, generator=g, dtype=torch.float64)
     clat = B["south"] + (B["north"] - B["south"]) * cu[:, 0]
@@ -154,14 +155,22 @@ def make_coords(wl, n, device, seed):
     lon = clon[which] + 0.1 * torch.randn(n, device=device, generator=g, dtype=torch.float64)
     alt = 50.0 * torch.rand(n, device=device, generator=g, dtype=torch.float64)
     t = FLORIDA_T_RANGE[0] + (FLORIDA_T_RANGE[1] - FLORIDA_T_RANGE[0]) * torch.rand(n, device=device, generator=g, dtype=torch.float64)
-    geo = torch.stack([lat, lon, alt], 1)
-    # bbox = the Central-Florida box at alt 0..50 m, fitted once from its 8 corners (+ edge midpoints)
+    geo = torch.stack([lat, lon, alt], 1).contiguous()
+    # bbox = the Central-Florida box at alt 0..50 m, fitted once from its corners (+ edge midpoints)
     conv = de.GeospatialConverter(device=str(device), t_range=FLORIDA_T_RANGE)
     lats = torch.linspace(B["south"], B["north"], 9, dtype=torch.float64, device=device)
     lons = torch.linspace(B["west"], B["east"], 9, dtype=torch.float64, device=device)
     alts = torch.tensor([B["alt_min"], B["alt_max"]], dtype=torch.float64, device=device)
     conv.update_bbox(torch.cartesian_prod(lats, lons, alts))
-    return conv.geodetic_to_xyzt_norm(geo, t)
+    return geo, t, conv
+
+
+def make_coords(wl, n, device, seed):
+    if wl["coords"] == "uniform":
+        g = torch.Generator(device=device).manual_seed(seed)
+        return torch.rand((n, 4), device=device, generator=g)
+    geo, t, conv = make_geo(n, device, seed)
+    return conv.geodetic_to_xyzt_norm(geo, t)       # the geo2xyz prologue kernel
 
 
 class Job:
@@ -185,9 +194,22 @@ class Job:
             self.table_ptrs = [w.data_ptr() for w in self.weights]
         self.flat_grad = torch.zeros(self.plan.grad_numel, dtype=torch.float32, device=device)
         self.grad_ptrs = [self.flat_grad.data_ptr() + 4 * o for o in self.plan.grad_offsets]
-        self.coords = make_coords(wl, n_points, device, seed)
+        self.head = None
         g = torch.Generator(device=device).manual_seed(seed + 1)
-        self.gout = torch.randn((n_points, self.plan.out_cols), device=device, generator=g)
+        if wl.get("head"):
+            # configs[4]: the step starts from geodetic points (prologue kernel inside the timed region) and
+            # ends in the 64-wide head; the incoming gradient is d(loss)/d(head output)
+            from deepearth_b200.mlp_head import FusedProjection
+            self.geo, self.t, self.conv = make_geo(n_points, device, seed)
+            self.coords = self.conv.geodetic_to_xyzt_norm(self.geo, self.t)
+            self.head = FusedProjection(self.enc.projection)
+            assert self.head.supported(), "64-wide head expected"
+            self.head_params = list(self.enc.projection.parameters())
+            self.gy = torch.randn((n_points, 64), device=device, generator=g)
+            self.gout = None
+        else:
+            self.coords = make_coords(wl, n_points, device, seed)
+            self.gout = torch.randn((n_points, self.plan.out_cols), device=device, generator=g)
         self.out = torch.empty((n_points, self.plan.out_cols), dtype=torch.float32, device=device)
         corners = 8 if self.linear else 1
         tb = 2 if self.plan.table_dtype == torch.float16 else 4
@@ -207,6 +229,22 @@ class Job:
                            levels_per_group=self.plan.bwd_levels_per_group, extra_flags=self.plan.extra_flags,
                            use_replicas=self.use_replicas)
 
+    # ---- configs[4] pieces ---------------------------------------------------------------------
+    def prologue(self):
+        self.coords = self.conv.geodetic_to_xyzt_norm(self.geo, self.t)
+
+    def head_forward(self):
+        self.y = self.head.fused(self.out)
+
+    def head_backward(self):
+        """Gradients of the head: recompute through the fp32 modules (cuBLAS), as the autograd path does."""
+        with torch.enable_grad():
+            xd = self.out.detach().requires_grad_(True)
+            y = self.enc.projection(xd)
+            grads = torch.autograd.grad(y, [xd] + self.head_params, self.gy)
+        self.gout = grads[0]
+        self.head_grads = grads[1:]
+
     def n_launches_per_step(self):
         # one launch per run of equal-D levels (<= 64) for forward and for backward
         runs, prev = 0, None
@@ -216,7 +254,7 @@ class Job:
                 runs += 1
                 prev, cnt = len(s.dims), 0
             cnt += 1
-        return 2 * runs
+        return 2 * runs + (2 if self.head is not None else 0)     # + prologue + head kernels (cuBLAS launches not counted)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -316,7 +354,16 @@ def run_gpu_arm(args, wl):
         job.flat_grad.zero_()
         if ev:
             ev[0].record()
+        if job.head is not None:
+            job.prologue()
         job.forward()
+        if job.head is not None:
+            if ev:
+                ev[4].record()
+            job.head_forward()
+            if ev:
+                ev[5].record()
+            job.head_backward()
         if ev:
             ev[1].record()
         job.backward()
@@ -338,7 +385,7 @@ def run_gpu_arm(args, wl):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(args.steps)]
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     w0 = sampler.mark()
@@ -368,7 +415,13 @@ def run_gpu_arm(args, wl):
     if clocks is not None:
         clocks["window"] = clock_window
     total_ms = t_start.elapsed_time(t_end)
-    fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+    head_ms = None
+    if job.head is not None:
+        fwd_ms = float(np.mean([e[0].elapsed_time(e[4]) for e in evs]))        # prologue + encode
+        head_ms = {"head_forward_tcgen05": float(np.mean([e[4].elapsed_time(e[5]) for e in evs])),
+                   "head_backward_cublas": float(np.mean([e[5].elapsed_time(e[1]) for e in evs]))}
+    else:
+        fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
     bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
     ar_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in evs])) if world > 1 else 0.0
     if world > 1:
@@ -379,21 +432,37 @@ def run_gpu_arm(args, wl):
     value = world * n / (ms_per_step * 1e-3) / 1e6
 
     # ---- end to end through the public nn.Module API, pinned-host coordinates in, scalar out --------
-    host = job.coords.cpu().pin_memory()
-    params = job.weights
+    if job.head is not None:
+        host_geo, host_t = job.geo.cpu().pin_memory(), job.t.cpu().pin_memory()
+        h2d_bytes = host_geo.numel() * 8 + host_t.numel() * 8
+        params = job.weights + job.head_params
+        api = "GeospatialConverter.geodetic_to_xyzt_norm + Grid4DEncoder.forward (tcgen05 head) + autograd backward, pinned host geodetic points -> device each step"
+        job.gout = job.head_grads = job.y = None
+    else:
+        host = job.coords.cpu().pin_memory()
+        h2d_bytes = host.numel() * 4
+        params = job.weights
+        api = "Grid4DEncoder.encode_features + autograd backward, pinned host xyzt -> device each step"
     del job.out      # the module allocates its own output
     torch.cuda.empty_cache()
 
     def e2e_step():
         for p in params:
             p.grad = None
-        xyzt = host.to(device, non_blocking=True)
-        feats = job.enc.encode_features(xyzt)
-        feats.backward(job.gout)
+        if job.head is not None:
+            geo = host_geo.to(device, non_blocking=True)
+            tt = host_t.to(device, non_blocking=True)
+            xyzt = job.conv.geodetic_to_xyzt_norm(geo, tt)
+            res = job.enc(xyzt)
+            res.backward(job.gy)
+        else:
+            xyzt = host.to(device, non_blocking=True)
+            res = job.enc.encode_features(xyzt)
+            res.backward(job.gout)
         if world > 1:
             from deepearth_b200.distributed import allreduce_table_grads
-            allreduce_table_grads(params, average=True)
-        chk = Fn.sum_f32(feats.detach())
+            allreduce_table_grads(job.weights, average=True)
+        chk = Fn.sum_f32(res.detach())
         return float(chk.item())          # device -> host read of the step's result
 
     for _ in range(3):
@@ -434,13 +503,13 @@ def run_gpu_arm(args, wl):
                        "l2_policy": "inputs larger than L2 (coords+grad_out+out > 4 GiB per step); no flush",
                        "l2_fetch_granularity": _gran.value,
                        "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"},
-            "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms},
+            "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms, **(head_ms or {})},
             "roofline": {"bound": "hbm", "kernel": f"grid4d_{dom}_kernel", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_point": {"forward": job.bytes_fwd, "backward": job.bytes_bwd}},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(host.numel() * 4 * world),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes * world),
                     "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps, "checksum": checksum,
-                    "api": "Grid4DEncoder.encode_features + autograd backward, pinned host xyzt -> device each step"},
+                    "api": api},
             "gpu_launches": job.n_launches_per_step() * args.steps,
             "clocks": clocks,
         }

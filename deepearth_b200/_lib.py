@@ -16,7 +16,7 @@ DE_OK = 0
 ABI_VERSION = 2
 DE_F32, DE_F16, DE_F64 = 0, 1, 2
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
-DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE = 0x100, 0x200
+DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS = 0x100, 0x200, 0x400
 DE_MAX_LEVELS_PER_CALL = 256
 
 c_void_p = ctypes.c_void_p

@@ -319,6 +319,7 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
             if (int rc = run_smem_forward(a, base, begin, end, taken, stream)) return rc;
 
         de::EncodeParams P = base;
+        P.l2_hints = (a.flags & DE_FLAG_NO_L2_HINTS) ? 0 : 1;
         int idx[de::kMaxLaunchLevels];
         int n = 0;
         for (int i = begin; i < end; ++i)

@@ -82,6 +82,7 @@ struct EncodeParams {
     int vec_rows;           // feature / grad rows are aligned for F-wide vector access
     int n_stages;           // staged kernels: ring depth
     int stage_points;       // staged kernels: points per stage (multiple of the points one CTA pass covers)
+    int l2_hints;           // pair kernels: evict_last on tables, evict_first on streams
     float out_scale;
     LevelParams levels[kMaxLaunchLevels];
 };
@@ -196,6 +197,98 @@ __device__ __forceinline__ float row_mask(const EncodeParams& P, const LevelPara
         return __ldg(P.mask_b + p) ? 1.0f : 0.0f;
     }
     return 1.0f;
+}
+
+// ---- L2 residency hints -----------------------------------------------------------------------
+// The working set that must stay in L2 is the level group's tables (forward) or gradient tables (backward);
+// coordinates, gradient rows and feature rows stream through once per group.  With plain loads the
+// streams evict the tables: profiles/r01c_kernels_c3.txt shows 81 GB read + 41 GB written to HBM by a
+// backward whose algorithmic HBM traffic is ~25 GB.  Table accesses therefore carry an evict_last
+// policy and the streams an evict_first one (createpolicy + .L2::cache_hint).
+struct L2Policies {
+    uint64_t keep;     // tables / gradient tables
+    uint64_t stream;   // coordinates, gradient rows
+};
+__device__ __forceinline__ L2Policies make_l2_policies(bool hints) {
+    L2Policies p;
+    if (hints) {
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p.keep));
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p.stream));
+    } else {
+        asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p.keep));
+        p.stream = p.keep;
+    }
+    return p;
+}
+__device__ __forceinline__ uint32_t ldg_hint_u32(const void* a, uint64_t pol) {
+    uint32_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ uint2 ldg_hint_u64(const void* a, uint64_t pol) {
+    uint2 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v2.b32 {%0, %1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ uint4 ldg_hint_u128(const void* a, uint64_t pol) {
+    uint4 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v4.b32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(a), "l"(pol));
+    return v;
+}
+// streaming loads: no L1 allocation, evict-first in L2
+__device__ __forceinline__ float4 ldg_stream_f4(const void* a, uint64_t pol) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ float2 ldg_stream_f2(const void* a, uint64_t pol) {
+    float2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f32 {%0, %1}, [%2], %3;" : "=f"(v.x), "=f"(v.y) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ float ldg_stream_f1(const void* a, uint64_t pol) {
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(a), "l"(pol));
+    return v;
+}
+
+// F-wide table entry with an L2 policy (F * sizeof(TT) in {2,4,8,16,32} bytes)
+template <typename TT, int F>
+__device__ __forceinline__ void load_entry_hint(const void* t, uint32_t i, float (&v)[F], uint64_t pol) {
+    constexpr int B = static_cast<int>(sizeof(TT)) * F;
+    const char* a = static_cast<const char*>(t) + static_cast<size_t>(i) * B;
+    uint32_t w[B >= 4 ? B / 4 : 1];
+    if constexpr (B == 2) {
+        unsigned short h;
+        asm volatile("ld.global.nc.L2::cache_hint.b16 %0, [%1], %2;" : "=h"(h) : "l"(a), "l"(pol));
+        w[0] = h;
+    } else if constexpr (B == 4) {
+        w[0] = ldg_hint_u32(a, pol);
+    } else if constexpr (B == 8) {
+        const uint2 x = ldg_hint_u64(a, pol);
+        w[0] = x.x; w[1] = x.y;
+    } else if constexpr (B == 16) {
+        const uint4 x = ldg_hint_u128(a, pol);
+        w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w;
+    } else {
+        static_assert(B == 32, "entry size");
+        const uint4 x = ldg_hint_u128(a, pol), y = ldg_hint_u128(a + 16, pol);
+        w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w; w[4] = y.x; w[5] = y.y; w[6] = y.z; w[7] = y.w;
+    }
+    if constexpr (sizeof(TT) == 4) {
+#pragma unroll
+        for (int f = 0; f < F; ++f) v[f] = __uint_as_float(w[f]);
+    } else if constexpr (F == 1) {
+        v[0] = __half2float(__ushort_as_half(static_cast<unsigned short>(w[0])));
+    } else {
+#pragma unroll
+        for (int f = 0; f < F / 2; ++f) {
+            const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&w[f]));
+            v[2 * f] = x.x; v[2 * f + 1] = x.y;
+        }
+    }
 }
 
 // ---- table entry loads: one vector load per entry where the entry is 2/4/8/16/32 bytes ----------
@@ -332,6 +425,31 @@ __device__ __forceinline__ void red_add_v2(float* p, float a, float b) {
 }
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+__device__ __forceinline__ void red_add_v2_hint(float* p, float a, float b, uint64_t pol) {
+    asm volatile("red.global.add.L2::cache_hint.v2.f32 [%0], {%1, %2}, %3;" ::"l"(p), "f"(a), "f"(b), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void red_add_v4_hint(float* p, float a, float b, float c, float d, uint64_t pol) {
+    asm volatile("red.global.add.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void red_add_f32_hint(float* p, float a, uint64_t pol) {
+    asm volatile("red.global.add.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(p), "f"(a), "l"(pol) : "memory");
+}
+template <int F>
+__device__ __forceinline__ void red_add_entry_hint(float* grad, uint32_t idx, const float (&v)[F], uint64_t pol) {
+    float* dst = grad + static_cast<unsigned long long>(idx) * F;
+    if constexpr (F == 2) {
+        red_add_v2_hint(dst, v[0], v[1], pol);
+    } else if constexpr (F == 4) {
+        red_add_v4_hint(dst, v[0], v[1], v[2], v[3], pol);
+    } else if constexpr (F == 8) {
+        red_add_v4_hint(dst, v[0], v[1], v[2], v[3], pol);
+        red_add_v4_hint(dst + 4, v[4], v[5], v[6], v[7], pol);
+    } else {
+#pragma unroll
+        for (int f = 0; f < F; ++f) red_add_f32_hint(dst + f, v[f], pol);
+    }
 }
 
 template <int F>

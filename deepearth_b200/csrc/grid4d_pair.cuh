@@ -105,6 +105,38 @@ __device__ __forceinline__ void load_coords(const EncodeParams& P, const LevelPa
     }
 }
 
+// same, as a stream: no L1 allocation, evict-first in L2
+template <int D>
+__device__ __forceinline__ void load_coords_stream(const EncodeParams& P, const LevelParams& lv, long long p, float (&x)[D], uint64_t pol) {
+    if (P.vec_coords) {
+        const float4 v = ldg_stream_f4(reinterpret_cast<const float4*>(P.coords) + p, pol);
+#pragma unroll
+        for (int d = 0; d < D; ++d) x[d] = pick4(v, lv.dim[d]);
+    } else {
+        const float* row = P.coords + p * P.coord_stride;
+#pragma unroll
+        for (int d = 0; d < D; ++d) x[d] = ldg_stream_f1(row + lv.dim[d], pol);
+    }
+}
+
+template <int F>
+__device__ __forceinline__ void load_row_stream(const float* src, float (&v)[F], bool vec, uint64_t pol) {
+    if constexpr (F == 2) {
+        if (vec) { const float2 x = ldg_stream_f2(src, pol); v[0] = x.x; v[1] = x.y; return; }
+    } else if constexpr (F == 4 || F == 8) {
+        if (vec) {
+#pragma unroll
+            for (int h = 0; h < F / 4; ++h) {
+                const float4 x = ldg_stream_f4(src + 4 * h, pol);
+                v[4 * h] = x.x; v[4 * h + 1] = x.y; v[4 * h + 2] = x.z; v[4 * h + 3] = x.w;
+            }
+            return;
+        }
+    }
+#pragma unroll
+    for (int f = 0; f < F; ++f) v[f] = ldg_stream_f1(src + f, pol);
+}
+
 // The two lanes of a pair hold identical sums; they split the F features of the level so that
 // consecutive lanes write consecutive floats of the feature row.
 template <int F>

@@ -62,10 +62,11 @@ grid4d_forward_pair_kernel(const __grid_constant__ EncodeParams P) {
     LevelParams lv;
     if (!pair_setup(P, s_lv, t, lv)) return;
     constexpr int J = PairGeom<D>::kCombos;
+    const L2Policies pol = make_l2_policies(P.l2_hints != 0);
 
     for (long long p = t.p0; p < t.p_end; p += t.p_step) {
         float x[D];
-        load_coords<D>(P, lv, p, x);
+        load_coords_stream<D>(P, lv, p, x, pol.stream);
         long long g[D];
         float w[D];
         cell_of<D>(lv, x, g, w);
@@ -79,7 +80,7 @@ grid4d_forward_pair_kernel(const __grid_constant__ EncodeParams P) {
         for (int j = 0; j < J; ++j) idx[j] = ct.index(lv, j);
         float v[J][F];
 #pragma unroll
-        for (int j = 0; j < J; ++j) EntryLoader<TT, F>::load(lv.table, idx[j], v[j]);   // all gathers in flight
+        for (int j = 0; j < J; ++j) load_entry_hint<TT, F>(lv.table, idx[j], v[j], pol.keep);   // all gathers in flight
         float acc[F];
 #pragma unroll
         for (int f = 0; f < F; ++f) acc[f] = 0.0f;
@@ -114,11 +115,12 @@ grid4d_backward_pair_kernel(const __grid_constant__ EncodeParams P) {
     constexpr int J = PairGeom<D>::kCombos;
     const bool vec = P.vec_rows != 0;
     const GradTarget gt = grad_target(lv, blockIdx.x % P.n_tiles);
+    const L2Policies pol = make_l2_policies(P.l2_hints != 0);
 
     float x_n[D], go_n[F];
     if (t.p0 < t.p_end) {
-        load_coords<D>(P, lv, t.p0, x_n);
-        load_row<F>(P.grad_out + t.p0 * P.out_stride + lv.out_col, go_n, vec);
+        load_coords_stream<D>(P, lv, t.p0, x_n, pol.stream);
+        load_row_stream<F>(P.grad_out + t.p0 * P.out_stride + lv.out_col, go_n, vec, pol.stream);
     }
     for (long long p = t.p0; p < t.p_end; p += t.p_step) {
         float x[D], go[F];
@@ -128,8 +130,8 @@ grid4d_backward_pair_kernel(const __grid_constant__ EncodeParams P) {
         for (int f = 0; f < F; ++f) go[f] = go_n[f];
         const long long pn = p + t.p_step;
         if (pn < t.p_end) {
-            load_coords<D>(P, lv, pn, x_n);
-            load_row<F>(P.grad_out + pn * P.out_stride + lv.out_col, go_n, vec);
+            load_coords_stream<D>(P, lv, pn, x_n, pol.stream);
+            load_row_stream<F>(P.grad_out + pn * P.out_stride + lv.out_col, go_n, vec, pol.stream);
         }
         bool has_mask;
         const float m = row_mask(P, lv, p, has_mask);
@@ -146,7 +148,7 @@ grid4d_backward_pair_kernel(const __grid_constant__ EncodeParams P) {
             float val[F];
 #pragma unroll
             for (int f = 0; f < F; ++f) val[f] = __fmul_rn(wk, go[f]);
-            red_add_entry<F>(idx < gt.live ? gt.base : lv.grad, idx, val);
+            red_add_entry_hint<F>(idx < gt.live ? gt.base : lv.grad, idx, val, pol.keep);
         }
     }
 }

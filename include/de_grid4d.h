@@ -55,7 +55,8 @@ extern "C" {
 /* opt-in code paths that measured SLOWER than the default on B200 (profiles/r01c_ab_matrix.txt); kept for A/B runs */
 #define DE_FLAG_STAGED_BWD 0x100u  /* backward: stage coordinates + gradient rows through TMA bulk copies + shared memory */
 #define DE_FLAG_SMEM_COARSE 0x200u /* forward: serve dense coarse levels from shared-memory copies of their tables      */
-#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE)
+#define DE_FLAG_NO_L2_HINTS 0x400u /* A/B: plain loads / reductions instead of evict_last tables + evict_first streams */
+#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE | DE_FLAG_NO_L2_HINTS)
 
 #define DE_MAX_DIMS 4
 #define DE_MAX_LEVELS_PER_CALL 256
