@@ -350,6 +350,12 @@ def run_gpu_arm(args, wl):
     job.plan.extra_flags = args.flags
     job.use_replicas = not args.no_replicas
 
+    sync = None
+    if world > 1 and not args.no_overlap:
+        from deepearth_b200.distributed import GradSync
+        sync = GradSync(average=False, chunks=args.sync_chunks)
+        job.enc.enable_grad_sync(average=True, chunks=args.sync_chunks)     # the e2e (autograd) path
+
     def step(ev=None):
         job.flat_grad.zero_()
         if ev:
@@ -366,13 +372,21 @@ def run_gpu_arm(args, wl):
             job.head_backward()
         if ev:
             ev[1].record()
-        job.backward()
-        if ev:
-            ev[2].record()
-        if world > 1:
-            dist.all_reduce(job.flat_grad)
+        if sync is not None:
+            # backward + all-reduce overlapped (distributed.GradSync): kernels_ms.allreduce is the exposed tail only
+            sync.backward(job.plan.specs, job.coords, job.gout, job.flat_grad, job.plan.grad_offsets, job.F, job.linear,
+                          levels_per_group=job.plan.bwd_levels_per_group, extra_flags=job.plan.extra_flags)
             if ev:
+                ev[2].record()
                 ev[3].record()
+        else:
+            job.backward()
+            if ev:
+                ev[2].record()
+            if world > 1:
+                dist.all_reduce(job.flat_grad)
+                if ev:
+                    ev[3].record()
 
     def barrier():
         if world > 1:
@@ -459,7 +473,7 @@ def run_gpu_arm(args, wl):
             xyzt = host.to(device, non_blocking=True)
             res = job.enc.encode_features(xyzt)
             res.backward(job.gout)
-        if world > 1:
+        if world > 1 and sync is None:
             from deepearth_b200.distributed import allreduce_table_grads
             allreduce_table_grads(job.weights, average=True)
         chk = Fn.sum_f32(res.detach())
@@ -502,7 +516,8 @@ def run_gpu_arm(args, wl):
                        "table_size": wl["T"], "interpolation": "linear" if job.linear else "nearest",
                        "l2_policy": "inputs larger than L2 (coords+grad_out+out > 4 GiB per step); no flush",
                        "l2_fetch_granularity": _gran.value,
-                       "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"},
+                       "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"
+                                      + (f" overlapped with the backward in {args.sync_chunks} level runs" if sync is not None else "")},
             "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms, **(head_ms or {})},
             "roofline": {"bound": "hbm", "kernel": f"grid4d_{dom}_kernel", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
@@ -535,6 +550,8 @@ def main():
     ap.add_argument("--levels-per-group", type=int, default=0)
     ap.add_argument("--bwd-levels-per-group", type=int, default=0)
     ap.add_argument("--coords", default="", choices=["", "uniform", "florida"], help="override the workload's coordinate distribution")
+    ap.add_argument("--no-overlap", action="store_true", help="N>1: one all-reduce after the backward instead of the overlapped slices")
+    ap.add_argument("--sync-chunks", type=int, default=4, help="N>1: level runs the backward / all-reduce overlap is cut into")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-replicas", action="store_true", help="backward without gradient replicas for contended coarse levels (A/B)")
     ap.add_argument("--flags", type=lambda v: int(v, 0), default=0, help="DE_FLAG_* opt-in paths (0x100 TMA-staged backward, 0x200 shared-memory coarse forward)")

@@ -53,3 +53,56 @@ def allreduce_table_grads(params: Iterable[torch.nn.Parameter], group: Optional[
             buf.div_(world)
         works.append(dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group, async_op=async_op))
     return works if async_op else None
+
+
+class GradSync:
+    """Overlaps the table-gradient all-reduce with the backward scatter.
+
+    The backward kernel walks level groups in order and each level's gradient is a contiguous slice of
+    the flat buffer, so the call is cut into ``chunks`` consecutive runs of levels: as soon as one run's
+    launch is queued, its slice is all-reduced on a side stream while the next run's reductions execute.
+    Only the last slice's collective is exposed.  Semantics are DDP's (mean over ranks when ``average``).
+    """
+
+    def __init__(self, group: Optional[dist.ProcessGroup] = None, average: bool = True, chunks: int = 4):
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed is not initialised")
+        self.group = group
+        self.average = bool(average)
+        self.chunks = max(1, int(chunks))
+        self.world = dist.get_world_size(group)
+        self._stream = None
+
+    def stream(self, device) -> torch.cuda.Stream:
+        if self._stream is None or self._stream.device != device:
+            self._stream = torch.cuda.Stream(device=device)
+        return self._stream
+
+    def level_runs(self, n_levels: int) -> List[Tuple[int, int]]:
+        k = min(self.chunks, n_levels)
+        return [shard_bounds(n_levels, i, k) for i in range(k)]
+
+    def backward(self, specs, coords, grad_out, flat: torch.Tensor, grad_offsets, n_features: int, linear: bool,
+                 mask_a=None, mask_b=None, levels_per_group: int = 0, extra_flags: int = 0) -> None:
+        """flat (zeroed) <- all-reduced table gradients of this rank's points."""
+        from . import functional as Fn
+        dev = flat.device
+        main = torch.cuda.current_stream(dev)
+        side = self.stream(dev)
+        base = flat.data_ptr()
+        ends = list(grad_offsets[1:]) + [flat.numel()]
+        for b, e in self.level_runs(len(specs)):
+            Fn.encode_backward(specs[b:e], coords, grad_out, [base + 4 * o for o in grad_offsets[b:e]], n_features,
+                               linear, mask_a, mask_b, levels_per_group=levels_per_group, extra_flags=extra_flags)
+            ready = torch.cuda.Event()
+            ready.record(main)
+            side.wait_event(ready)
+            piece = flat[grad_offsets[b]:ends[e - 1]]
+            with torch.cuda.stream(side):
+                if self.average:
+                    piece.div_(self.world)
+                dist.all_reduce(piece, op=dist.ReduceOp.SUM, group=self.group)
+        done = torch.cuda.Event()
+        done.record(side)
+        main.wait_event(done)
+        flat.record_stream(side)

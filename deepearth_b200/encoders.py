@@ -72,6 +72,7 @@ class Grid4DEncoder(nn.Module):
 
         self.feature_dim = sum(e.output_dim for e in self._encoders)
         self._fused_head = None   # FusedProjection | False, resolved on first forward
+        self._grad_sync = None
         self.projection = nn.Sequential(
             nn.Linear(self.feature_dim, config.hidden_dim),
             nn.LayerNorm(config.hidden_dim),
@@ -86,9 +87,21 @@ class Grid4DEncoder(nn.Module):
             specs += enc.level_specs(out_col0=col, mask_id=mid)
             col += enc.output_dim
         e0 = self._encoders[0]
-        return EncodePlan(specs, e0.n_features_per_level, self.feature_dim, e0.interpolation == "linear",
+        plan = EncodePlan(specs, e0.n_features_per_level, self.feature_dim, e0.interpolation == "linear",
                           e0.table_dtype, e0.table_scale, e0.levels_per_group, e0.bwd_levels_per_group,
                           e0.extra_flags)
+        plan.grad_sync = self._grad_sync
+        return plan
+
+    def enable_grad_sync(self, group=None, average: bool = True, chunks: int = 4) -> None:
+        """Data parallel without DDP around the tables: the backward all-reduces the flat table-gradient
+        buffer itself, slice by slice on a side stream, overlapped with the scatter (distributed.GradSync).
+        Replaces what DDP does for these parameters in hpc/train_distrbuted.py:499-504."""
+        from .distributed import GradSync
+        self._grad_sync = GradSync(group, average, chunks)
+
+    def disable_grad_sync(self) -> None:
+        self._grad_sync = None
 
     def encode_features(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,
                         temporal_mask: Optional[torch.Tensor] = None) -> torch.Tensor:

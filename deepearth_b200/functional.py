@@ -218,6 +218,7 @@ class EncodePlan:
                  levels_per_group: int = 0, bwd_levels_per_group: int = 0, extra_flags: int = 0):
         self.specs = list(specs)
         self.extra_flags = int(extra_flags)   # DE_FLAG_* A/B switches (include/de_grid4d.h)
+        self.grad_sync = None                 # distributed.GradSync: overlapped all-reduce inside backward
         self.n_features = int(n_features)
         self.out_cols = int(out_cols)
         self.linear = bool(linear)
@@ -264,9 +265,15 @@ class Grid4DFunction(torch.autograd.Function):
         coords, mask_a, mask_b = ctx.saved_tensors
         flat = torch.zeros(plan.grad_numel, dtype=torch.float32, device=grad_out.device)
         base = flat.data_ptr()
-        encode_backward(plan.specs, coords, grad_out, [base + 4 * o for o in plan.grad_offsets],
-                        plan.n_features, plan.linear, mask_a, mask_b,
-                        levels_per_group=plan.bwd_levels_per_group, extra_flags=plan.extra_flags)
+        if plan.grad_sync is not None:
+            # data parallel: all-reduce slices of the flat buffer on a side stream while later level runs scatter
+            plan.grad_sync.backward(plan.specs, coords, grad_out, flat, plan.grad_offsets, plan.n_features,
+                                    plan.linear, mask_a, mask_b, levels_per_group=plan.bwd_levels_per_group,
+                                    extra_flags=plan.extra_flags)
+        else:
+            encode_backward(plan.specs, coords, grad_out, [base + 4 * o for o in plan.grad_offsets],
+                            plan.n_features, plan.linear, mask_a, mask_b,
+                            levels_per_group=plan.bwd_levels_per_group, extra_flags=plan.extra_flags)
         grads = []
         for i, shape in enumerate(ctx.weight_shapes):
             o = plan.grad_offsets[i]

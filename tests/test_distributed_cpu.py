@@ -45,6 +45,10 @@ def _worker(rank, world, port, q):
         allreduce_table_grads([p1, p2], average=True)
         want = torch.arange(24, dtype=torch.float32) * (sum(range(1, world + 1)) / world)
         ok = torch.allclose(torch.cat([p1.grad.flatten(), p2.grad.flatten()]), want)
+        # level runs of the overlapped backward / all-reduce: contiguous, ordered, covering
+        from deepearth_b200.distributed import GradSync
+        runs = GradSync(chunks=4).level_runs(64)
+        ok = ok and runs == [(0, 16), (16, 32), (32, 48), (48, 64)] and GradSync(chunks=8).level_runs(3) == [(0, 1), (1, 2), (2, 3)]
         b, e = shard_bounds(1000, rank, world)
         tot = torch.tensor([e - b])
         dist.all_reduce(tot)
