@@ -48,7 +48,7 @@ WORKLOADS = {
                desc="configs[2]: 4 grids x 16 levels x 2 feat, T=2^22/level (HBM resident), 2^24 Florida-clustered points/GPU"),
     "c5": dict(mode="decomposed", T=2 ** 22, log2_points=24, coords="florida", table_dtype="float16", head=True,
                desc="configs[4]: geo2xyz prologue + 4 grids x 16 levels x 2 feat (T=2^22) + Linear-LayerNorm-GELU-Linear 64-wide head "
-                    "(tcgen05 kernel forward, cuBLAS recompute backward), 2^24 Florida-clustered geodetic points/GPU"),
+                    "(tcgen05 kernels forward and backward), 2^24 Florida-clustered geodetic points/GPU"),
     "c1r": dict(mode="reference", T=2 ** 19, log2_points=22, coords="uniform", table_dtype="float32",
                 desc="reference Grid4DEncoder geometry (xyz L16 T=2^19 + t L8 T=2^17, nearest, fp32 tables), 2^22 points/GPU"),
 }
@@ -216,6 +216,7 @@ class Job:
         self.bytes_fwd, self.bytes_bwd = algorithmic_bytes_per_point(len(self.plan.specs), corners, self.F, tb)
         self.out_scale = 1.0 / self.plan.table_scale if self.plan.table_scale != 1.0 else 1.0
         self.use_replicas = True
+        self.head_bwd = "tcgen05"
 
     def forward(self):
         from deepearth_b200 import functional as Fn
@@ -237,7 +238,13 @@ class Job:
         self.y = self.head.fused(self.out)
 
     def head_backward(self):
-        """Gradients of the head: recompute through the fp32 modules (cuBLAS), as the autograd path does."""
+        """Gradients of the head: the tcgen05 backward kernel (default) or, for A/B, a recompute through the fp32
+        modules (cuBLAS + eager LayerNorm / GELU), which is what autograd does with fused_backward=False."""
+        if self.head_bwd == "tcgen05":
+            g = self.head.backward_fused(self.out, self.gy)
+            self.gout = g.pop("x")
+            self.head_grads = g
+            return
         with torch.enable_grad():
             xd = self.out.detach().requires_grad_(True)
             y = self.enc.projection(xd)
@@ -254,7 +261,7 @@ class Job:
                 runs += 1
                 prev, cnt = len(s.dims), 0
             cnt += 1
-        return 2 * runs + (2 if self.head is not None else 0)     # + prologue + head kernels (cuBLAS launches not counted)
+        return 2 * runs + (3 if self.head is not None else 0)     # + prologue + head forward + head backward kernels
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -349,6 +356,9 @@ def run_gpu_arm(args, wl):
         job.plan.bwd_levels_per_group = args.bwd_levels_per_group
     job.plan.extra_flags = args.flags
     job.use_replicas = not args.no_replicas
+    job.head_bwd = args.head_bwd
+    if job.head is not None:
+        job.head.fused_backward = args.head_bwd == "tcgen05"
 
     sync = None
     if world > 1 and not args.no_overlap:
@@ -433,7 +443,7 @@ def run_gpu_arm(args, wl):
     if job.head is not None:
         fwd_ms = float(np.mean([e[0].elapsed_time(e[4]) for e in evs]))        # prologue + encode
         head_ms = {"head_forward_tcgen05": float(np.mean([e[4].elapsed_time(e[5]) for e in evs])),
-                   "head_backward_cublas": float(np.mean([e[5].elapsed_time(e[1]) for e in evs]))}
+                   f"head_backward_{args.head_bwd}": float(np.mean([e[5].elapsed_time(e[1]) for e in evs]))}
     else:
         fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
     bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
@@ -552,6 +562,7 @@ def main():
     ap.add_argument("--coords", default="", choices=["", "uniform", "florida"], help="override the workload's coordinate distribution")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: one all-reduce after the backward instead of the overlapped slices")
     ap.add_argument("--sync-chunks", type=int, default=4, help="N>1: level runs the backward / all-reduce overlap is cut into")
+    ap.add_argument("--head-bwd", default="tcgen05", choices=["tcgen05", "cublas"], help="c5: head backward kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-replicas", action="store_true", help="backward without gradient replicas for contended coarse levels (A/B)")
     ap.add_argument("--flags", type=lambda v: int(v, 0), default=0, help="DE_FLAG_* opt-in paths (0x100 TMA-staged backward, 0x200 shared-memory coarse forward)")

@@ -63,6 +63,9 @@ SIGNATURES = {
     "de_mlp_head_supported": (c_int, [c_int, c_int, c_int]),
     "de_mlp_head_forward": (c_int, [c_void_p, c_i64, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
                                     c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_i64, c_void_p]),
+    "de_mlp_head_backward": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_i64, c_i64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_float, c_int, c_int, c_int, c_int, c_void_p, c_i64, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "de_geo_bbox": (c_int, [c_void_p, c_int, c_void_p, c_i64, c_void_p]),
     "de_set_l2_fetch_granularity": (c_int, [c_int]),
     "de_get_l2_fetch_granularity": (c_int, [ctypes.POINTER(c_int)]),

@@ -583,6 +583,36 @@ DE_API int de_mlp_head_forward(const float* x, int64_t n_points, int in_dim, int
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "mlp_head launch");
 }
 
+DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_points, int in_dim, int64_t x_stride,
+                         int64_t gy_stride, const void* w1_bf16, const void* w1t_bf16, const void* w2t_bf16,
+                         const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps, int layernorm,
+                         int activation, int hidden, int out_dim, float* grad_x, int64_t gx_stride, float* grad_w1,
+                         float* grad_b1, float* grad_gamma, float* grad_beta, float* grad_w2, float* grad_b2,
+                         void* stream) {
+    if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (n_points == 0) return DE_OK;
+    if (!x || !grad_y || !w1_bf16 || !w1t_bf16 || !w2t_bf16 || !grad_x || !grad_w1 || !grad_w2)
+        return fail(DE_EINVAL, "mlp_head_backward: NULL pointer");
+    if (!de::mlp_head_supported(in_dim, hidden, out_dim))
+        return fail(DE_EUNSUPPORTED, "mlp_head_backward: in_dim=%d hidden=%d out_dim=%d", in_dim, hidden, out_dim);
+    if (activation < 0 || activation > 2) return fail(DE_EINVAL, "mlp_head_backward: activation=%d", activation);
+    if (x_stride < in_dim || gx_stride < in_dim || gy_stride < out_dim) return fail(DE_EINVAL, "mlp_head_backward: row stride shorter than the row");
+    const void* aligned[] = {x, grad_y, grad_x, w1_bf16, w1t_bf16, w2t_bf16};
+    for (const void* q : aligned)
+        if (reinterpret_cast<uintptr_t>(q) % 16) return fail(DE_EALIGN, "mlp_head_backward: pointer not 16-byte aligned");
+    if (x_stride % 4 || gy_stride % 4 || gx_stride % 4) return fail(DE_EALIGN, "mlp_head_backward: row strides must be multiples of 4 floats");
+    de::MlpHeadBwdParams P{};
+    P.x = x; P.gy = grad_y; P.n = n_points; P.x_stride = x_stride; P.gy_stride = gy_stride;
+    P.w1 = w1_bf16; P.w1t = w1t_bf16; P.w2t = w2t_bf16; P.b1 = b1; P.ln_gamma = ln_gamma; P.ln_beta = ln_beta;
+    P.ln_eps = ln_eps; P.layernorm = layernorm ? 1 : 0; P.activation = activation;
+    P.dx = grad_x; P.dx_stride = gx_stride; P.dw1 = grad_w1; P.db1 = grad_b1; P.dgamma = grad_gamma; P.dbeta = grad_beta;
+    P.dw2 = grad_w2; P.db2 = grad_b2;
+    int dev = 0, n_sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = de::launch_mlp_head_bwd(P, in_dim, n_sms, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "mlp_head_backward launch");
+}
+
 DE_API int de_set_l2_fetch_granularity(int bytes) {
     if (bytes != 32 && bytes != 64 && bytes != 128) return fail(DE_EINVAL, "l2 fetch granularity must be 32, 64 or 128, got %d", bytes);
     cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, static_cast<size_t>(bytes));

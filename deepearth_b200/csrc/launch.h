@@ -64,7 +64,32 @@ struct MlpHeadParams {
     long long y_stride;
     int n_tiles;
 };
+struct MlpHeadBwdParams {
+    const float* x;               // (n, in_dim) fp32 features (forward input)
+    const float* gy;              // (n, 64) fp32 gradient of the head output
+    long long n;
+    long long x_stride, gy_stride;
+    const void* w1;               // (64, in_dim) bf16
+    const void* w1t;              // (in_dim, 64) bf16 = W1 transposed
+    const void* w2t;              // (64 hidden, 64 out) bf16 = W2 transposed
+    const float* b1;
+    const float* ln_gamma;
+    const float* ln_beta;
+    float ln_eps;
+    int layernorm;
+    int activation;
+    float* dx;                    // (n, in_dim) fp32 out
+    long long dx_stride;
+    float* dw1;                   // (64, in_dim) fp32, accumulated (caller zeroes)
+    float* db1;                   // (64,) accumulated, or NULL
+    float* dgamma;                // (64,) accumulated, or NULL
+    float* dbeta;                 // (64,) accumulated, or NULL
+    float* dw2;                   // (64, 64) accumulated
+    float* db2;                   // (64,) accumulated, or NULL
+    int n_tiles;
+};
 bool mlp_head_supported(int in_dim, int hidden, int out_dim);
+cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s);
 
 cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,

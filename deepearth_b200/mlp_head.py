@@ -4,8 +4,9 @@ Mirrors ``Grid4DEncoder.projection`` (/root/reference/models/encoders.py:47-52).
 ordinary ``nn.Sequential`` (same state-dict keys as the reference: ``projection.0.weight`` ...); this module
 only changes how the forward is computed: ``de_mlp_head_forward`` (deepearth_b200/csrc/mlp_head.cu) runs both
 GEMMs as bf16 ``tcgen05.mma`` with fp32 accumulators in tensor memory, and the hidden row never leaves the SM.
-The backward pass recomputes through the fp32 PyTorch modules (cuBLAS): training keeps full-precision
-gradients, inference and the forward half of training use the fused kernel.
+The backward pass is a second tcgen05 kernel (``de_mlp_head_backward``, csrc/mlp_head_bwd.cu: hidden-row recompute,
+LayerNorm / activation backward in registers, weight gradients accumulated in tensor memory); with
+``fused_backward=False`` it recomputes through the fp32 PyTorch modules (cuBLAS) instead.
 """
 from __future__ import annotations
 
@@ -55,6 +56,37 @@ def mlp_head_forward(x: torch.Tensor, w1_bf16: torch.Tensor, b1: Optional[torch.
     return out
 
 
+def mlp_head_backward(x: torch.Tensor, grad_y: torch.Tensor, w1_bf16: torch.Tensor, w1t_bf16: torch.Tensor,
+                      w2t_bf16: torch.Tensor, b1, ln_gamma, ln_beta, ln_eps: float, layernorm: bool, activation: str,
+                      has_b2: bool = True):
+    """One tcgen05 kernel: (grad_x, grad_w1, grad_b1, grad_gamma, grad_beta, grad_w2, grad_b2), fp32."""
+    _require_cuda(x, "x")
+    _require_cuda(grad_y, "grad_y")
+    n, in_dim = x.shape
+    hidden = w1_bf16.shape[0]
+    if x.stride(1) != 1 or x.stride(0) % 4 or x.data_ptr() % 16:
+        x = x.contiguous()
+    grad_y = grad_y.float()
+    if grad_y.stride(1) != 1 or grad_y.stride(0) % 4 or grad_y.data_ptr() % 16:
+        grad_y = grad_y.contiguous()
+    dev = x.device
+    gx = torch.empty((n, in_dim), dtype=torch.float32, device=dev)
+    # one zeroed buffer for every accumulated gradient: w1 | w2 | b1 | gamma | beta | b2
+    sizes = [hidden * in_dim, hidden * hidden, hidden, hidden, hidden, hidden]
+    flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+    gw1, gw2, gb1, gg, gbeta, gb2 = torch.split(flat, sizes)
+    if n:
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            rc = lib.de_mlp_head_backward(_ptr(x), _ptr(grad_y), n, in_dim, x.stride(0), grad_y.stride(0), _ptr(w1_bf16),
+                                          _ptr(w1t_bf16), _ptr(w2t_bf16), _ptr(b1), _ptr(ln_gamma), _ptr(ln_beta),
+                                          float(ln_eps), int(bool(layernorm)), _ACT[activation], hidden, hidden,
+                                          _ptr(gx), gx.stride(0), _ptr(gw1), _ptr(gb1), _ptr(gg), _ptr(gbeta),
+                                          _ptr(gw2), _ptr(gb2), _stream_ptr(dev))
+        _lib.check(rc, "de_mlp_head_backward")
+    return gx, gw1.view(hidden, in_dim), gb1, gg, gbeta, gw2.view(hidden, hidden), gb2
+
+
 class _HeadFunction(torch.autograd.Function):
     """forward = fused tensor-core kernel; backward = recompute through the fp32 modules (cuBLAS)."""
 
@@ -69,6 +101,11 @@ class _HeadFunction(torch.autograd.Function):
         (x,) = ctx.saved_tensors
         head = ctx.head
         params = list(head.seq.parameters())
+        if head.fused_backward:
+            by_id = head.backward_fused(x, grad_y)
+            gx = by_id.pop("x") if ctx.needs_input_grad[0] else None
+            gp = [by_id.get(id(p)) if ctx.needs_input_grad[2 + i] else None for i, p in enumerate(params)]
+            return (gx, None, *gp)
         with torch.enable_grad():
             xd = x.detach().requires_grad_(ctx.needs_input_grad[0])
             y = head.seq(xd)
@@ -84,7 +121,8 @@ class FusedProjection:
     fused kernel.  Holds no parameters of its own: bf16 copies of the Linear weights are re-derived whenever the
     fp32 parameters change."""
 
-    def __init__(self, seq: nn.Sequential):
+    def __init__(self, seq: nn.Sequential, fused_backward: bool = True):
+        self.fused_backward = bool(fused_backward)   # False: gradients by fp32 recompute through the modules (cuBLAS)
         mods = list(seq)
         if not (isinstance(mods[0], nn.Linear) and isinstance(mods[-1], nn.Linear)):
             raise TypeError("expected Linear ... Linear")
@@ -104,7 +142,7 @@ class FusedProjection:
         else:
             raise TypeError(f"unsupported activation {acts[0]!r}")
         self._key = None
-        self._w1 = self._w2 = None
+        self._w1 = self._w2 = self._w1t = self._w2t = None
 
     def supported(self) -> bool:
         return mlp_head_supported(self.lin1.in_features, self.lin1.out_features, self.lin2.out_features)
@@ -115,8 +153,27 @@ class FusedProjection:
             with torch.no_grad():
                 self._w1 = self.lin1.weight.detach().to(torch.bfloat16).contiguous()
                 self._w2 = self.lin2.weight.detach().to(torch.bfloat16).contiguous()
+                self._w1t = self._w1.t().contiguous()
+                self._w2t = self._w2.t().contiguous()
             self._key = key
         return self._w1, self._w2
+
+    def backward_fused(self, x: torch.Tensor, grad_y: torch.Tensor) -> dict:
+        """Gradients by the tcgen05 backward kernel, keyed by id(parameter) (+ "x")."""
+        w1, _ = self._weights()
+        n = self.norm
+        gx, gw1, gb1, gg, gbeta, gw2, gb2 = mlp_head_backward(
+            x, grad_y, w1, self._w1t, self._w2t, self.lin1.bias, n.weight if n is not None else None,
+            n.bias if n is not None else None, n.eps if n is not None else 1e-5, n is not None, self.activation)
+        out = {"x": gx, id(self.lin1.weight): gw1, id(self.lin2.weight): gw2}
+        if self.lin1.bias is not None:
+            out[id(self.lin1.bias)] = gb1
+        if self.lin2.bias is not None:
+            out[id(self.lin2.bias)] = gb2
+        if n is not None and n.weight is not None:
+            out[id(n.weight)] = gg
+            out[id(n.bias)] = gbeta
+        return out
 
     def fused(self, x: torch.Tensor) -> torch.Tensor:
         w1, w2 = self._weights()

@@ -190,6 +190,21 @@ DE_API int de_mlp_head_forward(const float* x, int64_t n_points, int in_dim, int
                         int hidden, int out_dim, float* y, int64_t y_stride, void* stream);
 
 /*
+ * Backward of the same head, one tcgen05 kernel: recomputes the hidden row, returns grad_x (n, in_dim) -- the
+ * gradient the hash-grid backward consumes -- and ACCUMULATES the parameter gradients (caller zeroes them):
+ * grad_w1 (64, in_dim), grad_b1, grad_gamma, grad_beta, grad_w2 (64, 64), grad_b2 (each (64,), any may be NULL
+ * except the two weight gradients).  w1t_bf16 = W1 transposed (in_dim, 64), w2t_bf16 = W2 transposed (hidden, out).
+ * Replaces autograd's LinearBackward / GeluBackward / NativeLayerNormBackward chain for models/encoders.py:47-52.
+ */
+DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_points, int in_dim,
+                         int64_t x_stride, int64_t gy_stride,
+                         const void* w1_bf16, const void* w1t_bf16, const void* w2t_bf16,
+                         const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
+                         int layernorm, int activation, int hidden, int out_dim,
+                         float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1,
+                         float* grad_gamma, float* grad_beta, float* grad_w2, float* grad_b2, void* stream);
+
+/*
  * Device-wide L2 fetch granularity hint (cudaLimitMaxL2FetchGranularity) of the current device: 32, 64 or
  * 128 bytes.  The encoder reads gradient rows in pieces of G*F*4 bytes per level group; with the
  * default 128 B granularity the L2 over-fetches the rest of each line from HBM.  Application-level

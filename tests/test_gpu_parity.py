@@ -512,9 +512,10 @@ def test_mlp_head_vs_torch(dev, in_dim, layernorm, act):
         scale = float(want.abs().max())
         assert float((got - want).abs().max()) <= 2e-3 * scale, (n, float((got - want).abs().max()), scale)
         assert float((got - full).abs().max()) <= 3e-2 * scale      # bf16 operands vs the fp32 module
-    # training: forward through the kernel, gradients through the fp32 recompute
+    # training, fp32 recompute backward: forward through the kernel, exact module gradients
+    head_r = FusedProjection(seq, fused_backward=False)
     x = torch.randn((777, in_dim), device=dev, generator=g, requires_grad=True)
-    y = head(x)
+    y = head_r(x)
     gy = torch.randn(y.shape, device=dev, generator=g)
     y.backward(gy)
     gx, gw = x.grad.clone(), seq[0].weight.grad.clone()
@@ -522,6 +523,31 @@ def test_mlp_head_vs_torch(dev, in_dim, layernorm, act):
     seq.zero_grad()
     seq(x).backward(gy)
     assert torch.allclose(gx, x.grad, rtol=1e-5, atol=1e-6) and torch.allclose(gw, seq[0].weight.grad, rtol=1e-5, atol=1e-6)
+    # training, tcgen05 backward kernel (bf16 operands, fp32 accumulation) against autograd through an fp32 model
+    # that sees the same bf16-rounded operands in its forward (straight-through rounding): the recomputed hidden
+    # row -- and with it every ReLU mask / GELU slope -- is then the kernel's own, up to accumulation order
+    ste = lambda t: t + (t.to(torch.bfloat16).to(torch.float32) - t).detach()
+
+    def ref_model(x):
+        h = torch.nn.functional.linear(ste(x), ste(seq[0].weight), seq[0].bias)
+        for m in list(seq)[1:-1]:
+            h = m(h)
+        return torch.nn.functional.linear(ste(h), ste(seq[-1].weight), seq[-1].bias)
+
+    for n in (777, 128 * 148 * 3 + 5):
+        x = torch.randn((n, in_dim), device=dev, generator=g, requires_grad=True)
+        gy = torch.randn((n, 64), device=dev, generator=g)
+        seq.zero_grad()
+        ref_model(x).backward(gy)
+        want = {"x": x.grad.clone(), **{k: p.grad.clone() for k, p in seq.named_parameters()}}
+        x.grad = None
+        seq.zero_grad()
+        head(x).backward(gy)
+        got = {"x": x.grad, **{k: p.grad for k, p in seq.named_parameters()}}
+        for k, w in want.items():
+            assert got[k] is not None, k
+            err = float((got[k] - w).abs().max()) / max(float(w.abs().max()), 1e-20)
+            assert err <= 4e-2, (n, k, err)
 
 
 def test_grid4d_encoder_fused_head(dev):
