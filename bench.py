@@ -460,28 +460,47 @@ def run_gpu_arm(args, wl):
         host_geo, host_t = job.geo.cpu().pin_memory(), job.t.cpu().pin_memory()
         h2d_bytes = host_geo.numel() * 8 + host_t.numel() * 8
         params = job.weights + job.head_params
-        api = "GeospatialConverter.geodetic_to_xyzt_norm + Grid4DEncoder.forward (tcgen05 head) + autograd backward, pinned host geodetic points -> device each step"
+        api = "GeospatialConverter.geodetic_to_xyzt_norm + Grid4DEncoder.forward (tcgen05 head) + autograd backward; pinned host geodetic points -> device every step (copy of step i+1 overlaps step i)"
         job.gout = job.head_grads = job.y = None
     else:
         host = job.coords.cpu().pin_memory()
         h2d_bytes = host.numel() * 4
         params = job.weights
-        api = "Grid4DEncoder.encode_features + autograd backward, pinned host xyzt -> device each step"
+        api = "Grid4DEncoder.encode_features + autograd backward; pinned host xyzt -> device every step (copy of step i+1 overlaps step i)"
     del job.out      # the module allocates its own output
     torch.cuda.empty_cache()
+
+    # Input pipeline of the e2e loop: every step's inputs come from pinned host memory; the copy for step i+1 is
+    # issued on a copy stream at the start of step i (what a pinned-memory DataLoader with non_blocking copies
+    # does), so K timed steps issue K host->device copies inside the timed region.
+    copy_stream = torch.cuda.Stream(device=device)
+
+    def fetch():
+        with torch.cuda.stream(copy_stream):
+            if job.head is not None:
+                bufs = (host_geo.to(device, non_blocking=True), host_t.to(device, non_blocking=True))
+            else:
+                bufs = (host.to(device, non_blocking=True),)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return bufs, ev
+
+    pending = [fetch()]
 
     def e2e_step():
         for p in params:
             p.grad = None
+        bufs, ev = pending.pop()
+        pending.append(fetch())                      # next step's inputs travel while this step computes
+        torch.cuda.current_stream(device).wait_event(ev)
+        for b in bufs:
+            b.record_stream(torch.cuda.current_stream(device))
         if job.head is not None:
-            geo = host_geo.to(device, non_blocking=True)
-            tt = host_t.to(device, non_blocking=True)
-            xyzt = job.conv.geodetic_to_xyzt_norm(geo, tt)
+            xyzt = job.conv.geodetic_to_xyzt_norm(bufs[0], bufs[1])
             res = job.enc(xyzt)
             res.backward(job.gy)
         else:
-            xyzt = host.to(device, non_blocking=True)
-            res = job.enc.encode_features(xyzt)
+            res = job.enc.encode_features(bufs[0])
             res.backward(job.gout)
         if world > 1 and sync is None:
             from deepearth_b200.distributed import allreduce_table_grads

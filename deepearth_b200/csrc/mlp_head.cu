@@ -78,19 +78,32 @@ mlp_head_kernel(const __grid_constant__ MlpHeadParams P) {
 
         // ---- 1. features -> bf16 A tile: 8 consecutive lanes take 8 consecutive rows of one 16-byte chunk
         //         column (conflict-free shared stores), 4 chunk columns per request (128 B global segments)
-        // each warp fills its 32 rows: 4 groups of 8 rows x (K1/8) chunks; chunk c -> (row % 8 = c % 8, k8)
-#pragma unroll 2
-        for (int c = lane; c < 4 * K1; c += 32) {
-            const int rg = c / K1, rem = c % K1;
-            const int r = warp * 32 + rg * 8 + (rem & 7);
-            const int k8 = rem >> 3;
-            uint4 packed = make_uint4(0u, 0u, 0u, 0u);
-            if (p0 + r < P.n) {
-                const float4* src = reinterpret_cast<const float4*>(P.x + (p0 + r) * P.x_stride + k8 * 8);
-                const float4 a = __ldcs(src), b = __ldcs(src + 1);
-                packed = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w));
+        // each warp fills its 32 rows: 4 groups of 8 rows x (K1/8) chunks; chunk c -> (row % 8 = c % 8, k8).
+        // ALL of the tile's loads are issued before the first conversion: 64 B x (K1/8) per thread in flight
+        // (the tile is latency-bound otherwise: ncu r01d showed 1.7 TB/s with two chunks in flight)
+        {
+            constexpr int kIt = (4 * K1) / 32;
+            float4 va[kIt], vb[kIt];
+#pragma unroll
+            for (int it = 0; it < kIt; ++it) {
+                const int c = lane + 32 * it;
+                const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
+                const int k8 = (c % K1) >> 3;
+                va[it] = vb[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p0 + r < P.n) {
+                    const float4* src = reinterpret_cast<const float4*>(P.x + (p0 + r) * P.x_stride + k8 * 8);
+                    va[it] = __ldcs(src);
+                    vb[it] = __ldcs(src + 1);
+                }
             }
-            *reinterpret_cast<uint4*>(sA1 + canon_chunk_offset(r, k8, K1)) = packed;
+#pragma unroll
+            for (int it = 0; it < kIt; ++it) {
+                const int c = lane + 32 * it;
+                const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
+                const int k8 = (c % K1) >> 3;
+                *reinterpret_cast<uint4*>(sA1 + canon_chunk_offset(r, k8, K1)) =
+                    make_uint4(pack_bf16(va[it].x, va[it].y), pack_bf16(va[it].z, va[it].w), pack_bf16(vb[it].x, vb[it].y), pack_bf16(vb[it].z, vb[it].w));
+            }
         }
         fence_async_smem();          // generic-proxy writes -> visible to the tensor core's async proxy
         tc_fence_before();           // orders this thread's earlier tcgen05.ld (previous tile) before the barrier

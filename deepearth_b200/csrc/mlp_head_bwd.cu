@@ -68,19 +68,39 @@ __device__ __forceinline__ void red_f32(float* p, float v) {
 // fp32 rows of a (n, KT) matrix -> bf16 tile, K-major at `dst` and transposed (feature-major, point columns) at
 // `dst_t` rows [t_row0, t_row0 + KT).  Rows >= n are zero.  Warp w fills tile rows 32w .. 32w+31.
 template <int KT>
-__device__ __forceinline__ void load_tile(const float* src, long long stride, long long p0, long long n,
-                                          unsigned char* dst, unsigned char* dst_t, int t_row0, int warp, int lane) {
-#pragma unroll 2
-    for (int c = lane; c < 4 * KT; c += 32) {
-        const int rg = c / KT, rem = c % KT;
-        const int r = warp * 32 + rg * 8 + (rem & 7);
-        const int k8 = rem >> 3;
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+struct TileRegs {
+    static constexpr int kIt = (4 * KT) / 32;
+    float4 a[kIt], b[kIt];
+};
+
+// Issue every global load of a 128 x KT fp32 tile (64 B x KT/8 per thread in flight); rows >= n read as zero.
+template <int KT>
+__device__ __forceinline__ void tile_issue(TileRegs<KT>& t, const float* src, long long stride, long long p0, long long n,
+                                           int warp, int lane) {
+#pragma unroll
+    for (int it = 0; it < TileRegs<KT>::kIt; ++it) {
+        const int c = lane + 32 * it;
+        const int r = warp * 32 + (c / KT) * 8 + ((c % KT) & 7);
+        const int k8 = (c % KT) >> 3;
+        t.a[it] = t.b[it] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (p0 + r < n) {
             const float4* s4 = reinterpret_cast<const float4*>(src + (p0 + r) * stride + k8 * 8);
-            a = __ldcs(s4);
-            b = __ldcs(s4 + 1);
+            t.a[it] = __ldcs(s4);
+            t.b[it] = __ldcs(s4 + 1);
         }
+    }
+}
+
+// bf16 tile, K-major at `dst` and transposed (feature-major, point columns) at `dst_t` rows [t_row0, t_row0 + KT)
+template <int KT>
+__device__ __forceinline__ void tile_store(const TileRegs<KT>& t, unsigned char* dst, unsigned char* dst_t, int t_row0,
+                                           int warp, int lane) {
+#pragma unroll
+    for (int it = 0; it < TileRegs<KT>::kIt; ++it) {
+        const int c = lane + 32 * it;
+        const int r = warp * 32 + (c / KT) * 8 + ((c % KT) & 7);
+        const int k8 = (c % KT) >> 3;
+        const float4 a = t.a[it], b = t.b[it];
         *reinterpret_cast<uint4*>(dst + canon_chunk_offset(r, k8, KT)) =
             make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w));
         const float e[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
@@ -161,8 +181,14 @@ mlp_head_bwd_kernel(const __grid_constant__ MlpHeadBwdParams P) {
         const long long p0 = static_cast<long long>(tile) * kTileM;
 
         // ---- 1. stage X, X^T, GY, GY^T ---------------------------------------------------------
-        load_tile<K1>(P.x, P.x_stride, p0, P.n, sX, sBT, kH, warp, lane);
-        load_tile<kH>(P.gy, P.gy_stride, p0, P.n, sGY, sAT, 0, warp, lane);
+        {
+            TileRegs<K1> tx;
+            TileRegs<kH> tg;
+            tile_issue<K1>(tx, P.x, P.x_stride, p0, P.n, warp, lane);
+            tile_issue<kH>(tg, P.gy, P.gy_stride, p0, P.n, warp, lane);
+            tile_store<K1>(tx, sX, sBT, kH, warp, lane);
+            tile_store<kH>(tg, sGY, sAT, 0, warp, lane);
+        }
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
