@@ -61,6 +61,31 @@ def algorithmic_bytes_per_point(n_level_rows: int, corners: int, F: int, table_b
     return fwd, bwd
 
 
+# L1->L2 request ("packet" = distinct 32 B sector per instruction) peaks measured on B200 by scripts/peaks_gather.py
+# (profiles/r01c_peaks_gather.json, L2-resident working set, 2 adjacent lanes on adjacent entries):
+# loads 574 G lane-ops/s = 287 G packets/s (1.0 / clk / SM); red.global.add.v2.f32 430 G lane-ops/s = 215 G packets/s.
+PACKET_PEAK_G = {"forward": 287.0, "backward": 215.0}
+
+
+def packets_per_point(n_level_rows: int, corners: int, F: int, entry_bytes: int):
+    """Distinct 32 B sectors one point touches per level row when the x-neighbour pair is issued by adjacent lanes
+    (DESIGN.md 2.0): C/2 x-pairs, each one sector unless the pair straddles a sector boundary."""
+    if corners == 1:
+        return float(n_level_rows)
+    per_sector = max(1, 32 // (F * entry_bytes))
+    return n_level_rows * (corners / 2) * (1.0 + 1.0 / per_sector)
+
+
+def morton_sort(coords, bits=10):
+    """Experiment (--sort-points): order the points along a 4-D Morton curve of their 2^bits cells."""
+    q = (coords.clamp(0, 1 - 1e-7) * (1 << bits)).to(torch.int64)
+    key = torch.zeros(coords.shape[0], dtype=torch.int64, device=coords.device)
+    for b in range(bits):
+        for d in range(4):
+            key |= ((q[:, d] >> b) & 1) << (4 * b + d)
+    return coords[torch.argsort(key)].contiguous()
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -209,11 +234,15 @@ class Job:
             self.gout = None
         else:
             self.coords = make_coords(wl, n_points, device, seed)
+            if wl.get("sort_points"):
+                self.coords = morton_sort(self.coords)
             self.gout = torch.randn((n_points, self.plan.out_cols), device=device, generator=g)
         self.out = torch.empty((n_points, self.plan.out_cols), dtype=torch.float32, device=device)
         corners = 8 if self.linear else 1
         tb = 2 if self.plan.table_dtype == torch.float16 else 4
         self.bytes_fwd, self.bytes_bwd = algorithmic_bytes_per_point(len(self.plan.specs), corners, self.F, tb)
+        self.packets_fwd = packets_per_point(len(self.plan.specs), corners, self.F, tb)
+        self.packets_bwd = packets_per_point(len(self.plan.specs), corners, self.F, 4)
         self.out_scale = 1.0 / self.plan.table_scale if self.plan.table_scale != 1.0 else 1.0
         self.use_replicas = True
         self.head_bwd = "tcgen05"
@@ -345,6 +374,10 @@ def run_gpu_arm(args, wl):
     import ctypes as _ct
     if args.l2_fetch:
         _L.check(_L.load().de_set_l2_fetch_granularity(args.l2_fetch), "de_set_l2_fetch_granularity")
+    if args.persist_l2_mb:
+        _L.check(_L.load().de_set_persisting_l2(-1 if args.persist_l2_mb < 0 else args.persist_l2_mb << 20), "de_set_persisting_l2")
+    _pl2, _pl2max = _ct.c_longlong(0), _ct.c_longlong(0)
+    _L.load().de_get_persisting_l2(_ct.byref(_pl2), _ct.byref(_pl2max))
     _gran = _ct.c_int(0)
     _L.load().de_get_l2_fetch_granularity(_ct.byref(_gran))
 
@@ -446,6 +479,7 @@ def run_gpu_arm(args, wl):
                    f"head_backward_{args.head_bwd}": float(np.mean([e[5].elapsed_time(e[1]) for e in evs]))}
     else:
         fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+    fwd_enc_ms = fwd_ms          # c5: includes the ~0.15 ms prologue
     bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
     ar_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in evs])) if world > 1 else 0.0
     if world > 1:
@@ -545,12 +579,24 @@ def run_gpu_arm(args, wl):
                        "table_size": wl["T"], "interpolation": "linear" if job.linear else "nearest",
                        "l2_policy": "inputs larger than L2 (coords+grad_out+out > 4 GiB per step); no flush",
                        "l2_fetch_granularity": _gran.value,
+                       "l2_persisting_bytes": _pl2.value, "l2_persisting_max_bytes": _pl2max.value,
                        "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"
                                       + (f" overlapped with the backward in {args.sync_chunks} level runs" if sync is not None else "")},
             "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms, **(head_ms or {})},
             "roofline": {"bound": "hbm", "kernel": f"grid4d_{dom}_kernel", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_point": {"forward": job.bytes_fwd, "backward": job.bytes_bwd}},
+            # the bound that actually applies while a level group's tables sit in L2: distinct 32 B
+            # sectors requested per second against the probe-measured L1->L2 request rate of the same access shape
+            "roofline_packets": {
+                "bound": "l2_request_rate", "unit": "Gpackets/s",
+                "forward": {"packets_per_point": job.packets_fwd, "achieved": job.packets_fwd * n / (fwd_enc_ms * 1e-3) / 1e9,
+                            "peak": PACKET_PEAK_G["forward"],
+                            "frac": job.packets_fwd * n / (fwd_enc_ms * 1e-3) / 1e9 / PACKET_PEAK_G["forward"]},
+                "backward": {"packets_per_point": job.packets_bwd, "achieved": job.packets_bwd * n / (bwd_ms * 1e-3) / 1e9,
+                             "peak": PACKET_PEAK_G["backward"],
+                             "frac": job.packets_bwd * n / (bwd_ms * 1e-3) / 1e9 / PACKET_PEAK_G["backward"]},
+                "peak_source": "profiles/r01c_peaks_gather.json (scripts/peaks_gather.py on B200)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes * world),
                     "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps, "checksum": checksum,
                     "api": api},
@@ -582,15 +628,20 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="N>1: one all-reduce after the backward instead of the overlapped slices")
     ap.add_argument("--sync-chunks", type=int, default=4, help="N>1: level runs the backward / all-reduce overlap is cut into")
     ap.add_argument("--head-bwd", default="tcgen05", choices=["tcgen05", "cublas"], help="c5: head backward kernel")
+    ap.add_argument("--sort-points", action="store_true", help="experiment: Morton-order the synthetic points before timing")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-replicas", action="store_true", help="backward without gradient replicas for contended coarse levels (A/B)")
     ap.add_argument("--flags", type=lambda v: int(v, 0), default=0, help="DE_FLAG_* opt-in paths (0x100 TMA-staged backward, 0x200 shared-memory coarse forward)")
+    ap.add_argument("--persist-l2-mb", type=int, default=0, help="cudaLimitPersistingL2CacheSize in MiB (-1 = device maximum)")
     ap.add_argument("--l2-fetch", type=int, default=0, help="set cudaLimitMaxL2FetchGranularity (32/64/128)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.coords:
         wl["coords"] = args.coords
         wl["desc"] += f" [coords overridden: {args.coords}]"
+    if args.sort_points:
+        wl["sort_points"] = True
+        wl["desc"] += " [points Morton-sorted before timing]"
     if args.impl == "reference":
         run_reference_arm(args, wl)
     else:

@@ -69,6 +69,8 @@ SIGNATURES = {
     "de_geo_bbox": (c_int, [c_void_p, c_int, c_void_p, c_i64, c_void_p]),
     "de_set_l2_fetch_granularity": (c_int, [c_int]),
     "de_get_l2_fetch_granularity": (c_int, [ctypes.POINTER(c_int)]),
+    "de_set_persisting_l2": (c_int, [ctypes.c_longlong]),
+    "de_get_persisting_l2": (c_int, [ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_longlong)]),
     "de_sum_f32": (c_int, [c_void_p, c_i64, c_void_p, c_void_p]),
     "de_probe_gather": (c_int, [c_void_p, c_i64, c_int, c_int, c_i64, c_int, c_int, c_void_p, c_void_p]),
 }

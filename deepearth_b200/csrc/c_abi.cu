@@ -628,6 +628,33 @@ DE_API int de_get_l2_fetch_granularity(int* bytes) {
     return DE_OK;
 }
 
+DE_API int de_set_persisting_l2(long long bytes) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    int max_bytes = 0;
+    e = cudaDeviceGetAttribute(&max_bytes, cudaDevAttrMaxPersistingL2CacheSize, dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute(MaxPersistingL2CacheSize)");
+    if (bytes < 0 || bytes > max_bytes) bytes = max_bytes;
+    e = cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, static_cast<size_t>(bytes));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "cudaDeviceSetLimit(PersistingL2CacheSize)");
+}
+
+DE_API int de_get_persisting_l2(long long* bytes, long long* max_bytes) {
+    if (!bytes || !max_bytes) return fail(DE_EINVAL, "NULL pointer");
+    int dev = 0, mx = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    e = cudaDeviceGetAttribute(&mx, cudaDevAttrMaxPersistingL2CacheSize, dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute(MaxPersistingL2CacheSize)");
+    size_t v = 0;
+    e = cudaDeviceGetLimit(&v, cudaLimitPersistingL2CacheSize);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetLimit(PersistingL2CacheSize)");
+    *bytes = static_cast<long long>(v);
+    *max_bytes = mx;
+    return DE_OK;
+}
+
 DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream) {
     if (n < 0 || (n > 0 && (!x || !result))) return fail(DE_EINVAL, "sum_f32: bad arguments");
     cudaError_t e = de::launch_sum_f32(x, n, result, static_cast<cudaStream_t>(stream));

@@ -17,6 +17,8 @@
 //           D_dW stays in TMEM for the CTA's whole life (accumulate flag) and is reduced into global memory once.
 // All operands are bf16 in the UMMA canonical K-major no-swizzle layout; the point-major tiles (GY, DH, A, X)
 // are also written transposed (2-byte shared stores) so that GEMM 4 contracts over points with K-major operands.
+#include <cstdlib>
+
 #include "launch.h"
 #include "mlp_common.cuh"
 
@@ -383,6 +385,10 @@ static cudaError_t launch_bwd_k(const MlpHeadBwdParams& P, int n_sms, cudaStream
 }
 
 cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s) {
+    // default: the ping-pong kernel of mlp_head_bwd2.cu; DE_HEAD_BWD_VARIANT=1 selects this file's serial kernel (A/B)
+    const char* v = getenv("DE_HEAD_BWD_VARIANT");
+    P.variant = v ? atoi(v) : 0;
+    if (!(P.variant & 1)) return launch_mlp_head_bwd_pp(P, in_dim, n_sms, s);
     P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
     if (P.n_tiles == 0) return cudaSuccess;
     switch (in_dim) {

@@ -1,0 +1,480 @@
+// mlp_head_bwd2.cu -- backward of the 64-wide projection head, warp-specialised ping-pong version (sm_100a).
+//
+//   forward:  h = x W1^T + b1 ;  z = LN(h) (optional) ;  a = act(z) ;  y = a W2^T + b2
+//   (structure of Grid4DEncoder.projection, /root/reference/models/encoders.py:47-52, at the 64-wide size of
+//   BASELINE.json configs[4]); given gy = dL/dy this kernel produces dL/dx and accumulates dW1, db1, dgamma,
+//   dbeta, dW2, db2.  Same mathematics and the same four GEMMs per 128-point tile as mlp_head_bwd.cu:
+//
+//   GEMM 1  D_h  [128 x 64]  = X  [128 x K1] * W1^T           GEMM 2  D_da [128 x 64] = GY [128 x 64] * W2
+//   GEMM 3  D_dx [128 x K1]  = DH [128 x 64] * W1
+//   GEMM 4  D_dW [128 x N4] += [GY | DH]^T [128 cols x 128 pts] * [A | X | 1] [128 pts x N4]   (dW2, dW1, db2, db1)
+//
+// What changed against mlp_head_bwd.cu (16.8 ms per 2^24 points, one 4-warp CTA per SM, every phase serial):
+//   * GEMM 4 contracts over POINTS.  Its operands are the point-major tiles the other GEMMs already use, read
+//     as MN-major operands (instruction-descriptor bits 15/16): no transposed copies, which were ~400 two-byte
+//     shared stores per thread per tile and 84 KB of shared memory.
+//   * The freed shared memory holds TWO tiles in flight: two 128-thread consumer groups ping-pong (one stages /
+//     runs its register epilogue while the other waits on the tensor core), a ninth warp issues every
+//     tcgen05.mma in arrival order (so the shared dW accumulator in TMEM sees one in-order issuer), and each
+//     group prefetches its next tile's global loads into registers before it waits for GEMM 3/4.
+//   * TMEM: group g owns columns [128 g, 128 g + 128): D_h | D_da, then D_dx on top of them; dW at 256..256+N4.
+#include "launch.h"
+#include "mlp_common.cuh"
+
+namespace de {
+
+using namespace mlp;
+
+namespace {
+
+constexpr int kPPThreads = 384;          // 2 consumer warpgroups + 1 warpgroup whose first warp issues the MMAs
+                                         // (registers are allocated per warpgroup; setmaxnreg moves them to the consumers)
+constexpr int kColDw2 = 256;
+
+__device__ __forceinline__ void tmem_ld16b(uint32_t taddr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// lane l returns sum over the warp's 32 lanes of vals[l] (31 shuffles; vals is destroyed)
+__device__ __forceinline__ float colsum32(float (&vals)[32], int lane) {
+#pragma unroll
+    for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < n / 2; ++i) {
+            const float send = upper ? vals[i] : vals[i + n / 2];
+            const float keep = upper ? vals[i + n / 2] : vals[i];
+            vals[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return vals[0];
+}
+
+__device__ __forceinline__ void red_add_f32(float* p, float v) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+
+// A 128 x KT fp32 tile held in registers between its global loads and its shared-memory stores.
+template <int KT>
+struct TileR {
+    static constexpr int kIt = (4 * KT) / 32;
+    float4 a[kIt], b[kIt];
+};
+
+// Issue every global load of rows [p0, p0+128) (64 B x KT/8 per thread in flight); rows >= n read as zero.
+// Warp w (0..3 inside its group) covers tile rows 32w .. 32w+31; 8 consecutive lanes take 8 consecutive rows of
+// one 16-byte bf16 chunk column (conflict-free shared stores), 4 chunk columns per request (128 B segments).
+template <int KT>
+__device__ __forceinline__ void tile_issue2(TileR<KT>& t, const float* tile_base, int stride, int n_valid, int warp, int lane) {
+#pragma unroll
+    for (int it = 0; it < TileR<KT>::kIt; ++it) {
+        const int c = lane + 32 * it;
+        const int r = warp * 32 + (c / KT) * 8 + ((c % KT) & 7);
+        const int k8 = (c % KT) >> 3;
+        t.a[it] = t.b[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < n_valid) {
+            const float4* s4 = reinterpret_cast<const float4*>(tile_base + (r * stride + k8 * 8));
+            t.a[it] = __ldcs(s4);
+            t.b[it] = __ldcs(s4 + 1);
+        }
+    }
+}
+
+// registers -> bf16 chunks [chunk0, chunk0 + KT/8) of a canonical K-major tile that is `cols` columns wide
+template <int KT>
+__device__ __forceinline__ void tile_store2(const TileR<KT>& t, unsigned char* dst, int chunk0, int cols, int warp, int lane) {
+#pragma unroll
+    for (int it = 0; it < TileR<KT>::kIt; ++it) {
+        const int c = lane + 32 * it;
+        const int r = warp * 32 + (c / KT) * 8 + ((c % KT) & 7);
+        const int k8 = (c % KT) >> 3;
+        const float4 a = t.a[it], b = t.b[it];
+        *reinterpret_cast<uint4*>(dst + canon_chunk_offset(r, chunk0 + k8, cols)) =
+            make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w));
+    }
+}
+
+}  // namespace
+
+// dynamic shared memory (bf16, canonical K-major, no swizzle):
+//   W1 [64 x K1] | W1T [K1 x 64] | W2T [64 x 64] | per group g: XA_g [128 x NB] = [A | X | ones(16)] , GD_g [128 x 128] = [GY | DH]
+template <int K1>
+__global__ void __launch_bounds__(kPPThreads, 1)
+mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
+    constexpr int NB = kH + K1 + 16;                  // columns of XA = N of GEMM 4
+    constexpr uint32_t kXaBytes = kTileM * NB * 2, kGdBytes = kTileM * 128 * 2;
+    constexpr uint32_t kXaGroup = (NB / 8) * 128;     // bytes between 8-point groups of XA
+    constexpr uint32_t kGdGroup = (128 / 8) * 128;    // ... of GD
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ float s_vec[3][kH];                    // b1, ln gamma, ln beta
+    __shared__ __align__(8) uint64_t s_in_full[2], s_d12[2], s_mid_full[2], s_d34[2];
+    __shared__ uint32_t s_tmem;
+
+    unsigned char* sW1 = smem;
+    unsigned char* sW1T = sW1 + kH * K1 * 2;
+    unsigned char* sW2T = sW1T + K1 * kH * 2;
+    unsigned char* sTiles = sW2T + kH * kH * 2;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int grp = warp >> 2;                        // 0, 1: consumer groups; 2: the MMA warp
+
+    // ---- one-time setup ------------------------------------------------------------------------
+    const __nv_bfloat16* w1 = static_cast<const __nv_bfloat16*>(P.w1);
+    const __nv_bfloat16* w1t = static_cast<const __nv_bfloat16*>(P.w1t);
+    const __nv_bfloat16* w2t = static_cast<const __nv_bfloat16*>(P.w2t);
+    for (int c = tid; c < kH * (K1 / 8); c += kPPThreads) {         // W1 (64, K1): B of GEMM 1
+        const int n = c / (K1 / 8), k8 = c % (K1 / 8);
+        *reinterpret_cast<uint4*>(sW1 + canon_chunk_offset(n, k8, K1)) = *reinterpret_cast<const uint4*>(w1 + static_cast<size_t>(n) * K1 + k8 * 8);
+    }
+    for (int c = tid; c < K1 * (kH / 8); c += kPPThreads) {         // W1^T (K1, 64): B of GEMM 3
+        const int n = c / (kH / 8), k8 = c % (kH / 8);
+        *reinterpret_cast<uint4*>(sW1T + canon_chunk_offset(n, k8, kH)) = *reinterpret_cast<const uint4*>(w1t + static_cast<size_t>(n) * kH + k8 * 8);
+    }
+    for (int c = tid; c < kH * (kH / 8); c += kPPThreads) {         // W2^T (64 hidden, 64 out): B of GEMM 2
+        const int n = c / (kH / 8), k8 = c % (kH / 8);
+        *reinterpret_cast<uint4*>(sW2T + canon_chunk_offset(n, k8, kH)) = *reinterpret_cast<const uint4*>(w2t + static_cast<size_t>(n) * kH + k8 * 8);
+    }
+    for (int c = tid; c < 2 * kTileM * 2; c += kPPThreads) {        // the 16 columns of ones of both XA tiles (bias gradients)
+        const int g = c / (kTileM * 2), r = (c / 2) % kTileM, k8 = (kH + K1) / 8 + (c & 1);
+        *reinterpret_cast<uint4*>(sTiles + g * (kXaBytes + kGdBytes) + canon_chunk_offset(r, k8, NB)) =
+            make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
+    }
+    if (tid < kH) {
+        s_vec[0][tid] = P.b1 ? P.b1[tid] : 0.0f;
+        s_vec[1][tid] = P.ln_gamma ? P.ln_gamma[tid] : 1.0f;
+        s_vec[2][tid] = P.ln_beta ? P.ln_beta[tid] : 0.0f;
+    }
+    if (tid == 0) {
+        for (int g = 0; g < 2; ++g) {
+            mbar_init(&s_in_full[g], 128);
+            mbar_init(&s_mid_full[g], 128);
+            mbar_init(&s_d12[g], 1);
+            mbar_init(&s_d34[g], 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 8) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    // tiles of this CTA: blockIdx.x + m * gridDim.x, m = 0, 1, ...; group g takes m = g, g + 2, ...
+    const int n_mine = P.n_tiles > static_cast<int>(blockIdx.x) ? (P.n_tiles - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+    const int cnt0 = (n_mine + 1) / 2, cnt1 = n_mine / 2;
+
+    if (grp == 2) {
+        // =========================== MMA warp: one thread issues every tcgen05.mma ===================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        if (warp == 8 && lane == 0) {
+            int issued12[2] = {0, 0}, issued34[2] = {0, 0};
+            const int cnt[2] = {cnt0, cnt1};
+            bool dw_started = false;
+            constexpr uint32_t kIdesc64 = umma_idesc(kH), kIdescK1 = umma_idesc(K1);
+            constexpr uint32_t kIdescDw = umma_idesc(NB) | (1u << 15) | (1u << 16);     // A and B MN-major
+            const bool swap = (P.variant & 2) != 0;
+            while (issued34[0] < cnt[0] || issued34[1] < cnt[1]) {
+                bool any = false;
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    const uint32_t xa = smem_u32(sTiles + g * (kXaBytes + kGdBytes)), gd = xa + kXaBytes;
+                    const uint32_t tcol = tmem + g * 128;
+                    if (issued12[g] == issued34[g]) {
+                        if (issued12[g] < cnt[g] && mbar_test(&s_in_full[g], issued12[g] & 1)) {
+                            tc_fence_after();
+                            const uint32_t w1a = smem_u32(sW1), w2a = smem_u32(sW2T);
+#pragma unroll
+                            for (int k = 0; k < K1 / 16; ++k)       // GEMM 1: X (XA chunks 8..) * W1^T -> D_h
+                                umma_bf16(tcol, umma_desc(xa + (kH / 8) * 128 + k * 256, 128, kXaGroup), umma_desc(w1a + k * 256, 128, (K1 / 8) * 128),
+                                          kIdesc64, k > 0 ? 1u : 0u);
+#pragma unroll
+                            for (int k = 0; k < kH / 16; ++k)       // GEMM 2: GY (GD chunks 0..7) * W2 -> D_da
+                                umma_bf16(tcol + 64, umma_desc(gd + k * 256, 128, kGdGroup), umma_desc(w2a + k * 256, 128, (kH / 8) * 128),
+                                          kIdesc64, k > 0 ? 1u : 0u);
+                            umma_commit(&s_d12[g]);
+                            ++issued12[g];
+                            any = true;
+                        }
+                    } else if (mbar_test(&s_mid_full[g], issued34[g] & 1)) {
+                        tc_fence_after();
+                        const uint32_t w1ta = smem_u32(sW1T);
+#pragma unroll
+                        for (int k = 0; k < kH / 16; ++k)           // GEMM 3: DH (GD chunks 8..15) * W1 -> D_dx (over D_h | D_da)
+                            umma_bf16(tcol, umma_desc(gd + (kH / 8) * 128 + k * 256, 128, kGdGroup), umma_desc(w1ta + k * 256, 128, (kH / 8) * 128),
+                                      kIdescK1, k > 0 ? 1u : 0u);
+#pragma unroll
+                        for (int k = 0; k < kTileM / 16; ++k) {     // GEMM 4: [GY | DH]^T * [A | X | 1], K = 16 points per step
+                            const uint32_t aa = gd + k * 2 * kGdGroup, ba = xa + k * 2 * kXaGroup;
+                            // MN-major, no swizzle: SBO = bytes between 8-column core matrices (128), LBO = bytes between 8-point groups
+                            const uint64_t da = swap ? umma_desc(aa, 128, kGdGroup) : umma_desc(aa, kGdGroup, 128);
+                            const uint64_t db = swap ? umma_desc(ba, 128, kXaGroup) : umma_desc(ba, kXaGroup, 128);
+                            umma_bf16(tmem + kColDw2, da, db, kIdescDw, (dw_started || k > 0) ? 1u : 0u);
+                        }
+                        dw_started = true;
+                        umma_commit(&s_d34[g]);
+                        ++issued34[g];
+                        any = true;
+                    }
+                }
+                if (!any) __nanosleep(40);
+            }
+        }
+        __syncwarp();
+    } else {
+        // =========================== consumer groups ================================================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
+        const int cnt = grp == 0 ? cnt0 : cnt1;
+        const int wq = warp & 3;                                    // warp inside the group = TMEM lane quarter
+        const int row = wq * 32 + lane;                             // tile row (point) owned in the epilogues
+        unsigned char* sXA = sTiles + grp * (kXaBytes + kGdBytes);
+        unsigned char* sGD = sXA + kXaBytes;
+        const uint32_t tmem_row = tmem + (static_cast<uint32_t>(wq * 32) << 16) + grp * 128;
+        float acc_beta[2] = {0.f, 0.f}, acc_gamma[2] = {0.f, 0.f};  // lane l: columns l and 32 + l, this warp's rows
+
+        long long p0 = (static_cast<long long>(blockIdx.x) + static_cast<long long>(grp) * gridDim.x) * kTileM;
+        const long long p_step = 2LL * gridDim.x * kTileM;
+        const int xs = static_cast<int>(P.x_stride), gs = static_cast<int>(P.gy_stride);
+        for (int i = 0; i < cnt; ++i, p0 += p_step) {
+            const int n_valid = static_cast<int>(P.n - p0 < kTileM ? P.n - p0 : kTileM);
+            // ---- this tile's feature rows: loads issued now, in flight while the tensor core finishes GEMM 3 / 4
+            //      of the previous tile and its gradient rows are streamed out ---------------------------
+            TileR<K1> tx;
+            tile_issue2<K1>(tx, P.x + p0 * P.x_stride, xs, n_valid, wq, lane);
+            if (i > 0) {                                            // epilogue B of the previous tile
+                mbar_wait(&s_d34[grp], (i - 1) & 1);
+                tc_fence_after();
+                const long long pr = p0 - p_step + row;
+                float* dst_row = P.dx + pr * P.dx_stride;
+#pragma unroll
+                for (int c0 = 0; c0 < K1; c0 += 16) {
+                    float q[16];
+                    tmem_ld16b(tmem_row + c0, q);                   // warp-collective: outside the row predicate
+                    if (pr < P.n) {
+                        float4* dst = reinterpret_cast<float4*>(dst_row + c0);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) __stcs(dst + u, make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]));
+                    }
+                }
+            }
+            // ---- stage X and GY ----------------------------------------------------------------------
+            tile_store2<K1>(tx, sXA, kH / 8, NB, wq, lane);
+            {
+                TileR<kH> tg;
+                tile_issue2<kH>(tg, P.gy + p0 * P.gy_stride, gs, n_valid, wq, lane);
+                tile_store2<kH>(tg, sGD, 0, 128, wq, lane);
+            }
+            fence_async_smem();
+            tc_fence_before();
+            mbar_arrive(&s_in_full[grp]);
+
+            mbar_wait(&s_d12[grp], i & 1);
+            tc_fence_after();
+
+            // ---- epilogue A: one point per thread (LayerNorm statistics, activation and its derivative,
+            //      LayerNorm backward, all in registers) -----------------------------------------------
+            {
+                float v[kH];      // h, then xhat (LayerNorm) or h (no LayerNorm)
+                float d[kH];      // dz = da * act'(z), then dh
+                {
+                    float lo[32], hi[32];
+                    tmem_ld32(tmem_row, lo);
+                    tmem_ld32(tmem_row + 32, hi);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) { v[j] = lo[j] + s_vec[0][j]; v[32 + j] = hi[j] + s_vec[0][32 + j]; }
+                }
+                float rstd = 1.0f;
+                if (P.layernorm) {
+                    float mean = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < kH; ++j) mean += v[j];
+                    mean *= (1.0f / kH);
+                    float var = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < kH; ++j) { const float t = v[j] - mean; var = fmaf(t, t, var); }
+                    rstd = rsqrtf(var * (1.0f / kH) + P.ln_eps);
+#pragma unroll
+                    for (int j = 0; j < kH; ++j) v[j] = (v[j] - mean) * rstd;
+                }
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    float da[32];
+                    tmem_ld32(tmem_row + 64 + 32 * half, da);
+#pragma unroll
+                    for (int c8 = 0; c8 < 4; ++c8) {
+                        float a8[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const int i = 8 * c8 + u, j = 32 * half + i;
+                            const float z = P.layernorm ? fmaf(v[j], s_vec[1][j], s_vec[2][j]) : v[j];
+                            float a = z, g = 1.0f;
+                            if (P.activation == 1) {
+                                a = fmaxf(z, 0.0f);
+                                g = z > 0.0f ? 1.0f : 0.0f;
+                            } else if (P.activation == 2) {
+                                const float cdf = 0.5f * (1.0f + erff(z * 0.70710678118654752f));
+                                a = z * cdf;
+                                g = fmaf(z * 0.3989422804014327f, __expf(-0.5f * z * z), cdf);   // Phi(z) + z phi(z)
+                            }
+                            a8[u] = a;
+                            d[j] = da[i] * g;
+                        }
+                        // A: columns 0..63 of XA (B operand of GEMM 4)
+                        *reinterpret_cast<uint4*>(sXA + canon_chunk_offset(row, 4 * half + c8, NB)) =
+                            make_uint4(pack_bf16(a8[0], a8[1]), pack_bf16(a8[2], a8[3]), pack_bf16(a8[4], a8[5]), pack_bf16(a8[6], a8[7]));
+                    }
+                }
+                if (P.layernorm) {
+                    // dbeta_j += sum_p dz ; dgamma_j += sum_p dz * xhat  (this warp's 32 points, lane l <- column l)
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        float t[32];
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) t[i] = d[32 * half + i];
+                        acc_beta[half] += colsum32(t, lane);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) t[i] = d[32 * half + i] * v[32 * half + i];
+                        acc_gamma[half] += colsum32(t, lane);
+                    }
+                    float m1 = 0.0f, m2 = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < kH; ++j) {
+                        d[j] *= s_vec[1][j];                    // dxhat
+                        m1 += d[j];
+                        m2 = fmaf(d[j], v[j], m2);
+                    }
+                    m1 *= (1.0f / kH);
+                    m2 *= (1.0f / kH);
+#pragma unroll
+                    for (int j = 0; j < kH; ++j) d[j] = rstd * (d[j] - m1 - v[j] * m2);
+                }
+                // DH: columns 64..127 of GD (A operand of GEMM 3, rows 64..127 of GEMM 4's A)
+#pragma unroll
+                for (int k8 = 0; k8 < kH / 8; ++k8) {
+                    *reinterpret_cast<uint4*>(sGD + canon_chunk_offset(row, kH / 8 + k8, 128)) =
+                        make_uint4(pack_bf16(d[8 * k8], d[8 * k8 + 1]), pack_bf16(d[8 * k8 + 2], d[8 * k8 + 3]),
+                                   pack_bf16(d[8 * k8 + 4], d[8 * k8 + 5]), pack_bf16(d[8 * k8 + 6], d[8 * k8 + 7]));
+                }
+            }
+            fence_async_smem();
+            tc_fence_before();
+            mbar_arrive(&s_mid_full[grp]);
+
+        }
+        if (cnt > 0) {                                              // epilogue B of the last tile
+            mbar_wait(&s_d34[grp], (cnt - 1) & 1);
+            tc_fence_after();
+            const long long pr = p0 - p_step + row;
+#pragma unroll
+            for (int c0 = 0; c0 < K1; c0 += 16) {
+                float q[16];
+                tmem_ld16b(tmem_row + c0, q);
+                if (pr < P.n) {
+                    float4* dst = reinterpret_cast<float4*>(P.dx + pr * P.dx_stride + c0);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) __stcs(dst + u, make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]));
+                }
+            }
+            if (P.layernorm) {
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    if (P.dgamma) red_add_f32(P.dgamma + 32 * half + lane, acc_gamma[half]);
+                    if (P.dbeta) red_add_f32(P.dbeta + 32 * half + lane, acc_beta[half]);
+                }
+            }
+        }
+    }
+
+    // ---- weight / bias gradients of this CTA's tiles: TMEM -> global (fp32 reductions) ---------------
+    // every group has waited for its last GEMM 4 (s_d34), so after this barrier the dW accumulator is final
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (grp == 0 && n_mine > 0) {
+        const int row = tid;                                        // TMEM lane = row of D_dW
+        const uint32_t tmem_row = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+        if (row < kH) {                    // rows 0..63: output unit o = row -> dW2[o][:], db2[o]
+#pragma unroll
+            for (int c0 = 0; c0 < kH; c0 += 16) {
+                float q[16];
+                tmem_ld16b(tmem_row + kColDw2 + c0, q);
+#pragma unroll
+                for (int u = 0; u < 16; ++u) red_add_f32(P.dw2 + row * kH + c0 + u, q[u]);
+            }
+            float q[16];
+            tmem_ld16b(tmem_row + kColDw2 + kH + K1, q);
+            if (P.db2) red_add_f32(P.db2 + row, q[0]);
+        } else {                           // rows 64..127: hidden unit j = row - 64 -> dW1[j][:], db1[j]
+            const int j = row - kH;
+#pragma unroll
+            for (int c0 = 0; c0 < K1; c0 += 16) {
+                float q[16];
+                tmem_ld16b(tmem_row + kColDw2 + kH + c0, q);
+#pragma unroll
+                for (int u = 0; u < 16; ++u) red_add_f32(P.dw1 + j * K1 + c0 + u, q[u]);
+            }
+            float q[16];
+            tmem_ld16b(tmem_row + kColDw2 + kH + K1, q);
+            if (P.db1) red_add_f32(P.db1 + j, q[0]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// host launcher
+// ------------------------------------------------------------------------------------------------
+template <int K1>
+static cudaError_t launch_pp_k(const MlpHeadBwdParams& P, int n_sms, cudaStream_t s) {
+    auto kernel = mlp_head_bwd_pp_kernel<K1>;
+    constexpr int NB = kH + K1 + 16;
+    const size_t smem = static_cast<size_t>(kH) * K1 * 2 + K1 * kH * 2 + kH * kH * 2 + 2 * (static_cast<size_t>(kTileM) * NB * 2 + kTileM * 128 * 2);
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    int grid = n_sms;                                  // 512 TMEM columns: one CTA per SM
+    if (grid > P.n_tiles) grid = P.n_tiles;
+    kernel<<<grid, kPPThreads, smem, s>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_mlp_head_bwd_pp(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s) {
+    P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
+    if (P.n_tiles == 0) return cudaSuccess;
+    switch (in_dim) {
+        case 32: return launch_pp_k<32>(P, n_sms, s);
+        case 48: return launch_pp_k<48>(P, n_sms, s);
+        case 64: return launch_pp_k<64>(P, n_sms, s);
+        case 96: return launch_pp_k<96>(P, n_sms, s);
+        case 128: return launch_pp_k<128>(P, n_sms, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace de

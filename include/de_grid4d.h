@@ -213,6 +213,15 @@ DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_p
 DE_API int de_set_l2_fetch_granularity(int bytes);
 DE_API int de_get_l2_fetch_granularity(int* bytes);
 
+/*
+ * L2 set-aside for persisting accesses (cudaLimitPersistingL2CacheSize) of the current device.  The table
+ * gathers and gradient reductions carry an L2::evict_last policy; the set-aside is the share of L2 such lines
+ * may hold against the streamed coordinates / feature rows.  bytes < 0 asks for the device maximum
+ * (cudaDeviceProp::persistingL2CacheMaxSize); get returns the current value and the maximum.
+ */
+DE_API int de_set_persisting_l2(long long bytes);
+DE_API int de_get_persisting_l2(long long* bytes, long long* max_bytes);
+
 /* fp64 sum of an fp32 buffer into *result (device, caller-zeroed): bench/e2e checksum. */
 DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
 
