@@ -87,7 +87,7 @@ struct MlpHeadBwdParams {
     float* dw2;                   // (64, 64) accumulated
     float* db2;                   // (64,) accumulated, or NULL
     int n_tiles;
-    int variant;                  // A/B switch (env DE_HEAD_BWD_VARIANT): bit 0 = serial kernel (mlp_head_bwd.cu), bit 1 = swapped GEMM-4 LBO/SBO
+    int variant;                  // A/B switch (env DE_HEAD_BWD_VARIANT): bit 0 = serial kernel (mlp_head_bwd.cu)
 };
 bool mlp_head_supported(int in_dim, int hidden, int out_dim);
 cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);        // dispatcher

@@ -190,14 +190,15 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
 
     if (grp == 2) {
         // =========================== MMA warp: one thread issues every tcgen05.mma ===================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        // register budget: 384 threads x 168 at launch; this warpgroup gives back (168 - 56) x 128 = 14336 registers, exactly
+        // what the two consumer warpgroups take (2 x (224 - 168) x 128) -- a larger request would wait forever
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
         if (warp == 8 && lane == 0) {
             int issued12[2] = {0, 0}, issued34[2] = {0, 0};
             const int cnt[2] = {cnt0, cnt1};
             bool dw_started = false;
             constexpr uint32_t kIdesc64 = umma_idesc(kH), kIdescK1 = umma_idesc(K1);
             constexpr uint32_t kIdescDw = umma_idesc(NB) | (1u << 15) | (1u << 16);     // A and B MN-major
-            const bool swap = (P.variant & 2) != 0;
             while (issued34[0] < cnt[0] || issued34[1] < cnt[1]) {
                 bool any = false;
 #pragma unroll
@@ -230,10 +231,10 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
 #pragma unroll
                         for (int k = 0; k < kTileM / 16; ++k) {     // GEMM 4: [GY | DH]^T * [A | X | 1], K = 16 points per step
                             const uint32_t aa = gd + k * 2 * kGdGroup, ba = xa + k * 2 * kXaGroup;
-                            // MN-major, no swizzle: SBO = bytes between 8-column core matrices (128), LBO = bytes between 8-point groups
-                            const uint64_t da = swap ? umma_desc(aa, 128, kGdGroup) : umma_desc(aa, kGdGroup, 128);
-                            const uint64_t db = swap ? umma_desc(ba, 128, kXaGroup) : umma_desc(ba, kXaGroup, 128);
-                            umma_bf16(tmem + kColDw2, da, db, kIdescDw, (dw_started || k > 0) ? 1u : 0u);
+                            // MN-major, no swizzle: SBO = bytes between 8-column core matrices (128), LBO = bytes between
+                            // 8-point groups (checked on B200 against the serial kernel: scripts/head_bwd_check.py)
+                            umma_bf16(tmem + kColDw2, umma_desc(aa, kGdGroup, 128), umma_desc(ba, kXaGroup, 128), kIdescDw,
+                                      (dw_started || k > 0) ? 1u : 0u);
                         }
                         dw_started = true;
                         umma_commit(&s_d34[g]);
