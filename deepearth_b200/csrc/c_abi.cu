@@ -224,6 +224,74 @@ size_t replica_workspace_bytes(const de_level_desc* levels, int n_levels, int n_
     return total;
 }
 
+// Levels per CTA group of the pair kernels: as many as keep the group's (gradient) tables L2 resident, up to the 16
+// that make a point's slice of the feature row a full 128 B line (F = 2).
+unsigned long long level_bytes(const de_level_desc& L, int n_features, bool backward, int table_dtype) {
+    const unsigned long long live = L.dense ? live_cells(L) : L.table_size;      // a dense level only touches (R+1)^D cells
+    const unsigned long long eb = (unsigned long long)n_features * (backward ? 4u : (table_dtype == DE_F16 ? 2u : 4u));
+    return live * eb;
+}
+int pick_group_size(bool pair, int n_features, int levels_per_group, int n, unsigned long long max_level_bytes) {
+    int G = levels_per_group;
+    if (G == 0) {
+        if (pair) {
+            G = 16;
+            while (G > 1 && (unsigned long long)G * max_level_bytes > kL2BudgetBytes) G >>= 1;
+        } else {
+            G = 8 / n_features;   // the G lanes of a point cover at least one 32 B sector of its row
+            if (G < 1) G = 1;
+        }
+    }
+    G = floor_pow2(G > n ? n : G);
+    if (G > de::kMaxGroup) G = de::kMaxGroup;
+    return G;
+}
+
+// Backward of one launch (levels [begin, end), equal D): when a group's slice of a gradient row is at most 64 B the
+// rows are first re-laid group-major in the workspace (regroup_kernel, misc.cu), so that each walk over the points
+// streams contiguous bytes instead of one 128 B HBM line per 16..64 B slice.
+struct RegroupPlan {
+    bool on;
+    int G, W;           // levels per group, floats per slice
+    size_t bytes;       // workspace the regrouped rows take
+};
+constexpr long long kRegroupMinPoints = 1ll << 20;
+RegroupPlan plan_regroup(const de_level_desc* levels, int begin, int end, int n_features, int64_t n_points, bool linear,
+                         uint32_t flags, int levels_per_group) {
+    RegroupPlan r{false, 0, 0, 0};
+    const int n = end - begin;
+    if (!de::pair_layout_supported(linear, n_features) || (flags & (DE_FLAG_STAGED_BWD | DE_FLAG_NO_REGROUP))) return r;
+    if (n_points < kRegroupMinPoints) return r;
+    unsigned long long max_level_bytes = 1;
+    for (int i = begin; i < end; ++i) {
+        const unsigned long long b = level_bytes(levels[i], n_features, true, DE_F32);
+        if (b > max_level_bytes) max_level_bytes = b;
+        if (levels[i].out_col != levels[begin].out_col + static_cast<uint32_t>((i - begin) * n_features)) return r;   // columns must be consecutive
+    }
+    r.G = pick_group_size(true, n_features, levels_per_group, n, max_level_bytes);
+    r.W = r.G * n_features;
+    const int n_cols = n * n_features;
+    if (r.W % 4 || r.W * 4 > 64 || n % r.G || n / r.G < 4) return r;
+    if ((n_cols + 4) * 32 * 4 > 48 * 1024 || levels[begin].out_col % 4) return r;
+    if ((unsigned long long)n_cols * (unsigned long long)n_points >= (1ull << 32)) return r;            // out_col carries the plane offset (uint32)
+    r.bytes = (static_cast<size_t>(n_cols) * static_cast<size_t>(n_points) * 4 + 255) & ~static_cast<size_t>(255);
+    r.on = true;
+    return r;
+}
+size_t regroup_workspace_bytes(const de_level_desc* levels, int n_levels, int n_features, int64_t n_points, bool linear,
+                               uint32_t flags, int levels_per_group) {
+    size_t total = 0;
+    int begin = 0;
+    while (begin < n_levels) {
+        int end = begin + 1;
+        while (end < n_levels && levels[end].n_dims == levels[begin].n_dims && end - begin < de::kMaxLaunchLevels) ++end;
+        const RegroupPlan r = plan_regroup(levels, begin, end, n_features, n_points, linear, flags, levels_per_group);
+        if (r.on) total += r.bytes;
+        begin = end;
+    }
+    return total;
+}
+
 // Forward only: picks the dense levels of [begin, end) whose live cells fit shared memory, packs them into
 // shared-memory groups and launches grid4d_forward_smem_kernel for them.  taken[i] marks the levels served.
 int run_smem_forward(const CallArgs& a, const de::EncodeParams& base, int begin, int end, bool* taken,
@@ -300,12 +368,14 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
     if (a.n_points == 0) return DE_OK;
     const bool linear = (a.flags & DE_INTERP_MASK) == DE_INTERP_LINEAR;
     size_t ws_off = 0;
+    size_t regroup_off = 0;         // regrouped gradient rows live behind the replicas
     if (op == Op::Backward && a.workspace) {
         const size_t used = replica_workspace_bytes(a.levels, a.n_levels, a.n_features, a.n_points, linear);
         if (used > 0 && used <= a.workspace_bytes) {
             cudaError_t e = cudaMemsetAsync(a.workspace, 0, used, stream);
             if (e != cudaSuccess) return cuda_fail(e, "workspace memset");
         }
+        regroup_off = (used + 255) & ~static_cast<size_t>(255);
     }
     int begin = 0;
     while (begin < a.n_levels) {
@@ -354,24 +424,30 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
                 }
             }
             pow2_all = pow2_all && is_pow2(L.table_size);
-            const unsigned long long live = L.dense ? live_cells(L) : L.table_size;   // a dense level only touches (R+1)^D cells
-            const unsigned long long eb = (unsigned long long)a.n_features * (op == Op::Backward ? 4u : (a.table_dtype == DE_F16 ? 2u : 4u));
-            if (live * eb > max_level_bytes) max_level_bytes = live * eb;
+            const unsigned long long lb = level_bytes(L, a.n_features, op == Op::Backward, a.table_dtype);
+            if (lb > max_level_bytes) max_level_bytes = lb;
         }
-        int G = a.levels_per_group;
-        if (G == 0) {
-            if (pair) {
-                // as many levels per CTA group as keep the group's (gradient) tables L2 resident, up to the
-                // 16 that make a point's slice of the feature row a full 128 B line (F = 2)
-                G = 16;
-                while (G > 1 && (unsigned long long)G * max_level_bytes > kL2BudgetBytes) G >>= 1;
-            } else {
-                G = 8 / a.n_features;   // the G lanes of a point cover at least one 32 B sector of its row
-                if (G < 1) G = 1;
+        const int G = pick_group_size(pair, a.n_features, a.levels_per_group, n, max_level_bytes);
+        if (op == Op::Backward && a.workspace && pair) {
+            const RegroupPlan rg = plan_regroup(a.levels, begin, end, a.n_features, a.n_points, linear, a.flags, a.levels_per_group);
+            if (rg.on && rg.G == G && regroup_off + rg.bytes <= a.workspace_bytes &&
+                reinterpret_cast<uintptr_t>(base.grad_out) % 16 == 0 && base.out_stride % 4 == 0) {
+                float* dst = reinterpret_cast<float*>(static_cast<char*>(a.workspace) + regroup_off);
+                int dev = 0, n_sms = 148;
+                if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+                cudaError_t e = de::launch_regroup(base.grad_out, base.out_stride, static_cast<int>(a.levels[begin].out_col),
+                                                   n * a.n_features, rg.W, dst, a.n_points, n_sms, stream);
+                if (e != cudaSuccess) return cuda_fail(e, "regroup launch");
+                // the backward kernels address grad_out + p * out_stride + out_col: plane g = level / G starts at
+                // g * n_points * W floats, rows are W floats apart
+                P.grad_out = dst;
+                P.out_stride = rg.W;
+                P.vec_rows = 1;
+                for (int i = 0; i < n; ++i)
+                    P.levels[i].out_col = static_cast<uint32_t>(static_cast<unsigned long long>(i / G) * a.n_points * rg.W + (i % G) * a.n_features);
+                regroup_off += rg.bytes;
             }
         }
-        G = floor_pow2(G > n ? n : G);
-        if (G > de::kMaxGroup) G = de::kMaxGroup;
         P.group_size = G;
         P.n_groups = (n + G - 1) / G;
         const int lanes_per_point = pair ? 2 * G : G;
@@ -501,8 +577,16 @@ DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels, co
 
 DE_API size_t de_grid4d_backward_workspace_bytes(const de_level_desc* levels_host, int n_levels, int n_features,
                                                  int64_t n_points, uint32_t flags) {
+    return de_grid4d_backward_workspace_bytes_ex(levels_host, n_levels, n_features, n_points, flags, 0);
+}
+
+DE_API size_t de_grid4d_backward_workspace_bytes_ex(const de_level_desc* levels_host, int n_levels, int n_features,
+                                                    int64_t n_points, uint32_t flags, int levels_per_group) {
     if (!levels_host || n_levels <= 0 || n_features < 1 || n_points <= 0) return 0;
-    return replica_workspace_bytes(levels_host, n_levels, n_features, n_points, (flags & DE_INTERP_MASK) == DE_INTERP_LINEAR);
+    const bool linear = (flags & DE_INTERP_MASK) == DE_INTERP_LINEAR;
+    const size_t rep = replica_workspace_bytes(levels_host, n_levels, n_features, n_points, linear);
+    const size_t rg = regroup_workspace_bytes(levels_host, n_levels, n_features, n_points, linear, flags, levels_per_group);
+    return rg ? ((rep + 255) & ~static_cast<size_t>(255)) + rg : rep;
 }
 
 DE_API int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_features,

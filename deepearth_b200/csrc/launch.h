@@ -45,6 +45,9 @@ struct ReplicaFoldParams {
     int n;
 };
 cudaError_t launch_replica_fold(const ReplicaFoldParams& P, cudaStream_t s);
+// gradient rows -> group-major slices dst[g][p][0..W) = src[p][c0 + g*W ..) (misc.cu)
+cudaError_t launch_regroup(const float* src, long long stride, int c0, int n_cols, int W, float* dst, long long n, int n_sms,
+                           cudaStream_t s);
 
 // tensor-core MLP head (mlp_head.cu): y = W2 * act(LN(W1 * x + b1)) + b2, hidden = out = 64
 struct MlpHeadParams {

@@ -164,4 +164,49 @@ cudaError_t launch_probe(void* table, long long n_entries, int entry_bytes, int 
     return cudaGetLastError();
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// regroup_kernel: gradient rows (n, stride) -> group-major slices  dst[g][p][0..W)  = src[p][c0 + g*W .. + W)
+//
+// The backward walks the points once per level group and reads a W = G*F float slice of every gradient row per
+// walk.  For HBM-resident tables G is small (c3: G = 2, W = 4 floats = 16 B) and each 16 B slice costs a full
+// 128 B line from HBM (ncu r01e: 80.6 GB read by one c3 backward, 68.7 GB of it this over-fetch).  One streaming
+// pass through shared memory turns the slices of a group into one contiguous array, so every later walk streams
+// exactly the bytes it uses.  HBM-bound: reads and writes n * n_cols * 4 bytes once, fully coalesced both ways.
+// ------------------------------------------------------------------------------------------------
+constexpr int kRegroupPoints = 32;
+
+__global__ void __launch_bounds__(256) regroup_kernel(const float* __restrict__ src, long long stride, int c0, int n_cols,
+                                                      int W, float* __restrict__ dst, long long n) {
+    extern __shared__ __align__(16) float tile[];                 // [kRegroupPoints][n_cols + 4]
+    const int pitch = n_cols + 4;
+    const int c4n = n_cols >> 2, w4n = W >> 2, n_groups = n_cols / W;
+    for (long long p0 = static_cast<long long>(blockIdx.x) * kRegroupPoints; p0 < n; p0 += static_cast<long long>(gridDim.x) * kRegroupPoints) {
+        for (int i = threadIdx.x; i < kRegroupPoints * c4n; i += 256) {
+            const int r = i / c4n, c4 = i - r * c4n;
+            if (p0 + r < n)
+                *reinterpret_cast<float4*>(tile + r * pitch + 4 * c4) = __ldcs(reinterpret_cast<const float4*>(src + (p0 + r) * stride + c0) + c4);
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_groups * kRegroupPoints * w4n; i += 256) {
+            const int w4 = i % w4n, r = (i / w4n) % kRegroupPoints, g = i / (w4n * kRegroupPoints);
+            if (p0 + r < n)
+                *reinterpret_cast<float4*>(dst + (static_cast<long long>(g) * n + p0 + r) * W + 4 * w4) =
+                    *reinterpret_cast<const float4*>(tile + r * pitch + g * W + 4 * w4);
+        }
+        __syncthreads();
+    }
+}
+
+cudaError_t launch_regroup(const float* src, long long stride, int c0, int n_cols, int W, float* dst, long long n, int n_sms,
+                           cudaStream_t s) {
+    const size_t smem = static_cast<size_t>(kRegroupPoints) * (n_cols + 4) * sizeof(float);
+    if (smem > 48 * 1024) return cudaErrorInvalidValue;
+    long long tiles = (n + kRegroupPoints - 1) / kRegroupPoints;
+    long long grid = static_cast<long long>(n_sms) * 8;
+    if (grid > tiles) grid = tiles;
+    regroup_kernel<<<static_cast<unsigned>(grid), 256, smem, s>>>(src, stride, c0, n_cols, W, dst, n);
+    return cudaGetLastError();
+}
+
 }  // namespace de

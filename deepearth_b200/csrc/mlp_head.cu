@@ -16,6 +16,8 @@
 //      activation run in registers, the bf16 hidden row goes back to shared memory as the A operand of
 //   4. the second GEMM (4 tcgen05.mma), whose accumulators are read back, biased and streamed to HBM.
 // The hidden activations never leave the SM.  Weights are staged once per CTA.
+#include <cstdlib>
+
 #include "launch.h"
 #include "mlp_common.cuh"
 
@@ -150,7 +152,7 @@ mlp_head_kernel(const __grid_constant__ MlpHeadParams P) {
                 for (int j = 0; j < kH; ++j) h[j] = fmaxf(h[j], 0.0f);
             } else if (P.activation == 2) {
 #pragma unroll
-                for (int j = 0; j < kH; ++j) h[j] = 0.5f * h[j] * (1.0f + erff(h[j] * 0.70710678118654752f));   // nn.GELU() (erf form)
+                for (int j = 0; j < kH; ++j) h[j] = gelu_fwd(h[j]);   // nn.GELU() (erf form)
             }
 #pragma unroll
             for (int k8 = 0; k8 < kH / 8; ++k8) {
@@ -203,8 +205,212 @@ mlp_head_kernel(const __grid_constant__ MlpHeadParams P) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Dual-tile version (default): a 256-thread CTA runs TWO independent 128-point pipelines ("halves") that share the
+// staged weights.  The hidden row is written over the consumed A1 tile and D2 over D1's TMEM columns, so a CTA needs
+// 24 KB + 2 x 32 KB (K1 = 128) and 128 TMEM columns: two CTAs = 16 warps per SM against 12 for the kernel above,
+// whose phases (load, GEMM 1, LayerNorm/GELU, GEMM 2, store) are serial per CTA and latency-bound (ncu r01e: issue
+// slots 25 % busy).  The halves synchronise with named barriers (bar.sync 1 + half, 128) and their own mbarriers.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void half_sync(int half) {
+    asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
+}
+
+// dynamic shared memory: B1 [64 x K1] | B2 [64 x 64] | per half: A [128 x K1] (A1, then the hidden rows A2 in its first 16 KB)
+template <int K1>
+__global__ void __launch_bounds__(2 * kMlpThreads, 2)
+mlp_head_dual_kernel(const __grid_constant__ MlpHeadParams P) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ float s_vec[4][kH];            // b1, ln gamma, ln beta, b2
+    __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ uint32_t s_tmem;
+
+    const int tid = threadIdx.x, half = tid >> 7, warp = (tid >> 5) & 3, lane = tid & 31;
+    unsigned char* sB1 = smem;
+    unsigned char* sB2 = sB1 + kH * K1 * 2;
+    unsigned char* sA = sB2 + kH * kH * 2 + half * (kTileM * (K1 > kH ? K1 : kH) * 2);
+
+    for (int c = tid; c < kH * (K1 / 8); c += 2 * kMlpThreads) {
+        const int n = c / (K1 / 8), k8 = c % (K1 / 8);
+        const uint4 v = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(P.w1) + static_cast<size_t>(n) * K1 + k8 * 8);
+        *reinterpret_cast<uint4*>(sB1 + canon_chunk_offset(n, k8, K1)) = v;
+    }
+    for (int c = tid; c < kH * (kH / 8); c += 2 * kMlpThreads) {
+        const int n = c / (kH / 8), k8 = c % (kH / 8);
+        const uint4 v = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(P.w2) + static_cast<size_t>(n) * kH + k8 * 8);
+        *reinterpret_cast<uint4*>(sB2 + canon_chunk_offset(n, k8, kH)) = v;
+    }
+    if (tid < kH) {
+        s_vec[0][tid] = P.b1 ? P.b1[tid] : 0.0f;
+        s_vec[1][tid] = P.ln_gamma ? P.ln_gamma[tid] : 1.0f;
+        s_vec[2][tid] = P.ln_beta ? P.ln_beta[tid] : 0.0f;
+        s_vec[3][tid] = P.b2 ? P.b2[tid] : 0.0f;
+    }
+    if (tid == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem + half * kH;                                   // this half's 64 accumulator columns
+    const uint32_t tmem_row = tmem + (static_cast<uint32_t>(warp * 32) << 16);   // this warp's 32 TMEM lanes
+    constexpr uint32_t kIdesc = umma_idesc(kH);
+    uint64_t* bar = &s_bar[half];
+    uint32_t phase = 0;
+    const int row = tid & 127;
+
+    for (int tile = 2 * blockIdx.x + half; tile < P.n_tiles; tile += 2 * gridDim.x) {
+        const long long p0 = static_cast<long long>(tile) * kTileM;
+        const int n_valid = static_cast<int>(P.n - p0 < kTileM ? P.n - p0 : kTileM);
+        const float* tile_base = P.x + p0 * P.x_stride;
+        const int xs = static_cast<int>(P.x_stride);
+
+        // ---- 1. features -> bf16 A tile (same lane mapping as above), in two rounds of 32 B x K1/16 per thread
+        //         (128 registers per thread are all this occupancy leaves)
+        constexpr int kIt = (4 * K1) / 32;
+        constexpr int kRound = kIt >= 2 ? kIt / 2 : kIt;
+#pragma unroll
+        for (int it0 = 0; it0 < kIt; it0 += kRound) {
+            float4 va[kRound], vb[kRound];
+#pragma unroll
+            for (int u = 0; u < kRound; ++u) {
+                const int c = lane + 32 * (it0 + u);
+                const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
+                const int k8 = (c % K1) >> 3;
+                va[u] = vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < n_valid) {
+                    const float4* src = reinterpret_cast<const float4*>(tile_base + (r * xs + k8 * 8));
+                    va[u] = __ldcs(src);
+                    vb[u] = __ldcs(src + 1);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kRound; ++u) {
+                const int c = lane + 32 * (it0 + u);
+                const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
+                const int k8 = (c % K1) >> 3;
+                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(r, k8, K1)) =
+                    make_uint4(pack_bf16(va[u].x, va[u].y), pack_bf16(va[u].z, va[u].w), pack_bf16(vb[u].x, vb[u].y), pack_bf16(vb[u].z, vb[u].w));
+            }
+        }
+        fence_async_smem();
+        tc_fence_before();
+        half_sync(half);
+
+        // ---- 2. GEMM 1: D[128 x 64] = A1[128 x K1] * W1^T ---------------------------------------
+        if (row == 0) {
+            tc_fence_after();
+            const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB1);
+#pragma unroll
+            for (int k = 0; k < K1 / 16; ++k)
+                umma_bf16(tmem, umma_desc(a0 + k * 256, 128, (K1 / 8) * 128), umma_desc(b0 + k * 256, 128, (K1 / 8) * 128),
+                          kIdesc, k > 0 ? 1u : 0u);
+            umma_commit(bar);
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        tc_fence_after();
+
+        // ---- 3. epilogue 1: bias + LayerNorm + activation; the bf16 hidden row overwrites the consumed A1 tile
+        {
+            float h[kH];
+            {
+                float lo[32];
+                tmem_ld32(tmem_row, lo);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) h[j] = lo[j] + s_vec[0][j];
+                tmem_ld32(tmem_row + 32, lo);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) h[32 + j] = lo[j] + s_vec[0][32 + j];
+            }
+            if (P.layernorm) {
+                float mean = 0.0f;
+#pragma unroll
+                for (int j = 0; j < kH; ++j) mean += h[j];
+                mean *= (1.0f / kH);
+                float var = 0.0f;
+#pragma unroll
+                for (int j = 0; j < kH; ++j) { const float d = h[j] - mean; var = fmaf(d, d, var); }
+                const float rstd = rsqrtf(var * (1.0f / kH) + P.ln_eps);
+#pragma unroll
+                for (int j = 0; j < kH; ++j) h[j] = fmaf((h[j] - mean) * rstd, s_vec[1][j], s_vec[2][j]);
+            }
+            if (P.activation == 1) {
+#pragma unroll
+                for (int j = 0; j < kH; ++j) h[j] = fmaxf(h[j], 0.0f);
+            } else if (P.activation == 2) {
+#pragma unroll
+                for (int j = 0; j < kH; ++j) h[j] = gelu_fwd(h[j]);   // nn.GELU() (erf form)
+            }
+#pragma unroll
+            for (int k8 = 0; k8 < kH / 8; ++k8) {
+                const uint4 v = make_uint4(pack_bf16(h[8 * k8], h[8 * k8 + 1]), pack_bf16(h[8 * k8 + 2], h[8 * k8 + 3]),
+                                           pack_bf16(h[8 * k8 + 4], h[8 * k8 + 5]), pack_bf16(h[8 * k8 + 6], h[8 * k8 + 7]));
+                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(row, k8, kH)) = v;
+            }
+        }
+        fence_async_smem();
+        tc_fence_before();
+        half_sync(half);
+
+        // ---- 4. GEMM 2: D[128 x 64] = A2[128 x 64] * W2^T (over D1's columns: every row has been read) ----
+        if (row == 0) {
+            tc_fence_after();
+            const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB2);
+#pragma unroll
+            for (int k = 0; k < kH / 16; ++k)
+                umma_bf16(tmem, umma_desc(a0 + k * 256, 128, (kH / 8) * 128), umma_desc(b0 + k * 256, 128, (kH / 8) * 128),
+                          kIdesc, k > 0 ? 1u : 0u);
+            umma_commit(bar);
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        tc_fence_after();
+
+        // ---- 5. epilogue 2: bias, stream the output row ----------------------------------------
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            float q[32];
+            tmem_ld32(tmem_row + 32 * hh, q);                   // warp-collective: outside the row predicate
+            if (row < n_valid) {
+                float4* dst = reinterpret_cast<float4*>(P.y + (p0 + row) * P.y_stride + 32 * hh);
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    __stcs(dst + u, make_float4(q[4 * u] + s_vec[3][32 * hh + 4 * u], q[4 * u + 1] + s_vec[3][32 * hh + 4 * u + 1],
+                                                q[4 * u + 2] + s_vec[3][32 * hh + 4 * u + 2], q[4 * u + 3] + s_vec[3][32 * hh + 4 * u + 3]));
+            }
+        }
+        tc_fence_before();           // the next tile's GEMM 1 overwrites these columns: order the loads before the barrier
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (tid < 32)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(s_tmem), "r"(kTmemCols) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
 // host launcher
 // ------------------------------------------------------------------------------------------------
+template <int K1>
+static cudaError_t launch_dual_k(const MlpHeadParams& P, int n_sms, cudaStream_t s) {
+    auto kernel = mlp_head_dual_kernel<K1>;
+    const size_t smem = static_cast<size_t>(kH) * K1 * 2 + kH * kH * 2 + 2 * static_cast<size_t>(kTileM) * (K1 > kH ? K1 : kH) * 2;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    int grid = n_sms * 2;                              // 2 CTAs (4 tiles in flight) per SM
+    const int pairs = (P.n_tiles + 1) / 2;
+    if (grid > pairs) grid = pairs;
+    kernel<<<grid, 2 * kMlpThreads, smem, s>>>(P);
+    return cudaGetLastError();
+}
+
 template <int K1>
 static cudaError_t launch_k(const MlpHeadParams& P, int n_sms, cudaStream_t s) {
     auto kernel = mlp_head_kernel<K1>;
@@ -227,6 +433,17 @@ bool mlp_head_supported(int in_dim, int hidden, int out_dim) {
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s) {
     P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
     if (P.n_tiles == 0) return cudaSuccess;
+    const char* v = getenv("DE_HEAD_FWD_VARIANT");       // A/B: 1 = the single-tile kernel
+    if (!(v && atoi(v) == 1)) {
+        switch (in_dim) {
+            case 32: return launch_dual_k<32>(P, n_sms, s);
+            case 48: return launch_dual_k<48>(P, n_sms, s);
+            case 64: return launch_dual_k<64>(P, n_sms, s);
+            case 96: return launch_dual_k<96>(P, n_sms, s);
+            case 128: return launch_dual_k<128>(P, n_sms, s);
+            default: return cudaErrorInvalidValue;
+        }
+    }
     switch (in_dim) {
         case 32: return launch_k<32>(P, n_sms, s);
         case 48: return launch_k<48>(P, n_sms, s);

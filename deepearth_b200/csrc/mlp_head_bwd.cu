@@ -250,9 +250,7 @@ mlp_head_bwd_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                         a = fmaxf(z, 0.0f);
                         g = z > 0.0f ? 1.0f : 0.0f;
                     } else if (P.activation == 2) {
-                        const float cdf = 0.5f * (1.0f + erff(z * 0.70710678118654752f));
-                        a = z * cdf;
-                        g = fmaf(z * 0.3989422804014327f, __expf(-0.5f * z * z), cdf);   // Phi(z) + z phi(z)
+                        gelu_fwd_bwd(z, a, g);
                     }
                     st_bf16(sBT, canon_elem_offset(j, row, kTileM), a);                  // A^T: row = hidden unit, column = point
                     d[j] = da[i] * g;

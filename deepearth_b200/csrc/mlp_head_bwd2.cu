@@ -265,7 +265,9 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
             // ---- this tile's feature rows: loads issued now, in flight while the tensor core finishes GEMM 3 / 4
             //      of the previous tile and its gradient rows are streamed out ---------------------------
             TileR<K1> tx;
+            TileR<kH> tg;
             tile_issue2<K1>(tx, P.x + p0 * P.x_stride, xs, n_valid, wq, lane);
+            tile_issue2<kH>(tg, P.gy + p0 * P.gy_stride, gs, n_valid, wq, lane);
             if (i > 0) {                                            // epilogue B of the previous tile
                 mbar_wait(&s_d34[grp], (i - 1) & 1);
                 tc_fence_after();
@@ -282,13 +284,9 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                     }
                 }
             }
-            // ---- stage X and GY ----------------------------------------------------------------------
+            // ---- stage X and GY (both already in flight) ---------------------------------------------
             tile_store2<K1>(tx, sXA, kH / 8, NB, wq, lane);
-            {
-                TileR<kH> tg;
-                tile_issue2<kH>(tg, P.gy + p0 * P.gy_stride, gs, n_valid, wq, lane);
-                tile_store2<kH>(tg, sGD, 0, 128, wq, lane);
-            }
+            tile_store2<kH>(tg, sGD, 0, 128, wq, lane);
             fence_async_smem();
             tc_fence_before();
             mbar_arrive(&s_in_full[grp]);
@@ -337,9 +335,7 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                                 a = fmaxf(z, 0.0f);
                                 g = z > 0.0f ? 1.0f : 0.0f;
                             } else if (P.activation == 2) {
-                                const float cdf = 0.5f * (1.0f + erff(z * 0.70710678118654752f));
-                                a = z * cdf;
-                                g = fmaf(z * 0.3989422804014327f, __expf(-0.5f * z * z), cdf);   // Phi(z) + z phi(z)
+                                gelu_fwd_bwd(z, a, g);
                             }
                             a8[u] = a;
                             d[j] = da[i] * g;

@@ -178,7 +178,7 @@ def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: 
     levels = pack_levels(specs, None, grad_ptrs)
     ws, ws_bytes = None, 0
     if use_replicas:
-        ws_bytes = int(lib.de_grid4d_backward_workspace_bytes(levels, len(specs), n_features, n, flags))
+        ws_bytes = int(lib.de_grid4d_backward_workspace_bytes_ex(levels, len(specs), n_features, n, flags, levels_per_group))
         if ws_bytes:
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=coords.device)   # caching allocator: no cudaMalloc in steady state
     with torch.cuda.device(coords.device):

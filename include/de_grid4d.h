@@ -56,7 +56,8 @@ extern "C" {
 #define DE_FLAG_STAGED_BWD 0x100u  /* backward: stage coordinates + gradient rows through TMA bulk copies + shared memory */
 #define DE_FLAG_SMEM_COARSE 0x200u /* forward: serve dense coarse levels from shared-memory copies of their tables      */
 #define DE_FLAG_NO_L2_HINTS 0x400u /* A/B: plain loads / reductions instead of evict_last tables + evict_first streams */
-#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE | DE_FLAG_NO_L2_HINTS)
+#define DE_FLAG_NO_REGROUP 0x800u  /* A/B: backward reads gradient-row slices in place instead of regrouping them first  */
+#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE | DE_FLAG_NO_L2_HINTS | DE_FLAG_NO_REGROUP)
 
 #define DE_MAX_DIMS 4
 #define DE_MAX_LEVELS_PER_CALL 256
@@ -139,6 +140,15 @@ DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels,
  */
 DE_API size_t de_grid4d_backward_workspace_bytes(const de_level_desc* levels_host, int n_levels,
                                                  int n_features, int64_t n_points, uint32_t flags);
+/*
+ * Same, for an explicit levels_per_group.  Besides the replicas the scratch holds the gradient rows re-laid
+ * group-major when a level group's slice of a row is <= 64 B (large tables => few levels per group): every
+ * walk over the points then streams contiguous bytes instead of one 128 B HBM line per slice.  A smaller
+ * workspace is accepted; the call then skips what does not fit.
+ */
+DE_API size_t de_grid4d_backward_workspace_bytes_ex(const de_level_desc* levels_host, int n_levels,
+                                                    int n_features, int64_t n_points, uint32_t flags,
+                                                    int levels_per_group);
 
 /*
  * fp32 master tables -> fp16 working tables, dst = half(src * scale), one launch

@@ -471,6 +471,42 @@ def test_smem_coarse_and_staged_paths_match_plain_path(dev, oracle, table_dtype)
     assert gerr <= GRAD_TOL, gerr
 
 
+@pytest.mark.parametrize("levels_per_group,n_extra", [(2, 0), (4, 1234), (8, 7)])
+def test_regrouped_gradient_rows_match_in_place_rows(dev, levels_per_group, n_extra):
+    """Backward with the gradient rows re-laid group-major first (regroup_kernel; taken when a level group's slice of
+    a row is <= 64 B, i.e. large tables) against the same backward reading the slices in place (itself checked
+    against the C oracle by the tests above)."""
+    from deepearth_b200 import _lib
+    from deepearth_b200 import functional as Fn
+    from deepearth_b200.functional import LevelSpec
+    T, L, F = 2 ** 18, 32, 2
+    n = 2 ** 20 + n_extra
+    g = torch.Generator(device=dev).manual_seed(21)
+    res = [16 * 2 ** (l % 12) + l for l in range(L)]
+    specs = [LevelSpec(table_size=T, resolution=R, dims=(0, 1, 3) if l % 2 else (1, 2, 3), out_col=4 + l * F,
+                       dense=(R + 1) ** 3 <= T) for l, R in enumerate(res)]
+    coords = torch.rand((n, 4), device=dev, generator=g)
+    gout = torch.randn((n, 4 + L * F + 4), device=dev, generator=g)         # rows wider than the level columns, c0 = 4
+
+    def run(flags):
+        flat = torch.zeros(L * T * F, device=dev)
+        ptrs = [flat.data_ptr() + 4 * l * T * F for l in range(L)]
+        Fn.encode_backward(specs, coords, gout, ptrs, F, True, levels_per_group=levels_per_group, extra_flags=flags)
+        return flat
+
+    lib = _lib.load()
+    flat0 = torch.zeros(1, device=dev)
+    lv = Fn.pack_levels(specs, None, [flat0.data_ptr()] * L)
+    lin = _lib.DE_INTERP_LINEAR
+    with_rg = lib.de_grid4d_backward_workspace_bytes_ex(lv, L, F, n, lin, levels_per_group)
+    without = lib.de_grid4d_backward_workspace_bytes_ex(lv, L, F, n, lin | _lib.DE_FLAG_NO_REGROUP, levels_per_group)
+    assert with_rg >= without + n * L * F * 4                                 # the regrouped rows are part of the scratch
+    got = run(0)
+    ref = run(_lib.DE_FLAG_NO_REGROUP)
+    denom = float(ref.abs().max())
+    assert float((got - ref).abs().max()) <= GRAD_TOL * denom
+
+
 # ---------------------------------------------------------------------------------------------------
 # tensor-core MLP head (tcgen05): Linear -> LayerNorm -> GELU -> Linear, hidden = out = 64
 # ---------------------------------------------------------------------------------------------------
