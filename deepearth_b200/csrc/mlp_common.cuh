@@ -90,6 +90,32 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<const uint32_t*>(&h);
 }
 
+// Row reductions over the 64 hidden units with four independent accumulator chains: a CTA keeps only 8..16 warps
+// resident, so a 64-long dependent FADD chain per statistic would sit exposed (ncu r01f: one issue per 12 cycles per warp).
+__device__ __forceinline__ float sum64(const float (&v)[kH]) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int j = 0; j < kH; j += 4) { a0 += v[j]; a1 += v[j + 1]; a2 += v[j + 2]; a3 += v[j + 3]; }
+    return (a0 + a1) + (a2 + a3);
+}
+__device__ __forceinline__ float sumsq_centered64(const float (&v)[kH], float mean) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int j = 0; j < kH; j += 4) {
+        const float d0 = v[j] - mean, d1 = v[j + 1] - mean, d2 = v[j + 2] - mean, d3 = v[j + 3] - mean;
+        a0 = fmaf(d0, d0, a0); a1 = fmaf(d1, d1, a1); a2 = fmaf(d2, d2, a2); a3 = fmaf(d3, d3, a3);
+    }
+    return (a0 + a1) + (a2 + a3);
+}
+__device__ __forceinline__ float dot64(const float (&a)[kH], const float (&b)[kH]) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int j = 0; j < kH; j += 4) {
+        a0 = fmaf(a[j], b[j], a0); a1 = fmaf(a[j + 1], b[j + 1], a1); a2 = fmaf(a[j + 2], b[j + 2], a2); a3 = fmaf(a[j + 3], b[j + 3], a3);
+    }
+    return (a0 + a1) + (a2 + a3);
+}
+
 // GELU (erf form, nn.GELU()): Phi(z) by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, far below the bf16 rounding of
 // the hidden row), 1 - Phi(|z|) = 0.5 t (a1 + t (a2 + ...)) exp(-z^2/2), t = 1 / (1 + p |z| / sqrt 2): one MUFU.RCP and
 // one MUFU.EX2 -- and the exponential is the one the derivative Phi(z) + z phi(z) needs.  ~16 instructions against

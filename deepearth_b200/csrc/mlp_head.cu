@@ -136,14 +136,8 @@ mlp_head_kernel(const __grid_constant__ MlpHeadParams P) {
                 for (int j = 0; j < 32; ++j) { h[j] = lo[j] + s_vec[0][j]; h[32 + j] = hi[j] + s_vec[0][32 + j]; }
             }
             if (P.layernorm) {
-                float mean = 0.0f;
-#pragma unroll
-                for (int j = 0; j < kH; ++j) mean += h[j];
-                mean *= (1.0f / kH);
-                float var = 0.0f;
-#pragma unroll
-                for (int j = 0; j < kH; ++j) { const float d = h[j] - mean; var = fmaf(d, d, var); }
-                const float rstd = rsqrtf(var * (1.0f / kH) + P.ln_eps);
+                const float mean = sum64(h) * (1.0f / kH);
+                const float rstd = rsqrtf(sumsq_centered64(h, mean) * (1.0f / kH) + P.ln_eps);
 #pragma unroll
                 for (int j = 0; j < kH; ++j) h[j] = fmaf((h[j] - mean) * rstd, s_vec[1][j], s_vec[2][j]);
             }
@@ -330,14 +324,8 @@ mlp_head_dual_kernel(const __grid_constant__ MlpHeadParams P) {
                 for (int j = 0; j < 32; ++j) h[32 + j] = lo[j] + s_vec[0][32 + j];
             }
             if (P.layernorm) {
-                float mean = 0.0f;
-#pragma unroll
-                for (int j = 0; j < kH; ++j) mean += h[j];
-                mean *= (1.0f / kH);
-                float var = 0.0f;
-#pragma unroll
-                for (int j = 0; j < kH; ++j) { const float d = h[j] - mean; var = fmaf(d, d, var); }
-                const float rstd = rsqrtf(var * (1.0f / kH) + P.ln_eps);
+                const float mean = sum64(h) * (1.0f / kH);
+                const float rstd = rsqrtf(sumsq_centered64(h, mean) * (1.0f / kH) + P.ln_eps);
 #pragma unroll
                 for (int j = 0; j < kH; ++j) h[j] = fmaf((h[j] - mean) * rstd, s_vec[1][j], s_vec[2][j]);
             }

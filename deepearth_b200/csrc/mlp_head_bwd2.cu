@@ -308,14 +308,8 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                 }
                 float rstd = 1.0f;
                 if (P.layernorm) {
-                    float mean = 0.0f;
-#pragma unroll
-                    for (int j = 0; j < kH; ++j) mean += v[j];
-                    mean *= (1.0f / kH);
-                    float var = 0.0f;
-#pragma unroll
-                    for (int j = 0; j < kH; ++j) { const float t = v[j] - mean; var = fmaf(t, t, var); }
-                    rstd = rsqrtf(var * (1.0f / kH) + P.ln_eps);
+                    const float mean = sum64(v) * (1.0f / kH);
+                    rstd = rsqrtf(sumsq_centered64(v, mean) * (1.0f / kH) + P.ln_eps);
 #pragma unroll
                     for (int j = 0; j < kH; ++j) v[j] = (v[j] - mean) * rstd;
                 }
@@ -357,15 +351,10 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                         for (int i = 0; i < 32; ++i) t[i] = d[32 * half + i] * v[32 * half + i];
                         acc_gamma[half] += colsum32(t, lane);
                     }
-                    float m1 = 0.0f, m2 = 0.0f;
 #pragma unroll
-                    for (int j = 0; j < kH; ++j) {
-                        d[j] *= s_vec[1][j];                    // dxhat
-                        m1 += d[j];
-                        m2 = fmaf(d[j], v[j], m2);
-                    }
-                    m1 *= (1.0f / kH);
-                    m2 *= (1.0f / kH);
+                    for (int j = 0; j < kH; ++j) d[j] *= s_vec[1][j];      // dxhat
+                    const float m1 = sum64(d) * (1.0f / kH);
+                    const float m2 = dot64(d, v) * (1.0f / kH);
 #pragma unroll
                     for (int j = 0; j < kH; ++j) d[j] = rstd * (d[j] - m1 - v[j] * m2);
                 }
