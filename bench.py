@@ -246,6 +246,7 @@ class Job:
         self.out_scale = 1.0 / self.plan.table_scale if self.plan.table_scale != 1.0 else 1.0
         self.use_replicas = True
         self.head_bwd = "tcgen05"
+        self.group_w = 0          # > 0: the head backward writes d(loss)/d(features) group-major for the hash-grid backward
 
     def forward(self):
         from deepearth_b200 import functional as Fn
@@ -257,7 +258,7 @@ class Job:
         from deepearth_b200 import functional as Fn
         Fn.encode_backward(self.plan.specs, self.coords, self.gout, self.grad_ptrs, self.F, self.linear,
                            levels_per_group=self.plan.bwd_levels_per_group, extra_flags=self.plan.extra_flags,
-                           use_replicas=self.use_replicas)
+                           use_replicas=self.use_replicas, group_width=self.group_w)
 
     # ---- configs[4] pieces ---------------------------------------------------------------------
     def prologue(self):
@@ -270,7 +271,7 @@ class Job:
         """Gradients of the head: the tcgen05 backward kernel (default) or, for A/B, a recompute through the fp32
         modules (cuBLAS + eager LayerNorm / GELU), which is what autograd does with fused_backward=False."""
         if self.head_bwd == "tcgen05":
-            g = self.head.backward_fused(self.out, self.gy)
+            g = self.head.backward_fused(self.out, self.gy, group_width=self.group_w)
             self.gout = g.pop("x")
             self.head_grads = g
             return
@@ -392,6 +393,9 @@ def run_gpu_arm(args, wl):
     job.head_bwd = args.head_bwd
     if job.head is not None:
         job.head.fused_backward = args.head_bwd == "tcgen05"
+        if args.head_bwd == "tcgen05" and world == 1 and not args.no_grouped_head:
+            job.group_w = Fn.backward_group_width(job.plan.specs, n, job.F, job.linear, job.plan.bwd_levels_per_group,
+                                                  job.plan.extra_flags)
 
     sync = None
     if world > 1 and not args.no_overlap:
@@ -578,7 +582,7 @@ def run_gpu_arm(args, wl):
                        "coords": wl["coords"], "levels": len(job.plan.specs), "features_per_level": job.F,
                        "table_size": wl["T"], "interpolation": "linear" if job.linear else "nearest",
                        "l2_policy": "inputs larger than L2 (coords+grad_out+out > 4 GiB per step); no flush",
-                       "l2_fetch_granularity": _gran.value,
+                       "l2_fetch_granularity": _gran.value, "head_grad_group_width": job.group_w,
                        "l2_persisting_bytes": _pl2.value, "l2_persisting_max_bytes": _pl2max.value,
                        "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"
                                       + (f" overlapped with the backward in {args.sync_chunks} level runs" if sync is not None else "")},
@@ -628,6 +632,7 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="N>1: one all-reduce after the backward instead of the overlapped slices")
     ap.add_argument("--sync-chunks", type=int, default=4, help="N>1: level runs the backward / all-reduce overlap is cut into")
     ap.add_argument("--head-bwd", default="tcgen05", choices=["tcgen05", "cublas"], help="c5: head backward kernel")
+    ap.add_argument("--no-grouped-head", action="store_true", help="c5 A/B: head backward writes row-major gradients (the hash-grid backward regroups them)")
     ap.add_argument("--sort-points", action="store_true", help="experiment: Morton-order the synthetic points before timing")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-replicas", action="store_true", help="backward without gradient replicas for contended coarse levels (A/B)")

@@ -17,6 +17,7 @@ ABI_VERSION = 2
 DE_F32, DE_F16, DE_F64 = 0, 1, 2
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS, DE_FLAG_NO_REGROUP = 0x100, 0x200, 0x400, 0x800
+DE_FLAG_GRAD_GROUPED = 0x1000
 DE_MAX_LEVELS_PER_CALL = 256
 
 c_void_p = ctypes.c_void_p
@@ -56,6 +57,7 @@ SIGNATURES = {
                                    c_void_p]),
     "de_grid4d_backward_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32]),
     "de_grid4d_backward_workspace_bytes_ex": (ctypes.c_size_t, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32, c_int]),
+    "de_grid4d_backward_group_width": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32, c_int]),
     "de_tables_to_f16": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_int, ctypes.POINTER(c_void_p), c_float,
                                  c_void_p]),
     "de_geo2xyzt_norm": (c_int, [c_void_p, c_int, c_void_p, c_int, ctypes.POINTER(ctypes.c_double),

@@ -280,6 +280,7 @@ RegroupPlan plan_regroup(const de_level_desc* levels, int begin, int end, int n_
 }
 size_t regroup_workspace_bytes(const de_level_desc* levels, int n_levels, int n_features, int64_t n_points, bool linear,
                                uint32_t flags, int levels_per_group) {
+    if (flags & DE_FLAG_GRAD_GROUPED) return 0;         // the producer wrote the group-major layout itself
     size_t total = 0;
     int begin = 0;
     while (begin < n_levels) {
@@ -428,7 +429,17 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
             if (lb > max_level_bytes) max_level_bytes = lb;
         }
         const int G = pick_group_size(pair, a.n_features, a.levels_per_group, n, max_level_bytes);
-        if (op == Op::Backward && a.workspace && pair) {
+        if (op == Op::Backward && (a.flags & DE_FLAG_GRAD_GROUPED)) {
+            // the caller (the head's backward kernel) already wrote the rows group-major: same addressing, no pass
+            const RegroupPlan rg = plan_regroup(a.levels, begin, end, a.n_features, a.n_points, linear,
+                                                a.flags & ~DE_FLAG_NO_REGROUP, a.levels_per_group);
+            if (!(begin == 0 && end == a.n_levels && pair && rg.on && rg.G == G && base.out_stride == rg.W))
+                return fail(DE_EINVAL, "DE_FLAG_GRAD_GROUPED: grad_out layout (W=%lld) does not match this call's level groups "
+                            "(de_grid4d_backward_group_width)", (long long)base.out_stride);
+            P.vec_rows = 1;
+            for (int i = 0; i < n; ++i)
+                P.levels[i].out_col = static_cast<uint32_t>(static_cast<unsigned long long>(i / G) * a.n_points * rg.W + (i % G) * a.n_features);
+        } else if (op == Op::Backward && a.workspace && pair) {
             const RegroupPlan rg = plan_regroup(a.levels, begin, end, a.n_features, a.n_points, linear, a.flags, a.levels_per_group);
             if (rg.on && rg.G == G && regroup_off + rg.bytes <= a.workspace_bytes &&
                 reinterpret_cast<uintptr_t>(base.grad_out) % 16 == 0 && base.out_stride % 4 == 0) {
@@ -557,9 +568,10 @@ DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels, co
     if (a.workspace && reinterpret_cast<uintptr_t>(a.workspace) % 16) return fail(DE_EALIGN, "workspace not 16-byte aligned");
     if (int rc = validate(a)) return rc;
     if (n_points > 0 && !grad_out) return fail(DE_EINVAL, "grad_out is NULL");
-    for (int i = 0; i < n_levels; ++i)
+    for (int i = 0; i < n_levels && !(flags & DE_FLAG_GRAD_GROUPED); ++i)
         if ((int64_t)levels_host[i].out_col + n_features > grad_stride)
             return fail(DE_EINVAL, "level %d: out_col %u + F %d exceeds grad_stride %lld", i, levels_host[i].out_col, n_features, (long long)grad_stride);
+    if ((flags & DE_FLAG_GRAD_GROUPED) && reinterpret_cast<uintptr_t>(grad_out) % 16) return fail(DE_EALIGN, "grouped grad_out not 16-byte aligned");
     de::EncodeParams P{};
     P.coords = coords;
     P.mask_a = mask_a;
@@ -587,6 +599,16 @@ DE_API size_t de_grid4d_backward_workspace_bytes_ex(const de_level_desc* levels_
     const size_t rep = replica_workspace_bytes(levels_host, n_levels, n_features, n_points, linear);
     const size_t rg = regroup_workspace_bytes(levels_host, n_levels, n_features, n_points, linear, flags, levels_per_group);
     return rg ? ((rep + 255) & ~static_cast<size_t>(255)) + rg : rep;
+}
+
+DE_API int de_grid4d_backward_group_width(const de_level_desc* levels_host, int n_levels, int n_features,
+                                          int64_t n_points, uint32_t flags, int levels_per_group) {
+    if (!levels_host || n_levels <= 0 || n_levels > de::kMaxLaunchLevels || n_features < 1 || n_points <= 0) return 0;
+    for (int i = 1; i < n_levels; ++i)
+        if (levels_host[i].n_dims != levels_host[0].n_dims) return 0;           // one launch only
+    const RegroupPlan rg = plan_regroup(levels_host, 0, n_levels, n_features, n_points, (flags & DE_INTERP_MASK) == DE_INTERP_LINEAR,
+                                        flags & ~DE_FLAG_NO_REGROUP, levels_per_group);
+    return rg.on && levels_host[0].out_col == 0 ? rg.W : 0;
 }
 
 DE_API int de_tables_to_f16(const de_level_desc* levels_host, int n_levels, int n_features,
@@ -680,6 +702,13 @@ DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_p
     if (!de::mlp_head_supported(in_dim, hidden, out_dim))
         return fail(DE_EUNSUPPORTED, "mlp_head_backward: in_dim=%d hidden=%d out_dim=%d", in_dim, hidden, out_dim);
     if (activation < 0 || activation > 2) return fail(DE_EINVAL, "mlp_head_backward: activation=%d", activation);
+    int gx_group_w = 0;
+    if (gx_stride < 0) {                       // group-major grad_x: slices of W = -gx_stride floats (include/de_grid4d.h)
+        gx_group_w = static_cast<int>(-gx_stride);
+        if (gx_group_w < 4 || (gx_group_w & (gx_group_w - 1)) || in_dim % gx_group_w)
+            return fail(DE_EINVAL, "mlp_head_backward: group width %d must be a power of two >= 4 dividing in_dim=%d", gx_group_w, in_dim);
+        gx_stride = in_dim;
+    }
     if (x_stride < in_dim || gx_stride < in_dim || gy_stride < out_dim) return fail(DE_EINVAL, "mlp_head_backward: row stride shorter than the row");
     const void* aligned[] = {x, grad_y, grad_x, w1_bf16, w1t_bf16, w2t_bf16};
     for (const void* q : aligned)
@@ -689,7 +718,7 @@ DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_p
     P.x = x; P.gy = grad_y; P.n = n_points; P.x_stride = x_stride; P.gy_stride = gy_stride;
     P.w1 = w1_bf16; P.w1t = w1t_bf16; P.w2t = w2t_bf16; P.b1 = b1; P.ln_gamma = ln_gamma; P.ln_beta = ln_beta;
     P.ln_eps = ln_eps; P.layernorm = layernorm ? 1 : 0; P.activation = activation;
-    P.dx = grad_x; P.dx_stride = gx_stride; P.dw1 = grad_w1; P.db1 = grad_b1; P.dgamma = grad_gamma; P.dbeta = grad_beta;
+    P.dx = grad_x; P.dx_stride = gx_stride; P.dx_group_w = gx_group_w; P.dw1 = grad_w1; P.db1 = grad_b1; P.dgamma = grad_gamma; P.dbeta = grad_beta;
     P.dw2 = grad_w2; P.db2 = grad_b2;
     int dev = 0, n_sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);

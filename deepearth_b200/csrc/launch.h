@@ -83,6 +83,8 @@ struct MlpHeadBwdParams {
     int activation;
     float* dx;                    // (n, in_dim) fp32 out
     long long dx_stride;
+    int dx_group_w;               // 0: rows of dx_stride floats; W (power of two >= 4): group-major dx[c / W][p][c % W], the
+                                  // layout de_grid4d_backward reads with DE_FLAG_GRAD_GROUPED (ping-pong kernel only)
     float* dw1;                   // (64, in_dim) fp32, accumulated (caller zeroes)
     float* db1;                   // (64,) accumulated, or NULL
     float* dgamma;                // (64,) accumulated, or NULL

@@ -386,7 +386,7 @@ cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaS
     // default: the ping-pong kernel of mlp_head_bwd2.cu; DE_HEAD_BWD_VARIANT=1 selects this file's serial kernel (A/B)
     const char* v = getenv("DE_HEAD_BWD_VARIANT");
     P.variant = v ? atoi(v) : 0;
-    if (!(P.variant & 1)) return launch_mlp_head_bwd_pp(P, in_dim, n_sms, s);
+    if (!(P.variant & 1) || P.dx_group_w) return launch_mlp_head_bwd_pp(P, in_dim, n_sms, s);
     P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
     if (P.n_tiles == 0) return cudaSuccess;
     switch (in_dim) {

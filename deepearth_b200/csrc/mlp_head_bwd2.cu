@@ -116,6 +116,28 @@ __device__ __forceinline__ void tile_store2(const TileR<KT>& t, unsigned char* d
     }
 }
 
+// Epilogue B: one row of D_dx (TMEM) -> dL/dx.  Row-major rows, or the group-major planes the hash-grid backward walks
+// (dx[c / W][p][c % W]: consecutive threads = consecutive points write consecutive 16 B pieces of one plane).
+template <int K1>
+__device__ __forceinline__ void store_dx_row(const MlpHeadBwdParams& P, uint32_t tmem_row, long long pr) {
+    const bool ok = pr < P.n;
+    const int W = P.dx_group_w ? P.dx_group_w : (1 << 30);          // row-major = one "plane" as wide as the row
+    const long long plane = P.dx_group_w ? P.n * P.dx_group_w : 0;  // floats between planes
+    float* pl = P.dx + (P.dx_group_w ? pr * P.dx_group_w : pr * P.dx_stride);
+    int within = 0;
+#pragma unroll
+    for (int c0 = 0; c0 < K1; c0 += 16) {
+        float q[16];
+        tmem_ld16b(tmem_row + c0, q);                               // warp-collective: outside the row predicate
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (ok) __stcs(reinterpret_cast<float4*>(pl + within), make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]));
+            within += 4;
+            if (within == W) { within = 0; pl += plane; }
+        }
+    }
+}
+
 }  // namespace
 
 // dynamic shared memory (bf16, canonical K-major, no swizzle):
@@ -271,18 +293,7 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
             if (i > 0) {                                            // epilogue B of the previous tile
                 mbar_wait(&s_d34[grp], (i - 1) & 1);
                 tc_fence_after();
-                const long long pr = p0 - p_step + row;
-                float* dst_row = P.dx + pr * P.dx_stride;
-#pragma unroll
-                for (int c0 = 0; c0 < K1; c0 += 16) {
-                    float q[16];
-                    tmem_ld16b(tmem_row + c0, q);                   // warp-collective: outside the row predicate
-                    if (pr < P.n) {
-                        float4* dst = reinterpret_cast<float4*>(dst_row + c0);
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) __stcs(dst + u, make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]));
-                    }
-                }
+                store_dx_row<K1>(P, tmem_row, p0 - p_step + row);
             }
             // ---- stage X and GY (both already in flight) ---------------------------------------------
             tile_store2<K1>(tx, sXA, kH / 8, NB, wq, lane);
@@ -374,17 +385,7 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
         if (cnt > 0) {                                              // epilogue B of the last tile
             mbar_wait(&s_d34[grp], (cnt - 1) & 1);
             tc_fence_after();
-            const long long pr = p0 - p_step + row;
-#pragma unroll
-            for (int c0 = 0; c0 < K1; c0 += 16) {
-                float q[16];
-                tmem_ld16b(tmem_row + c0, q);
-                if (pr < P.n) {
-                    float4* dst = reinterpret_cast<float4*>(P.dx + pr * P.dx_stride + c0);
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) __stcs(dst + u, make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]));
-                }
-            }
+            store_dx_row<K1>(P, tmem_row, p0 - p_step + row);
             if (P.layernorm) {
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {

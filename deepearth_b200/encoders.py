@@ -140,4 +140,32 @@ class Grid4DEncoder(nn.Module):
 
     def forward(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,
                 temporal_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
-        return self._project(self.encode_features(xyzt, spatial_mask, temporal_mask))
+        feats = self.encode_features(xyzt, spatial_mask, temporal_mask)
+        offered = self._offer_grouped_grads(feats)
+        try:
+            return self._project(feats)
+        finally:
+            if offered:
+                self._fused_head._grouped_next = None      # consumed by _HeadFunction.forward, or never used
+
+    def _offer_grouped_grads(self, feats: torch.Tensor) -> bool:
+        """Fused head + large tables: let the head's backward kernel write d(loss)/d(features) in the group-major
+        layout the hash-grid backward walks (functional.backward_group_width), instead of rows that the backward
+        would first regroup.  The features tensor never leaves forward(), so its gradient has exactly one producer
+        and one consumer; both sides share a per-call token."""
+        head = self._fused_head
+        if head is None and _cfg(self.config, "grid4d_fused_head", False) and not torch.is_autocast_enabled():
+            self._project(feats[:0])                       # resolves self._fused_head
+            head = self._fused_head
+        fn = feats.grad_fn
+        if not head or not getattr(head, "fused_backward", False) or fn is None or self._grad_sync is not None:
+            return False
+        if torch.is_autocast_enabled() or not hasattr(fn, "plan") or feats.shape[0] < (1 << 20):
+            return False
+        plan = fn.plan
+        W = Fn.backward_group_width(plan.specs, feats.shape[0], plan.n_features, plan.linear,
+                                    plan.bwd_levels_per_group, plan.extra_flags)
+        if W:
+            plan.grouped_token = object()
+            head._grouped_next = (plan.grouped_token, W)
+        return bool(W)

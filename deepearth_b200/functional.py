@@ -159,17 +159,25 @@ def encode_forward(specs: Sequence[LevelSpec], coords: torch.Tensor, table_ptrs:
 def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: torch.Tensor,
                     grad_ptrs: Sequence[int], n_features: int, linear: bool,
                     mask_a: Optional[torch.Tensor] = None, mask_b: Optional[torch.Tensor] = None,
-                    levels_per_group: int = 0, extra_flags: int = 0, use_replicas: bool = True) -> None:
-    """Accumulate table gradients into the fp32 buffers at ``grad_ptrs`` (caller zeroes them)."""
+                    levels_per_group: int = 0, extra_flags: int = 0, use_replicas: bool = True,
+                    group_width: int = 0) -> None:
+    """Accumulate table gradients into the fp32 buffers at ``grad_ptrs`` (caller zeroes them).
+
+    ``group_width`` = W > 0: ``grad_out``'s memory is already group-major, g[c // W][p][c % W] (what
+    ``backward_group_width`` returned and ``mlp_head_backward(..., group_width=W)`` wrote); 0: ordinary rows."""
     _require_cuda(coords, "coords")
     _require_cuda(grad_out, "grad_out")
     coords, stride = _coords_view(coords)
     n = coords.shape[0]
     if n == 0:
         return
-    if grad_out.dtype != torch.float32:
+    if group_width:
+        if grad_out.dtype != torch.float32 or not grad_out.is_contiguous():
+            raise ValueError("a group-major grad_out must be a contiguous float32 buffer")
+        extra_flags |= _lib.DE_FLAG_GRAD_GROUPED
+    elif grad_out.dtype != torch.float32:
         grad_out = grad_out.float()
-    if grad_out.dim() != 2 or grad_out.shape[0] != n or grad_out.stride(1) != 1:
+    if not group_width and (grad_out.dim() != 2 or grad_out.shape[0] != n or grad_out.stride(1) != 1):
         grad_out = grad_out.reshape(n, -1).contiguous()
     ma = _mask_u8(mask_a, n, coords.device)
     mb = _mask_u8(mask_b, n, coords.device)
@@ -184,9 +192,20 @@ def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: 
     with torch.cuda.device(coords.device):
         rc = lib.de_grid4d_backward(levels, len(specs), _ptr(coords), n, stride,
                                     n_features, _ptr(ma), _ptr(mb), _ptr(grad_out),
-                                    grad_out.stride(0) if n > 1 else grad_out.shape[1],
+                                    group_width if group_width else (grad_out.stride(0) if n > 1 else grad_out.shape[1]),
                                     flags, levels_per_group, _ptr(ws), ws_bytes, _stream_ptr(coords.device))
     _lib.check(rc, "de_grid4d_backward")
+
+
+def backward_group_width(specs: Sequence[LevelSpec], n_points: int, n_features: int, linear: bool,
+                         levels_per_group: int = 0, extra_flags: int = 0) -> int:
+    """W > 0 when ``encode_backward`` for these arguments would regroup the gradient rows (large tables => few levels
+    per group): a producer may then write g[c // W][p][c % W] itself and pass ``group_width=W``.  0 otherwise."""
+    if n_points <= 0:
+        return 0
+    flags = (_lib.DE_INTERP_LINEAR if linear else _lib.DE_INTERP_NEAREST) | extra_flags
+    levels = pack_levels(specs, None, [16] * len(specs))
+    return int(_lib.load().de_grid4d_backward_group_width(levels, len(specs), n_features, int(n_points), flags, levels_per_group))
 
 
 def tables_to_f16(specs: Sequence[LevelSpec], src_ptrs: Sequence[int], dst_ptrs: Sequence[int],
@@ -219,6 +238,7 @@ class EncodePlan:
         self.specs = list(specs)
         self.extra_flags = int(extra_flags)   # DE_FLAG_* A/B switches (include/de_grid4d.h)
         self.grad_sync = None                 # distributed.GradSync: overlapped all-reduce inside backward
+        self.grouped_token = None             # set per call by Grid4DEncoder.forward (fused head writes grads group-major)
         self.n_features = int(n_features)
         self.out_cols = int(out_cols)
         self.linear = bool(linear)
@@ -271,9 +291,18 @@ class Grid4DFunction(torch.autograd.Function):
                                     plan.linear, mask_a, mask_b, levels_per_group=plan.bwd_levels_per_group,
                                     extra_flags=plan.extra_flags)
         else:
+            W = 0
+            if plan.grouped_token is not None:
+                from .mlp_head import GROUPED_GRADS
+                tagged = GROUPED_GRADS.pop(plan.grouped_token, None)
+                if tagged is not None:
+                    if tagged[0] != grad_out.data_ptr() or not grad_out.is_contiguous():
+                        raise RuntimeError("Grid4DFunction.backward: the fused head wrote a group-major gradient buffer, but "
+                                           "autograd delivered a different tensor (features consumed more than once?)")
+                    W = tagged[1]
             encode_backward(plan.specs, coords, grad_out, [base + 4 * o for o in plan.grad_offsets],
                             plan.n_features, plan.linear, mask_a, mask_b,
-                            levels_per_group=plan.bwd_levels_per_group, extra_flags=plan.extra_flags)
+                            levels_per_group=plan.bwd_levels_per_group, extra_flags=plan.extra_flags, group_width=W)
         grads = []
         for i, shape in enumerate(ctx.weight_shapes):
             o = plan.grad_offsets[i]

@@ -58,8 +58,11 @@ def mlp_head_forward(x: torch.Tensor, w1_bf16: torch.Tensor, b1: Optional[torch.
 
 def mlp_head_backward(x: torch.Tensor, grad_y: torch.Tensor, w1_bf16: torch.Tensor, w1t_bf16: torch.Tensor,
                       w2t_bf16: torch.Tensor, b1, ln_gamma, ln_beta, ln_eps: float, layernorm: bool, activation: str,
-                      has_b2: bool = True):
-    """One tcgen05 kernel: (grad_x, grad_w1, grad_b1, grad_gamma, grad_beta, grad_w2, grad_b2), fp32."""
+                      has_b2: bool = True, group_width: int = 0):
+    """One tcgen05 kernel: (grad_x, grad_w1, grad_b1, grad_gamma, grad_beta, grad_w2, grad_b2), fp32.
+
+    ``group_width`` = W > 0: grad_x's memory is written group-major, g[c // W][p][c % W], for
+    ``functional.encode_backward(..., group_width=W)``; the returned tensor still has shape (n, in_dim)."""
     _require_cuda(x, "x")
     _require_cuda(grad_y, "grad_y")
     n, in_dim = x.shape
@@ -81,10 +84,17 @@ def mlp_head_backward(x: torch.Tensor, grad_y: torch.Tensor, w1_bf16: torch.Tens
             rc = lib.de_mlp_head_backward(_ptr(x), _ptr(grad_y), n, in_dim, x.stride(0), grad_y.stride(0), _ptr(w1_bf16),
                                           _ptr(w1t_bf16), _ptr(w2t_bf16), _ptr(b1), _ptr(ln_gamma), _ptr(ln_beta),
                                           float(ln_eps), int(bool(layernorm)), _ACT[activation], hidden, hidden,
-                                          _ptr(gx), gx.stride(0), _ptr(gw1), _ptr(gb1), _ptr(gg), _ptr(gbeta),
+                                          _ptr(gx), -int(group_width) if group_width else gx.stride(0), _ptr(gw1), _ptr(gb1), _ptr(gg), _ptr(gbeta),
                                           _ptr(gw2), _ptr(gb2), _stream_ptr(dev))
         _lib.check(rc, "de_mlp_head_backward")
     return gx, gw1.view(hidden, in_dim), gb1, gg, gbeta, gw2.view(hidden, hidden), gb2
+
+
+# token -> (data_ptr, W) of a gradient buffer the head backward wrote group-major; consumed (popped) by
+# functional.Grid4DFunction.backward of the same Grid4DEncoder.forward call.  The features tensor between the two
+# autograd nodes is internal to that call, so the gradient reaches the consumer as the very buffer written here;
+# the consumer checks the pointer and fails loudly otherwise.
+GROUPED_GRADS: dict = {}
 
 
 class _HeadFunction(torch.autograd.Function):
@@ -93,6 +103,8 @@ class _HeadFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, head, *params):
         ctx.head = head
+        ctx.grouped = head._grouped_next     # (token, W) set by Grid4DEncoder.forward for this call, or None
+        head._grouped_next = None
         ctx.save_for_backward(x)
         return head.fused(x)
 
@@ -102,8 +114,12 @@ class _HeadFunction(torch.autograd.Function):
         head = ctx.head
         params = list(head.seq.parameters())
         if head.fused_backward:
-            by_id = head.backward_fused(x, grad_y)
+            W = ctx.grouped[1] if (ctx.grouped and ctx.needs_input_grad[0]) else 0
+            by_id = head.backward_fused(x, grad_y, group_width=W)
             gx = by_id.pop("x") if ctx.needs_input_grad[0] else None
+            if W:
+                # tell the hash-grid backward (Grid4DFunction.backward, same token) that this buffer is group-major
+                GROUPED_GRADS[ctx.grouped[0]] = (gx.data_ptr(), W)
             gp = [by_id.get(id(p)) if ctx.needs_input_grad[2 + i] else None for i, p in enumerate(params)]
             return (gx, None, *gp)
         with torch.enable_grad():
@@ -143,6 +159,7 @@ class FusedProjection:
             raise TypeError(f"unsupported activation {acts[0]!r}")
         self._key = None
         self._w1 = self._w2 = self._w1t = self._w2t = None
+        self._grouped_next = None
 
     def supported(self) -> bool:
         return mlp_head_supported(self.lin1.in_features, self.lin1.out_features, self.lin2.out_features)
@@ -158,13 +175,14 @@ class FusedProjection:
             self._key = key
         return self._w1, self._w2
 
-    def backward_fused(self, x: torch.Tensor, grad_y: torch.Tensor) -> dict:
+    def backward_fused(self, x: torch.Tensor, grad_y: torch.Tensor, group_width: int = 0) -> dict:
         """Gradients by the tcgen05 backward kernel, keyed by id(parameter) (+ "x")."""
         w1, _ = self._weights()
         n = self.norm
         gx, gw1, gb1, gg, gbeta, gw2, gb2 = mlp_head_backward(
             x, grad_y, w1, self._w1t, self._w2t, self.lin1.bias, n.weight if n is not None else None,
-            n.bias if n is not None else None, n.eps if n is not None else 1e-5, n is not None, self.activation)
+            n.bias if n is not None else None, n.eps if n is not None else 1e-5, n is not None, self.activation,
+            group_width=group_width)
         out = {"x": gx, id(self.lin1.weight): gw1, id(self.lin2.weight): gw2}
         if self.lin1.bias is not None:
             out[id(self.lin1.bias)] = gb1

@@ -57,7 +57,8 @@ extern "C" {
 #define DE_FLAG_SMEM_COARSE 0x200u /* forward: serve dense coarse levels from shared-memory copies of their tables      */
 #define DE_FLAG_NO_L2_HINTS 0x400u /* A/B: plain loads / reductions instead of evict_last tables + evict_first streams */
 #define DE_FLAG_NO_REGROUP 0x800u  /* A/B: backward reads gradient-row slices in place instead of regrouping them first  */
-#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE | DE_FLAG_NO_L2_HINTS | DE_FLAG_NO_REGROUP)
+#define DE_FLAG_GRAD_GROUPED 0x1000u /* backward: grad_out is already group-major (see de_grid4d_backward_group_width)            */
+#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE | DE_FLAG_NO_L2_HINTS | DE_FLAG_NO_REGROUP | DE_FLAG_GRAD_GROUPED)
 
 #define DE_MAX_DIMS 4
 #define DE_MAX_LEVELS_PER_CALL 256
@@ -151,6 +152,16 @@ DE_API size_t de_grid4d_backward_workspace_bytes_ex(const de_level_desc* levels_
                                                     int levels_per_group);
 
 /*
+ * Producer-side regrouping.  When this returns W > 0, de_grid4d_backward for the same arguments would re-lay the
+ * gradient rows as  g[c / W][p][c % W]  (c = feature column, W = levels-per-group * n_features floats) before
+ * walking them.  A producer that can write that layout itself -- de_mlp_head_backward with gx_stride = -W --
+ * passes the buffer with DE_FLAG_GRAD_GROUPED and grad_stride = W, and the pass is skipped.  0 = not applicable
+ * (levels of several dimensionalities, first column not 0, small inputs, wide slices): use the row-major layout.
+ */
+DE_API int de_grid4d_backward_group_width(const de_level_desc* levels_host, int n_levels, int n_features,
+                                          int64_t n_points, uint32_t flags, int levels_per_group);
+
+/*
  * fp32 master tables -> fp16 working tables, dst = half(src * scale), one launch
  * for all levels (level i: src = levels_host[i].table (fp32), dst =
  * dst_tables[i]).  dst_tables_host: host array of n_levels device pointers.
@@ -205,6 +216,8 @@ DE_API int de_mlp_head_forward(const float* x, int64_t n_points, int in_dim, int
  * grad_w1 (64, in_dim), grad_b1, grad_gamma, grad_beta, grad_w2 (64, 64), grad_b2 (each (64,), any may be NULL
  * except the two weight gradients).  w1t_bf16 = W1 transposed (in_dim, 64), w2t_bf16 = W2 transposed (hidden, out).
  * Replaces autograd's LinearBackward / GeluBackward / NativeLayerNormBackward chain for models/encoders.py:47-52.
+ * gx_stride > 0: grad_x rows are gx_stride floats apart.  gx_stride = -W (W a power of two >= 4 dividing in_dim):
+ * grad_x is written group-major, grad_x[c / W][p][c % W] -- the layout de_grid4d_backward_group_width() describes.
  */
 DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_points, int in_dim,
                          int64_t x_stride, int64_t gy_stride,

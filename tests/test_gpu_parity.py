@@ -507,6 +507,47 @@ def test_regrouped_gradient_rows_match_in_place_rows(dev, levels_per_group, n_ex
     assert float((got - ref).abs().max()) <= GRAD_TOL * denom
 
 
+def test_fused_head_hands_group_major_gradients_to_the_encoder(dev, monkeypatch):
+    """Large tables + fused head: the head's backward kernel writes d(loss)/d(features) group-major and the hash-grid
+    backward walks it directly (no regroup pass).  Same gradients as the row-major hand-off, and the path is taken."""
+    import deepearth_b200 as de
+    from deepearth_b200 import functional as Fn
+    res = [2 ** i for i in range(4, 12)]
+    cfg = de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=2 ** 21, n_spatial_levels=8,
+                             n_temporal_levels=8, spatial_resolutions=res, temporal_resolutions=res,
+                             grid4d_mode="decomposed", grid4d_table_dtype="float16", grid4d_fused_head=True)
+    torch.manual_seed(7)
+    enc = de.Grid4DEncoder(cfg).to(dev)
+    n = 2 ** 20 + 3
+    g = torch.Generator(device=dev).manual_seed(9)
+    xyzt = torch.rand((n, 4), device=dev, generator=g)
+    gy = torch.randn((n, 64), device=dev, generator=g)
+    widths = []
+    real_backward = Fn.encode_backward
+
+    def spy(*a, **k):
+        widths.append(k.get("group_width", 0))
+        return real_backward(*a, **k)
+
+    monkeypatch.setattr(Fn, "encode_backward", spy)
+
+    def run():
+        for p in enc.parameters():
+            p.grad = None
+        enc(xyzt).backward(gy)
+        tables = torch.cat([p.grad.reshape(-1) for k, p in enc.named_parameters() if "hash_tables" in k])
+        head = torch.cat([p.grad.reshape(-1) for k, p in enc.named_parameters() if "projection" in k])
+        return tables, head
+
+    t_grouped, h_grouped = run()
+    assert widths and widths[-1] == 8, widths                     # 16 MiB gradient tables -> 4 levels per group x F = 2
+    monkeypatch.setattr(Fn, "backward_group_width", lambda *a, **k: 0)
+    t_rows, h_rows = run()
+    assert widths[-1] == 0
+    assert float((t_grouped - t_rows).abs().max()) <= GRAD_TOL * float(t_rows.abs().max())
+    assert float((h_grouped - h_rows).abs().max()) <= 1e-4 * float(h_rows.abs().max())
+
+
 # ---------------------------------------------------------------------------------------------------
 # tensor-core MLP head (tcgen05): Linear -> LayerNorm -> GELU -> Linear, hidden = out = 64
 # ---------------------------------------------------------------------------------------------------
