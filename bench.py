@@ -291,7 +291,18 @@ class Job:
                 runs += 1
                 prev, cnt = len(s.dims), 0
             cnt += 1
-        return 2 * runs + (3 if self.head is not None else 0)     # + prologue + head forward + head backward kernels
+        from deepearth_b200 import functional as Fn, _lib
+        extra = 0
+        # backward helpers: the regroup pass (unless the head wrote the group-major layout itself) and the replica fold
+        if not self.group_w and Fn.backward_group_width(self.plan.specs, self.n, self.F, self.linear,
+                                                        self.plan.bwd_levels_per_group, self.plan.extra_flags):
+            extra += 1
+        lin = _lib.DE_INTERP_LINEAR if self.linear else _lib.DE_INTERP_NEAREST
+        lv = Fn.pack_levels(self.plan.specs, None, self.grad_ptrs)
+        if self.use_replicas and _lib.load().de_grid4d_backward_workspace_bytes_ex(
+                lv, len(self.plan.specs), self.F, self.n, lin | _lib.DE_FLAG_NO_REGROUP, self.plan.bwd_levels_per_group):
+            extra += runs
+        return 2 * runs + extra + (3 if self.head is not None else 0)     # + prologue + head forward + head backward kernels
 
 
 # ---------------------------------------------------------------------------------------------------

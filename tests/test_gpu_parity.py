@@ -291,6 +291,66 @@ def test_frozen_tables_and_grad_accumulation(dev):
     assert float(g0.sum()) == pytest.approx(500 * 2, rel=1e-6)
 
 
+def test_training_step_contract_autocast_scaler_clip(dev):
+    """One optimiser step the way the reference's trainer drives the encoder (hpc/train_distrbuted.py:284-313:
+    autocast, GradScaler, unscale_ + clip_grad_norm_, AdamW) against the torch restatement of the reference
+    modules holding the same state dict; also state-dict interchange in both directions and .eval() / no_grad."""
+    import deepearth_b200 as de
+    from oracle.grid4d_torch import RefGrid4DFeatures
+    T = 2 ** 14
+    cfg = de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=T)
+
+    class RefEncoder(torch.nn.Module):                       # models/encoders.py:19-85, same attribute names
+        def __init__(self):
+            super().__init__()
+            f = RefGrid4DFeatures(hash_table_size=T)
+            self.spatial_encoder, self.temporal_encoder = f.spatial_encoder, f.temporal_encoder
+            self._features = [f]
+            self.projection = torch.nn.Sequential(torch.nn.Linear(48, 64), torch.nn.LayerNorm(64), torch.nn.GELU(),
+                                                  torch.nn.Linear(64, 64))
+
+        def forward(self, xyzt, spatial_mask=None, temporal_mask=None):
+            return self.projection(self._features[0](xyzt, spatial_mask, temporal_mask))
+
+    torch.manual_seed(11)
+    mine = de.Grid4DEncoder(cfg).to(dev)
+    ref = RefEncoder().to(dev)
+    with torch.no_grad():
+        for p in mine.parameters():
+            if p.dim() == 2 and p.shape[1] == 2:
+                p.uniform_(-0.5, 0.5)                        # gradients that survive the clip visibly
+    assert set(mine.state_dict().keys()) == set(ref.state_dict().keys())
+    ref.load_state_dict(mine.state_dict())                   # ours -> reference layout
+    mine.load_state_dict(ref.state_dict())                   # and back
+    g = torch.Generator(device=dev).manual_seed(12)
+    xyzt = torch.randn((20000, 4), device=dev, generator=g) * 0.6 + 0.3     # negative and > 1 coordinates included
+    smask = torch.rand(20000, device=dev, generator=g) > 0.2
+    target = torch.randn((20000, 64), device=dev, generator=g)
+
+    def step(model):
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-2)
+        scaler = torch.amp.GradScaler("cuda", init_scale=1024.0)
+        with torch.autocast("cuda", dtype=torch.float16):
+            loss = torch.nn.functional.mse_loss(model(xyzt, spatial_mask=smask).float(), target)
+        scaler.scale(loss).backward()
+        scaler.unscale_(opt)
+        norm = torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        scaler.step(opt)
+        scaler.update()
+        return float(loss.detach()), float(norm)
+
+    loss_m, norm_m = step(mine)
+    loss_r, norm_r = step(ref)
+    assert loss_m == pytest.approx(loss_r, rel=1e-5)
+    assert norm_m == pytest.approx(norm_r, rel=1e-4)
+    sd_m, sd_r = mine.state_dict(), ref.state_dict()
+    for k in sd_r:
+        assert float((sd_m[k] - sd_r[k]).abs().max()) <= 1e-4 * max(float(sd_r[k].abs().max()), 1e-6) + 1e-7, k
+    mine.eval(), ref.eval()
+    with torch.no_grad():
+        assert float((mine(xyzt) - ref(xyzt)).abs().max()) <= 1e-4
+
+
 # ---------------------------------------------------------------------------------------------------
 # BASELINE.json sizes: size-independent properties + the device-resident torch restatement
 # ---------------------------------------------------------------------------------------------------
