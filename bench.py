@@ -509,13 +509,13 @@ def run_gpu_arm(args, wl):
         host_geo, host_t = job.geo.cpu().pin_memory(), job.t.cpu().pin_memory()
         h2d_bytes = host_geo.numel() * 8 + host_t.numel() * 8
         params = job.weights + job.head_params
-        api = "GeospatialConverter.geodetic_to_xyzt_norm + Grid4DEncoder.forward (tcgen05 head) + autograd backward; pinned host geodetic points -> device every step (copy of step i+1 overlaps step i)"
+        api = "GeospatialConverter.geodetic_to_xyzt_norm + Grid4DEncoder.forward (tcgen05 head) + autograd backward; pinned host geodetic points -> device every step (copy of step i+1 overlaps step i); output checksum reduced + read back on a side stream during the backward"
         job.gout = job.head_grads = job.y = None
     else:
         host = job.coords.cpu().pin_memory()
         h2d_bytes = host.numel() * 4
         params = job.weights
-        api = "Grid4DEncoder.encode_features + autograd backward; pinned host xyzt -> device every step (copy of step i+1 overlaps step i)"
+        api = "Grid4DEncoder.encode_features + autograd backward; pinned host xyzt -> device every step (copy of step i+1 overlaps step i); output checksum reduced + read back on a side stream during the backward"
     del job.out      # the module allocates its own output
     torch.cuda.empty_cache()
 
@@ -535,27 +535,42 @@ def run_gpu_arm(args, wl):
         return bufs, ev
 
     pending = [fetch()]
+    # The step's result metric (fp64 sum of the forward output) is reduced and read back on a side stream as soon as
+    # the forward has finished, while the backward runs: what a training loop that logs a forward metric does.
+    metric_stream = torch.cuda.Stream(device=device)
+    metric_host = torch.zeros((), dtype=torch.float64).pin_memory()
 
     def e2e_step():
         for p in params:
             p.grad = None
         bufs, ev = pending.pop()
         pending.append(fetch())                      # next step's inputs travel while this step computes
-        torch.cuda.current_stream(device).wait_event(ev)
+        main = torch.cuda.current_stream(device)
+        main.wait_event(ev)
         for b in bufs:
-            b.record_stream(torch.cuda.current_stream(device))
+            b.record_stream(main)
         if job.head is not None:
             xyzt = job.conv.geodetic_to_xyzt_norm(bufs[0], bufs[1])
             res = job.enc(xyzt)
-            res.backward(job.gy)
+            gres = job.gy
         else:
             res = job.enc.encode_features(bufs[0])
-            res.backward(job.gout)
+            gres = job.gout
+        fwd_done = torch.cuda.Event()
+        fwd_done.record(main)
+        with torch.cuda.stream(metric_stream):
+            metric_stream.wait_event(fwd_done)
+            out_d = res.detach()
+            out_d.record_stream(metric_stream)
+            metric_host.copy_(Fn.sum_f32(out_d), non_blocking=True)
+            metric_done = torch.cuda.Event()
+            metric_done.record(metric_stream)
+        res.backward(gres)
         if world > 1 and sync is None:
             from deepearth_b200.distributed import allreduce_table_grads
             allreduce_table_grads(job.weights, average=True)
-        chk = Fn.sum_f32(res.detach())
-        return float(chk.item())          # device -> host read of the step's result
+        metric_done.synchronize()         # device -> host read of the step's result
+        return float(metric_host)
 
     for _ in range(3):
         e2e_step()

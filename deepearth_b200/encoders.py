@@ -11,6 +11,8 @@ fp16 working tables; masks zero the *coordinates* as the spec does (:1159-1164).
 """
 from __future__ import annotations
 
+import copy
+
 from typing import List, Optional
 
 import torch
@@ -82,14 +84,23 @@ class Grid4DEncoder(nn.Module):
 
     # ---- fused feature path -------------------------------------------------------------------------
     def _plan(self) -> EncodePlan:
-        specs, col = [], 0
-        for enc, mid in zip(self._encoders, self._mask_ids):
-            specs += enc.level_specs(out_col0=col, mask_id=mid)
-            col += enc.output_dim
         e0 = self._encoders[0]
-        plan = EncodePlan(specs, e0.n_features_per_level, self.feature_dim, e0.interpolation == "linear",
-                          e0.table_dtype, e0.table_scale, e0.levels_per_group, e0.bwd_levels_per_group,
-                          e0.extra_flags)
+        key = (tuple(e._geometry_key() + (e.dims,) for e in self._encoders), tuple(self._mask_ids), e0.interpolation,
+               e0.table_dtype, e0.table_scale, e0.levels_per_group, e0.bwd_levels_per_group, e0.extra_flags)
+        cache = self.__dict__.setdefault("_plan_cache", {})
+        plan = cache.get(key)
+        if plan is None:
+            specs, col = [], 0
+            for enc, mid in zip(self._encoders, self._mask_ids):
+                specs += enc.level_specs(out_col0=col, mask_id=mid)
+                col += enc.output_dim
+            plan = EncodePlan(specs, e0.n_features_per_level, self.feature_dim, e0.interpolation == "linear",
+                              e0.table_dtype, e0.table_scale, e0.levels_per_group, e0.bwd_levels_per_group,
+                              e0.extra_flags)
+            if len(cache) > 16:
+                cache.clear()
+            cache[key] = plan
+        plan = copy.copy(plan)          # per-call fields live on the copy; the level list is shared (and packed once)
         plan.grad_sync = self._grad_sync
         return plan
 
@@ -110,12 +121,10 @@ class Grid4DEncoder(nn.Module):
             raise ValueError(f"xyzt must be (B, 4), got {tuple(xyzt.shape)}")
         Fn._require_cuda(xyzt, "xyzt")
         weights: List[torch.Tensor] = []
-        ptrs: Optional[List[int]] = [] if self._encoders[0].table_dtype == torch.float16 else None
         for enc in self._encoders:
             weights += enc.weights()
-            if ptrs is not None:
-                ptrs += enc.working_ptrs()
         Fn._require_cuda(weights[0], "hash table weights")
+        ptrs = self._working_ptrs(weights) if self._encoders[0].table_dtype == torch.float16 else None
         if self.mode == "decomposed" and (spatial_mask is not None or temporal_mask is not None):
             xyzt = xyzt.clone()                       # SPECIFICATIONS.MD:1159-1164: mask coordinates
             if spatial_mask is not None:
@@ -124,6 +133,27 @@ class Grid4DEncoder(nn.Module):
                 xyzt[~temporal_mask.bool(), 3] = 0
             spatial_mask = temporal_mask = None
         return Grid4DFunction.apply(xyzt, spatial_mask, temporal_mask, self._plan(), ptrs, *weights)
+
+    def _working_ptrs(self, weights: List[torch.Tensor]) -> List[int]:
+        """fp16 working tables of ALL grids, refreshed by ONE de_tables_to_f16 launch when the fp32 parameters may have
+        changed (same rule as MultiResolutionHashEncoding.working_ptrs, without one launch + host round per grid)."""
+        dev = weights[0].device
+        ptrs: List[int] = []
+        fresh = True
+        for enc in self._encoders:
+            had = enc._work is not None and enc._work.device == dev
+            ptrs += enc._ensure_work(dev)
+            fresh = fresh and had
+        key = (dev, tuple(w._version for w in weights), tuple(w.data_ptr() for w in weights))
+        if not fresh or key != self.__dict__.get("_work_key_all") or (self.training and torch.is_grad_enabled()):
+            e0 = self._encoders[0]
+            with torch.no_grad():
+                Fn.tables_to_f16(self._plan().specs, [w.data_ptr() for w in weights], ptrs, e0.n_features_per_level,
+                                 e0.table_scale, dev)
+            self.__dict__["_work_key_all"] = key
+            for enc in self._encoders:
+                enc._work_key = None          # a stand-alone call of one grid re-derives its own key
+        return ptrs
 
     def _project(self, feats: torch.Tensor) -> torch.Tensor:
         # opt-in (config.grid4d_fused_head = True): a hidden_dim = 64 head runs as one bf16 tcgen05 kernel

@@ -13,6 +13,8 @@ arguments add multilinear interpolation, the dense-index fallback and fp16 worki
 """
 from __future__ import annotations
 
+import copy
+
 from typing import List, Optional, Sequence
 
 import torch
@@ -77,13 +79,26 @@ class MultiResolutionHashEncoding(nn.Module):
     def output_dim(self) -> int:
         return self.n_levels * self.n_features_per_level
 
+    def _geometry_key(self):
+        return (self.hash_table_size, self.n_levels, self.n_features_per_level, self.dense_fallback,
+                tuple(int(r) for r in self.resolutions[:self.n_levels]))
+
     def level_specs(self, dims: Optional[Sequence[int]] = None, out_col0: int = 0, mask_id: int = 0) -> List[LevelSpec]:
+        """Level geometry (cached: callers get the same list object for the same geometry and must not mutate it)."""
         dims = tuple(dims) if dims is not None else self.dims
-        F = self.n_features_per_level
-        return [LevelSpec(table_size=self.hash_table_size, resolution=int(R), dims=dims, out_col=out_col0 + l * F,
-                          dense=self.dense_fallback and dense_fits(R, len(dims), self.hash_table_size),
-                          mask_id=mask_id)
-                for l, R in enumerate(self.resolutions[:self.n_levels])]
+        key = (dims, out_col0, mask_id, self._geometry_key())
+        cache = self.__dict__.setdefault("_spec_cache", {})
+        specs = cache.get(key)
+        if specs is None:
+            F = self.n_features_per_level
+            specs = [LevelSpec(table_size=self.hash_table_size, resolution=int(R), dims=dims, out_col=out_col0 + l * F,
+                               dense=self.dense_fallback and dense_fits(R, len(dims), self.hash_table_size),
+                               mask_id=mask_id)
+                     for l, R in enumerate(self.resolutions[:self.n_levels])]
+            if len(cache) > 16:
+                cache.clear()
+            cache[key] = specs
+        return specs
 
     def weights(self) -> List[torch.Tensor]:
         return [t.weight for t in self.hash_tables]
@@ -103,6 +118,16 @@ class MultiResolutionHashEncoding(nn.Module):
             self._work_key = key
         per = self.hash_table_size * self.n_features_per_level * 2
         return [self._work.data_ptr() + l * per for l in range(self.n_levels)]
+
+    def _ensure_work(self, dev: torch.device) -> List[int]:
+        """Allocate the fp16 working copy if needed; returns its per-level device pointers."""
+        if self._work is None or self._work.device != dev:
+            self._work = torch.empty((self.n_levels, self.hash_table_size, self.n_features_per_level),
+                                     dtype=torch.float16, device=dev)
+            self._work_key = None
+        per = self.hash_table_size * self.n_features_per_level * 2
+        base = self._work.data_ptr()
+        return [base + l * per for l in range(self.n_levels)]
 
     @torch.no_grad()
     def refresh_tables(self) -> None:
@@ -134,9 +159,19 @@ class MultiResolutionHashEncoding(nn.Module):
         return Fn.hash_indices([spec], coords, linear=False)[0, 0]
 
     def plan(self, dims: Optional[Sequence[int]] = None) -> EncodePlan:
-        return EncodePlan(self.level_specs(dims), self.n_features_per_level, self.output_dim,
-                          self.interpolation == "linear", self.table_dtype, self.table_scale,
-                          self.levels_per_group, self.bwd_levels_per_group, self.extra_flags)
+        dims = tuple(dims) if dims is not None else self.dims
+        key = (dims, self._geometry_key(), self.interpolation, self.table_dtype, self.table_scale,
+               self.levels_per_group, self.bwd_levels_per_group, self.extra_flags)
+        cache = self.__dict__.setdefault("_plan_cache", {})
+        plan = cache.get(key)
+        if plan is None:
+            plan = EncodePlan(self.level_specs(dims), self.n_features_per_level, self.output_dim,
+                              self.interpolation == "linear", self.table_dtype, self.table_scale,
+                              self.levels_per_group, self.bwd_levels_per_group, self.extra_flags)
+            if len(cache) > 16:
+                cache.clear()
+            cache[key] = plan
+        return copy.copy(plan)          # per-call fields (grad_sync, grouped_token) live on the copy
 
     def forward(self, coords: torch.Tensor) -> torch.Tensor:
         if coords.dim() != 2 or coords.shape[1] < self.coords_dim:
