@@ -404,7 +404,7 @@ def run_gpu_arm(args, wl):
     job.head_bwd = args.head_bwd
     if job.head is not None:
         job.head.fused_backward = args.head_bwd == "tcgen05"
-        if args.head_bwd == "tcgen05" and world == 1 and not args.no_grouped_head:
+        if args.head_bwd == "tcgen05" and not args.no_grouped_head:
             job.group_w = Fn.backward_group_width(job.plan.specs, n, job.F, job.linear, job.plan.bwd_levels_per_group,
                                                   job.plan.extra_flags)
 
@@ -413,6 +413,9 @@ def run_gpu_arm(args, wl):
         from deepearth_b200.distributed import GradSync
         sync = GradSync(average=False, chunks=args.sync_chunks)
         job.enc.enable_grad_sync(average=True, chunks=args.sync_chunks)     # the e2e (autograd) path
+        if job.group_w and not sync.grouped_ok(job.plan.specs, n, job.F, job.linear, job.plan.bwd_levels_per_group,
+                                               job.plan.extra_flags, job.group_w):
+            job.group_w = 0
 
     def step(ev=None):
         job.flat_grad.zero_()
@@ -433,7 +436,8 @@ def run_gpu_arm(args, wl):
         if sync is not None:
             # backward + all-reduce overlapped (distributed.GradSync): kernels_ms.allreduce is the exposed tail only
             sync.backward(job.plan.specs, job.coords, job.gout, job.flat_grad, job.plan.grad_offsets, job.F, job.linear,
-                          levels_per_group=job.plan.bwd_levels_per_group, extra_flags=job.plan.extra_flags)
+                          levels_per_group=job.plan.bwd_levels_per_group, extra_flags=job.plan.extra_flags,
+                          group_width=job.group_w)
             if ev:
                 ev[2].record()
                 ev[3].record()

@@ -96,6 +96,7 @@ void fill_level(const de_level_desc& L, de::LevelParams& o) {
     o.res_f = static_cast<float>(L.resolution);   // Python int -> fp32 scalar, round to nearest
     o.res_p1 = L.resolution + 1u;
     o.out_col = L.out_col;
+    o.pad0 = 0;
     for (int d = 0; d < 4; ++d) o.dim[d] = L.dim[d];
     o.dense = L.dense ? 1 : 0;
     o.pow2 = is_pow2(L.table_size) ? 1 : 0;
@@ -273,7 +274,6 @@ RegroupPlan plan_regroup(const de_level_desc* levels, int begin, int end, int n_
     const int n_cols = n * n_features;
     if (r.W % 4 || r.W * 4 > 64 || n % r.G || n / r.G < 4) return r;
     if ((n_cols + 4) * 32 * 4 > 48 * 1024 || levels[begin].out_col % 4) return r;
-    if ((unsigned long long)n_cols * (unsigned long long)n_points >= (1ull << 32)) return r;            // out_col carries the plane offset (uint32)
     r.bytes = (static_cast<size_t>(n_cols) * static_cast<size_t>(n_points) * 4 + 255) & ~static_cast<size_t>(255);
     r.on = true;
     return r;
@@ -438,7 +438,7 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
                             "(de_grid4d_backward_group_width)", (long long)base.out_stride);
             P.vec_rows = 1;
             for (int i = 0; i < n; ++i)
-                P.levels[i].out_col = static_cast<uint32_t>(static_cast<unsigned long long>(i / G) * a.n_points * rg.W + (i % G) * a.n_features);
+                P.levels[i].out_col = static_cast<unsigned long long>(i / G) * a.n_points * rg.W + (i % G) * a.n_features;
         } else if (op == Op::Backward && a.workspace && pair) {
             const RegroupPlan rg = plan_regroup(a.levels, begin, end, a.n_features, a.n_points, linear, a.flags, a.levels_per_group);
             if (rg.on && rg.G == G && regroup_off + rg.bytes <= a.workspace_bytes &&
@@ -455,7 +455,7 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
                 P.out_stride = rg.W;
                 P.vec_rows = 1;
                 for (int i = 0; i < n; ++i)
-                    P.levels[i].out_col = static_cast<uint32_t>(static_cast<unsigned long long>(i / G) * a.n_points * rg.W + (i % G) * a.n_features);
+                    P.levels[i].out_col = static_cast<unsigned long long>(i / G) * a.n_points * rg.W + (i % G) * a.n_features;
                 regroup_off += rg.bytes;
             }
         }

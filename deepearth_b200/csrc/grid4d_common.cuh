@@ -26,10 +26,12 @@ __device__ __constant__ const uint64_t kPrime64[4] = {1ull, 2654435761ull, 80545
 struct LevelParams {
     const void* table;  // (T,F) entries
     float* grad;        // (T,F) fp32 accumulators (backward)
+    unsigned long long out_col;   // float offset of the level's slice inside a row (or, for regrouped gradient
+                                  // rows, plane offset + position inside the slice: can exceed 2^32)
     uint32_t T;
     float res_f;        // (float)R
     uint32_t res_p1;    // R+1: dense stride base
-    uint32_t out_col;
+    uint32_t pad0;
     uint8_t dim[4];
     uint8_t dense;
     uint8_t pow2;       // T is a power of two: 32-bit hash fast path is bit-identical

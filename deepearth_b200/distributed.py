@@ -82,18 +82,42 @@ class GradSync:
         k = min(self.chunks, n_levels)
         return [shard_bounds(n_levels, i, k) for i in range(k)]
 
+    def grouped_ok(self, specs, n_points: int, n_features: int, linear: bool, levels_per_group: int, extra_flags: int,
+                   group_width: int) -> bool:
+        """True when a group-major gradient buffer of slice width ``group_width`` (functional.backward_group_width of the
+        whole level list) can be walked run by run: every run must choose the same levels-per-group on its own."""
+        import dataclasses
+        from . import functional as Fn
+        if not group_width or group_width % n_features:
+            return False
+        G = group_width // n_features
+        for b, e in self.level_runs(len(specs)):
+            if b % G or e % G:
+                return False
+            c0 = specs[b].out_col
+            rebased = [dataclasses.replace(s, out_col=s.out_col - c0) for s in specs[b:e]]
+            if Fn.backward_group_width(rebased, n_points, n_features, linear, levels_per_group, extra_flags) != group_width:
+                return False
+        return True
+
     def backward(self, specs, coords, grad_out, flat: torch.Tensor, grad_offsets, n_features: int, linear: bool,
-                 mask_a=None, mask_b=None, levels_per_group: int = 0, extra_flags: int = 0) -> None:
-        """flat (zeroed) <- all-reduced table gradients of this rank's points."""
+                 mask_a=None, mask_b=None, levels_per_group: int = 0, extra_flags: int = 0, group_width: int = 0) -> None:
+        """flat (zeroed) <- all-reduced table gradients of this rank's points.  ``group_width`` = W > 0: ``grad_out`` is the
+        group-major buffer g[c // W][p][c % W] (see functional.encode_backward); each run walks its own planes."""
         from . import functional as Fn
         dev = flat.device
         main = torch.cuda.current_stream(dev)
         side = self.stream(dev)
         base = flat.data_ptr()
         ends = list(grad_offsets[1:]) + [flat.numel()]
+        n = coords.shape[0]
+        G = group_width // n_features if group_width else 0
+        planes = grad_out.reshape(-1) if group_width else None
         for b, e in self.level_runs(len(specs)):
-            Fn.encode_backward(specs[b:e], coords, grad_out, [base + 4 * o for o in grad_offsets[b:e]], n_features,
-                               linear, mask_a, mask_b, levels_per_group=levels_per_group, extra_flags=extra_flags)
+            go = planes[(b // G) * n * group_width:(e // G) * n * group_width] if group_width else grad_out
+            Fn.encode_backward(specs[b:e], coords, go, [base + 4 * o for o in grad_offsets[b:e]], n_features,
+                               linear, mask_a, mask_b, levels_per_group=levels_per_group, extra_flags=extra_flags,
+                               group_width=group_width)
             ready = torch.cuda.Event()
             ready.record(main)
             side.wait_event(ready)

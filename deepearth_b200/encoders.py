@@ -188,13 +188,16 @@ class Grid4DEncoder(nn.Module):
             self._project(feats[:0])                       # resolves self._fused_head
             head = self._fused_head
         fn = feats.grad_fn
-        if not head or not getattr(head, "fused_backward", False) or fn is None or self._grad_sync is not None:
+        if not head or not getattr(head, "fused_backward", False) or fn is None:
             return False
         if torch.is_autocast_enabled() or not hasattr(fn, "plan") or feats.shape[0] < (1 << 20):
             return False
         plan = fn.plan
         W = Fn.backward_group_width(plan.specs, feats.shape[0], plan.n_features, plan.linear,
                                     plan.bwd_levels_per_group, plan.extra_flags)
+        if W and self._grad_sync is not None and not self._grad_sync.grouped_ok(
+                plan.specs, feats.shape[0], plan.n_features, plan.linear, plan.bwd_levels_per_group, plan.extra_flags, W):
+            W = 0                                          # the overlapped backward walks level runs: they must agree on W
         if W:
             plan.grouped_token = object()
             head._grouped_next = (plan.grouped_token, W)

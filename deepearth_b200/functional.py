@@ -311,21 +311,21 @@ class Grid4DFunction(torch.autograd.Function):
         coords, mask_a, mask_b = ctx.saved_tensors
         flat = torch.zeros(plan.grad_numel, dtype=torch.float32, device=grad_out.device)
         base = flat.data_ptr()
+        W = 0
+        if plan.grouped_token is not None:
+            from .mlp_head import GROUPED_GRADS
+            tagged = GROUPED_GRADS.pop(plan.grouped_token, None)
+            if tagged is not None:
+                if tagged[0] != grad_out.data_ptr() or not grad_out.is_contiguous():
+                    raise RuntimeError("Grid4DFunction.backward: the fused head wrote a group-major gradient buffer, but "
+                                       "autograd delivered a different tensor (features consumed more than once?)")
+                W = tagged[1]
         if plan.grad_sync is not None:
             # data parallel: all-reduce slices of the flat buffer on a side stream while later level runs scatter
             plan.grad_sync.backward(plan.specs, coords, grad_out, flat, plan.grad_offsets, plan.n_features,
                                     plan.linear, mask_a, mask_b, levels_per_group=plan.bwd_levels_per_group,
-                                    extra_flags=plan.extra_flags)
+                                    extra_flags=plan.extra_flags, group_width=W)
         else:
-            W = 0
-            if plan.grouped_token is not None:
-                from .mlp_head import GROUPED_GRADS
-                tagged = GROUPED_GRADS.pop(plan.grouped_token, None)
-                if tagged is not None:
-                    if tagged[0] != grad_out.data_ptr() or not grad_out.is_contiguous():
-                        raise RuntimeError("Grid4DFunction.backward: the fused head wrote a group-major gradient buffer, but "
-                                           "autograd delivered a different tensor (features consumed more than once?)")
-                    W = tagged[1]
             encode_backward(plan.specs, coords, grad_out, [base + 4 * o for o in plan.grad_offsets],
                             plan.n_features, plan.linear, mask_a, mask_b,
                             levels_per_group=plan.bwd_levels_per_group, extra_flags=plan.extra_flags, group_width=W)

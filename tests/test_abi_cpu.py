@@ -120,3 +120,35 @@ def test_state_dict_contract_matches_reference(golden_dir):
     for e in ref:
         torch.nn.init.uniform_(e.weight, -1e-4, 1e-4)
     assert all(torch.equal(x.weight, y.weight) for x, y in zip(a.hash_tables, ref))
+
+
+def test_backward_group_width_plan(lib):
+    """Host-side planning of the regrouped gradient layout (no device work): W = levels-per-group x F when the level
+    tables are so large that a group's slice of a gradient row is <= 64 B, 0 otherwise; level runs agree with the whole."""
+    import dataclasses
+    from deepearth_b200 import functional as Fn
+    from deepearth_b200.functional import LevelSpec
+
+    def specs(T):
+        out = []
+        for g, d in enumerate([(0, 1, 2), (0, 1, 3), (1, 2, 3), (0, 2, 3)]):
+            for l in range(16):
+                R = 2 ** (4 + l)
+                out.append(LevelSpec(T, R, d, (g * 16 + l) * 2, (R + 1) ** 3 <= T))
+        return out
+
+    assert Fn.backward_group_width(specs(2 ** 22), 2 ** 24, 2, True) == 4        # c3: 32 MiB gradient tables -> 2 levels per group
+    assert Fn.backward_group_width(specs(2 ** 22), 2 ** 25, 2, True) == 4        # plane offsets beyond 2^32 floats
+    assert Fn.backward_group_width(specs(2 ** 21), 2 ** 24, 2, True) == 8
+    assert Fn.backward_group_width(specs(2 ** 19), 2 ** 22, 2, True) == 0        # c2: 16 levels per group, 128 B slices
+    assert Fn.backward_group_width(specs(2 ** 22), 2 ** 18, 2, True) == 0        # small batches stay row-major
+    assert Fn.backward_group_width(specs(2 ** 22), 2 ** 24, 2, False) == 0       # nearest mode: no lane-pair kernels
+    run = specs(2 ** 22)[16:32]
+    rebased = [dataclasses.replace(s, out_col=s.out_col - run[0].out_col) for s in run]
+    assert Fn.backward_group_width(rebased, 2 ** 24, 2, True) == 4
+    lv = Fn.pack_levels(specs(2 ** 22), None, [16] * 64)
+    from deepearth_b200 import _lib
+    lin = _lib.DE_INTERP_LINEAR
+    with_rows = lib.de_grid4d_backward_workspace_bytes_ex(lv, 64, 2, 2 ** 24, lin, 0)
+    grouped = lib.de_grid4d_backward_workspace_bytes_ex(lv, 64, 2, 2 ** 24, lin | _lib.DE_FLAG_GRAD_GROUPED, 0)
+    assert with_rows - grouped >= 2 ** 24 * 128 * 4                              # the regroup scratch is only asked for when needed
