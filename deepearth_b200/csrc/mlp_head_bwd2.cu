@@ -18,6 +18,8 @@
 //     tcgen05.mma in arrival order (so the shared dW accumulator in TMEM sees one in-order issuer), and each
 //     group prefetches its next tile's global loads into registers before it waits for GEMM 3/4.
 //   * TMEM: group g owns columns [128 g, 128 g + 128): D_h | D_da, then D_dx on top of them; dW at 256..256+N4.
+#include <cstdlib>
+
 #include "launch.h"
 #include "mlp_common.cuh"
 
@@ -142,7 +144,7 @@ __device__ __forceinline__ void store_dx_row(const MlpHeadBwdParams& P, uint32_t
 
 // dynamic shared memory (bf16, canonical K-major, no swizzle):
 //   W1 [64 x K1] | W1T [K1 x 64] | W2T [64 x 64] | per group g: XA_g [128 x NB] = [A | X | ones(16)] , GD_g [128 x 128] = [GY | DH]
-template <int K1>
+template <int K1, int SPLIT>
 __global__ void __launch_bounds__(kPPThreads, 1)
 mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
     constexpr int NB = kH + K1 + 16;                  // columns of XA = N of GEMM 4
@@ -213,8 +215,10 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
     if (grp == 2) {
         // =========================== MMA warp: one thread issues every tcgen05.mma ===================
         // register budget: 384 threads x 168 at launch; this warpgroup gives back (168 - 56) x 128 = 14336 registers, exactly
-        // what the two consumer warpgroups take (2 x (224 - 168) x 128) -- a larger request would wait forever
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        // what the two consumer warpgroups take (2 x (224 - 168) x 128) -- a larger request would wait forever.
+        // SPLIT 1 (A/B, DE_HEAD_BWD_SPLIT=1): 88 / 208 -- the MMA thread keeps its descriptors in registers.
+        if constexpr (SPLIT == 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
         if (warp == 8 && lane == 0) {
             int issued12[2] = {0, 0}, issued34[2] = {0, 0};
             const int cnt[2] = {cnt0, cnt1};
@@ -270,7 +274,8 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
         __syncwarp();
     } else {
         // =========================== consumer groups ================================================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
+        if constexpr (SPLIT == 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
+        else asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
         const int cnt = grp == 0 ? cnt0 : cnt1;
         const int wq = warp & 3;                                    // warp inside the group = TMEM lane quarter
         const int row = wq * 32 + lane;                             // tile row (point) owned in the epilogues
@@ -440,7 +445,8 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
 // ------------------------------------------------------------------------------------------------
 template <int K1>
 static cudaError_t launch_pp_k(const MlpHeadBwdParams& P, int n_sms, cudaStream_t s) {
-    auto kernel = mlp_head_bwd_pp_kernel<K1>;
+    const char* sp = getenv("DE_HEAD_BWD_SPLIT");
+    auto kernel = (sp && atoi(sp) == 1) ? mlp_head_bwd_pp_kernel<K1, 1> : mlp_head_bwd_pp_kernel<K1, 0>;
     constexpr int NB = kH + K1 + 16;
     const size_t smem = static_cast<size_t>(kH) * K1 * 2 + K1 * kH * 2 + kH * kH * 2 + 2 * (static_cast<size_t>(kTileM) * NB * 2 + kTileM * 128 * 2);
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
