@@ -216,9 +216,13 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
         // =========================== MMA warp: one thread issues every tcgen05.mma ===================
         // register budget: 384 threads x 168 at launch; this warpgroup gives back (168 - 56) x 128 = 14336 registers, exactly
         // what the two consumer warpgroups take (2 x (224 - 168) x 128) -- a larger request would wait forever.
-        // SPLIT 1 (A/B, DE_HEAD_BWD_SPLIT=1): 88 / 208 -- the MMA thread keeps its descriptors in registers.
+        // SPLIT (DE_HEAD_BWD_SPLIT, default 2): 0 = 56 / 224, 1 = 88 / 208, 2 = 104 / 200, 3 = 120 / 192.  With 56 registers
+        // the MMA thread spilled its descriptors and every GEMM 1 / 2 issue took ~1 us (13 % of the consumers' time was the
+        // wait for it); measured per 2^24 points: 10.6 / 9.2 / 8.4 / 8.7 ms.
         if constexpr (SPLIT == 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-        else asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
+        else if constexpr (SPLIT == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
+        else if constexpr (SPLIT == 2 || SPLIT == 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 120;");
         if (warp == 8 && lane == 0) {
             int issued12[2] = {0, 0}, issued34[2] = {0, 0};
             const int cnt[2] = {cnt0, cnt1};
@@ -268,14 +272,16 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                         any = true;
                     }
                 }
-                if (!any) __nanosleep(40);
+                if constexpr (SPLIT != 4) { if (!any) __nanosleep(40); }      // SPLIT 4 (A/B): spin without backing off
             }
         }
         __syncwarp();
     } else {
         // =========================== consumer groups ================================================
         if constexpr (SPLIT == 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
-        else asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+        else if constexpr (SPLIT == 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+        else if constexpr (SPLIT == 2 || SPLIT == 4) asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
+        else asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");
         const int cnt = grp == 0 ? cnt0 : cnt1;
         const int wq = warp & 3;                                    // warp inside the group = TMEM lane quarter
         const int row = wq * 32 + lane;                             // tile row (point) owned in the epilogues
@@ -446,7 +452,9 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
 template <int K1>
 static cudaError_t launch_pp_k(const MlpHeadBwdParams& P, int n_sms, cudaStream_t s) {
     const char* sp = getenv("DE_HEAD_BWD_SPLIT");
-    auto kernel = (sp && atoi(sp) == 1) ? mlp_head_bwd_pp_kernel<K1, 1> : mlp_head_bwd_pp_kernel<K1, 0>;
+    const int split = sp ? atoi(sp) : 2;
+    auto kernel = split == 0 ? mlp_head_bwd_pp_kernel<K1, 0> : split == 1 ? mlp_head_bwd_pp_kernel<K1, 1>
+                : split == 3 ? mlp_head_bwd_pp_kernel<K1, 3> : split == 4 ? mlp_head_bwd_pp_kernel<K1, 4> : mlp_head_bwd_pp_kernel<K1, 2>;
     constexpr int NB = kH + K1 + 16;
     const size_t smem = static_cast<size_t>(kH) * K1 * 2 + K1 * kH * 2 + kH * kH * 2 + 2 * (static_cast<size_t>(kTileM) * NB * 2 + kTileM * 128 * 2);
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
