@@ -85,6 +85,29 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 32 contiguous bytes of a feature / gradient row (streamed: evict-first).  One 256-bit load (sm_100: LDG.256) when the
+// address is 32 B aligned: one L1 request per 32 B sector instead of two half-used ones -- the head kernels issue
+// 48 such loads per thread per tile, and the L1 request rate of those loads was ~1/3 of a tile's time (ncu r01g).
+__device__ __forceinline__ void ld_stream_32B(const float* p, float4& a, float4& b, bool aligned32) {
+    if (aligned32) {
+        asm volatile("ld.global.cs.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+    } else {
+        a = __ldcs(reinterpret_cast<const float4*>(p));
+        b = __ldcs(reinterpret_cast<const float4*>(p) + 1);
+    }
+}
+
+__device__ __forceinline__ void st_stream_32B(float* p, const float4& a, const float4& b, bool aligned32) {
+    if (aligned32) {
+        asm volatile("st.global.cs.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                     ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
+    } else {
+        __stcs(reinterpret_cast<float4*>(p), a);
+        __stcs(reinterpret_cast<float4*>(p) + 1, b);
+    }
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<const uint32_t*>(&h);

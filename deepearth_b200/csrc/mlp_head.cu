@@ -264,6 +264,7 @@ mlp_head_dual_kernel(const __grid_constant__ MlpHeadParams P) {
         const int n_valid = static_cast<int>(P.n - p0 < kTileM ? P.n - p0 : kTileM);
         const float* tile_base = P.x + p0 * P.x_stride;
         const int xs = static_cast<int>(P.x_stride);
+        const bool a32 = ((reinterpret_cast<uintptr_t>(tile_base) | (static_cast<uintptr_t>(xs) << 2)) & 31) == 0;
 
         // ---- 1. features -> bf16 A tile (same lane mapping as above), in two rounds of 32 B x K1/16 per thread
         //         (128 registers per thread are all this occupancy leaves)
@@ -275,14 +276,10 @@ mlp_head_dual_kernel(const __grid_constant__ MlpHeadParams P) {
 #pragma unroll
             for (int u = 0; u < kRound; ++u) {
                 const int c = lane + 32 * (it0 + u);
-                const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
+                // rows past the end of the batch re-read the last valid row (their outputs are never stored)
+                const int r = min(warp * 32 + (c / K1) * 8 + ((c % K1) & 7), n_valid - 1);
                 const int k8 = (c % K1) >> 3;
-                va[u] = vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (r < n_valid) {
-                    const float4* src = reinterpret_cast<const float4*>(tile_base + (r * xs + k8 * 8));
-                    va[u] = __ldcs(src);
-                    vb[u] = __ldcs(src + 1);
-                }
+                ld_stream_32B(tile_base + (r * xs + k8 * 8), va[u], vb[u], a32);
             }
 #pragma unroll
             for (int u = 0; u < kRound; ++u) {
@@ -367,11 +364,15 @@ mlp_head_dual_kernel(const __grid_constant__ MlpHeadParams P) {
             float q[32];
             tmem_ld32(tmem_row + 32 * hh, q);                   // warp-collective: outside the row predicate
             if (row < n_valid) {
-                float4* dst = reinterpret_cast<float4*>(P.y + (p0 + row) * P.y_stride + 32 * hh);
+                float* dst = P.y + (p0 + row) * P.y_stride + 32 * hh;
+                const bool y32 = ((reinterpret_cast<uintptr_t>(P.y) | (static_cast<uintptr_t>(P.y_stride) << 2)) & 31) == 0;
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    __stcs(dst + u, make_float4(q[4 * u] + s_vec[3][32 * hh + 4 * u], q[4 * u + 1] + s_vec[3][32 * hh + 4 * u + 1],
-                                                q[4 * u + 2] + s_vec[3][32 * hh + 4 * u + 2], q[4 * u + 3] + s_vec[3][32 * hh + 4 * u + 3]));
+                for (int u = 0; u < 8; u += 2) {
+                    const float* bias = &s_vec[3][32 * hh + 4 * u];
+                    st_stream_32B(dst + 4 * u,
+                                  make_float4(q[4 * u] + bias[0], q[4 * u + 1] + bias[1], q[4 * u + 2] + bias[2], q[4 * u + 3] + bias[3]),
+                                  make_float4(q[4 * u + 4] + bias[4], q[4 * u + 5] + bias[5], q[4 * u + 6] + bias[6], q[4 * u + 7] + bias[7]), y32);
+                }
             }
         }
         tc_fence_before();           // the next tile's GEMM 1 overwrites these columns: order the loads before the barrier

@@ -90,17 +90,28 @@ struct TileR {
 // one 16-byte bf16 chunk column (conflict-free shared stores), 4 chunk columns per request (128 B segments).
 template <int KT>
 __device__ __forceinline__ void tile_issue2(TileR<KT>& t, const float* tile_base, int stride, int n_valid, int warp, int lane) {
+    const bool a32 = ((reinterpret_cast<uintptr_t>(tile_base) | (static_cast<uintptr_t>(stride) << 2)) & 31) == 0;
 #pragma unroll
     for (int it = 0; it < TileR<KT>::kIt; ++it) {
         const int c = lane + 32 * it;
         const int r = warp * 32 + (c / KT) * 8 + ((c % KT) & 7);
         const int k8 = (c % KT) >> 3;
         t.a[it] = t.b[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < n_valid) {
-            const float4* s4 = reinterpret_cast<const float4*>(tile_base + (r * stride + k8 * 8));
-            t.a[it] = __ldcs(s4);
-            t.b[it] = __ldcs(s4 + 1);
-        }
+        if (r < n_valid) ld_stream_32B(tile_base + (r * stride + k8 * 8), t.a[it], t.b[it], a32);
+    }
+}
+
+// Same, without predicates or zero fill: rows past the end of the batch re-read the last valid row.  Only for the
+// FEATURE tile: a padded row's gradient row is zero, so whatever features it holds drop out of every product.
+template <int KT>
+__device__ __forceinline__ void tile_issue2_clamped(TileR<KT>& t, const float* tile_base, int stride, int n_valid, int warp, int lane) {
+    const bool a32 = ((reinterpret_cast<uintptr_t>(tile_base) | (static_cast<uintptr_t>(stride) << 2)) & 31) == 0;
+#pragma unroll
+    for (int it = 0; it < TileR<KT>::kIt; ++it) {
+        const int c = lane + 32 * it;
+        const int r = min(warp * 32 + (c / KT) * 8 + ((c % KT) & 7), n_valid - 1);
+        const int k8 = (c % KT) >> 3;
+        ld_stream_32B(tile_base + (r * stride + k8 * 8), t.a[it], t.b[it], a32);
     }
 }
 
@@ -126,16 +137,27 @@ __device__ __forceinline__ void store_dx_row(const MlpHeadBwdParams& P, uint32_t
     const int W = P.dx_group_w ? P.dx_group_w : (1 << 30);          // row-major = one "plane" as wide as the row
     const long long plane = P.dx_group_w ? P.n * P.dx_group_w : 0;  // floats between planes
     float* pl = P.dx + (P.dx_group_w ? pr * P.dx_group_w : pr * P.dx_stride);
+    const bool a32 = ((reinterpret_cast<uintptr_t>(P.dx) | (static_cast<uintptr_t>(P.dx_group_w ? P.dx_group_w : P.dx_stride) << 2)) & 31) == 0;
     int within = 0;
 #pragma unroll
     for (int c0 = 0; c0 < K1; c0 += 16) {
         float q[16];
         tmem_ld16b(tmem_row + c0, q);                               // warp-collective: outside the row predicate
+        if (W >= 8) {                                               // 32 B pieces stay inside one plane (or one row)
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (ok) __stcs(reinterpret_cast<float4*>(pl + within), make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]));
-            within += 4;
-            if (within == W) { within = 0; pl += plane; }
+            for (int u = 0; u < 4; u += 2) {
+                if (ok) st_stream_32B(pl + within, make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]),
+                                      make_float4(q[4 * u + 4], q[4 * u + 5], q[4 * u + 6], q[4 * u + 7]), a32);
+                within += 8;
+                if (within == W) { within = 0; pl += plane; }
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (ok) __stcs(reinterpret_cast<float4*>(pl + within), make_float4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]));
+                within += 4;
+                if (within == W) { within = 0; pl += plane; }
+            }
         }
     }
 }
@@ -299,7 +321,7 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
             //      of the previous tile and its gradient rows are streamed out ---------------------------
             TileR<K1> tx;
             TileR<kH> tg;
-            tile_issue2<K1>(tx, P.x + p0 * P.x_stride, xs, n_valid, wq, lane);
+            tile_issue2_clamped<K1>(tx, P.x + p0 * P.x_stride, xs, n_valid, wq, lane);
             tile_issue2<kH>(tg, P.gy + p0 * P.gy_stride, gs, n_valid, wq, lane);
             if (i > 0) {                                            // epilogue B of the previous tile
                 mbar_wait(&s_d34[grp], (i - 1) & 1);
