@@ -390,7 +390,7 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
             if (int rc = run_smem_forward(a, base, begin, end, taken, stream)) return rc;
 
         de::EncodeParams P = base;
-        P.l2_hints = (a.flags & DE_FLAG_NO_L2_HINTS) ? 0 : 1;
+        P.l2_hints = (a.flags & DE_FLAG_NO_L2_HINTS) ? 0 : ((a.flags & DE_FLAG_COHERENT_GATHER) ? 2 : 1);
         int idx[de::kMaxLaunchLevels];
         int n = 0;
         for (int i = begin; i < end; ++i)

@@ -256,9 +256,22 @@ __device__ __forceinline__ float ldg_stream_f1(const void* a, uint64_t pol) {
     return v;
 }
 
+// Experiment (DE_FLAG_COHERENT_GATHER): the same 4 / 8 byte gathers as GPU-scope relaxed loads, which are served by the
+// line's home L2 partition instead of being cached a second time in the requesting SM's partition.
+__device__ __forceinline__ uint32_t ldg_coherent_u32(const void* a, uint64_t pol) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ uint2 ldg_coherent_u64(const void* a, uint64_t pol) {
+    uint2 v;
+    asm volatile("ld.relaxed.gpu.global.L2::cache_hint.v2.b32 {%0, %1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(a), "l"(pol));
+    return v;
+}
+
 // F-wide table entry with an L2 policy (F * sizeof(TT) in {2,4,8,16,32} bytes)
 template <typename TT, int F>
-__device__ __forceinline__ void load_entry_hint(const void* t, uint32_t i, float (&v)[F], uint64_t pol) {
+__device__ __forceinline__ void load_entry_hint(const void* t, uint32_t i, float (&v)[F], uint64_t pol, bool coherent = false) {
     constexpr int B = static_cast<int>(sizeof(TT)) * F;
     const char* a = static_cast<const char*>(t) + static_cast<size_t>(i) * B;
     uint32_t w[B >= 4 ? B / 4 : 1];
@@ -267,9 +280,9 @@ __device__ __forceinline__ void load_entry_hint(const void* t, uint32_t i, float
         asm volatile("ld.global.nc.L2::cache_hint.b16 %0, [%1], %2;" : "=h"(h) : "l"(a), "l"(pol));
         w[0] = h;
     } else if constexpr (B == 4) {
-        w[0] = ldg_hint_u32(a, pol);
+        w[0] = coherent ? ldg_coherent_u32(a, pol) : ldg_hint_u32(a, pol);
     } else if constexpr (B == 8) {
-        const uint2 x = ldg_hint_u64(a, pol);
+        const uint2 x = coherent ? ldg_coherent_u64(a, pol) : ldg_hint_u64(a, pol);
         w[0] = x.x; w[1] = x.y;
     } else if constexpr (B == 16) {
         const uint4 x = ldg_hint_u128(a, pol);

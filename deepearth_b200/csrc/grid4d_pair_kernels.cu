@@ -80,7 +80,7 @@ grid4d_forward_pair_kernel(const __grid_constant__ EncodeParams P) {
         for (int j = 0; j < J; ++j) idx[j] = ct.index(lv, j);
         float v[J][F];
 #pragma unroll
-        for (int j = 0; j < J; ++j) load_entry_hint<TT, F>(lv.table, idx[j], v[j], pol.keep);   // all gathers in flight
+        for (int j = 0; j < J; ++j) load_entry_hint<TT, F>(lv.table, idx[j], v[j], pol.keep, P.l2_hints == 2);   // all gathers in flight
         float acc[F];
 #pragma unroll
         for (int f = 0; f < F; ++f) acc[f] = 0.0f;
