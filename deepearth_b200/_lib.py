@@ -13,7 +13,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libde_grid4d.so")
 
 DE_OK = 0
-ABI_VERSION = 2
+ABI_VERSION = 3
 DE_F32, DE_F16, DE_F64 = 0, 1, 2
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS, DE_FLAG_NO_REGROUP = 0x100, 0x200, 0x400, 0x800

@@ -4,7 +4,7 @@ Mirrors ``Grid4DEncoder.projection`` (/root/reference/models/encoders.py:47-52).
 ordinary ``nn.Sequential`` (same state-dict keys as the reference: ``projection.0.weight`` ...); this module
 only changes how the forward is computed: ``de_mlp_head_forward`` (deepearth_b200/csrc/mlp_head.cu) runs both
 GEMMs as bf16 ``tcgen05.mma`` with fp32 accumulators in tensor memory, and the hidden row never leaves the SM.
-The backward pass is a second tcgen05 kernel (``de_mlp_head_backward``, csrc/mlp_head_bwd.cu: hidden-row recompute,
+The backward pass is a second tcgen05 kernel (``de_mlp_head_backward``, csrc/mlp_head_bwd2.cu: hidden-row recompute,
 LayerNorm / activation backward in registers, weight gradients accumulated in tensor memory); with
 ``fused_backward=False`` it recomputes through the fp32 PyTorch modules (cuBLAS) instead.
 """

@@ -35,7 +35,7 @@ extern "C" {
 #define DE_API
 #endif
 
-#define DE_ABI_VERSION 2
+#define DE_ABI_VERSION 3
 
 /* status codes (negative = caller error) */
 #define DE_OK 0
