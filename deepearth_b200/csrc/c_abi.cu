@@ -232,14 +232,19 @@ unsigned long long level_bytes(const de_level_desc& L, int n_features, bool back
     const unsigned long long eb = (unsigned long long)n_features * (backward ? 4u : (table_dtype == DE_F16 ? 2u : 4u));
     return live * eb;
 }
-int pick_group_size(bool pair, int n_features, int levels_per_group, int n, unsigned long long max_level_bytes) {
+int pick_group_size(bool pair, int n_features, int levels_per_group, int n, unsigned long long max_level_bytes,
+                    bool nearest = false) {
     int G = levels_per_group;
     if (G == 0) {
         if (pair) {
             G = 16;
             while (G > 1 && (unsigned long long)G * max_level_bytes > kL2BudgetBytes) G >>= 1;
         } else {
-            G = 8 / n_features;   // the G lanes of a point cover at least one 32 B sector of its row
+            // the G lanes of a point cover one 32 B sector of its row; two sectors in nearest-cell mode, where a
+            // lane issues ONE gather per point and the coordinate re-read per group is a visible share
+            // (c1r, run ak: forward 0.675 -> 0.595 ms, backward 0.966 -> 0.811 ms; 16 = same, 2 = far slower)
+            G = (nearest ? 16 : 8) / n_features;
+            if (nearest && G > 1 && (unsigned long long)G * max_level_bytes > kL2BudgetBytes) G >>= 1;   // as before
             if (G < 1) G = 1;
         }
     }
@@ -428,7 +433,7 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
             const unsigned long long lb = level_bytes(L, a.n_features, op == Op::Backward, a.table_dtype);
             if (lb > max_level_bytes) max_level_bytes = lb;
         }
-        const int G = pick_group_size(pair, a.n_features, a.levels_per_group, n, max_level_bytes);
+        const int G = pick_group_size(pair, a.n_features, a.levels_per_group, n, max_level_bytes, !linear);
         if (op == Op::Backward && (a.flags & DE_FLAG_GRAD_GROUPED)) {
             // the caller (the head's backward kernel) already wrote the rows group-major: same addressing, no pass
             const RegroupPlan rg = plan_regroup(a.levels, begin, end, a.n_features, a.n_points, linear,
