@@ -467,7 +467,11 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
         P.group_size = G;
         P.n_groups = (n + G - 1) / G;
         const int lanes_per_point = pair ? 2 * G : G;
-        const int iters = pair ? 8 : 4;
+        // loop trips per CTA (run ao / ap): the forward kernels want long-lived CTAs (set-up amortised, fewer block
+        // launches), the backward kernels do not (shorter tiles spread the reductions of a group more evenly)
+        const bool fwd_like = op != Op::Backward;
+        const int iters = pair ? tune_env(fwd_like ? "DE_PAIR_TILE_ITERS_FWD" : "DE_PAIR_TILE_ITERS_BWD", fwd_like ? 32 : 8, 1, 4096)
+                               : tune_env(fwd_like ? "DE_TILE_ITERS_FWD" : "DE_TILE_ITERS_BWD", fwd_like ? 16 : 8, 1, 4096);
         P.points_per_cta = (de::kThreads / lanes_per_point) * iters;
         const long long tiles = (a.n_points + P.points_per_cta - 1) / P.points_per_cta;
         if (tiles * P.n_groups >= (1ll << 31)) return fail(DE_EUNSUPPORTED, "n_points=%lld too large for one launch", (long long)a.n_points);
