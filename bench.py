@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- Grid4D hash-encode forward+backward throughput (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c1r] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5|c1r] [--impl reference]
 
 A "step" is one pass of the hot path over one batch of synthetic points: zero the table-gradient
 buffer, forward encode (de_grid4d_forward), backward scatter (de_grid4d_backward) and -- at N>1 -- the
@@ -13,6 +13,8 @@ Workloads (BASELINE.json configs):
       fp16 working tables, fp32 output and gradients                       [configs[1]]
   c3  same grids with T=2^22 (HBM-resident tables), 2^24 Florida-clustered points run through the
       geo2xyz prologue first                                               [configs[2]]
+  c4  the c2 grids on 2^26 points IN TOTAL, sharded over the ranks ("scaling": "strong")   [configs[3]]
+  c5  c3 + geo2xyz prologue + 64-wide tcgen05 projection head, forward and backward        [configs[4]]
   c1r the reference's own Grid4DEncoder geometry (xyz 16 levels T=2^19 + t 8 levels T=2^17, nearest,
       fp32 tables), 2^22 points                                            [configs[0] geometry on GPU]
 
@@ -49,6 +51,9 @@ WORKLOADS = {
     "c5": dict(mode="decomposed", T=2 ** 22, log2_points=24, coords="florida", table_dtype="float16", head=True,
                desc="configs[4]: geo2xyz prologue + 4 grids x 16 levels x 2 feat (T=2^22) + Linear-LayerNorm-GELU-Linear 64-wide head "
                     "(tcgen05 kernels forward and backward), 2^24 Florida-clustered geodetic points/GPU"),
+    "c4": dict(mode="decomposed", T=2 ** 19, log2_points=26, total=True, coords="uniform", table_dtype="float16",
+               desc="configs[3]: 2^26 points in total, sharded over the ranks (2^26 / N per GPU), 4 grids x 16 levels x 2 feat, "
+                    "T=2^19/level, replicated tables, all-reduce of the table gradients"),
     "c1r": dict(mode="reference", T=2 ** 19, log2_points=22, coords="uniform", table_dtype="float32",
                 desc="reference Grid4DEncoder geometry (xyz L16 T=2^19 + t L8 T=2^17, nearest, fp32 tables), 2^22 points/GPU"),
 }
@@ -359,7 +364,7 @@ def run_reference_arm(args, wl):
     cb = cpu_baseline_run(wl, log2_sample, max(1, args.steps), max(1, args.warmup))
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong" if wl.get("total") else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "description": wl["desc"], "sample": cb["sample"]},
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -394,6 +399,8 @@ def run_gpu_arm(args, wl):
     _L.load().de_get_l2_fetch_granularity(_ct.byref(_gran))
 
     n = 2 ** (args.log2_points if args.log2_points else wl["log2_points"])
+    if wl.get("total"):
+        n //= world                      # strong scaling: the workload fixes the job's points, not the rank's
     job = Job(wl, device, seed=1234 + rank, n_points=n)
     if args.levels_per_group:
         job.plan.levels_per_group = args.levels_per_group
@@ -605,7 +612,8 @@ def run_gpu_arm(args, wl):
                 traffic = json.load(f).get(args.workload, {}).get(dom)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong" if wl.get("total") else "weak",
             "vs_baseline": None, "dtype": "f16 tables / f32 accumulate" if wl["table_dtype"] == "float16" else "f32",
             "data": "synthetic",
             "config": {"workload": args.workload, "description": wl["desc"], "points_per_gpu": n,

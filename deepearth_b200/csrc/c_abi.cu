@@ -185,6 +185,7 @@ unsigned long long live_cells(const de_level_desc& L) {
 // clustered points).  Such a level gets K copies of its live entries -- CTA tile t adds into copy t % K --
 // which are folded into the real table by one small kernel afterwards.
 constexpr unsigned long long kRepTargetBytes = 8ull << 20;   // replicas of one level stay within this much L2
+constexpr unsigned long long kRepGroupBytes = 16ull << 20;   // ... and the copies of one level group within this much
 constexpr unsigned kRepMax = 64;
 constexpr unsigned long long kRepMinUpdatesPerEntry = 256;
 
@@ -408,32 +409,39 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
         for (int i = 0; i < n; ++i) {
             const de_level_desc& L = a.levels[idx[i]];
             fill_level(L, P.levels[i]);
-            if (op == Op::Backward && a.workspace) {
-                // same walk as replica_workspace_bytes(): ws_off advances over ALL levels of the call in order
-                const RepPlan r = plan_replicas(L, a.n_features, a.n_points, linear);
-                if (r.count > 1) {
-                    const size_t need = static_cast<size_t>(r.count - 1) * r.stride * 4;
-                    if (ws_off + need <= a.workspace_bytes) {
-                        de::LevelParams& lp = P.levels[i];
-                        lp.rep_base = reinterpret_cast<float*>(static_cast<char*>(a.workspace) + ws_off);
-                        lp.rep_count = r.count;
-                        lp.rep_stride = r.stride;
-                        lp.rep_live = r.live;
-                        fold.dst[fold.n] = L.grad_table;
-                        fold.rep[fold.n] = lp.rep_base;
-                        fold.n_floats[fold.n] = r.live * static_cast<unsigned>(a.n_features);
-                        fold.count[fold.n] = r.count - 1;
-                        fold.stride[fold.n] = r.stride;
-                        ++fold.n;
-                        ws_off += need;
-                    }
-                }
-            }
             pow2_all = pow2_all && is_pow2(L.table_size);
             const unsigned long long lb = level_bytes(L, a.n_features, op == Op::Backward, a.table_dtype);
             if (lb > max_level_bytes) max_level_bytes = lb;
         }
         const int G = pick_group_size(pair, a.n_features, a.levels_per_group, n, max_level_bytes, !linear);
+        if (op == Op::Backward && a.workspace) {
+            // Replicas are extra L2 footprint of the group being walked: grant them coarse level first, while one
+            // group's copies stay within kRepGroupBytes.  (Without the cap, 2^26 points make every T = 2^19 level
+            // "contended" by the updates-per-entry rule, each gets one 4 MiB copy, the group's 64 MiB becomes 116 MiB
+            // and the backward runs 2.7x slower -- bench c4, run as.)
+            unsigned long long group_extra = 0;
+            for (int i = 0; i < n; ++i) {
+                if (i % G == 0) group_extra = 0;
+                const de_level_desc& L = a.levels[idx[i]];
+                const RepPlan r = plan_replicas(L, a.n_features, a.n_points, linear);
+                if (r.count <= 1) continue;
+                const size_t need = static_cast<size_t>(r.count - 1) * r.stride * 4;
+                if (group_extra + need > kRepGroupBytes || ws_off + need > a.workspace_bytes) continue;
+                de::LevelParams& lp = P.levels[i];
+                lp.rep_base = reinterpret_cast<float*>(static_cast<char*>(a.workspace) + ws_off);
+                lp.rep_count = r.count;
+                lp.rep_stride = r.stride;
+                lp.rep_live = r.live;
+                fold.dst[fold.n] = L.grad_table;
+                fold.rep[fold.n] = lp.rep_base;
+                fold.n_floats[fold.n] = r.live * static_cast<unsigned>(a.n_features);
+                fold.count[fold.n] = r.count - 1;
+                fold.stride[fold.n] = r.stride;
+                ++fold.n;
+                ws_off += need;
+                group_extra += need;
+            }
+        }
         if (op == Op::Backward && (a.flags & DE_FLAG_GRAD_GROUPED)) {
             // the caller (the head's backward kernel) already wrote the rows group-major: same addressing, no pass
             const RegroupPlan rg = plan_regroup(a.levels, begin, end, a.n_features, a.n_points, linear,
