@@ -567,6 +567,32 @@ def test_regrouped_gradient_rows_match_in_place_rows(dev, levels_per_group, n_ex
     assert float((got - ref).abs().max()) <= GRAD_TOL * denom
 
 
+def test_replica_budget_mixes_replicated_and_plain_levels(dev):
+    """Many points per table entry make every level of a group eligible for gradient replicas; only the coarsest ones
+    get them (16 MiB of copies per level group, c_abi.cu kRepGroupBytes).  The mixed state -- some levels reduced
+    into copies and folded, the rest reduced in place -- must give the same gradients as no replicas at all."""
+    from deepearth_b200 import functional as Fn
+    from deepearth_b200.functional import LevelSpec
+    T, L, F = 2 ** 16, 8, 2                  # 512 KiB of gradients per level -> 16 copies = 7.5 MiB extra each
+    n = 2 ** 21 + 5                          # 8 corners * n / T = 256 updates per entry: every level qualifies
+    g = torch.Generator(device=dev).manual_seed(33)
+    res = [48 * 2 ** l + 1 for l in range(L)]
+    specs = [LevelSpec(table_size=T, resolution=R, dims=(0, 1, 2), out_col=l * F, dense=False) for l, R in enumerate(res)]
+    coords = torch.rand((n, 4), device=dev, generator=g)
+    gout = torch.randn((n, L * F), device=dev, generator=g)
+
+    def run(use_replicas):
+        flat = torch.zeros(L * T * F, device=dev)
+        ptrs = [flat.data_ptr() + 4 * l * T * F for l in range(L)]
+        Fn.encode_backward(specs, coords, gout, ptrs, F, True, use_replicas=use_replicas)
+        return flat
+
+    got, ref = run(True), run(False)
+    denom = float(ref.abs().max())
+    assert denom > 0
+    assert float((got - ref).abs().max()) <= GRAD_TOL * denom
+
+
 def test_fused_head_hands_group_major_gradients_to_the_encoder(dev, monkeypatch):
     """Large tables + fused head: the head's backward kernel writes d(loss)/d(features) group-major and the hash-grid
     backward walks it directly (no regroup pass).  Same gradients as the row-major hand-off, and the path is taken."""
