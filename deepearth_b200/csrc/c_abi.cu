@@ -480,7 +480,15 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
         const bool fwd_like = op != Op::Backward;
         const int iters = pair ? tune_env(fwd_like ? "DE_PAIR_TILE_ITERS_FWD" : "DE_PAIR_TILE_ITERS_BWD", fwd_like ? 32 : 8, 1, 4096)
                                : tune_env(fwd_like ? "DE_TILE_ITERS_FWD" : "DE_TILE_ITERS_BWD", fwd_like ? 16 : 8, 1, 4096);
-        P.points_per_cta = (de::kThreads / lanes_per_point) * iters;
+        int trips = iters;
+        {
+            // small batches: never fewer CTAs than the short tiles of r01h gave (8 / 4 trips) until there are a few
+            // waves of them (148 SMs x 8 resident CTAs x 4)
+            const int floor_trips = pair ? 8 : 4;
+            const long long per_pass = de::kThreads / lanes_per_point;
+            while (trips > floor_trips && ((a.n_points + per_pass * trips - 1) / (per_pass * trips)) * P.n_groups < 4736) trips >>= 1;
+        }
+        P.points_per_cta = (de::kThreads / lanes_per_point) * trips;
         const long long tiles = (a.n_points + P.points_per_cta - 1) / P.points_per_cta;
         if (tiles * P.n_groups >= (1ll << 31)) return fail(DE_EUNSUPPORTED, "n_points=%lld too large for one launch", (long long)a.n_points);
         P.n_tiles = static_cast<int>(tiles);

@@ -144,8 +144,9 @@ class Grid4DEncoder(nn.Module):
             had = enc._work is not None and enc._work.device == dev
             ptrs += enc._ensure_work(dev)
             fresh = fresh and had
-        key = (dev, tuple(w._version for w in weights), tuple(w.data_ptr() for w in weights))
-        if not fresh or key != self.__dict__.get("_work_key_all") or (self.training and torch.is_grad_enabled()):
+        stepping = self.training and torch.is_grad_enabled()      # an optimiser is rewriting the tables: always refresh
+        key = None if stepping else (dev, tuple(w._version for w in weights), tuple(w.data_ptr() for w in weights))
+        if stepping or not fresh or key != self.__dict__.get("_work_key_all"):
             e0 = self._encoders[0]
             with torch.no_grad():
                 Fn.tables_to_f16(self._plan().specs, [w.data_ptr() for w in weights], ptrs, e0.n_features_per_level,
