@@ -67,6 +67,39 @@ class GeospatialConverter:
             raise RuntimeError("deepearth_b200.GeospatialConverter runs on CUDA devices only")
         self._bbox = bbox
         self.t_range = t_range
+        self._affine: Optional[Tuple[Tuple[float, float, float], Tuple[float, float, float]]] = None
+
+    # dataset-statistics normalisation (SPECIFICATIONS.MD:707-733, 843-858) -------------------------------
+    @classmethod
+    def from_statistics(cls, center: Sequence[float], scale: float, *, bound: Optional[float] = None,
+                        t_range: Optional[Tuple[float, float]] = None, device: str = "cuda") -> "GeospatialConverter":
+        """Converter for the spec's ``xyz_norm = (ecef - center) / scale`` (``center`` = mean ECEF, ``scale`` =
+        2 * max per-axis std, SPECIFICATIONS.MD:729, :853-854).  With ``bound`` the result is also mapped from
+        [-bound, bound] to [0, 1] the way the upstream Grid4D encoder does before hashing (``grid4d_bound = 1.6``,
+        SPECIFICATIONS.MD:294): ``(v + bound) / (2 bound)``.  Both are one affine map, folded into the offset and span
+        the prologue kernel already divides by in fp64 -- no extra pass, no extra rounding step."""
+        scale = float(scale)
+        if not scale > 0.0:
+            raise ValueError("scale must be positive")
+        if bound is not None and not float(bound) > 0.0:
+            raise ValueError("bound must be positive")                      # SPECIFICATIONS.MD:297-298
+        c = tuple(float(v) for v in center)
+        if len(c) != 3:
+            raise ValueError("center must have three components")
+        conv = cls(device=device, t_range=t_range)
+        if bound is None:
+            conv._affine = (c, (scale, scale, scale))
+        else:
+            b = float(bound)
+            conv._affine = (tuple(v - b * scale for v in c), (2.0 * b * scale,) * 3)
+        return conv
+
+    def fit_statistics(self, geo: torch.Tensor) -> dict:
+        """``center`` / ``scale`` of a point set as the spec's preprocessor computes them (SPECIFICATIONS.MD:843-858):
+        mean ECEF and twice the largest per-axis standard deviation.  Returns Python floats (one host read)."""
+        ecef = self.geodetic_to_xyz(geo).reshape(-1, 3)
+        stats = torch.cat([ecef.mean(dim=0), (ecef.std(dim=0).max() * 2.0).reshape(1)]).tolist()
+        return {"center": tuple(stats[:3]), "scale": stats[3]}
 
     @property
     def bbox(self) -> Optional[BoundingBox]:
@@ -98,8 +131,14 @@ class GeospatialConverter:
         loop wants.
         """
         g = _geo_arg(geo)
-        if update_bbox or self._bbox is None:
-            self.update_bbox(g)
+        if self._affine is not None:
+            if update_bbox:
+                raise ValueError("a statistics-normalised converter has no bounding box to update")
+            offset, span = self._affine
+        else:
+            if update_bbox or self._bbox is None:
+                self.update_bbox(g)
+            offset, span = self._bbox.min_point, self._bbox.span
         n = g.shape[0]
         tt = None
         t_range = None
@@ -118,7 +157,7 @@ class GeospatialConverter:
         ecef = torch.empty((n, 3), dtype=torch.float64, device=g.device) if return_ecef else None
         with torch.cuda.device(g.device):
             rc = _lib.load().de_geo2xyzt_norm(_ptr(g), _DT[g.dtype], _ptr(tt), _DT[tt.dtype] if tt is not None else 0,
-                                              _dbl3(self._bbox.min_point), _dbl3(self._bbox.span), t_range,
+                                              _dbl3(offset), _dbl3(span), t_range,
                                               _ptr(xyzt), _ptr(ecef), n, _stream_ptr(g.device))
         _lib.check(rc, "de_geo2xyzt_norm")
         return (xyzt, ecef) if return_ecef else xyzt
@@ -127,13 +166,14 @@ class GeospatialConverter:
     def geodetic_to_xyz(self, geo: torch.Tensor) -> torch.Tensor:
         """(…,3) geodetic -> (…,3) fp64 ECEF metres (geo2xyz.py:146-160, position branch only)."""
         g = _geo_arg(geo)
-        keep = self._bbox
+        keep = (self._bbox, self._affine)
+        self._affine = None
         if self._bbox is None:
             self._bbox = BoundingBox(0, 0, 0, 1, 1, 1)
         try:
             _, ecef = self.geodetic_to_xyzt_norm(g, None, return_ecef=True)
         finally:
-            self._bbox = keep
+            self._bbox, self._affine = keep
         return ecef.reshape(*geo.shape[:-1], 3)
 
 

@@ -466,6 +466,40 @@ def test_geo2xyz_vs_reference_and_oracle(dev, oracle, golden_dir):
     assert abs(float(x) - g["landmarks_ecef"][-1, 0]) < 1e-6
 
 
+def test_geo2xyz_statistics_normalisation_and_bound(dev, oracle, golden_dir):
+    """Spec pipeline (SPECIFICATIONS.MD:729, :853-854, :294): (ecef - mean) / (2 max std), optionally remapped from
+    [-bound, bound] to [0, 1]; ECEF taken from the reference's own converter (golden), statistics as the spec computes
+    them (torch .std = unbiased).  One affine map inside the prologue kernel."""
+    import deepearth_b200 as de
+    g = load(golden_dir, "geo2xyz")
+    geo = torch.from_numpy(g["florida_geo"]).to(dev)
+    ecef = torch.from_numpy(g["florida_ecef"])
+    center = ecef.mean(dim=0)
+    scale = float(ecef.std(dim=0).max() * 2.0)
+    fit = de.GeospatialConverter(device="cuda:0").fit_statistics(geo)
+    assert np.allclose(fit["center"], center.numpy(), rtol=0, atol=1e-5) and abs(fit["scale"] - scale) <= 1e-6 * scale
+    want = ((ecef - center) / scale).numpy()
+    conv = de.GeospatialConverter.from_statistics(center.tolist(), scale, t_range=(0.0, 4.0))
+    tt = torch.linspace(0, 4, geo.shape[0], dtype=torch.float64, device=dev)
+    got = conv.geodetic_to_xyzt_norm(geo, tt).cpu().numpy()
+    assert np.abs(got[:, :3] - want.astype(np.float32)).max() <= 2.4e-7 * max(1.0, np.abs(want).max())
+    assert np.abs(got[:, 3] - (tt.cpu().numpy() / 4.0).astype(np.float32)).max() <= 1.2e-7
+    o = oracle.geo2xyzt_norm(g["florida_geo"], tt.cpu().numpy(), center.numpy(), np.full(3, scale), (0.0, 4.0))
+    assert np.abs(got - o).max() <= 2.4e-7 and (got != o).mean() <= 1e-3
+    bound = 1.6
+    conv_b = de.GeospatialConverter.from_statistics(center.tolist(), scale, bound=bound)
+    got_b = conv_b.geodetic_to_xyzt_norm(geo).cpu().numpy()[:, :3]
+    want_b = (want + bound) / (2 * bound)
+    assert np.abs(got_b - want_b.astype(np.float32)).max() <= 1.2e-7
+    assert got_b.min() >= 0.0 and got_b.max() <= 1.0
+    with pytest.raises(ValueError):
+        de.GeospatialConverter.from_statistics(center.tolist(), scale, bound=0.0)
+    with pytest.raises(ValueError):
+        conv.geodetic_to_xyzt_norm(geo, tt, update_bbox=True)
+    # ECEF itself is unaffected by the normalisation the converter carries
+    assert np.abs(conv.geodetic_to_xyz(geo).cpu().numpy() - g["florida_ecef"]).max() <= 1e-6
+
+
 def test_sum_and_probe_helpers(dev):
     from deepearth_b200 import functional as Fn
     x = torch.randn(1_000_003, device=dev)
