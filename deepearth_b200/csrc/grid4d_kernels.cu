@@ -41,7 +41,7 @@ __device__ __forceinline__ bool setup_thread(const EncodeParams& P, LevelParams*
 // forward
 // ------------------------------------------------------------------------------------------------
 template <int D, bool LINEAR, typename TT, int F>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, LINEAR ? 1 : 8)
 grid4d_forward_kernel(const __grid_constant__ EncodeParams P) {
     __shared__ LevelParams s_lv[kMaxGroup];
     int lane_level, p_step;
@@ -110,7 +110,7 @@ grid4d_forward_kernel(const __grid_constant__ EncodeParams P) {
 // backward: grad_table[idx_k] += mask * w_k * grad_out[p, out_col:out_col+F]
 // ------------------------------------------------------------------------------------------------
 template <int D, bool LINEAR, int F>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, LINEAR ? 1 : 8)
 grid4d_backward_kernel(const __grid_constant__ EncodeParams P) {
     __shared__ LevelParams s_lv[kMaxGroup];
     int lane_level, p_step;
@@ -162,7 +162,7 @@ grid4d_backward_kernel(const __grid_constant__ EncodeParams P) {
 // indices[level][corner][point] (int64) -- the public hash_coords and the bit-exactness tests
 // ------------------------------------------------------------------------------------------------
 template <int D, bool LINEAR>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, LINEAR ? 1 : 8)
 grid4d_indices_kernel(const __grid_constant__ EncodeParams P) {
     __shared__ LevelParams s_lv[kMaxGroup];
     int lane_level, p_step;
