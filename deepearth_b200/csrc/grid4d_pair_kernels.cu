@@ -55,7 +55,7 @@ __device__ __forceinline__ bool pair_setup(const EncodeParams& P, LevelParams* s
 // forward
 // ------------------------------------------------------------------------------------------------
 template <int D, typename TT, int F, bool POW2>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 8)
 grid4d_forward_pair_kernel(const __grid_constant__ EncodeParams P) {
     __shared__ LevelParams s_lv[kMaxGroup];
     PairThread t;
