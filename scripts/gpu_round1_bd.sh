@@ -1,5 +1,5 @@
 #!/bin/bash
-# lane-pair forward kernel compiled for 8 resident CTAs (32 registers): c2, c3, suite
+# lane-pair kernels compiled for more resident CTAs (forward 8, backward 6): c2, c3, suite
 mkdir -p gpurun_out
 B="timeout 300 python bench.py --no-cpu-baseline"
 $B --workload c2 > gpurun_out/bd_c2.json 2> gpurun_out/bd.err
