@@ -84,3 +84,59 @@ def test_forward_backward_random_geometries(oracle, ref_cls):
             scale = max(np.abs(want).max(), 1e-30)
             assert np.abs(grads[l * T:(l + 1) * T] - want).max() <= 1e-5 * scale, f"backward: case {k} level {l}"
         assert x.grad is None                                       # graph cut at floor().long(), hash_encoding.py:61
+
+
+def test_grid4d_encoder_features_and_masks_random(oracle):
+    """Reference Grid4DEncoder (models/encoders.py:54-85) feature half with random row masks, three seeds."""
+    sys.path.insert(0, REF)
+    try:
+        from models.configs import DeepEarthConfig                            # reference
+        from models.encoders import Grid4DEncoder                             # reference
+    finally:
+        sys.path.remove(REF)
+    T, F = 2 ** 12, 2
+    for seed in (1, 2, 3):
+        cfg = DeepEarthConfig(hidden_dim=16, n_heads=4, n_layers=1, hash_table_size=T)
+        enc = Grid4DEncoder(cfg)
+        levels, tabs, off = [], [], 0
+        for sub, dims, col0, mid, s0 in ((enc.spatial_encoder, (0, 1, 2), 0, 1, 100), (enc.temporal_encoder, (3,), 32, 2, 200)):
+            for l, emb in enumerate(sub.hash_tables):
+                t = synth_table(sub.hash_table_size, F, 1000 * seed + s0 + l, lo=-1.0, hi=1.0)
+                with torch.no_grad():
+                    emb.weight.copy_(torch.from_numpy(t))
+                levels.append(Level(T=sub.hash_table_size, R=int(sub.resolutions[l]), dims=dims, out_col=col0 + l * F,
+                                    table_off=off, mask_id=mid))
+                tabs.append(t)
+                off += sub.hash_table_size
+        n = 400
+        xyzt = coords_mixed(n, 4, seed=300 + seed, res_hint=16)
+        sm, tm = uniform01(n, 310 + seed) > 0.4, uniform01(n, 320 + seed) > 0.6
+        captured = {}
+        h = enc.projection.register_forward_hook(lambda m, i, o: captured.__setitem__("feat", i[0].detach().clone()))
+        enc(torch.from_numpy(xyzt), spatial_mask=torch.from_numpy(sm), temporal_mask=torch.from_numpy(tm))
+        h.remove()
+        got = oracle.forward(levels, xyzt, np.concatenate(tabs, 0), F, linear=False, mask_a=sm, mask_b=tm)
+        assert np.array_equal(got, captured["feat"].numpy()), f"seed {seed}"
+
+
+def test_geo2xyz_random_points(oracle):
+    """Reference GeospatialConverter.geodetic_to_xyz + xyz_to_norm (geo2xyz.py:146-160, :327-332) on random points
+    incl. poles and the date line: ECEF within 1e-6 m, normalised fp32 within one ulp of [0,1]."""
+    sys.path.insert(0, REF)
+    try:
+        from geospatial.geo2xyz import GeospatialConverter                    # reference
+    finally:
+        sys.path.remove(REF)
+    for seed in (11, 12, 13):
+        n = 1000
+        geo = np.stack([uniform01(n, seed) * 180 - 90, uniform01(n, seed + 50) * 360 - 180,
+                        uniform01(n, seed + 90) * 9500 - 450], 1)
+        geo[:4] = [[90, 0, 0], [-90, 12, 100], [0, 180, 0], [0, -180, 5]]
+        conv = GeospatialConverter()
+        xyz, _ = conv.geodetic_to_xyz(torch.from_numpy(geo))
+        norm = conv.xyz_to_norm(xyz).numpy()
+        bmin, span = conv.bbox.min_point.numpy(), conv.bbox.span.numpy()
+        got, ecef = oracle.geo2xyzt_norm(geo, None, bmin, span, (0.0, 1.0), want_ecef=True)
+        assert np.abs(ecef - xyz.numpy()).max() <= 1e-6
+        assert np.abs(got[:, :3] - norm.astype(np.float32)).max() <= 1.2e-7
+        assert (got[:, 3] == 0).all()
