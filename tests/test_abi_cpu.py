@@ -152,3 +152,27 @@ def test_backward_group_width_plan(lib):
     with_rows = lib.de_grid4d_backward_workspace_bytes_ex(lv, 64, 2, 2 ** 24, lin, 0)
     grouped = lib.de_grid4d_backward_workspace_bytes_ex(lv, 64, 2, 2 ** 24, lin | _lib.DE_FLAG_GRAD_GROUPED, 0)
     assert with_rows - grouped >= 2 ** 24 * 128 * 4                              # the regroup scratch is only asked for when needed
+
+
+def test_import_shim_serves_the_reference_import_lines():
+    """examples/quick_test.py:15-19 style imports resolve to the B200 classes after shim.install() (own process:
+    the shim edits sys.modules)."""
+    import subprocess
+    import sys
+    code = (
+        "import deepearth_b200 as de\n"
+        "from deepearth_b200 import shim\n"
+        "shim.install()\n"
+        "from models.hash_encoding import MultiResolutionHashEncoding\n"
+        "from models.encoders import Grid4DEncoder\n"
+        "from models.configs import DeepEarthConfig, ModalityConfig, TransformerConfig\n"
+        "import models\n"
+        "assert MultiResolutionHashEncoding is de.MultiResolutionHashEncoding and Grid4DEncoder is de.Grid4DEncoder\n"
+        "assert models.Grid4DEncoder is de.Grid4DEncoder and DeepEarthConfig is de.DeepEarthConfig\n"
+        "enc = Grid4DEncoder(DeepEarthConfig(hidden_dim=32, n_heads=4, n_layers=1, hash_table_size=2 ** 10))\n"
+        "assert len(enc.spatial_encoder.hash_tables) == 16 and len(enc.temporal_encoder.hash_tables) == 8\n"
+        "assert enc.spatial_encoder.hash_tables[0].weight.shape == (2 ** 10, 2)\n"
+        "print('ok')\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stderr[-2000:]
