@@ -20,6 +20,17 @@ Workloads (BASELINE.json configs):
 
 One JSON line on stdout (rank 0).  `value` times the C-ABI calls with device-resident inputs;
 `e2e` times the public nn.Module API with pinned-host coordinates copied in and a scalar read back.
+
+Besides the headline workload the default line carries (key "extra"):
+  N = 1:  "c3"  -- the north_star's target configuration (2^24 Florida-clustered points, T = 2^22) with its own
+                   kernels_ms / roofline / e2e;  "c1r" -- the reference's own geometry (the only mode with a reference
+                   implementation);  "eager_cuda_baseline" -- the reference op chain through PyTorch-CUDA eager on the
+                   same GPU (the restatement oracle/grid4d_torch.py at the c2 geometry; at the c1r geometry the
+                   UNMODIFIED reference classes from oracle/_ref when build() could copy them);
+  N > 1:  "c4"  -- configs[3], 2^26 points in total (strong scaling) beside the weak-scaling headline;
+          "grad_check" -- max relative error of the all-reduced gradient against the gradient of the union of all
+                   ranks' points computed locally (mean over ranks, hpc/train_distrbuted.py:499-504).
+--extras none switches them off (development runs); an explicit --workload runs that workload alone.
 """
 from __future__ import annotations
 
@@ -69,7 +80,19 @@ def algorithmic_bytes_per_point(n_level_rows: int, corners: int, F: int, table_b
 # L1->L2 request ("packet" = distinct 32 B sector per instruction) peaks measured on B200 by scripts/peaks_gather.py
 # (profiles/r01c_peaks_gather.json, L2-resident working set, 2 adjacent lanes on adjacent entries):
 # loads 574 G lane-ops/s = 287 G packets/s (1.0 / clk / SM); red.global.add.v2.f32 430 G lane-ops/s = 215 G packets/s.
-PACKET_PEAK_G = {"forward": 287.0, "backward": 215.0}
+PEAKS_FILE = os.path.join("profiles", "r01c_peaks_gather.json")
+
+
+def packet_peaks():
+    """Best L2-resident rate of the "2 adjacent lanes" pattern (one packet per lane pair): 4 B entries for the
+    forward's fp16 x 2 gathers, 8 B entries for the backward's red.v2.f32 -- read from the committed probe output."""
+    with open(os.path.join(ROOT, PEAKS_FILE)) as f:
+        rows = json.load(f)["rows"]
+
+    def best(op, eb):
+        return max(r["gops"] for r in rows if r["working_set"].startswith("L2_") and r["op"] == op
+                   and r["entry_bytes"] == eb and r["pattern"] == "2 adjacent lanes") / 2.0
+    return {"forward": best("load", 4), "backward": best("red.add.f32", 8)}
 
 
 def packets_per_point(n_level_rows: int, corners: int, F: int, entry_bytes: int):
@@ -222,6 +245,7 @@ class Job:
             self.table_ptrs = [p for e in self.enc._encoders for p in e.working_ptrs()]
         else:
             self.table_ptrs = [w.data_ptr() for w in self.weights]
+        self.weight_ptrs = [w.data_ptr() for w in self.weights]
         self.flat_grad = torch.zeros(self.plan.grad_numel, dtype=torch.float32, device=device)
         self.grad_ptrs = [self.flat_grad.data_ptr() + 4 * o for o in self.plan.grad_offsets]
         self.head = None
@@ -238,10 +262,7 @@ class Job:
             self.gy = torch.randn((n_points, 64), device=device, generator=g)
             self.gout = None
         else:
-            self.coords = make_coords(wl, n_points, device, seed)
-            if wl.get("sort_points"):
-                self.coords = morton_sort(self.coords)
-            self.gout = torch.randn((n_points, self.plan.out_cols), device=device, generator=g)
+            self.coords, self.gout = Job.inputs(wl, n_points, device, seed, self.plan.out_cols)
         self.out = torch.empty((n_points, self.plan.out_cols), dtype=torch.float32, device=device)
         corners = 8 if self.linear else 1
         tb = 2 if self.plan.table_dtype == torch.float16 else 4
@@ -252,6 +273,22 @@ class Job:
         self.use_replicas = True
         self.head_bwd = "tcgen05"
         self.group_w = 0          # > 0: the head backward writes d(loss)/d(features) group-major for the hash-grid backward
+
+    @staticmethod
+    def inputs(wl, n_points, device, seed, out_cols):
+        """(coords, grad_out) of the rank whose seed this is: reproducible on any rank (grad_check rebuilds them)."""
+        coords = make_coords(wl, n_points, device, seed)
+        if wl.get("sort_points"):
+            coords = morton_sort(coords)
+        g = torch.Generator(device=device).manual_seed(seed + 1)
+        return coords, torch.randn((n_points, out_cols), device=device, generator=g)
+
+    def refresh_tables(self):
+        """fp32 master tables -> fp16 working tables (one de_tables_to_f16 launch over all 64 levels); no-op for fp32."""
+        if self.plan.table_dtype != torch.float16:
+            return
+        from deepearth_b200 import functional as Fn
+        Fn.tables_to_f16(self.plan.specs, self.weight_ptrs, self.table_ptrs, self.F, self.plan.table_scale, self.device)
 
     def forward(self):
         from deepearth_b200 import functional as Fn
@@ -307,39 +344,62 @@ class Job:
         if self.use_replicas and _lib.load().de_grid4d_backward_workspace_bytes_ex(
                 lv, len(self.plan.specs), self.F, self.n, lin | _lib.DE_FLAG_NO_REGROUP, self.plan.bwd_levels_per_group):
             extra += runs
-        return 2 * runs + extra + (3 if self.head is not None else 0)     # + prologue + head forward + head backward kernels
+        cast = 1 if self.plan.table_dtype == torch.float16 else 0            # de_tables_to_f16 refresh
+        return 2 * runs + extra + cast + (3 if self.head is not None else 0)     # + prologue + head forward + head backward kernels
 
 
 # ---------------------------------------------------------------------------------------------------
-# CPU baseline (the reference is PyTorch eager on CPU; oracle/grid4d_torch.py issues the same ATen ops)
+# CPU baseline / reference arm.  The reference is PyTorch eager; oracle/grid4d_torch.py issues the same ATen ops
+# (and is pinned to the reference's golden vectors by tests/test_torch_port_cpu.py).  At the reference's own
+# geometry (c1r) the UNMODIFIED reference classes are used when build() could copy them to oracle/_ref.
 # ---------------------------------------------------------------------------------------------------
-def cpu_baseline_run(wl, log2_sample, steps, warmup):
+def reference_step_factory(wl, n, device, threads_note=""):
+    """-> (step(), kind, description): one fwd+bwd of the reference op chain on `device` over n uniform points."""
     from oracle.grid4d_torch import RefGrid4DFeatures, grid4d_forward
-    n = 2 ** log2_sample
-    torch.manual_seed(1234)
-    threads = torch.get_num_threads()
-    g = torch.Generator().manual_seed(99)
-    xyzt = torch.rand((n, 4), generator=g)
+    g = torch.Generator(device=device).manual_seed(99)
+    xyzt = torch.rand((n, 4), generator=g, device=device)
     res = [2 ** i for i in range(4, 20)]
     if wl["mode"] == "decomposed":
         T = wl["T"]
         dims_list = [(0, 1, 2), (0, 1, 3), (1, 2, 3), (0, 2, 3)]
         specs = [(d, R, T, (R + 1) ** 3 <= T) for d in dims_list for R in res]
-        tabs = [torch.nn.Parameter((torch.rand((T, 2), generator=g) * 2e-4 - 1e-4)) for _ in specs]
-        gout = torch.randn((n, 128), generator=g)
+        tabs = [torch.nn.Parameter((torch.rand((T, 2), generator=g, device=device) * 2e-4 - 1e-4)) for _ in specs]
+        gout = torch.randn((n, 128), generator=g, device=device)
 
         def step():
             for t in tabs:
                 t.grad = None
             out = grid4d_forward(xyzt, tabs, specs, linear=True)
             out.backward(gout)
-    else:
-        model = RefGrid4DFeatures(hash_table_size=wl["T"])
-        gout = torch.randn((n, 48), generator=g)
+        return step, "port", ("oracle/grid4d_torch.py: the reference's hash_coords op chain per corner + multilinear weights "
+                              "(the reference holds no implementation of the decomposed mode), fp32 tables")
+    from oracle.ref_loader import load_reference_models
+    ref = load_reference_models()
+    gout = torch.randn((n, 48), generator=g, device=device)
+    if ref is not None:
+        torch.manual_seed(1234)
+        sp = ref.MultiResolutionHashEncoding(16, 2, res, wl["T"], 3).to(device)
+        tp = ref.MultiResolutionHashEncoding(8, 2, [2 ** i for i in range(2, 10)], wl["T"] // 4, 1).to(device)
+        params = list(sp.parameters()) + list(tp.parameters())
 
         def step():
-            model.zero_grad(set_to_none=True)
-            model(xyzt).backward(gout)
+            for q in params:
+                q.grad = None
+            torch.cat([sp(xyzt[:, :3]), tp(xyzt[:, 3:4])], dim=-1).backward(gout)      # models/encoders.py:68-82
+        return step, "reference", "unmodified /root/reference/models/hash_encoding.py classes (oracle/_ref), fp32"
+    model = RefGrid4DFeatures(hash_table_size=wl["T"]).to(device)
+
+    def step():
+        model.zero_grad(set_to_none=True)
+        model(xyzt).backward(gout)
+    return step, "port", "oracle/grid4d_torch.py RefGrid4DFeatures (op-by-op port of models/hash_encoding.py), fp32"
+
+
+def cpu_baseline_run(wl, log2_sample, steps, warmup):
+    n = 2 ** log2_sample
+    torch.manual_seed(1234)
+    threads = torch.get_num_threads()
+    step, kind, what = reference_step_factory(wl, n, torch.device("cpu"))
     for _ in range(warmup):
         step()
     times = []
@@ -348,24 +408,60 @@ def cpu_baseline_run(wl, log2_sample, steps, warmup):
         step()
         times.append(time.perf_counter() - t0)
     sec = float(np.mean(times))
-    return {"value": n / sec / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
+    return {"value": n / sec / 1e6, "unit": UNIT, "cores": threads, "kind": kind,
             "sample": f"{steps} fwd+bwd steps of 2^{log2_sample} uniform points, same grids/levels/T as the GPU arm, "
-                      f"fp32 tables, PyTorch eager CPU ops (oracle/grid4d_torch.py), {threads} threads",
+                      f"PyTorch eager CPU ops, {threads} threads; {what}",
             "ms_per_step": sec * 1e3}
+
+
+def eager_cuda_baseline(wl, n, device, steps=3, warmup=2):
+    """The reference op chain through PyTorch-CUDA eager on the same GPU: the like-for-like comparator of `value`."""
+    step, kind, what = reference_step_factory(wl, n, device)
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    peak_gib = torch.cuda.max_memory_allocated(device) / 2 ** 30
+    return {"value": n / (ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms, "points": n, "kind": kind,
+            "what": what + "; fwd+bwd, CUDA events, same B200", "peak_mem_gib": round(peak_gib, 1)}
+
+
+def cpu_sample_log2(wl, steps, warmup):
+    """Bounded CPU sample: the decomposed mode runs ~0.03 Mpoints/s on 16 host threads, so 2^17 points x 13 steps is
+    about a minute; more steps shrink the sample."""
+    if wl["mode"] != "decomposed":
+        return 18
+    log2 = 17 if steps + warmup <= 16 else 16
+    if wl["T"] > 2 ** 20:
+        log2 -= 1
+    return log2
+
+
+def describe_config(name, wl, n_points, world=1):
+    return {"workload": name, "description": wl["desc"], "points_per_gpu": n_points, "coords": wl["coords"],
+            "levels": 64 if wl["mode"] == "decomposed" else 24, "features_per_level": 2, "table_size": wl["T"],
+            "interpolation": "linear" if wl["mode"] == "decomposed" else "nearest",
+            "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"}
 
 
 def run_reference_arm(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    log2_sample = 16 if wl["mode"] == "decomposed" else 18
-    if wl["T"] > 2 ** 20:
-        log2_sample = 15
+    log2_sample = cpu_sample_log2(wl, max(1, args.steps), max(1, args.warmup))
     cb = cpu_baseline_run(wl, log2_sample, max(1, args.steps), max(1, args.warmup))
+    cfg = describe_config(args.workload, wl, 2 ** wl["log2_points"], args.gpus)
+    cfg["sample"] = cb["sample"]
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
             "scaling": "strong" if wl.get("total") else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "description": wl["desc"], "sample": cb["sample"]},
+            "config": cfg,
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -375,24 +471,41 @@ def run_reference_arm(args, wl):
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
-def run_gpu_arm(args, wl):
-    import torch.distributed as dist
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU port)")
-    torch.cuda.set_device(local)
-    device = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=device)
+class Ctx:
+    """Process-wide state of the GPU arm: ranks, device, clock sampler."""
+
+    def __init__(self):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU port)")
+        torch.cuda.set_device(self.local)
+        self.device = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.device)
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, v: float) -> float:
+        if self.world == 1:
+            return v
+        t = torch.tensor([v], device=self.device, dtype=torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t)
+
+
+def measure(args, name, wl, ctx, steps, want_clocks=True):
+    """Times one workload on this rank (device-resident `value` leg, then the `e2e` leg); rank 0 gets the result dict."""
+    dist, world, rank, device = ctx.dist, ctx.world, ctx.rank, ctx.device
     from deepearth_b200 import functional as Fn
     from deepearth_b200 import _lib as _L
     import ctypes as _ct
-    if args.l2_fetch:
-        _L.check(_L.load().de_set_l2_fetch_granularity(args.l2_fetch), "de_set_l2_fetch_granularity")
-    if args.persist_l2_mb:
-        _L.check(_L.load().de_set_persisting_l2(-1 if args.persist_l2_mb < 0 else args.persist_l2_mb << 20), "de_set_persisting_l2")
     _pl2, _pl2max = _ct.c_longlong(0), _ct.c_longlong(0)
     _L.load().de_get_persisting_l2(_ct.byref(_pl2), _ct.byref(_pl2max))
     _gran = _ct.c_int(0)
@@ -426,6 +539,7 @@ def run_gpu_arm(args, wl):
 
     def step(ev=None):
         job.flat_grad.zero_()
+        job.refresh_tables()             # fp32 masters -> fp16 working tables: what a training step does after the optimiser
         if ev:
             ev[0].record()
         if job.head is not None:
@@ -457,33 +571,28 @@ def run_gpu_arm(args, wl):
                 if ev:
                     ev[3].record()
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    sampler = ClockSampler(local)
-    if rank == 0:
+    sampler = ClockSampler(ctx.local)
+    if rank == 0 and want_clocks:
         sampler.start()                    # nvidia-smi takes ~0.5 s to deliver its first sample
     for _ in range(max(args.warmup, 3)):
         step()
-    barrier()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(args.steps)]
+    ctx.barrier()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(steps)]
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
+    ctx.barrier()
     w0 = sampler.mark()
     t_start.record()
-    for k in range(args.steps):
+    for k in range(steps):
         step(evs[k])
     t_end.record()
-    barrier()
+    ctx.barrier()
     w1 = sampler.mark()
     clock_window = "timed region"
     # the timed region may be shorter than a few nvidia-smi periods: then every rank keeps the same load
     # running (untimed) until rank 0 has enough samples, and the JSON line says so
     extra = 0
     if rank == 0 and sampler.proc is not None and sampler.n_between(w0, w1) < 4:
-        extra = max(1, int(1500.0 / max(t_start.elapsed_time(t_end) / args.steps, 0.05)))
+        extra = max(1, int(1500.0 / max(t_start.elapsed_time(t_end) / steps, 0.05)))
     if world > 1:
         ex = torch.tensor([extra], device=device, dtype=torch.int64)
         dist.broadcast(ex, 0)
@@ -492,9 +601,9 @@ def run_gpu_arm(args, wl):
         clock_window = "timed region + identical untimed steps run straight after it"
         for _ in range(extra):
             step()
-        barrier()
+        ctx.barrier()
         w1 = sampler.mark()
-    clocks = sampler.stop(w0, w1) if rank == 0 else None
+    clocks = sampler.stop(w0, w1) if (rank == 0 and want_clocks) else None
     if clocks is not None:
         clocks["window"] = clock_window
     total_ms = t_start.elapsed_time(t_end)
@@ -508,11 +617,8 @@ def run_gpu_arm(args, wl):
     fwd_enc_ms = fwd_ms          # c5: includes the ~0.15 ms prologue
     bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
     ar_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in evs])) if world > 1 else 0.0
-    if world > 1:
-        t = torch.tensor([total_ms], device=device, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t)
-    ms_per_step = total_ms / args.steps
+    total_ms = ctx.max_over_ranks(total_ms)
+    ms_per_step = total_ms / steps
     value = world * n / (ms_per_step * 1e-3) / 1e6
 
     # ---- end to end through the public nn.Module API, pinned-host coordinates in, scalar out --------
@@ -585,75 +691,148 @@ def run_gpu_arm(args, wl):
 
     for _ in range(3):
         e2e_step()
-    barrier()
+    ctx.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         checksum = e2e_step()
     e1.record()
-    barrier()
-    e2e_ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([e2e_ms], device=device, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t)
-    e2e_value = world * n / (e2e_ms / args.steps * 1e-3) / 1e6
-
+    ctx.barrier()
+    e2e_ms = ctx.max_over_ranks(e0.elapsed_time(e1))
+    e2e_value = world * n / (e2e_ms / steps * 1e-3) / 1e6
+    launches = job.n_launches_per_step() * steps
+    result = None
     if rank == 0:
         peak, peak_src = measured_peaks()
+        pk = packet_peaks()
         dom = "backward" if bwd_ms >= fwd_ms else "forward"
         dom_ms = max(bwd_ms, fwd_ms)
         dom_bytes = (job.bytes_bwd if dom == "backward" else job.bytes_fwd) * n
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
-        traffic = None
+        traffic, traffic_src = None, None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
             with open(tpath) as f:
-                traffic = json.load(f).get(args.workload, {}).get(dom)
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                tj = json.load(f).get(name, {})
+            traffic, traffic_src = tj.get(dom), tj.get("source")
+        # where the dominant kernel's working set lives: one level group's tables (forward) / gradient tables (backward)
+        lvl_bytes = wl["T"] * job.F * (4 if dom == "backward" else (2 if wl["table_dtype"] == "float16" else 4))
+        resident = "l2" if lvl_bytes * 16 <= 64 * 2 ** 20 or wl["mode"] != "decomposed" else "hbm"
+        cfg = describe_config(name, wl, n, world)
+        if sync is not None:
+            cfg["parallelism"] += f" overlapped with the backward in {args.sync_chunks} level runs"
+        cfg.update({"l2_policy": "inputs larger than L2 (coords + grad_out + out > 4 GiB per step); no flush",
+                    "l2_fetch_granularity": _gran.value, "head_grad_group_width": job.group_w,
+                    "l2_persisting_bytes": _pl2.value, "l2_persisting_max_bytes": _pl2max.value,
+                    "step": "zero grad buffer + fp32->fp16 table refresh + forward + backward" + (" + all-reduce" if world > 1 else "")})
+        result = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong" if wl.get("total") else "weak",
             "vs_baseline": None, "dtype": "f16 tables / f32 accumulate" if wl["table_dtype"] == "float16" else "f32",
             "data": "synthetic",
-            "config": {"workload": args.workload, "description": wl["desc"], "points_per_gpu": n,
-                       "coords": wl["coords"], "levels": len(job.plan.specs), "features_per_level": job.F,
-                       "table_size": wl["T"], "interpolation": "linear" if job.linear else "nearest",
-                       "l2_policy": "inputs larger than L2 (coords+grad_out+out > 4 GiB per step); no flush",
-                       "l2_fetch_granularity": _gran.value, "head_grad_group_width": job.group_w,
-                       "l2_persisting_bytes": _pl2.value, "l2_persisting_max_bytes": _pl2max.value,
-                       "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"
-                                      + (f" overlapped with the backward in {args.sync_chunks} level runs" if sync is not None else "")},
+            "config": cfg,
             "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms, **(head_ms or {})},
             "roofline": {"bound": "hbm", "kernel": f"grid4d_{dom}_kernel", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
+                         "working_set": ("one level group's tables stay L2-resident: the unit that binds is the L1->L2 request "
+                                         "rate (roofline_packets), HBM carries only the streamed rows" if resident == "l2" else
+                                         "tables exceed L2 (HBM-resident): gathers / reductions miss to HBM per level group"),
+                         "working_set_level": resident,
                          "algorithmic_bytes_per_point": {"forward": job.bytes_fwd, "backward": job.bytes_bwd}},
             # the bound that actually applies while a level group's tables sit in L2: distinct 32 B
             # sectors requested per second against the probe-measured L1->L2 request rate of the same access shape
             "roofline_packets": {
                 "bound": "l2_request_rate", "unit": "Gpackets/s",
                 "forward": {"packets_per_point": job.packets_fwd, "achieved": job.packets_fwd * n / (fwd_enc_ms * 1e-3) / 1e9,
-                            "peak": PACKET_PEAK_G["forward"],
-                            "frac": job.packets_fwd * n / (fwd_enc_ms * 1e-3) / 1e9 / PACKET_PEAK_G["forward"]},
+                            "peak": pk["forward"],
+                            "frac": job.packets_fwd * n / (fwd_enc_ms * 1e-3) / 1e9 / pk["forward"]},
                 "backward": {"packets_per_point": job.packets_bwd, "achieved": job.packets_bwd * n / (bwd_ms * 1e-3) / 1e9,
-                             "peak": PACKET_PEAK_G["backward"],
-                             "frac": job.packets_bwd * n / (bwd_ms * 1e-3) / 1e9 / PACKET_PEAK_G["backward"]},
-                "peak_source": "profiles/r01c_peaks_gather.json (scripts/peaks_gather.py on B200)"},
+                             "peak": pk["backward"],
+                             "frac": job.packets_bwd * n / (bwd_ms * 1e-3) / 1e9 / pk["backward"]},
+                "peak_source": PEAKS_FILE + " (scripts/peaks_gather.py on B200; best L2-resident rate, 2 adjacent lanes)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes * world),
-                    "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / args.steps, "checksum": checksum,
+                    "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms / steps, "checksum": checksum,
                     "api": api},
-            "gpu_launches": job.n_launches_per_step() * args.steps,
+            "gpu_launches": launches,
             "clocks": clocks,
         }
-        if world == 1 and not args.no_cpu_baseline:
-            log2_sample = 16 if wl["mode"] == "decomposed" else 18
-            if wl["T"] > 2 ** 20:
-                log2_sample = 15
-            cb = cpu_baseline_run(wl, log2_sample, 3, 1)
+    # release this workload's device memory before the next one
+    job.enc.disable_grad_sync()
+    del job, pending, params
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    return result
+
+
+def grad_check(args, ctx, log2_points=16):
+    """N > 1: the all-reduced (mean) table gradient of a small deterministic batch, computed through the overlapped
+    GradSync path bench.py times, against the gradient of the UNION of all ranks' points computed locally by one plain
+    de_grid4d_backward per rank's batch (rank r's points and gradient rows are rebuilt from seeds 1234 + r)."""
+    from deepearth_b200 import functional as Fn
+    from deepearth_b200.distributed import GradSync
+    wl = dict(WORKLOADS["c2"])
+    n = 2 ** log2_points
+    job = Job(wl, ctx.device, seed=1234 + ctx.rank, n_points=n)
+    sync = GradSync(average=True, chunks=args.sync_chunks)
+    flat = torch.zeros_like(job.flat_grad)
+    sync.backward(job.plan.specs, job.coords, job.gout, flat, job.plan.grad_offsets, job.F, job.linear)
+    ref = torch.zeros_like(job.flat_grad)
+    ptrs = [ref.data_ptr() + 4 * o for o in job.plan.grad_offsets]
+    for r in range(ctx.world):
+        other = Job.inputs(wl, n, ctx.device, 1234 + r, job.plan.out_cols)
+        Fn.encode_backward(job.plan.specs, other[0], other[1], ptrs, job.F, job.linear)
+    ref.div_(ctx.world)
+    torch.cuda.synchronize()
+    err = float((flat - ref).abs().max()) / max(float(ref.abs().max()), 1e-30)
+    err = ctx.max_over_ranks(err)
+    del job
+    torch.cuda.empty_cache()
+    return {"max_rel_err": err, "tolerance": 1e-4, "ok": bool(err <= 1e-4), "points_per_rank": n, "ranks": ctx.world,
+            "what": "GradSync.backward (mean over ranks, overlapped level runs) vs plain backward over the union of all "
+                    "ranks' points / world, max over ranks of max|diff| / max|ref| on the flat 256 MiB gradient buffer"}
+
+
+def run_gpu_arm(args, wl):
+    ctx = Ctx()
+    from deepearth_b200 import _lib as _L
+    if args.l2_fetch:
+        _L.check(_L.load().de_set_l2_fetch_granularity(args.l2_fetch), "de_set_l2_fetch_granularity")
+    if args.persist_l2_mb:
+        _L.check(_L.load().de_set_persisting_l2(-1 if args.persist_l2_mb < 0 else args.persist_l2_mb << 20), "de_set_persisting_l2")
+    extras_on = args.extras == "all" or (args.extras == "auto" and not args.workload_given)
+    line = measure(args, args.workload, wl, ctx, args.steps)
+    extra = {}
+    if extras_on:
+        side_steps = max(2, min(args.steps, 5))
+        if ctx.world == 1:
+            for nm in ("c3", "c1r"):
+                r = measure(args, nm, dict(WORKLOADS[nm]), ctx, side_steps)
+                extra[nm] = {k: r[k] for k in ("value", "unit", "steps", "ms_per_step", "config", "kernels_ms", "roofline",
+                                               "roofline_packets", "e2e", "gpu_launches", "clocks")}
+            torch.cuda.reset_peak_memory_stats(ctx.device)
+            extra["eager_cuda_baseline"] = {
+                "c2": eager_cuda_baseline(dict(WORKLOADS["c2"]), 2 ** 22, ctx.device),
+                "c1r": eager_cuda_baseline(dict(WORKLOADS["c1r"]), 2 ** 22, ctx.device)}
+            torch.cuda.empty_cache()
+        else:
+            r = measure(args, "c4", dict(WORKLOADS["c4"]), ctx, side_steps, want_clocks=False)
+            if ctx.rank == 0:
+                extra["c4"] = {k: r[k] for k in ("value", "unit", "scaling", "steps", "ms_per_step", "config", "kernels_ms", "e2e")}
+            gc_res = grad_check(args, ctx)
+            extra["grad_check"] = gc_res
+    if ctx.rank == 0:
+        if extra:
+            line["extra"] = extra
+            line["gpu_launches"] += sum(v.get("gpu_launches", 0) for v in extra.values() if isinstance(v, dict))
+        if ctx.world == 1 and not args.no_cpu_baseline:
+            cb = cpu_baseline_run(wl, cpu_sample_log2(wl, 3, 1) - 1, 3, 1)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    if ctx.world > 1:
+        ctx.dist.destroy_process_group()
 
 
 def main():
@@ -662,7 +841,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
+    ap.add_argument("--extras", default="auto", choices=["auto", "all", "none"],
+                    help="side measurements in the same line: auto = on for the default workload, off for an explicit --workload")
     ap.add_argument("--log2-points", type=int, default=0, help="override points per GPU (power of two)")
     ap.add_argument("--levels-per-group", type=int, default=0)
     ap.add_argument("--bwd-levels-per-group", type=int, default=0)
@@ -678,6 +859,9 @@ def main():
     ap.add_argument("--persist-l2-mb", type=int, default=0, help="cudaLimitPersistingL2CacheSize in MiB (-1 = device maximum)")
     ap.add_argument("--l2-fetch", type=int, default=0, help="set cudaLimitMaxL2FetchGranularity (32/64/128)")
     args = ap.parse_args()
+    args.workload_given = args.workload is not None
+    if args.workload is None:
+        args.workload = "c2"
     wl = dict(WORKLOADS[args.workload])
     if args.coords:
         wl["coords"] = args.coords

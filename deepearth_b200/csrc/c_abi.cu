@@ -145,25 +145,27 @@ bool staging_ok(const CallArgs& a, const de::EncodeParams& P, const int* idx, in
     return true;
 }
 
-// Developer tuning knobs read from the environment per call (never required; defaults are the measured best).
-int tune_env(const char* name, int dflt, int lo, int hi) {
+// Developer tuning knobs (never required; defaults are the measured best).  Each knob is read from the environment
+// ONCE per process, at its first use, so a later setenv() cannot silently change the launch geometry of a running job.
+int read_env(const char* name, int dflt, int lo, int hi) {
     const char* v = getenv(name);
     if (!v || !*v) return dflt;
     const long x = strtol(v, nullptr, 0);
     return (x < lo || x > hi) ? dflt : static_cast<int>(x);
 }
+#define DE_KNOB(name, dflt, lo, hi) ([]() -> int { static const int v = read_env(name, dflt, lo, hi); return v; }())
 
 // Ring geometry: ~64 points per stage (a whole number of CTA passes), 4 stages, long-lived CTAs.
 void plan_stages(const CallArgs& a, de::EncodeParams& P) {
     const int p_step = de::kThreads / (2 * P.group_size);
-    int tp = tune_env("DE_BWD_STAGE_POINTS", 64, 8, 1024);
+    int tp = DE_KNOB("DE_BWD_STAGE_POINTS", 64, 8, 1024);
     tp = ((tp + p_step - 1) / p_step) * p_step;
     P.stage_points = tp;
-    P.n_stages = tune_env("DE_BWD_STAGES", 4, 2, 8);
+    P.n_stages = DE_KNOB("DE_BWD_STAGES", 4, 2, 8);
     while (P.n_stages > 2 && de::staged_smem_bytes(P, a.n_features) > 96 * 1024) --P.n_stages;
     long long per_cta = (a.n_points + 148ll * 8 - 1) / (148ll * 8);      // >= 8 CTAs per SM and group
     long long stages = (per_cta + tp - 1) / tp;
-    const int max_stages = tune_env("DE_BWD_CTA_STAGES", 32, 1, 4096);
+    const int max_stages = DE_KNOB("DE_BWD_CTA_STAGES", 32, 1, 4096);
     if (stages < 1) stages = 1;
     if (stages > max_stages) stages = max_stages;
     P.points_per_cta = static_cast<int>(stages) * tp;
@@ -378,8 +380,11 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
     size_t regroup_off = 0;         // regrouped gradient rows live behind the replicas
     if (op == Op::Backward && a.workspace) {
         const size_t used = replica_workspace_bytes(a.levels, a.n_levels, a.n_features, a.n_points, linear);
-        if (used > 0 && used <= a.workspace_bytes) {
-            cudaError_t e = cudaMemsetAsync(a.workspace, 0, used, stream);
+        // replicas are granted front to back while they fit (below), so every granted range lies inside
+        // [0, min(used, workspace_bytes)): zero exactly that, also when the caller's scratch is smaller than asked for
+        const size_t zeroed = used < a.workspace_bytes ? used : a.workspace_bytes;
+        if (zeroed > 0) {
+            cudaError_t e = cudaMemsetAsync(a.workspace, 0, zeroed, stream);
             if (e != cudaSuccess) return cuda_fail(e, "workspace memset");
         }
         regroup_off = (used + 255) & ~static_cast<size_t>(255);
@@ -478,8 +483,8 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
         // loop trips per CTA (run ao / ap): the forward kernels want long-lived CTAs (set-up amortised, fewer block
         // launches), the backward kernels do not (shorter tiles spread the reductions of a group more evenly)
         const bool fwd_like = op != Op::Backward;
-        const int iters = pair ? tune_env(fwd_like ? "DE_PAIR_TILE_ITERS_FWD" : "DE_PAIR_TILE_ITERS_BWD", fwd_like ? 32 : 8, 1, 4096)
-                               : tune_env(fwd_like ? "DE_TILE_ITERS_FWD" : "DE_TILE_ITERS_BWD", fwd_like ? 16 : 8, 1, 4096);
+        const int iters = pair ? (fwd_like ? DE_KNOB("DE_PAIR_TILE_ITERS_FWD", 32, 1, 4096) : DE_KNOB("DE_PAIR_TILE_ITERS_BWD", 8, 1, 4096))
+                               : (fwd_like ? DE_KNOB("DE_TILE_ITERS_FWD", 16, 1, 4096) : DE_KNOB("DE_TILE_ITERS_BWD", 8, 1, 4096));
         int trips = iters;
         {
             // small batches: never fewer CTAs than the short tiles of r01h gave (8 / 4 trips) until there are a few

@@ -92,11 +92,9 @@ struct MlpHeadBwdParams {
     float* dw2;                   // (64, 64) accumulated
     float* db2;                   // (64,) accumulated, or NULL
     int n_tiles;
-    int variant;                  // A/B switch (env DE_HEAD_BWD_VARIANT): bit 0 = serial kernel (mlp_head_bwd.cu)
 };
 bool mlp_head_supported(int in_dim, int hidden, int out_dim);
-cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);        // dispatcher
-cudaError_t launch_mlp_head_bwd_pp(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);     // mlp_head_bwd2.cu
+cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);        // mlp_head_bwd2.cu
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s);
 
 cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,

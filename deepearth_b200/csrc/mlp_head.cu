@@ -422,8 +422,8 @@ bool mlp_head_supported(int in_dim, int hidden, int out_dim) {
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s) {
     P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
     if (P.n_tiles == 0) return cudaSuccess;
-    const char* v = getenv("DE_HEAD_FWD_VARIANT");       // A/B: 1 = the single-tile kernel
-    if (!(v && atoi(v) == 1)) {
+    static const bool single = []() { const char* v = getenv("DE_HEAD_FWD_VARIANT"); return v && atoi(v) == 1; }();   // A/B knob, read once
+    if (!single) {
         switch (in_dim) {
             case 32: return launch_dual_k<32>(P, n_sms, s);
             case 48: return launch_dual_k<48>(P, n_sms, s);

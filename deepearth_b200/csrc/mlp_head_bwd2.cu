@@ -3,13 +3,13 @@
 //   forward:  h = x W1^T + b1 ;  z = LN(h) (optional) ;  a = act(z) ;  y = a W2^T + b2
 //   (structure of Grid4DEncoder.projection, /root/reference/models/encoders.py:47-52, at the 64-wide size of
 //   BASELINE.json configs[4]); given gy = dL/dy this kernel produces dL/dx and accumulates dW1, db1, dgamma,
-//   dbeta, dW2, db2.  Same mathematics and the same four GEMMs per 128-point tile as mlp_head_bwd.cu:
+//   dbeta, dW2, db2.  Four GEMMs per 128-point tile:
 //
 //   GEMM 1  D_h  [128 x 64]  = X  [128 x K1] * W1^T           GEMM 2  D_da [128 x 64] = GY [128 x 64] * W2
 //   GEMM 3  D_dx [128 x K1]  = DH [128 x 64] * W1
 //   GEMM 4  D_dW [128 x N4] += [GY | DH]^T [128 cols x 128 pts] * [A | X | 1] [128 pts x N4]   (dW2, dW1, db2, db1)
 //
-// What changed against mlp_head_bwd.cu (16.8 ms per 2^24 points, one 4-warp CTA per SM, every phase serial):
+// What changed against the first version (16.8 ms per 2^24 points, one 4-warp CTA per SM, every phase serial; removed):
 //   * GEMM 4 contracts over POINTS.  Its operands are the point-major tiles the other GEMMs already use, read
 //     as MN-major operands (instruction-descriptor bits 15/16): no transposed copies, which were ~400 two-byte
 //     shared stores per thread per tile and 84 KB of shared memory.
@@ -284,7 +284,7 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                         for (int k = 0; k < kTileM / 16; ++k) {     // GEMM 4: [GY | DH]^T * [A | X | 1], K = 16 points per step
                             const uint32_t aa = gd + k * 2 * kGdGroup, ba = xa + k * 2 * kXaGroup;
                             // MN-major, no swizzle: SBO = bytes between 8-column core matrices (128), LBO = bytes between
-                            // 8-point groups (checked on B200 against the serial kernel: scripts/head_bwd_check.py)
+                            // 8-point groups (checked on B200 against the first, serial version of this kernel, since removed)
                             umma_bf16(tmem + kColDw2, umma_desc(aa, kGdGroup, 128), umma_desc(ba, kXaGroup, 128), kIdescDw,
                                       (dw_started || k > 0) ? 1u : 0u);
                         }
@@ -473,8 +473,8 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
 // ------------------------------------------------------------------------------------------------
 template <int K1>
 static cudaError_t launch_pp_k(const MlpHeadBwdParams& P, int n_sms, cudaStream_t s) {
-    const char* sp = getenv("DE_HEAD_BWD_SPLIT");
-    const int split = sp ? atoi(sp) : 2;
+    // register split between the MMA warp and the consumer warpgroups (A/B knob, read once per process; 2 = measured best)
+    static const int split = []() { const char* sp = getenv("DE_HEAD_BWD_SPLIT"); return sp ? atoi(sp) : 2; }();
     auto kernel = split == 0 ? mlp_head_bwd_pp_kernel<K1, 0> : split == 1 ? mlp_head_bwd_pp_kernel<K1, 1>
                 : split == 3 ? mlp_head_bwd_pp_kernel<K1, 3> : split == 4 ? mlp_head_bwd_pp_kernel<K1, 4> : mlp_head_bwd_pp_kernel<K1, 2>;
     constexpr int NB = kH + K1 + 16;
@@ -487,7 +487,7 @@ static cudaError_t launch_pp_k(const MlpHeadBwdParams& P, int n_sms, cudaStream_
     return cudaGetLastError();
 }
 
-cudaError_t launch_mlp_head_bwd_pp(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s) {
+cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s) {
     P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
     if (P.n_tiles == 0) return cudaSuccess;
     switch (in_dim) {

@@ -186,8 +186,11 @@ def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: 
                     grad_ptrs: Sequence[int], n_features: int, linear: bool,
                     mask_a: Optional[torch.Tensor] = None, mask_b: Optional[torch.Tensor] = None,
                     levels_per_group: int = 0, extra_flags: int = 0, use_replicas: bool = True,
-                    group_width: int = 0) -> None:
+                    group_width: int = 0, workspace_fraction: float = 1.0) -> None:
     """Accumulate table gradients into the fp32 buffers at ``grad_ptrs`` (caller zeroes them).
+
+    ``workspace_fraction`` < 1 hands the call a smaller scratch than it asked for (the C ABI accepts that and
+    skips the replicas / regrouped rows that do not fit; tests exercise it).
 
     ``group_width`` = W > 0: ``grad_out``'s memory is already group-major, g[c // W][p][c % W] (what
     ``backward_group_width`` returned and ``mlp_head_backward(..., group_width=W)`` wrote); 0: ordinary rows."""
@@ -213,6 +216,8 @@ def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: 
     ws, ws_bytes = None, 0
     if use_replicas:
         ws_bytes = int(lib.de_grid4d_backward_workspace_bytes_ex(levels, len(specs), n_features, n, flags, levels_per_group))
+        if workspace_fraction < 1.0:
+            ws_bytes = (int(ws_bytes * workspace_fraction) // 256) * 256
         if ws_bytes:
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=coords.device)   # caching allocator: no cudaMalloc in steady state
     with torch.cuda.device(coords.device):

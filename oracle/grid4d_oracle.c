@@ -37,6 +37,39 @@
  *   NEAREST:    out = table[idx_0][f] * out_scale * mask  (pure gather, :92)
  *   backward:   grad[idx_k][f] += mask * wk * grad_out[p][out_col+f]
  *               (embedding_dense_backward for NEAREST; accumulated here in fp64)
+ *
+ * LINEAR mode is frozen on purpose by known-answer vectors: tests/golden/modeg_kat.npz
+ * (tests/golden/make_golden_modeg.py: dense + hashed + prime-T levels, D = 3, in- and
+ * out-of-range points, one value derived by hand in that file's header), computed by this file
+ * and cross-checked there against independent numpy and torch restatements.
+ *
+ * Where the stated LINEAR math DEPARTS from the upstream Grid4D / torch-ngp grid encoder that
+ * SPECIFICATIONS.MD:1090-1098 names (not vendored; recalled semantics) -- each
+ * departure follows the code that IS in /root/reference:
+ *   1. Level geometry: upstream uses a float per-level scale  scale_l = base * s^l - 1,
+ *      res_l = ceil(scale_l) + 1.  Here a level is an INTEGER resolution R from the reference's own
+ *      list (models/configs.py:56-60: [2^i]), exactly as hash_coords scales by it (:58).
+ *   2. Cell position: upstream pos = x * scale + 0.5 (half-cell shift, align_corners = false).
+ *      Here s = fl32(x * R), no shift -- so the floor corner IS the reference's hash_coords cell
+ *      and NEAREST is the exact collapse of LINEAR onto corner 0.
+ *   3. Input range: upstream maps (x + bound) / (2 bound) inside the encoder and writes ZEROS for
+ *      inputs outside [0, 1].  Here the encoder takes coordinates as they come (the bound remap is
+ *      the prologue's job: deepearth_b200/geo2xyz.py `bound=`), and out-of-range coordinates are
+ *      encoded like any other: negative / large cells wrap through the hash or the dense index's
+ *      floor-mod, as the reference's hash_coords does for the randn inputs its tests feed.
+ *   4. Hash arithmetic: upstream XORs uint32 products; the reference XORs int64 products and takes
+ *      a Python floor-mod (:64-72).  Same primes.  Bit-identical for power-of-two T (low 32 bits),
+ *      different for other T -- the int64 rule is the one implemented (tests: T = 1009, 30011).
+ *   5. Table sizing: upstream gives level l min(T, align8((res+1)^D)) entries at packed offsets.
+ *      Here every level owns T entries (the reference's nn.Embedding(T, F) per level, :38-41), a
+ *      dense level simply uses the first (R+1)^D of them; dense iff (R+1)^D <= T.
+ *   6. Dense stride: upstream strides by res_l (= ceil(scale)+1); here by R+1 -- the same count of
+ *      lattice points per axis, expressed in this file's R.
+ *   7. Storage / gradients: upstream keeps fp16 tables and accumulates half2 atomics.  Here the
+ *      parameters stay fp32 (state-dict compatible), the optional fp16 WORKING copy is
+ *      half(w * 2^12) re-derived from them, and gradients are fp32.
+ *   8. No coordinate gradients and no smoothstep interpolation (the reference cuts the graph at
+ *      floor().long(), :61); masks zero coordinates in decomposed mode (SPECIFICATIONS.MD:1159-1164).
  */
 #include <math.h>
 #include <stdint.h>

@@ -34,6 +34,19 @@ def test_reference_arm_prints_the_contract_line():
     assert e2e["value"] == d["value"] and e2e["unit"] == d["unit"]
     assert e2e["h2d_bytes_per_step"] == 0 and e2e["d2h_bytes_per_step"] == 0
     assert d["gpu_launches"] == 0
+    # same config keys as the GPU arm's line (the driver compares them), plus what the bounded sample was
+    assert {"workload", "description", "points_per_gpu", "coords", "levels", "table_size", "interpolation", "sample"} <= set(d["config"])
+
+
+def test_reference_arm_at_the_reference_geometry_runs_the_reference_or_its_port():
+    """--workload c1r: the reference's own Grid4DEncoder geometry.  With oracle/_ref built (this container: build()
+    copies the unmodified modules) the arm times the reference classes themselves, kind "reference"; else the port."""
+    r = _run("--impl", "reference", "--workload", "c1r", "--steps", "1", "--warmup", "1")
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][0])
+    have_ref = os.path.exists(os.path.join(ROOT, "oracle", "_ref", "models", "hash_encoding.py"))
+    assert d["cpu_baseline"]["kind"] == ("reference" if have_ref else "port")
+    assert d["config"]["workload"] == "c1r" and d["value"] > 0
 
 
 def test_reference_arm_under_torchrun_only_rank0_prints():

@@ -136,3 +136,53 @@ def test_geo2xyz_vs_reference(oracle, golden_dir):
     xyzt, ecef = oracle.geo2xyzt_norm(geo, None, [0, 0, 0], [1, 1, 1], (0, 1), want_ecef=True)
     x2 = oracle.geo2xyzt_norm(geo, None, ecef.min(0), ecef.max(0) - ecef.min(0), (0, 1))
     assert np.array_equal(x2[:, :3], g["degenerate_norm"].astype(np.float32))   # all 0.5
+
+
+def kat_levels(g):
+    """Level list + tables of tests/golden/modeg_kat.npz (make_golden_modeg.py: table[i][f] = ((7i+3f+11l)%64-32)/64)."""
+    F = int(g["F"][0])
+    levels, tabs, off = [], [], 0
+    for l in range(int(g["n_levels"][0])):
+        R, T, dense, *dims = (int(v) for v in g[f"meta_{l}"])
+        levels.append(Level(T=T, R=R, dims=tuple(dims), out_col=l * F, table_off=off, dense=bool(dense)))
+        i = np.arange(T, dtype=np.int64)[:, None]
+        f = np.arange(F, dtype=np.int64)[None, :]
+        tabs.append((((7 * i + 3 * f + 11 * l) % 64 - 32) / 64.0).astype(np.float32))
+        off += T
+    return levels, tabs, F
+
+
+def test_modeg_known_answers(oracle, golden_dir):
+    """The interpolated mode has no reference implementation: its stated math (grid4d_oracle.c header) is frozen by
+    committed known-answer vectors -- dense, hashed and prime-T levels, in- and out-of-range points -- and by one
+    value derived by hand (make_golden_modeg.py header): level A, point 0 -> corners, weights and feature."""
+    g = load(golden_dir, "modeg_kat")
+    levels, tabs, F = kat_levels(g)
+    pts = g["points"]
+    assert g["idx_0"][:, 0].tolist() == [86, 87, 91, 92, 111, 112, 116, 117]
+    assert g["w_0"][:, 0].tolist() == [.28125, .28125, .09375, .09375, .09375, .09375, .03125, .03125]
+    assert float(g["features"][0, 0]) == -0.0625
+    idx = oracle.hash_indices(levels, pts, True)
+    for l in range(len(levels)):
+        assert np.array_equal(idx[l], g[f"idx_{l}"]), l
+    tables = np.concatenate(tabs, 0)
+    out = oracle.forward(levels, pts, tables, F, True)
+    assert np.array_equal(out, g["features"])
+    # fp16 working tables hold these values exactly (multiples of 1/64 times 2^12): same features
+    half = (tables * np.float32(4096.0)).astype(np.float16)
+    assert np.array_equal(half.astype(np.float32), tables * np.float32(4096.0))
+    assert np.abs(oracle.forward(levels, pts, half, F, True, out_scale=1.0 / 4096.0) - g["features"]).max() <= 1e-7
+    grad = oracle.backward(levels, pts, g["grad_out"], sum(lv.T for lv in levels), F, True)
+    for l, lv in enumerate(levels):
+        want = np.zeros((lv.T, F))
+        want[g[f"grad_rows_{l}"]] = g[f"grad_vals_{l}"]
+        assert np.abs(grad[lv.table_off:lv.table_off + lv.T] - want).max() <= 1e-12, l
+    # the torch restatement (the device-resident checker of the full-size GPU tests) reproduces them too
+    import torch
+    from oracle.grid4d_torch import grid4d_forward, level_indices_weights
+    tp = torch.from_numpy(pts)
+    for l, lv in enumerate(levels):
+        it, wt = level_indices_weights(tp, lv.dims, lv.R, lv.T, lv.dense)
+        assert np.array_equal(it.numpy().T, g[f"idx_{l}"]) and np.array_equal(wt.numpy().T, g[f"w_{l}"]), l
+    t_out = grid4d_forward(tp, [torch.from_numpy(t) for t in tabs], [(lv.dims, lv.R, lv.T, lv.dense) for lv in levels], True)
+    assert np.abs(t_out.numpy() - g["features"]).max() <= 2e-7
