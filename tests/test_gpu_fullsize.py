@@ -171,7 +171,10 @@ def test_c3_geometry_florida_vs_device_restatement(dev):
     torch.manual_seed(1234)
     enc = de.Grid4DEncoder(decomposed_config(de, T)).to(dev)
     xyzt = florida_xyzt(n, dev, 1234)
-    assert float(xyzt[:, :3].min()) >= 0.0 and float(xyzt[:, :3].max()) <= 1.0
+    # cluster centres sit anywhere in the box and spread 0.1 degree: a minority of points falls outside the fitted
+    # bbox (normalised coordinates < 0 or > 1), which the kernels must index exactly as the restatement does
+    inside = ((xyzt[:, :3] >= 0) & (xyzt[:, :3] <= 1)).all(1).float().mean()
+    assert float(inside) >= 0.6 and bool(torch.isfinite(xyzt).all())
     # the clustered inputs really are clustered: most points share a few coarse cells
     cells = (xyzt[:, 0] * 16).floor() * 17 + (xyzt[:, 1] * 16).floor()
     assert int(torch.unique(cells).numel()) < 17 * 17
