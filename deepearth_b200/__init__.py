@@ -11,7 +11,8 @@ from .configs import DeepEarthConfig, ModalityConfig, TransformerConfig
 from .encoders import Grid4DEncoder
 from .geo2xyz import BoundingBox, GeospatialConverter, geo2xyz
 from .hash_encoding import MultiResolutionHashEncoding
+from .st_embedding import SpatialTemporalEmbedding
 
-__all__ = ["DeepEarthConfig", "ModalityConfig", "TransformerConfig", "Grid4DEncoder", "BoundingBox",
+__all__ = ["SpatialTemporalEmbedding", "DeepEarthConfig", "ModalityConfig", "TransformerConfig", "Grid4DEncoder", "BoundingBox",
            "GeospatialConverter", "geo2xyz", "MultiResolutionHashEncoding"]
 __version__ = "0.1.0"

@@ -13,7 +13,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libde_grid4d.so")
 
 DE_OK = 0
-ABI_VERSION = 3
+ABI_VERSION = 4
 DE_F32, DE_F16, DE_F64 = 0, 1, 2
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS, DE_FLAG_NO_REGROUP = 0x100, 0x200, 0x400, 0x800
@@ -74,6 +74,11 @@ SIGNATURES = {
     "de_get_l2_fetch_granularity": (c_int, [ctypes.POINTER(c_int)]),
     "de_set_persisting_l2": (c_int, [ctypes.c_longlong]),
     "de_get_persisting_l2": (c_int, [ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_longlong)]),
+    "de_st_embedding_forward": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_int,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "de_st_embedding_backward": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i64, c_void_p, c_int, c_void_p, c_void_p,
+                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_void_p, c_void_p]),
     "de_sum_f32": (c_int, [c_void_p, c_i64, c_void_p, c_void_p]),
     "de_probe_gather": (c_int, [c_void_p, c_i64, c_int, c_int, c_i64, c_int, c_int, c_void_p, c_void_p]),
 }

@@ -27,7 +27,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 EXTRA = {
     "geo2xyz.cu": ["-fmad=false"],   # one IEEE rounding per fp64 op, reference order
 }
-SOURCES = ["c_abi.cu", "grid4d_kernels.cu", "grid4d_pair_kernels.cu", "grid4d_staged_kernels.cu", "grid4d_smem_kernels.cu", "geo2xyz.cu", "misc.cu", "mlp_head.cu", "mlp_head_bwd2.cu"]
+SOURCES = ["c_abi.cu", "grid4d_kernels.cu", "grid4d_pair_kernels.cu", "grid4d_staged_kernels.cu", "grid4d_smem_kernels.cu", "geo2xyz.cu", "misc.cu", "mlp_head.cu", "mlp_head_bwd2.cu", "st_embed.cu"]
 
 
 def _nvcc() -> str:

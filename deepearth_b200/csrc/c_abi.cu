@@ -756,6 +756,46 @@ DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_p
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "mlp_head_backward launch");
 }
 
+DE_API int de_st_embedding_forward(const float* tokens, int64_t n_tokens, int dim, const float* pos, int64_t pos_stride,
+                            const float* t, const float* embed_x, const float* embed_y, int resolution,
+                            const float* t_w1, const float* t_b1, const float* t_w2, const float* t_b2,
+                            const float* modality, float* out, int* error_flag, void* stream) {
+    if (n_tokens < 0) return fail(DE_EINVAL, "n_tokens < 0");
+    if (n_tokens == 0) return DE_OK;
+    if (!tokens || !out) return fail(DE_EINVAL, "st_embedding: tokens / out is NULL");
+    if (dim < 4 || dim % 4) return fail(DE_EUNSUPPORTED, "st_embedding: dim=%d must be a positive multiple of 4", dim);
+    if (pos && (!embed_x || !embed_y || resolution < 1)) return fail(DE_EINVAL, "st_embedding: spatial positions without tables");
+    if (pos && pos_stride < 2) return fail(DE_EINVAL, "st_embedding: pos_stride=%lld < 2", (long long)pos_stride);
+    if (t && (!t_w1 || !t_b1 || !t_w2 || !t_b2)) return fail(DE_EINVAL, "st_embedding: temporal positions without MLP parameters");
+    de::StEmbedParams P{};
+    P.tokens = tokens; P.pos = pos; P.t = t; P.ex = embed_x; P.ey = embed_y; P.w1 = t_w1; P.b1 = t_b1; P.w2 = t_w2; P.b2 = t_b2;
+    P.mod = modality; P.out = out; P.err = error_flag; P.n = n_tokens; P.pos_stride = pos_stride; P.D = dim; P.R = resolution;
+    cudaError_t e = de::launch_st_embed_forward(P, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "st_embedding forward launch");
+}
+
+DE_API int de_st_embedding_backward(const float* grad_out, int64_t n_tokens, int dim, const float* pos, int64_t pos_stride,
+                             const float* t, int resolution, const float* t_w1, const float* t_b1, const float* t_w2,
+                             float* grad_embed_x, float* grad_embed_y, float* grad_t_w1, float* grad_t_b1,
+                             float* grad_t_w2, float* grad_t_b2, float* grad_modality, float* scratch, void* stream) {
+    if (n_tokens < 0) return fail(DE_EINVAL, "n_tokens < 0");
+    if (n_tokens == 0) return DE_OK;
+    if (!grad_out) return fail(DE_EINVAL, "st_embedding_backward: grad_out is NULL");
+    if (dim < 4 || dim % 4) return fail(DE_EUNSUPPORTED, "st_embedding_backward: dim=%d must be a positive multiple of 4", dim);
+    if (pos && pos_stride < 2) return fail(DE_EINVAL, "st_embedding_backward: pos_stride=%lld < 2", (long long)pos_stride);
+    if (pos && resolution < 1) return fail(DE_EINVAL, "st_embedding_backward: resolution=%d", resolution);
+    if (pos && static_cast<size_t>(resolution) * 32 * sizeof(float) > 48 * 1024)
+        return fail(DE_EUNSUPPORTED, "st_embedding_backward: resolution=%d > 384 table rows", resolution);
+    if (t && (!t_w1 || !t_b1 || !t_w2 || !scratch || !grad_t_w1 || !grad_t_b1 || !grad_t_w2))
+        return fail(DE_EINVAL, "st_embedding_backward: temporal branch needs w1, b1, w2, scratch and the three weight gradients");
+    de::StEmbedBwdParams P{};
+    P.g = grad_out; P.pos = pos; P.t = t; P.w1 = t_w1; P.b1 = t_b1; P.w2 = t_w2; P.dpre = scratch;
+    P.d_ex = grad_embed_x; P.d_ey = grad_embed_y; P.d_w1 = grad_t_w1; P.d_b1 = grad_t_b1; P.d_w2 = grad_t_w2; P.d_b2 = grad_t_b2;
+    P.d_mod = grad_modality; P.n = n_tokens; P.pos_stride = pos_stride; P.D = dim; P.R = resolution;
+    cudaError_t e = de::launch_st_embed_backward(P, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "st_embedding backward launch");
+}
+
 DE_API int de_set_l2_fetch_granularity(int bytes) {
     if (bytes != 32 && bytes != 64 && bytes != 128) return fail(DE_EINVAL, "l2 fetch granularity must be 32, 64 or 128, got %d", bytes);
     cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, static_cast<size_t>(bytes));

@@ -97,6 +97,46 @@ bool mlp_head_supported(int in_dim, int hidden, int out_dim);
 cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);        // mlp_head_bwd2.cu
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s);
 
+// SpatialTemporalEmbedding (st_embed.cu; models/cross_modal_fusion.py:130-164)
+struct StEmbedParams {
+    const float* tokens;          // (n, D)
+    const float* pos;             // (n, >= 2) spatial positions, rows pos_stride floats apart, or NULL
+    const float* t;               // (n,) temporal positions, or NULL
+    const float* ex;              // (R, D/4) spatial_embed_x
+    const float* ey;              // (R, D/4) spatial_embed_y
+    const float* w1;              // (D/2,)  temporal_embed.0.weight[:, 0]
+    const float* b1;              // (D/2,)
+    const float* w2;              // (D/2, D/2) temporal_embed.2.weight
+    const float* b2;              // (D/2,)
+    const float* mod;             // (D,) modality embedding, or NULL
+    float* out;                   // (n, D)
+    int* err;                     // device flag: bit 0 set when a spatial index falls outside [-R, R); may be NULL
+    long long n;
+    long long pos_stride;
+    int D, R;
+};
+struct StEmbedBwdParams {
+    const float* g;               // (n, D) gradient of the output (= gradient of the tokens)
+    const float* pos;
+    const float* t;
+    const float* w1;
+    const float* b1;
+    const float* w2;
+    float* dpre;                  // (n, D/2) scratch (temporal branch)
+    float* d_ex;                  // accumulated (caller zeroes); any may be NULL
+    float* d_ey;
+    float* d_w1;
+    float* d_b1;
+    float* d_w2;
+    float* d_b2;
+    float* d_mod;
+    long long n;
+    long long pos_stride;
+    int D, R;
+};
+cudaError_t launch_st_embed_forward(const StEmbedParams& P, cudaStream_t s);
+cudaError_t launch_st_embed_backward(const StEmbedBwdParams& P, cudaStream_t s);
+
 cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,
                             const double* bbox_span, const double* t_range, float* xyzt, double* ecef,
                             long long n, cudaStream_t s);

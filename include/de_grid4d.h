@@ -35,7 +35,7 @@ extern "C" {
 #define DE_API
 #endif
 
-#define DE_ABI_VERSION 3
+#define DE_ABI_VERSION 4
 
 /* status codes (negative = caller error) */
 #define DE_OK 0
@@ -245,6 +245,36 @@ DE_API int de_get_l2_fetch_granularity(int* bytes);
  */
 DE_API int de_set_persisting_l2(long long bytes);
 DE_API int de_get_persisting_l2(long long* bytes, long long* max_bytes);
+
+/*
+ * SpatialTemporalEmbedding -- replaces SpatialTemporalEmbedding.forward (models/cross_modal_fusion.py:130-164), the other
+ * consumer of xyzt in the integrated model:
+ *   out[m, :D/4]      = tokens + embed_x[(pos[m,0] * R).long()]   (:145-152; negative indices wrap, as PyTorch indexing)
+ *   out[m, D/4:D/2]   = tokens + embed_y[(pos[m,1] * R).long()]
+ *   out[m, D/2:]      = tokens + W2 . GELU(t[m] * w1 + b1) + b2    (:155-158, fp32)
+ *   (+ modality[c] inside the bracket when given, :161-162; summation order of the reference)
+ * tokens/out: (n, dim) fp32 contiguous; pos: (n, >=2) rows pos_stride floats apart or NULL; t: (n,) or NULL;
+ * embed_x/embed_y: (resolution, dim/4); t_w1, t_b1, t_b2: (dim/2,); t_w2: (dim/2, dim/2) row-major (nn.Linear.weight);
+ * modality: (dim,) or NULL.  dim must be a multiple of 4.  error_flag: optional device int, bit 0 is set when an index
+ * falls outside [-resolution, resolution) (the reference raises IndexError there); such rows are written as NaN.
+ */
+DE_API int de_st_embedding_forward(const float* tokens, int64_t n_tokens, int dim,
+                            const float* pos, int64_t pos_stride, const float* t,
+                            const float* embed_x, const float* embed_y, int resolution,
+                            const float* t_w1, const float* t_b1, const float* t_w2, const float* t_b2,
+                            const float* modality, float* out, int* error_flag, void* stream);
+/*
+ * Backward of the same module -- replaces autograd's IndexBackward / AddmmBackward / GeluBackward chain for
+ * models/cross_modal_fusion.py:143-164.  grad_out (n, dim) is also the gradient of `tokens` (identity).  Parameter
+ * gradients are ACCUMULATED (caller zeroes them); any may be NULL.  scratch: (n, dim/2) floats, required when t is given.
+ * Positions receive no gradient (the spatial ones are cut by .long(); temporal positions are data).
+ */
+DE_API int de_st_embedding_backward(const float* grad_out, int64_t n_tokens, int dim,
+                             const float* pos, int64_t pos_stride, const float* t, int resolution,
+                             const float* t_w1, const float* t_b1, const float* t_w2,
+                             float* grad_embed_x, float* grad_embed_y, float* grad_t_w1, float* grad_t_b1,
+                             float* grad_t_w2, float* grad_t_b2, float* grad_modality,
+                             float* scratch, void* stream);
 
 /* fp64 sum of an fp32 buffer into *result (device, caller-zeroed): bench/e2e checksum. */
 DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
