@@ -43,6 +43,14 @@ class DeLevelDesc(ctypes.Structure):
     ]
 
 
+class DeFieldDesc(ctypes.Structure):
+    """Mirror of ``de_field_desc`` (include/de_grid4d.h)."""
+    _fields_ = [("lat_start", ctypes.c_double), ("lat_stop", ctypes.c_double), ("lon_start", ctypes.c_double),
+                ("lon_stop", ctypes.c_double), ("altitude", ctypes.c_double), ("time", ctypes.c_double),
+                ("n_lat", ctypes.c_int32), ("n_lon", ctypes.c_int32), ("has_time", ctypes.c_int32),
+                ("reserved", ctypes.c_int32)]
+
+
 # name -> (restype, argtypes); every symbol include/de_grid4d.h declares
 SIGNATURES = {
     "de_abi_version": (c_int, []),
@@ -74,6 +82,12 @@ SIGNATURES = {
     "de_get_l2_fetch_granularity": (c_int, [ctypes.POINTER(c_int)]),
     "de_set_persisting_l2": (c_int, [ctypes.c_longlong]),
     "de_get_persisting_l2": (c_int, [ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_longlong)]),
+    "de_field_xyzt": (c_int, [ctypes.POINTER(DeFieldDesc), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                              ctypes.POINTER(ctypes.c_double), c_void_p, c_void_p]),
+    "de_grid4d_field_forward": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, ctypes.POINTER(DeFieldDesc),
+                                        ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                                        ctypes.POINTER(ctypes.c_double), c_int, c_int, c_float, c_void_p, c_i64, c_void_p,
+                                        c_u32, c_int, c_void_p]),
     "de_st_embedding_forward": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_int,
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "de_st_embedding_backward": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i64, c_void_p, c_int, c_void_p, c_void_p,

@@ -26,8 +26,9 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 # per-file extra flags
 EXTRA = {
     "geo2xyz.cu": ["-fmad=false"],   # one IEEE rounding per fp64 op, reference order
+    "grid4d_field_kernels.cu": ["-fmad=false"],   # same prologue arithmetic, generated in place
 }
-SOURCES = ["c_abi.cu", "grid4d_kernels.cu", "grid4d_pair_kernels.cu", "grid4d_staged_kernels.cu", "grid4d_smem_kernels.cu", "geo2xyz.cu", "misc.cu", "mlp_head.cu", "mlp_head_bwd2.cu", "st_embed.cu"]
+SOURCES = ["c_abi.cu", "grid4d_kernels.cu", "grid4d_pair_kernels.cu", "grid4d_staged_kernels.cu", "grid4d_smem_kernels.cu", "geo2xyz.cu", "misc.cu", "mlp_head.cu", "mlp_head_bwd2.cu", "st_embed.cu", "grid4d_field_kernels.cu"]
 
 
 def _nvcc() -> str:

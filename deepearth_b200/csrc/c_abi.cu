@@ -756,6 +756,79 @@ DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_p
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "mlp_head_backward launch");
 }
 
+static int fill_field(const de_field_desc* f, const double* bbox_min, const double* bbox_span, const double* t_range,
+                      de::FieldParams& Fp) {
+    if (!f || !bbox_min || !bbox_span) return fail(DE_EINVAL, "field: NULL pointer");
+    if (f->n_lat < 1 || f->n_lon < 1) return fail(DE_EINVAL, "field: n_lat=%d n_lon=%d must be >= 1", f->n_lat, f->n_lon);
+    if (f->has_time && !t_range) return fail(DE_EINVAL, "field: time given without t_range");
+    Fp = de::FieldParams{};
+    Fp.lat_start = f->lat_start; Fp.lat_stop = f->lat_stop;
+    Fp.lon_start = f->lon_start; Fp.lon_stop = f->lon_stop;
+    Fp.lat_step = f->n_lat > 1 ? (f->lat_stop - f->lat_start) / static_cast<double>(f->n_lat - 1) : 0.0;   // np.linspace
+    Fp.lon_step = f->n_lon > 1 ? (f->lon_stop - f->lon_start) / static_cast<double>(f->n_lon - 1) : 0.0;
+    Fp.altitude = f->altitude; Fp.time = f->time; Fp.has_time = f->has_time ? 1 : 0;
+    for (int d = 0; d < 3; ++d) { Fp.bbox_min[d] = bbox_min[d]; Fp.bbox_span[d] = bbox_span[d]; }
+    Fp.t_min = t_range ? t_range[0] : 0.0;
+    Fp.t_span = t_range ? t_range[1] - t_range[0] : 1.0;
+    Fp.n_lat = f->n_lat; Fp.n_lon = f->n_lon;
+    return DE_OK;
+}
+
+DE_API int de_field_xyzt(const de_field_desc* field_host, const double* bbox_min_host, const double* bbox_span_host,
+                  const double* t_range_host, float* xyzt, void* stream) {
+    de::FieldParams Fp;
+    if (int rc = fill_field(field_host, bbox_min_host, bbox_span_host, t_range_host, Fp)) return rc;
+    if (!xyzt) return fail(DE_EINVAL, "field_xyzt: xyzt is NULL");
+    if (reinterpret_cast<uintptr_t>(xyzt) % 16) return fail(DE_EALIGN, "field_xyzt: xyzt not 16-byte aligned");
+    cudaError_t e = de::launch_field_xyzt(Fp, xyzt, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "field_xyzt launch");
+}
+
+DE_API int de_grid4d_field_forward(const de_level_desc* levels_host, int n_levels, const de_field_desc* field_host,
+                            const double* bbox_min_host, const double* bbox_span_host, const double* t_range_host,
+                            int table_dtype, int n_features, float out_scale, float* out, int64_t out_stride,
+                            float* xyzt_out, uint32_t flags, int levels_per_group, void* stream) {
+    de::FieldParams Fp;
+    if (int rc = fill_field(field_host, bbox_min_host, bbox_span_host, t_range_host, Fp)) return rc;
+    static const float kDummy = 0.0f;
+    CallArgs a{levels_host, n_levels, &kDummy, static_cast<int64_t>(Fp.n_lat) * Fp.n_lon, 4, table_dtype, n_features, flags,
+               levels_per_group, true, false};
+    if (int rc = validate(a)) return rc;
+    if (!out) return fail(DE_EINVAL, "field_forward: out is NULL");
+    if ((flags & DE_INTERP_MASK) != DE_INTERP_LINEAR) return fail(DE_EUNSUPPORTED, "field_forward: DE_INTERP_LINEAR levels only");
+    if (!(n_features == 1 || n_features == 2 || n_features == 4)) return fail(DE_EUNSUPPORTED, "field_forward: n_features=%d not in {1,2,4}", n_features);
+    if (n_levels > de::kMaxLaunchLevels) return fail(DE_EUNSUPPORTED, "field_forward: n_levels=%d > %d", n_levels, de::kMaxLaunchLevels);
+    if (xyzt_out && reinterpret_cast<uintptr_t>(xyzt_out) % 16) return fail(DE_EALIGN, "field_forward: xyzt_out not 16-byte aligned");
+    Fp.xyzt_out = xyzt_out;
+    de::EncodeParams P{};
+    P.out = out;
+    P.n_points = a.n_points;
+    P.out_stride = out_stride;
+    P.coord_stride = 4;
+    P.n_features = n_features;
+    P.out_scale = out_scale;
+    P.l2_hints = (flags & DE_FLAG_NO_L2_HINTS) ? 0 : 1;
+    P.n_levels = n_levels;
+    bool pow2_all = true;
+    unsigned long long max_level_bytes = 1;
+    for (int i = 0; i < n_levels; ++i) {
+        const de_level_desc& L = levels_host[i];
+        if (L.n_dims != 3) return fail(DE_EUNSUPPORTED, "field_forward: level %d has n_dims=%d (3-D grids only)", i, L.n_dims);
+        if (L.mask_id) return fail(DE_EUNSUPPORTED, "field_forward: level %d carries a row mask", i);
+        if ((int64_t)L.out_col + n_features > out_stride) return fail(DE_EINVAL, "level %d: out_col %u + F %d exceeds out_stride %lld", i, L.out_col, n_features, (long long)out_stride);
+        fill_level(L, P.levels[i]);
+        pow2_all = pow2_all && is_pow2(L.table_size);
+        const unsigned long long lb = level_bytes(L, n_features, false, table_dtype);
+        if (lb > max_level_bytes) max_level_bytes = lb;
+    }
+    int G = pick_group_size(true, n_features, levels_per_group, n_levels, max_level_bytes);
+    while (G > de::field_max_group(n_features)) G >>= 1;
+    P.group_size = G;
+    P.n_groups = (n_levels + G - 1) / G;
+    cudaError_t e = de::launch_field_forward(P, Fp, table_dtype == DE_F16, n_features, pow2_all, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "field_forward launch");
+}
+
 DE_API int de_st_embedding_forward(const float* tokens, int64_t n_tokens, int dim, const float* pos, int64_t pos_stride,
                             const float* t, const float* embed_x, const float* embed_y, int resolution,
                             const float* t_w1, const float* t_b1, const float* t_w2, const float* t_b2,

@@ -7,6 +7,7 @@
 #include <math_constants.h>
 #include <stdint.h>
 
+#include "geo_math.cuh"
 #include "launch.h"
 
 namespace de {
@@ -25,10 +26,6 @@ struct GeoParams {
 };
 
 __device__ __forceinline__ void ecef_of(const GeoParams& P, long long p, double (&xyz)[3]) {
-    constexpr double A = 6378137.0;                       // geo2xyz.py:98
-    constexpr double FL = 1.0 / 298.257223563;            // :99
-    constexpr double E2 = 2.0 * FL - FL * FL;             // :100
-    constexpr double D2R = 0.017453292519943295769236907684886;  // torch.deg2rad
     double lat, lon, alt;
     if (P.geo_f64) {
         const double* g = static_cast<const double*>(P.geo) + 3 * p;
@@ -37,13 +34,7 @@ __device__ __forceinline__ void ecef_of(const GeoParams& P, long long p, double 
         const float* g = static_cast<const float*>(P.geo) + 3 * p;
         lat = __ldg(g); lon = __ldg(g + 1); alt = __ldg(g + 2);   // _as_fp64 (:147)
     }
-    double sl, cl, so, co;
-    sincos(lat * D2R, &sl, &cl);
-    sincos(lon * D2R, &so, &co);
-    const double N = A / sqrt(1.0 - E2 * (sl * sl));      // :153
-    xyz[0] = ((N + alt) * cl) * co;                       // :157
-    xyz[1] = ((N + alt) * cl) * so;                       // :158
-    xyz[2] = (N * (1.0 - E2) + alt) * sl;                 // :159
+    ecef_from_geodetic(lat, lon, alt, xyz);
 }
 
 __global__ void __launch_bounds__(256) geo2xyzt_kernel(const __grid_constant__ GeoParams P) {
@@ -56,17 +47,16 @@ __global__ void __launch_bounds__(256) geo2xyzt_kernel(const __grid_constant__ G
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
         if (P.ecef) P.ecef[3 * p + d] = xyz[d];
-        const double span = P.bbox_span[d];
-        // _safe_div: |span| < 1e-9 -> 0.5 (utils.py:54-77)
-        of[d] = static_cast<float>(fabs(span) < 1e-9 ? 0.5 : (xyz[d] - P.bbox_min[d]) / span);
+        of[d] = norm_coord(xyz[d], P.bbox_min[d], P.bbox_span[d]);
     }
     double tv = 0.0;
     if (P.t) {
         const double tt = P.t_f64 ? __ldg(static_cast<const double*>(P.t) + p)
                                   : static_cast<double>(__ldg(static_cast<const float*>(P.t) + p));
-        tv = fabs(P.t_span) < 1e-9 ? 0.5 : (tt - P.t_min) / P.t_span;   // SPECIFICATIONS.MD:765
+        o.w = norm_coord(tt, P.t_min, P.t_span);                         // SPECIFICATIONS.MD:765
+    } else {
+        o.w = static_cast<float>(tv);
     }
-    o.w = static_cast<float>(tv);
     reinterpret_cast<float4*>(P.xyzt)[p] = o;
 }
 

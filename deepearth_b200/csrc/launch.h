@@ -97,6 +97,21 @@ bool mlp_head_supported(int in_dim, int hidden, int out_dim);
 cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);        // mlp_head_bwd2.cu
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s);
 
+// dense-field evaluation over a regular lat/lon grid (grid4d_field_kernels.cu; SPECIFICATIONS.MD:1963-2088)
+struct FieldParams {
+    double lat_start, lat_stop, lat_step;     // np.linspace(lat_start, lat_stop, n_lat): step = (stop - start) / (n - 1)
+    double lon_start, lon_stop, lon_step;
+    double altitude, time;
+    double bbox_min[3], bbox_span[3];
+    double t_min, t_span;
+    float* xyzt_out;                          // optional (n_lat * n_lon, 4): the generated normalised coordinates
+    int n_lat, n_lon;
+    int has_time;
+};
+int field_max_group(int F);
+cudaError_t launch_field_forward(EncodeParams P, const FieldParams& Fp, bool half_tables, int F, bool pow2, cudaStream_t s);
+cudaError_t launch_field_xyzt(const FieldParams& Fp, float* xyzt, cudaStream_t s);
+
 // SpatialTemporalEmbedding (st_embed.cu; models/cross_modal_fusion.py:130-164)
 struct StEmbedParams {
     const float* tokens;          // (n, D)

@@ -134,6 +134,54 @@ class Grid4DEncoder(nn.Module):
             spatial_mask = temporal_mask = None
         return Grid4DFunction.apply(xyzt, spatial_mask, temporal_mask, self._plan(), ptrs, *weights)
 
+    @torch.no_grad()
+    def encode_field(self, converter, lat_range, lon_range, n_lat: int, n_lon: int, altitude: float = 0.0,
+                     time: Optional[float] = None, return_coords: bool = False):
+        """Hash features over the regular grid ``np.linspace(*lat_range, n_lat)`` x ``np.linspace(*lon_range, n_lon)`` at a
+        fixed altitude / time -- the query set of `visualize_embedding_field` (SPECIFICATIONS.MD:1963-2088) -- without a
+        coordinate tensor from the host.  -> (n_lat * n_lon, feature_dim), latitude-major; inference only (no autograd).
+        Decomposed mode runs the patch-ordered kernel (csrc/grid4d_field_kernels.cu); the reference geometry generates
+        the coordinates on the device and runs the general forward.  Either way the features are bit-identical to
+        ``encode_features(converter.geodetic_to_xyzt_norm(points))``."""
+        import ctypes
+        from . import _lib
+        weights: List[torch.Tensor] = []
+        for enc in self._encoders:
+            weights += enc.weights()
+        Fn._require_cuda(weights[0], "hash table weights")
+        dev = weights[0].device
+        e0 = self._encoders[0]
+        plan = self._plan()
+        n = int(n_lat) * int(n_lon)
+        fused = (self.mode == "decomposed" and plan.linear and plan.n_features in (1, 2, 4) and len(plan.specs) <= 64
+                 and all(len(s.dims) == 3 for s in plan.specs))
+        if not fused:
+            xyzt = converter.field_xyzt(lat_range, lon_range, n_lat, n_lon, altitude, time)
+            feats = self.encode_features(xyzt)
+            return (feats, xyzt) if return_coords else feats
+        ptrs = self._working_ptrs(weights) if e0.table_dtype == torch.float16 else [w.data_ptr() for w in weights]
+        offset, span = converter._norm_constants()
+        desc = converter.field_desc(lat_range, lon_range, n_lat, n_lon, altitude, time)
+        out = torch.empty((n, self.feature_dim), dtype=torch.float32, device=dev)
+        xyzt = torch.empty((n, 4), dtype=torch.float32, device=dev) if return_coords else None
+        dbl = lambda v: (ctypes.c_double * len(v))(*[float(x) for x in v])      # noqa: E731
+        dt = _lib.DE_F16 if e0.table_dtype == torch.float16 else _lib.DE_F32
+        with torch.cuda.device(dev):
+            rc = _lib.load().de_grid4d_field_forward(
+                Fn.pack_levels(plan.specs, ptrs), len(plan.specs), ctypes.byref(desc), dbl(offset), dbl(span),
+                dbl(converter.t_range) if converter.t_range is not None else None, dt, plan.n_features,
+                1.0 / plan.table_scale if plan.table_scale != 1.0 else 1.0, Fn._ptr(out), out.stride(0), Fn._ptr(xyzt),
+                _lib.DE_INTERP_LINEAR | plan.extra_flags, plan.levels_per_group, Fn._stream_ptr(dev))
+        _lib.check(rc, "de_grid4d_field_forward")
+        return (out, xyzt) if return_coords else out
+
+    @torch.no_grad()
+    def forward_field(self, converter, lat_range, lon_range, n_lat: int, n_lon: int, altitude: float = 0.0,
+                      time: Optional[float] = None) -> torch.Tensor:
+        """(n_lat, n_lon, hidden_dim) embedding field: ``encode_field`` followed by the projection."""
+        feats = self.encode_field(converter, lat_range, lon_range, n_lat, n_lon, altitude, time)
+        return self._project(feats).reshape(int(n_lat), int(n_lon), -1)
+
     def _working_ptrs(self, weights: List[torch.Tensor]) -> List[int]:
         """fp16 working tables of ALL grids, refreshed by ONE de_tables_to_f16 launch when the fp32 parameters may have
         changed (same rule as MultiResolutionHashEncoding.working_ptrs, without one launch + host round per grid)."""

@@ -162,6 +162,36 @@ class GeospatialConverter:
         _lib.check(rc, "de_geo2xyzt_norm")
         return (xyzt, ecef) if return_ecef else xyzt
 
+    # dense fields (SPECIFICATIONS.MD:1963-2088) -----------------------------------------------------------
+    def _norm_constants(self):
+        if self._affine is not None:
+            return self._affine
+        if self._bbox is None:
+            raise ValueError("the converter has no bounding box yet (update_bbox / pass bbox=...)")
+        return self._bbox.min_point, self._bbox.span
+
+    def field_desc(self, lat_range, lon_range, n_lat: int, n_lon: int, altitude: float = 0.0, time: Optional[float] = None):
+        """ctypes descriptor of the regular grid ``np.linspace(*lat_range, n_lat)`` x ``np.linspace(*lon_range, n_lon)``."""
+        if time is not None and self.t_range is None:
+            raise ValueError("time given but the converter has no t_range")
+        return _lib.DeFieldDesc(float(lat_range[0]), float(lat_range[1]), float(lon_range[0]), float(lon_range[1]),
+                                float(altitude), float(time) if time is not None else 0.0, int(n_lat), int(n_lon),
+                                1 if time is not None else 0, 0)
+
+    def field_xyzt(self, lat_range, lon_range, n_lat: int, n_lon: int, altitude: float = 0.0,
+                   time: Optional[float] = None) -> torch.Tensor:
+        """(n_lat * n_lon, 4) normalised fp32 rows of a regular lat/lon grid (latitude-major), generated on the device:
+        bit-identical to ``geodetic_to_xyzt_norm`` over the same ``np.linspace`` points."""
+        offset, span = self._norm_constants()
+        desc = self.field_desc(lat_range, lon_range, n_lat, n_lon, altitude, time)
+        xyzt = torch.empty((int(n_lat) * int(n_lon), 4), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = _lib.load().de_field_xyzt(ctypes.byref(desc), _dbl3(offset), _dbl3(span),
+                                           _dbl3(self.t_range) if self.t_range is not None else None, _ptr(xyzt),
+                                           _stream_ptr(self.device))
+        _lib.check(rc, "de_field_xyzt")
+        return xyzt
+
     # reference-named conveniences --------------------------------------------------------------------
     def geodetic_to_xyz(self, geo: torch.Tensor) -> torch.Tensor:
         """(…,3) geodetic -> (…,3) fp64 ECEF metres (geo2xyz.py:146-160, position branch only)."""

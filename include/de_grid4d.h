@@ -247,6 +247,36 @@ DE_API int de_set_persisting_l2(long long bytes);
 DE_API int de_get_persisting_l2(long long* bytes, long long* max_bytes);
 
 /*
+ * Dense-field evaluation -- the encoder over a regular lat/lon grid at fixed altitude and time, inference only.
+ * Replaces the query construction + preprocessing + encoder forward of `visualize_embedding_field`
+ * (SPECIFICATIONS.MD:1963-2088: np.linspace latitudes x np.linspace longitudes, latitude-major point order) and of the
+ * species distribution maps (core/plant_data_loader.py:543-549).  No coordinate tensor exists: each CTA generates the
+ * geodetic points of its 16 x 16 patch, runs the de_geo2xyzt_norm arithmetic on them and encodes them; neighbouring points
+ * share a warp so coarse-level gathers coalesce.  Point p = i_lat * n_lon + i_lon.
+ */
+typedef struct de_field_desc {
+    double lat_start, lat_stop;   /* np.linspace(lat_start, lat_stop, n_lat), degrees */
+    double lon_start, lon_stop;
+    double altitude;              /* metres, one value for the whole grid             */
+    double time;                  /* raw time value, normalised with t_range_host     */
+    int32_t n_lat, n_lon;
+    int32_t has_time;             /* 0: t column = 0                                  */
+    int32_t reserved;
+} de_field_desc;
+/* Normalised coordinates of the grid, (n_lat * n_lon, 4) fp32 -- bit-identical to de_geo2xyzt_norm on the same points. */
+DE_API int de_field_xyzt(const de_field_desc* field_host, const double* bbox_min_host, const double* bbox_span_host,
+                  const double* t_range_host, float* xyzt, void* stream);
+/*
+ * Features of the grid: out[p, out_col + f] as de_grid4d_forward would produce for the same points (bit-identical).
+ * Levels must be 3-D with DE_INTERP_LINEAR and n_features in {1, 2, 4}; other level lists return DE_EUNSUPPORTED
+ * (use de_field_xyzt + de_grid4d_forward).  xyzt_out: optional (n_lat * n_lon, 4) copy of the generated coordinates.
+ */
+DE_API int de_grid4d_field_forward(const de_level_desc* levels_host, int n_levels, const de_field_desc* field_host,
+                            const double* bbox_min_host, const double* bbox_span_host, const double* t_range_host,
+                            int table_dtype, int n_features, float out_scale, float* out, int64_t out_stride,
+                            float* xyzt_out, uint32_t flags, int levels_per_group, void* stream);
+
+/*
  * SpatialTemporalEmbedding -- replaces SpatialTemporalEmbedding.forward (models/cross_modal_fusion.py:130-164), the other
  * consumer of xyzt in the integrated model:
  *   out[m, :D/4]      = tokens + embed_x[(pos[m,0] * R).long()]   (:145-152; negative indices wrap, as PyTorch indexing)
