@@ -681,6 +681,24 @@ DE_API int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "geo2xyzt launch");
 }
 
+DE_API int de_time_from_components(const void* components, int dtype, int64_t n, int64_t stride, int n_cols,
+                            int default_month, int default_day, int default_hour, const double* t_range_host,
+                            double* timestamps, float* t_norm, void* stream) {
+    if (n < 0) return fail(DE_EINVAL, "n < 0");
+    if (n == 0) return DE_OK;
+    if (!components || (!timestamps && !t_norm)) return fail(DE_EINVAL, "time_from_components: NULL pointer");
+    if (dtype != DE_I32 && dtype != DE_F64) return fail(DE_EUNSUPPORTED, "time_from_components: dtype=%d (DE_I32 or DE_F64)", dtype);
+    if (n_cols < 1 || n_cols > 6 || stride < n_cols) return fail(DE_EINVAL, "time_from_components: n_cols=%d stride=%lld", n_cols, (long long)stride);
+    if (default_month < 1 || default_month > 12 || default_day < 1 || default_day > 31 || default_hour < 0 || default_hour > 23)
+        return fail(DE_EINVAL, "time_from_components: defaults out of range");
+    if (t_norm && !t_range_host) return fail(DE_EINVAL, "time_from_components: t_norm without t_range");
+    const double t_min = t_range_host ? t_range_host[0] : 0.0;
+    const double t_span = t_range_host ? t_range_host[1] - t_range_host[0] : 1.0;
+    cudaError_t e = de::launch_time_components(components, dtype == DE_F64, n, stride, n_cols, default_month, default_day,
+                                               default_hour, t_min, t_span, timestamps, t_norm, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "time_from_components launch");
+}
+
 DE_API int de_geo_bbox(const void* geo, int geo_dtype, double* minmax, int64_t n_points, void* stream) {
     if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
     if (n_points == 0) return DE_OK;

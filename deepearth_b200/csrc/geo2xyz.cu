@@ -110,6 +110,54 @@ __global__ void __launch_bounds__(256) geo_bbox_kernel(const __grid_constant__ G
     }
 }
 
+// ---- timestamps from date columns (SPECIFICATIONS.MD:740-768, `_process_temporal`) ----------------------------------
+// datetime(year, month, day, hour, minute, int(second)).timestamp() with the microseconds int((second % 1) * 1e6) added,
+// evaluated for UTC: whole seconds since 1970-01-01 by the proleptic-Gregorian day count (exact integers), then
+// `seconds + microseconds / 1e6` in fp64 as CPython's naive-datetime path does; t_norm = (ts - t_min) / (t_max - t_min).
+struct TimeParams {
+    const void* comp;         // (n, n_cols) columns year[, month, day, hour, minute, second]
+    double* ts_out;           // (n,) fp64 epoch seconds, or NULL
+    float* tn_out;            // (n,) fp32 normalised time, or NULL
+    long long n;
+    long long stride;
+    int n_cols, is_f64;
+    int def_month, def_day, def_hour;
+    double t_min, t_span;
+};
+
+__global__ void __launch_bounds__(256) time_components_kernel(const TimeParams P) {
+    const long long p = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (p >= P.n) return;
+    double c[6] = {1970.0, static_cast<double>(P.def_month), static_cast<double>(P.def_day), static_cast<double>(P.def_hour), 0.0, 0.0};
+    for (int k = 0; k < P.n_cols && k < 6; ++k)
+        c[k] = P.is_f64 ? __ldg(static_cast<const double*>(P.comp) + p * P.stride + k)
+                        : static_cast<double>(__ldg(static_cast<const int*>(P.comp) + p * P.stride + k));
+    long long y = static_cast<long long>(c[0]);                   // int(row['year']) ...
+    const long long m = static_cast<long long>(c[1]), d = static_cast<long long>(c[2]);
+    const long long hh = static_cast<long long>(c[3]), mi = static_cast<long long>(c[4]), ss = static_cast<long long>(c[5]);
+    y -= (m <= 2);
+    const long long era = (y >= 0 ? y : y - 399) / 400;
+    const long long yoe = y - era * 400;
+    const long long doy = (153 * (m + (m > 2 ? -3 : 9)) + 2) / 5 + d - 1;
+    const long long doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+    const long long days = era * 146097 + doe - 719468;
+    const long long secs = days * 86400 + hh * 3600 + mi * 60 + ss;
+    long long us = 0;
+    if (P.is_f64 && P.n_cols >= 6) us = static_cast<long long>(fmod(c[5], 1.0) * 1e6);    // int((second % 1) * 1e6)
+    const double ts = static_cast<double>(secs) + static_cast<double>(us) / 1e6;
+    if (P.ts_out) P.ts_out[p] = ts;
+    if (P.tn_out) P.tn_out[p] = static_cast<float>((ts - P.t_min) / P.t_span);             // SPECIFICATIONS.MD:765
+}
+
+cudaError_t launch_time_components(const void* comp, bool is_f64, long long n, long long stride, int n_cols, int def_month,
+                                   int def_day, int def_hour, double t_min, double t_span, double* ts_out, float* tn_out,
+                                   cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    TimeParams P{comp, ts_out, tn_out, n, stride, n_cols, is_f64 ? 1 : 0, def_month, def_day, def_hour, t_min, t_span};
+    time_components_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,
                             const double* bbox_span, const double* t_range, float* xyzt, double* ecef,
                             long long n, cudaStream_t s) {

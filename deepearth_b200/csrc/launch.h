@@ -155,6 +155,9 @@ cudaError_t launch_st_embed_backward(const StEmbedBwdParams& P, cudaStream_t s);
 cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,
                             const double* bbox_span, const double* t_range, float* xyzt, double* ecef,
                             long long n, cudaStream_t s);
+cudaError_t launch_time_components(const void* comp, bool is_f64, long long n, long long stride, int n_cols, int def_month,
+                                   int def_day, int def_hour, double t_min, double t_span, double* ts_out, float* tn_out,
+                                   cudaStream_t s);
 cudaError_t launch_geo_bbox(const void* geo, bool geo_f64, double* minmax, long long n, cudaStream_t s);
 cudaError_t launch_sum_f32(const float* x, long long n, double* result, cudaStream_t s);
 cudaError_t launch_probe(void* table, long long n_entries, int entry_bytes, int mode, long long n_threads,

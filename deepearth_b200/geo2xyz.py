@@ -162,6 +162,33 @@ class GeospatialConverter:
         _lib.check(rc, "de_geo2xyzt_norm")
         return (xyzt, ecef) if return_ecef else xyzt
 
+    # timestamps from date columns (SPECIFICATIONS.MD:740-768) ----------------------------------------------
+    def timestamps_from_components(self, components: torch.Tensor, *, default_month: int = 6, default_day: int = 15,
+                                   default_hour: int = 12, normalise: bool = False) -> torch.Tensor:
+        """(n, k) columns [year, month, day, hour, minute, second][:k] (int32 / int64 / float64) -> (n,) fp64 UTC epoch
+        seconds, or with ``normalise=True`` (n,) fp32 ``(ts - t_min) / (t_max - t_min)`` -- what the spec's
+        ``_process_temporal`` computes row by row with ``datetime(...).timestamp()``.  One launch, no host loop."""
+        _require_cuda(components, "components")
+        if components.dim() != 2 or not 1 <= components.shape[1] <= 6:
+            raise ValueError("components must be (n, 1..6): year[, month, day, hour, minute, second]")
+        if components.dtype == torch.int32:
+            dt = _lib.DE_I32
+        else:
+            components = components.to(torch.float64)
+            dt = _lib.DE_F64
+        components = components.contiguous()
+        n, k = components.shape
+        if normalise and self.t_range is None:
+            raise ValueError("normalise=True but the converter has no t_range")
+        out = torch.empty(n, dtype=torch.float32 if normalise else torch.float64, device=components.device)
+        with torch.cuda.device(components.device):
+            rc = _lib.load().de_time_from_components(
+                _ptr(components), dt, n, k, k, int(default_month), int(default_day), int(default_hour),
+                _dbl3(self.t_range) if self.t_range is not None else None,
+                None if normalise else _ptr(out), _ptr(out) if normalise else None, _stream_ptr(components.device))
+        _lib.check(rc, "de_time_from_components")
+        return out
+
     # dense fields (SPECIFICATIONS.MD:1963-2088) -----------------------------------------------------------
     def _norm_constants(self):
         if self._affine is not None:

@@ -47,6 +47,7 @@ extern "C" {
 #define DE_F32 0
 #define DE_F16 1
 #define DE_F64 2
+#define DE_I32 3
 
 /* flags */
 #define DE_INTERP_NEAREST 0u /* floor cell only: models/hash_encoding.py:57-72     */
@@ -184,6 +185,18 @@ DE_API int de_geo2xyzt_norm(const void* geo, int geo_dtype, const void* t, int t
                      const double* bbox_min_host, const double* bbox_span_host,
                      const double* t_range_host,
                      float* xyzt, double* ecef, int64_t n_points, void* stream);
+
+/*
+ * Timestamps from date columns -- replaces the per-row `datetime(...).timestamp()` loop of the spec's preprocessor
+ * (SPECIFICATIONS.MD:740-768, `_process_temporal`).  components: (n, n_cols) rows, `stride` elements apart, of
+ * [year, month, day, hour, minute, second] (n_cols in 1..6; missing month / day / hour take the defaults, minute and
+ * second 0), dtype DE_I32 or DE_F64 (fractional seconds give microseconds, int((second % 1) * 1e6)).  Times are UTC.
+ * timestamps: optional (n,) fp64 epoch seconds; t_norm: optional (n,) fp32 (ts - t_min) / (t_max - t_min) with
+ * t_range_host = {t_min, t_max} (required when t_norm is given).
+ */
+DE_API int de_time_from_components(const void* components, int dtype, int64_t n, int64_t stride, int n_cols,
+                            int default_month, int default_day, int default_hour, const double* t_range_host,
+                            double* timestamps, float* t_norm, void* stream);
 
 /*
  * Bounding box of ECEF positions of a geodetic batch -- replaces

@@ -67,3 +67,38 @@ def test_field_reference_geometry_uses_generated_coordinates():
     with torch.no_grad():
         want = enc.encode_features(conv.geodetic_to_xyzt_norm(geo, t))
     assert torch.equal(feats, want)
+
+
+def test_timestamps_from_date_columns_match_python_datetime():
+    """SPECIFICATIONS.MD:740-768: datetime(y, m, d, h, mi, int(s)).timestamp() (+ microseconds), evaluated for UTC."""
+    import calendar
+    import deepearth_b200 as de
+    from datetime import datetime, timezone
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(11)
+    n = 4000
+    y = rng.integers(1901, 2200, n)
+    m = rng.integers(1, 13, n)
+    d = np.array([rng.integers(1, calendar.monthrange(int(a), int(b))[1] + 1) for a, b in zip(y, m)])
+    h, mi = rng.integers(0, 24, n), rng.integers(0, 60, n)
+    s = np.round(rng.uniform(0, 59.999999, n), 6)
+    y[:4], m[:4], d[:4] = [2000, 1900 + 4, 2024, 1970], [2, 2, 2, 1], [29, 29, 29, 1]          # leap days, the epoch
+    h[3] = mi[3] = 0
+    s[3] = 0.0
+    comp = np.stack([y, m, d, h, mi, s], 1).astype(np.float64)
+    want = []
+    for row in comp:
+        dt = datetime(int(row[0]), int(row[1]), int(row[2]), int(row[3]), int(row[4]), int(row[5]), tzinfo=timezone.utc)
+        whole = calendar.timegm(dt.timetuple())
+        want.append(whole + int((row[5] % 1) * 1e6) / 1e6)
+    want = np.array(want)
+    conv = de.GeospatialConverter(device=str(dev), t_range=(1262304000.0, 1767139200.0))
+    got = conv.timestamps_from_components(torch.from_numpy(comp).to(dev))
+    assert np.array_equal(got.cpu().numpy(), want)
+    tn = conv.timestamps_from_components(torch.from_numpy(comp).to(dev), normalise=True)
+    want_n = ((want - 1262304000.0) / (1767139200.0 - 1262304000.0)).astype(np.float32)
+    assert np.array_equal(tn.cpu().numpy(), want_n)
+    # integer columns with defaults: year only -> June 15th, 12:00 (config.default_month / day / hour)
+    yo = torch.tensor([[2015], [1999]], dtype=torch.int32, device=dev)
+    got2 = conv.timestamps_from_components(yo).cpu().numpy()
+    assert list(got2) == [calendar.timegm((2015, 6, 15, 12, 0, 0)), calendar.timegm((1999, 6, 15, 12, 0, 0))]
