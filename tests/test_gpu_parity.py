@@ -466,6 +466,27 @@ def test_large_vs_torch_restatement_on_device(dev):
 # ---------------------------------------------------------------------------------------------------
 # geodetic prologue
 # ---------------------------------------------------------------------------------------------------
+def test_geo2xyz_reference_scenario_groups_on_device(dev, golden_dir):
+    """Prologue kernel on the reference's own scenario groups (geospatial/tests/geospatial_tests.py:67-215): ECEF within
+    1e-6 m, normalised coordinates within fp32 rounding (+ the ECEF noise over the box span for the cm-sized boxes), the
+    bounding box the kernel folds itself equal to the reference's."""
+    import deepearth_b200 as de
+    from test_oracle_golden import scenario_tolerance
+    g = load(golden_dir, "geo_scenarios")
+    for i in range(len(g["names"])):
+        geo = torch.from_numpy(g[f"s{i}_geo"]).to(dev)
+        conv = de.GeospatialConverter(device="cuda:0")
+        xyzt, ecef = conv.geodetic_to_xyzt_norm(geo, update_bbox=True, return_ecef=True)
+        assert np.abs(ecef.cpu().numpy() - g[f"s{i}_ecef"]).max() <= 1e-6, g["names"][i]
+        assert np.allclose(np.array(conv.bbox.min_point), g[f"s{i}_bbox_min"], rtol=0, atol=1e-8), g["names"][i]
+        err = np.abs(xyzt[:, :3].cpu().numpy().astype(np.float64) - g[f"s{i}_norm"])
+        assert (err <= scenario_tolerance(g[f"s{i}_bbox_span"])[None, :]).all(), (g["names"][i], err.max(0))
+        # the same points as fp32 tensors (how the reference's test builds them) take the _as_fp64 path
+        x32 = conv.geodetic_to_xyzt_norm(geo.float())
+        if bool((geo.float().double() == geo).all()):
+            assert torch.equal(x32, xyzt)
+
+
 def test_geo2xyz_vs_reference_and_oracle(dev, oracle, golden_dir):
     import deepearth_b200 as de
     g = load(golden_dir, "geo2xyz")

@@ -138,6 +138,27 @@ def test_geo2xyz_vs_reference(oracle, golden_dir):
     assert np.array_equal(x2[:, :3], g["degenerate_norm"].astype(np.float32))   # all 0.5
 
 
+def scenario_tolerance(span):
+    """|d norm| allowed per axis: fp32 rounding of a value in [0, 1] plus the fp64 ECEF ulp noise (libm / CUDA vs ATen
+    sin, cos: <= 4e-9 m) amplified by a small box -- the mm-precision scenarios have spans of centimetres."""
+    span = np.abs(np.asarray(span, np.float64))
+    return 6e-8 + 4e-9 / np.maximum(span, 1e-9)
+
+
+def test_geo2xyz_reference_scenario_groups(oracle, golden_dir):
+    """The reference's own geodetic scenario groups (geospatial/tests/geospatial_tests.py:67-215), captured by running
+    its test routine (tests/golden/make_golden_geo_scenarios.py): ECEF and bbox-normalised coordinates per group."""
+    g = load(golden_dir, "geo_scenarios")
+    n = len(g["names"])
+    assert n >= 30
+    for i in range(n):
+        geo, lo, span = g[f"s{i}_geo"], g[f"s{i}_bbox_min"], g[f"s{i}_bbox_span"]
+        xyzt, ecef = oracle.geo2xyzt_norm(geo, None, lo, span, (0.0, 1.0), want_ecef=True)
+        assert np.abs(ecef - g[f"s{i}_ecef"]).max() <= 4e-9, (g["names"][i], np.abs(ecef - g[f"s{i}_ecef"]).max())
+        err = np.abs(xyzt[:, :3].astype(np.float64) - g[f"s{i}_norm"])
+        assert (err <= scenario_tolerance(span)[None, :]).all(), (g["names"][i], err.max(0), span)
+
+
 def kat_levels(g):
     """Level list + tables of tests/golden/modeg_kat.npz (make_golden_modeg.py: table[i][f] = ((7i+3f+11l)%64-32)/64)."""
     F = int(g["F"][0])
