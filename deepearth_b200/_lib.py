@@ -18,6 +18,7 @@ DE_F32, DE_F16, DE_F64, DE_I32 = 0, 1, 2, 3
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS, DE_FLAG_NO_REGROUP = 0x100, 0x200, 0x400, 0x800
 DE_FLAG_GRAD_GROUPED = 0x1000
+DE_FLAG_NO_SMALL1D = 0x4000
 DE_MAX_LEVELS_PER_CALL = 256
 
 c_void_p = ctypes.c_void_p

@@ -191,6 +191,39 @@ constexpr unsigned long long kRepGroupBytes = 16ull << 20;   // ... and the copi
 constexpr unsigned kRepMax = 64;
 constexpr unsigned long long kRepMinUpdatesPerEntry = 256;
 
+// ---- nearest-cell 1-D levels served from shared memory (grid4d_small1d_kernels.cu) ---------------------------------
+// prime[0] = 1 (hash_encoding.py:64) makes a 1-D level's index the cell number: coordinates in [0, 1] touch rows 0 .. R.
+bool small1d_level(const de_level_desc& L, bool linear, int n_features) {
+    return !linear && L.n_dims == 1 && (n_features == 1 || n_features == 2 || n_features == 4 || n_features == 8);
+}
+constexpr unsigned kSmall1dBudget = 40u << 10;      // shared memory per CTA spent on live rows / accumulators
+bool plan_small1d(const de_level_desc* levels, int begin, int end, int n_features, int elem_bytes, bool backward,
+                  de::Small1dPlan& S) {
+    const int n = end - begin;
+    if (n > de::kSmall1dMaxLevels) return false;
+    S = de::Small1dPlan{};
+    const int slots_per_warp = 32 / (n <= 1 ? 1 : (n <= 2 ? 2 : (n <= 4 ? 4 : (n <= 8 ? 8 : 16))));
+    unsigned used = 0;
+    bool any = false;
+    for (int i = 0; i < n; ++i) {                    // coarse levels first: they are the contended ones
+        const de_level_desc& L = levels[begin + i];
+        unsigned long long live = (unsigned long long)L.resolution + 1ull;
+        if (live > L.table_size) live = L.table_size;
+        unsigned copies = 1;
+        if (backward) { copies = slots_per_warp > 4 ? 4 : slots_per_warp; }
+        unsigned long long bytes = (live * n_features * elem_bytes * copies + 15ull) & ~15ull;
+        while (copies > 1 && used + bytes > kSmall1dBudget) { copies >>= 1; bytes = (live * n_features * elem_bytes * copies + 15ull) & ~15ull; }
+        S.off[i] = used;
+        S.copies[i] = copies;
+        if (used + bytes > kSmall1dBudget) { S.live[i] = 0; continue; }
+        S.live[i] = static_cast<uint32_t>(live);
+        used += static_cast<unsigned>(bytes);
+        any = true;
+    }
+    S.total_bytes = used;
+    return any;
+}
+
 struct RepPlan {
     unsigned count;      // replicas including the table itself (1 = none)
     unsigned live;       // entries per replica
@@ -199,6 +232,8 @@ struct RepPlan {
 
 RepPlan plan_replicas(const de_level_desc& L, int n_features, int64_t n_points, bool linear) {
     RepPlan r{1, 0, 0};
+    if (small1d_level(L, linear, n_features)) return r;   // accumulated in shared memory instead (plan_small1d); a 1-D level
+                                                          // too fine for that has no contended rows either
     unsigned long long live = L.dense ? live_cells(L) : L.table_size;
     if (!L.dense) {
         // a hashed level touches min(T, (R+1)^D) entries scattered over the whole table -- except in 1-D,
@@ -475,6 +510,31 @@ int run(const CallArgs& a, Op op, de::EncodeParams& base, cudaStream_t stream) {
                 for (int i = 0; i < n; ++i)
                     P.levels[i].out_col = static_cast<unsigned long long>(i / G) * a.n_points * rg.W + (i % G) * a.n_features;
                 regroup_off += rg.bytes;
+            }
+        }
+        if ((op == Op::Forward || op == Op::Backward) && n == end - begin && small1d_level(a.levels[begin], linear, a.n_features) &&
+            !(a.flags & DE_FLAG_NO_SMALL1D)) {
+            de::Small1dPlan S;
+            const int eb = (op == Op::Forward && a.table_dtype == DE_F16) ? 2 : 4;
+            if (plan_small1d(a.levels, begin, end, a.n_features, eb, op == Op::Backward, S)) {
+                int G1 = 1;
+                while (G1 < n) G1 <<= 1;
+                P.group_size = G1;
+                P.n_groups = 1;
+                const long long p_step = de::kThreads / G1;
+                long long ppc = (a.n_points + 148 * 4 - 1) / (148 * 4);      // a few long-lived CTAs per SM: one flush each
+                if (ppc < p_step * 8) ppc = p_step * 8;
+                ppc = ((ppc + p_step - 1) / p_step) * p_step;
+                if (ppc > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "n_points=%lld too large for one launch", (long long)a.n_points);
+                P.points_per_cta = static_cast<int>(ppc);
+                const long long ctas = (a.n_points + ppc - 1) / ppc;
+                P.n_tiles = static_cast<int>(ctas);
+                cudaError_t e1 = op == Op::Forward
+                    ? de::launch_small1d_forward(P, S, a.table_dtype == DE_F16, a.n_features, static_cast<int>(ctas), stream)
+                    : de::launch_small1d_backward(P, S, a.n_features, static_cast<int>(ctas), stream);
+                if (e1 != cudaSuccess) return cuda_fail(e1, "shared-memory 1-D launch");
+                begin = end;
+                continue;
             }
         }
         P.group_size = G;

@@ -26,6 +26,17 @@ bool smem_layout_supported(bool half_tables, int F);
 cudaError_t launch_forward_smem(const EncodeParams& P, const SmemPlan& S, int D, bool half_tables, int F, bool pow2,
                                 cudaStream_t s);
 
+// nearest-cell 1-D levels whose live rows fit shared memory (grid4d_small1d_kernels.cu)
+constexpr int kSmall1dMaxLevels = 16;
+struct Small1dPlan {
+    uint32_t off[kSmall1dMaxLevels];      // byte offset of the level's rows (forward) / accumulators (backward), 16 B aligned
+    uint32_t live[kSmall1dMaxLevels];     // rows kept in shared memory (0 = level served from global memory only)
+    uint32_t copies[kSmall1dMaxLevels];   // backward: private accumulator copies (power of two)
+    uint32_t total_bytes;
+};
+cudaError_t launch_small1d_forward(const EncodeParams& P, const Small1dPlan& S, bool half_tables, int F, int n_ctas, cudaStream_t s);
+cudaError_t launch_small1d_backward(const EncodeParams& P, const Small1dPlan& S, int F, int n_ctas, cudaStream_t s);
+
 struct CastParams {
     const float* src[64];
     void* dst[64];

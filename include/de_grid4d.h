@@ -60,7 +60,8 @@ extern "C" {
 #define DE_FLAG_NO_REGROUP 0x800u  /* A/B: backward reads gradient-row slices in place instead of regrouping them first  */
 #define DE_FLAG_GRAD_GROUPED 0x1000u /* backward: grad_out is already group-major (see de_grid4d_backward_group_width)            */
 #define DE_FLAG_COHERENT_GATHER 0x2000u /* A/B: forward table gathers as GPU-scope relaxed loads (home L2 partition only)         */
-#define DE_FLAG_MASK (DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE | DE_FLAG_NO_L2_HINTS | DE_FLAG_NO_REGROUP | DE_FLAG_GRAD_GROUPED | DE_FLAG_COHERENT_GATHER)
+#define DE_FLAG_NO_SMALL1D 0x4000u /* A/B: nearest-cell 1-D levels through the general kernels instead of the shared-memory path */
+#define DE_FLAG_MASK (DE_FLAG_NO_SMALL1D | DE_INTERP_MASK | DE_FLAG_STAGED_BWD | DE_FLAG_SMEM_COARSE | DE_FLAG_NO_L2_HINTS | DE_FLAG_NO_REGROUP | DE_FLAG_GRAD_GROUPED | DE_FLAG_COHERENT_GATHER)
 
 #define DE_MAX_DIMS 4
 #define DE_MAX_LEVELS_PER_CALL 256

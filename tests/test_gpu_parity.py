@@ -819,3 +819,30 @@ def test_grid4d_encoder_fused_head(dev):
     assert float((got - want).abs().max()) <= 3e-2 * float(want.abs().max())
     enc(xyzt).sum().backward()
     assert all(p.grad is not None for p in enc.parameters())
+
+
+def test_small1d_shared_memory_path_equals_general_kernels(dev):
+    """Nearest-cell 1-D levels (the reference's temporal encoder) served from shared memory: features identical to the
+    general kernels' (DE_FLAG_NO_SMALL1D), gradients equal up to summation order -- coordinates partly outside [0, 1]
+    (those rows take the global path), a temporal row mask, fp32 and fp16 tables, ragged tails."""
+    import deepearth_b200 as de
+    from deepearth_b200 import _lib
+    for n, table_dtype in ((70001, "float32"), (333, "float16"), (1 << 20, "float32")):
+        torch.manual_seed(n)
+        cfg = de.DeepEarthConfig(hidden_dim=32, n_heads=4, n_layers=1, hash_table_size=2 ** 17, grid4d_table_dtype=table_dtype)
+        enc = de.Grid4DEncoder(cfg).to(dev)
+        g = torch.Generator(device=dev).manual_seed(7)
+        xyzt = torch.rand((n, 4), device=dev, generator=g) * 1.4 - 0.2
+        tmask = torch.rand(n, device=dev, generator=g) > 0.25
+        gout = torch.randn((n, 48), device=dev, generator=g)
+        res = []
+        for flags in (0, _lib.DE_FLAG_NO_SMALL1D):
+            for e in enc._encoders:
+                e.extra_flags = flags
+            enc.zero_grad(set_to_none=True)
+            f = enc.encode_features(xyzt, temporal_mask=tmask)
+            f.backward(gout)
+            res.append((f.detach().clone(), [w.grad.clone() for w in enc.temporal_encoder.weights()]))
+        assert torch.equal(res[0][0], res[1][0])
+        for a, b in zip(res[0][1], res[1][1]):
+            assert float((a - b).abs().max()) <= 1e-5 * max(float(b.abs().max()), 1e-30)
