@@ -432,6 +432,76 @@ def eager_cuda_baseline(wl, n, device, steps=3, warmup=2):
             "what": what + "; fwd+bwd, CUDA events, same B200", "peak_mem_gib": round(peak_gib, 1)}
 
 
+def _time_cuda(fn, steps=5, warmup=2):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def field_bench(device, n_side=2048):
+    """forward-only evaluation of the c2 grids over a regular n_side x n_side lat/lon grid (2^22 points):
+    the patch-ordered field kernel (coordinates generated on the device) against the general forward over the same
+    points (coordinate tensor from the prologue kernel) -- identical features, checked here on every run."""
+    import deepearth_b200 as de
+    from _synth import FLORIDA_BBOX_GEO as B, FLORIDA_T_RANGE
+    torch.manual_seed(1234)
+    enc = de.Grid4DEncoder(build_config(WORKLOADS["c2"])).to(device).eval()
+    _, _, conv = make_geo(16, device, 1)
+    lat_range, lon_range = (B["south"], B["north"]), (B["west"], B["east"])
+    args = (conv, lat_range, lon_range, n_side, n_side)
+    kw = dict(altitude=25.0, time=0.5 * (FLORIDA_T_RANGE[0] + FLORIDA_T_RANGE[1]))
+    feats, xyzt = enc.encode_field(*args, return_coords=True, **kw)
+    with torch.no_grad():
+        same = bool(torch.equal(feats, enc.encode_features(xyzt)))
+    del feats
+    ms_field = _time_cuda(lambda: enc.encode_field(*args, **kw))
+    with torch.no_grad():
+        ms_general = _time_cuda(lambda: enc.encode_features(xyzt))
+    n = n_side * n_side
+    return {"points": n, "grid": [n_side, n_side], "field_forward_ms": ms_field, "general_forward_ms": ms_general,
+            "speedup": ms_general / ms_field, "mpoints_per_s": n / ms_field / 1e3, "bit_identical": same, "gpu_launches": 14,
+            "what": "Grid4DEncoder.encode_field (de_grid4d_field_forward: 16 x 16-point patches per CTA, a warp = 16 neighbouring "
+                    "points of one level) vs Grid4DEncoder.encode_features over the same 2^22 points; c2 grids, fp16 tables, no_grad"}
+
+
+def st_embed_bench(device, n_tokens=1 << 16, dim=512):
+    """SpatialTemporalEmbedding forward + backward; achieved bytes/s of the streamed tensors (tokens in,
+    out written, gradient in) against the HBM copy peak -- the temporal MLP (fp32 SIMT) is what keeps it below."""
+    import deepearth_b200 as de
+    torch.manual_seed(7)
+    m = de.SpatialTemporalEmbedding(dim, check_indices=False).to(device)
+    m.add_modality("vision")
+    g = torch.Generator(device=device).manual_seed(3)
+    tok = torch.randn((n_tokens // 256, 256, dim), device=device, generator=g, requires_grad=True)
+    pos = torch.rand((n_tokens // 256, 256, 2), device=device, generator=g) * 0.999
+    t = torch.rand((n_tokens // 256, 256, 1), device=device, generator=g)
+    gout = torch.randn_like(tok)
+    with torch.no_grad():
+        ms_fwd = _time_cuda(lambda: m(tok, pos, t, "vision"))
+        ms_gather = _time_cuda(lambda: m(tok, pos, None, "vision"))
+
+    def step():
+        m.zero_grad(set_to_none=True)
+        m(tok, pos, t, "vision").backward(gout)
+    ms_step = _time_cuda(step)
+    peak, _ = measured_peaks()
+    stream_bytes = n_tokens * dim * 4 * 2
+    return {"tokens": n_tokens, "dim": dim, "forward_ms": ms_fwd, "forward_gather_only_ms": ms_gather, "fwd_bwd_ms": ms_step,
+            "gather_only_gbs": stream_bytes / ms_gather / 1e6, "gather_only_frac_of_hbm_peak": stream_bytes / ms_gather / 1e6 / peak,
+            "forward_gbs": stream_bytes / ms_fwd / 1e6, "forward_frac_of_hbm_peak": stream_bytes / ms_fwd / 1e6 / peak,
+            "temporal_mlp_gflops": 2.0 * n_tokens * (dim // 2) ** 2 / (max(ms_fwd - ms_gather, 1e-3) * 1e6),
+            "gpu_launches": 2 * 7 + 7 * 7,
+            "what": "deepearth_b200.SpatialTemporalEmbedding (de_st_embedding_forward / _backward): table gathers + modality + "
+                    "residual in one streaming pass (tokens read + out written = the streamed bytes), temporal MLP as an fp32 tile GEMM"}
+
+
 def cpu_sample_log2(wl, steps, warmup):
     """Bounded CPU sample: the decomposed mode runs ~0.03 Mpoints/s on 16 host threads, so 2^17 points x 13 steps is
     about a minute; more steps shrink the sample."""
@@ -812,6 +882,9 @@ def run_gpu_arm(args, wl):
                 r = measure(args, nm, dict(WORKLOADS[nm]), ctx, side_steps)
                 extra[nm] = {k: r[k] for k in ("value", "unit", "steps", "ms_per_step", "config", "kernels_ms", "roofline",
                                                "roofline_packets", "e2e", "gpu_launches", "clocks")}
+            extra["field"] = field_bench(ctx.device)
+            extra["st_embed"] = st_embed_bench(ctx.device)
+            torch.cuda.empty_cache()
             torch.cuda.reset_peak_memory_stats(ctx.device)
             extra["eager_cuda_baseline"] = {
                 "c2": eager_cuda_baseline(dict(WORKLOADS["c2"]), 2 ** 22, ctx.device),

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_PKG, "libde_grid4d.so")
 
 DE_OK = 0
 ABI_VERSION = 4
-DE_F32, DE_F16, DE_F64, DE_I32 = 0, 1, 2, 3
+DE_F32, DE_F16, DE_F64, DE_I32, DE_BF16 = 0, 1, 2, 3, 4
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS, DE_FLAG_NO_REGROUP = 0x100, 0x200, 0x400, 0x800
 DE_FLAG_GRAD_GROUPED = 0x1000
@@ -80,6 +80,10 @@ SIGNATURES = {
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "de_time_from_components": (c_int, [c_void_p, c_int, c_i64, c_i64, c_int, c_int, c_int, c_int,
                                         ctypes.POINTER(ctypes.c_double), c_void_p, c_void_p, c_void_p]),
+    "de_projection_supported": (c_int, [c_int, c_int, c_int]),
+    "de_projection_forward": (c_int, [c_void_p, c_i64, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                      c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "de_gemm_bf16": (c_int, [c_void_p, c_i64, c_void_p, c_i64, c_i64, c_int, c_int, c_void_p, c_void_p, c_i64, c_int, c_void_p]),
     "de_geo_bbox": (c_int, [c_void_p, c_int, c_void_p, c_i64, c_void_p]),
     "de_set_l2_fetch_granularity": (c_int, [c_int]),
     "de_get_l2_fetch_granularity": (c_int, [ctypes.POINTER(c_int)]),

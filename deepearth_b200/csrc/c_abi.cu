@@ -947,6 +947,60 @@ DE_API int de_st_embedding_backward(const float* grad_out, int64_t n_tokens, int
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "st_embedding backward launch");
 }
 
+static int device_sms() {
+    int dev = 0, n_sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    return n_sms;
+}
+
+DE_API int de_gemm_bf16(const void* a_bf16, int64_t lda, const void* b_bf16, int64_t ldb, int64_t m, int n, int k,
+                 const float* bias, void* c, int64_t ldc, int out_dtype, void* stream) {
+    if (m < 0 || n < 1 || k < 1) return fail(DE_EINVAL, "gemm_bf16: m=%lld n=%d k=%d", (long long)m, n, k);
+    if (m == 0) return DE_OK;
+    if (!a_bf16 || !b_bf16 || !c) return fail(DE_EINVAL, "gemm_bf16: NULL pointer");
+    if (out_dtype != DE_F32 && out_dtype != DE_BF16) return fail(DE_EUNSUPPORTED, "gemm_bf16: out_dtype=%d", out_dtype);
+    if (reinterpret_cast<uintptr_t>(a_bf16) % 16 || reinterpret_cast<uintptr_t>(b_bf16) % 16 || lda % 8 || ldb % 8)
+        return fail(DE_EALIGN, "gemm_bf16: operand rows must be 16-byte aligned (TMA)");
+    if (lda < k || ldb < k || ldc < n) return fail(DE_EINVAL, "gemm_bf16: leading dimension shorter than the row");
+    if (m > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "gemm_bf16: m=%lld too large", (long long)m);
+    de::GemmParams P{};
+    P.M = m; P.N = n; P.K = k; P.c = c; P.ldc = ldc; P.bias = bias;
+    cudaError_t e = de::launch_gemm_bf16(a_bf16, lda, b_bf16, ldb, P, out_dtype == DE_BF16, device_sms(), static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "gemm_bf16 launch (TMA descriptor or kernel)");
+}
+
+DE_API int de_projection_supported(int in_dim, int hidden, int out_dim) {
+    return (de::proj_hidden_supported(in_dim, hidden) && out_dim >= 8 && out_dim % 8 == 0) ? 1 : 0;
+}
+
+DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, int64_t x_stride,
+                          const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
+                          const void* w2_bf16, const float* b2, int hidden, int out_dim,
+                          void* hidden_bf16, float* row_stats, float* y, int64_t y_stride, void* stream) {
+    if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (n_points == 0) return DE_OK;
+    if (!x || !w1_bf16 || !b1 || !ln_gamma || !ln_beta || !w2_bf16 || !hidden_bf16 || !y) return fail(DE_EINVAL, "projection: NULL pointer");
+    if (!de_projection_supported(in_dim, hidden, out_dim))
+        return fail(DE_EUNSUPPORTED, "projection: in_dim=%d hidden=%d out_dim=%d (in_dim in {32,48,64,96,128}, hidden a multiple of 128, out_dim of 8)", in_dim, hidden, out_dim);
+    if (x_stride < in_dim || y_stride < out_dim) return fail(DE_EINVAL, "projection: row stride shorter than the row");
+    if (reinterpret_cast<uintptr_t>(x) % 16 || x_stride % 4) return fail(DE_EALIGN, "projection: x rows not 16-byte aligned");
+    const void* aligned[] = {w1_bf16, w2_bf16, hidden_bf16, y};
+    for (const void* q : aligned)
+        if (reinterpret_cast<uintptr_t>(q) % 16) return fail(DE_EALIGN, "projection: pointer not 16-byte aligned");
+    if (n_points > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "projection: n_points too large");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int n_sms = device_sms();
+    de::ProjHiddenParams H{};
+    H.x = x; H.n = n_points; H.x_stride = x_stride; H.w1 = w1_bf16; H.b1 = b1; H.ln_gamma = ln_gamma; H.ln_beta = ln_beta;
+    H.ln_eps = ln_eps; H.hidden = hidden; H.hidden_out = hidden_bf16; H.hidden_stride = hidden; H.stats_out = row_stats;
+    cudaError_t e = de::launch_proj_hidden(H, in_dim, n_sms, s);
+    if (e != cudaSuccess) return cuda_fail(e, "projection hidden launch");
+    de::GemmParams G{};
+    G.M = n_points; G.N = out_dim; G.K = hidden; G.c = y; G.ldc = y_stride; G.bias = b2;
+    e = de::launch_gemm_bf16(hidden_bf16, hidden, w2_bf16, hidden, G, 0, n_sms, s);
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "projection GEMM launch");
+}
+
 DE_API int de_set_l2_fetch_granularity(int bytes) {
     if (bytes != 32 && bytes != 64 && bytes != 128) return fail(DE_EINVAL, "l2 fetch granularity must be 32, 64 or 128, got %d", bytes);
     cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, static_cast<size_t>(bytes));

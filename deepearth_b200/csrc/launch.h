@@ -104,6 +104,34 @@ struct MlpHeadBwdParams {
     float* db2;                   // (64,) accumulated, or NULL
     int n_tiles;
 };
+// wide projection (proj_kernels.cu): hidden = GELU(LN(W1 x + b1)) as bf16, then a TMA / tcgen05 GEMM
+struct ProjHiddenParams {
+    const float* x;               // (n, in_dim) fp32 features, rows x_stride floats apart (16 B aligned)
+    long long n;
+    long long x_stride;
+    const void* w1;               // (hidden, in_dim) bf16 row-major
+    const float* b1;              // (hidden,)
+    const float* ln_gamma;        // (hidden,)
+    const float* ln_beta;         // (hidden,)
+    float ln_eps;
+    int hidden;                   // multiple of 128
+    void* hidden_out;             // (n, hidden) bf16, rows hidden_stride elements apart
+    long long hidden_stride;
+    float* stats_out;             // (n, 2) {mean, rstd} of the pre-LayerNorm row, or NULL
+    int n_tiles;
+};
+struct GemmParams {
+    long long M;                  // rows of A and C
+    int N, K;
+    void* c;                      // (M, N) fp32 or bf16, rows ldc elements apart
+    long long ldc;
+    const float* bias;            // (N,) or NULL
+    int vec_ok;
+};
+bool proj_hidden_supported(int in_dim, int hidden);
+cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaStream_t s);
+cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, GemmParams P, int out_bf16, int n_sms,
+                             cudaStream_t s);
 bool mlp_head_supported(int in_dim, int hidden, int out_dim);
 cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);        // mlp_head_bwd2.cu
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s);

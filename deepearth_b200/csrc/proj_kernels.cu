@@ -1,0 +1,473 @@
+// proj_kernels.cu -- Grid4DEncoder.projection at its real width (hidden_dim = 768 by default, 2048 in the integrated
+// model) on the 5th-generation tensor cores (sm_100a: tcgen05.mma + TMEM + TMA).
+//
+//   y = W2 . GELU( LayerNorm( W1 . x + b1 ) ) + b2        /root/reference/models/encoders.py:47-52, models/configs.py:44
+//
+// Two kernels, because a 128-row tile's hidden row (H >= 768 fp32 accumulators) does not fit tensor memory (512 columns)
+// next to the output accumulators, and the LayerNorm statistics need the whole row before any of it can be normalised:
+//
+//   proj_hidden_kernel<K1>   x (n, K1) fp32  ->  a = GELU(LN(W1 x + b1)) (n, H) bf16.   The first Linear is small (K1 = 48
+//       or 128), so it is simply run TWICE per tile in 128-column chunks: pass 1 reads the chunks back from TMEM only to
+//       accumulate the row statistics (chunk-wise mean / M2, merged with Chan's formula -- no E[h^2] - mean^2 cancellation),
+//       pass 2 recomputes each chunk, normalises, applies GELU and writes bf16.  The pre-activation never exists in
+//       memory; the tile's features are read once, the hidden row is written once.  W1 chunks are staged through a
+//       double buffer while the previous chunk's epilogue runs.
+//
+//   gemm_bf16_tma_kernel     C (M, N) = A (M, K) . B (N, K)^T [+ bias]: the second Linear (and, with other operands, the
+//       GEMMs of the backward pass).  Persistent, warp specialised: warp 0 issues TMA loads (cp.async.bulk.tensor, 128 B
+//       swizzle) into a 4-stage shared-memory ring, warp 1 issues tcgen05.mma (M = 128, N = 256, K = 16) into one of two
+//       256-column TMEM accumulators, warps 4..7 drain the other accumulator (tcgen05.ld, bias, 32-byte stores), so the
+//       epilogue of tile i overlaps the mainloop of tile i + 1.
+//
+// Operand layouts follow cute::UMMA (CUTLASS 4.x, cute/atom/mma_traits_sm100.hpp): K-major SWIZZLE_128B tiles are 8-row x
+// 128-byte atoms (stride byte offset 1024), exactly what a TMA box {64 bf16, rows} with CU_TENSOR_MAP_SWIZZLE_128B writes.
+#include <cuda.h>
+
+#include "launch.h"
+#include "mlp_common.cuh"
+
+namespace de {
+
+using namespace mlp;
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// shared pieces
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ constexpr uint32_t idesc_bf16(int m, int n, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn ? (1u << 15) : 0u) | (b_mn ? (1u << 16) : 0u) |
+           (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+// K-major SWIZZLE_128B operand: start address, LBO (unused for swizzled K-major: 1), SBO = 1024 B between 8-row atoms
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFFu);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= 1ull << 46;                        // descriptor version 1 (Blackwell)
+    d |= 2ull << 61;                        // layout type SWIZZLE_128B
+    return d;
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+
+// Chan's parallel update: fold a block of `nb` values with mean mb and centred sum of squares m2b into (n, mean, m2)
+__device__ __forceinline__ void chan_merge(float& n, float& mean, float& m2, float nb, float mb, float m2b) {
+    const float tot = n + nb;
+    const float delta = mb - mean;
+    mean += delta * (nb / tot);
+    m2 += m2b + delta * delta * (n * nb / tot);
+    n = tot;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// kernel 1: hidden activations
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kChunkN = 128;                                    // hidden columns per MMA chunk / TMEM buffer
+
+// dynamic shared memory: A [128 x K1] | B[2] [128 x K1]   (bf16, UMMA canonical K-major no-swizzle)
+template <int K1>
+__global__ void __launch_bounds__(kMlpThreads)
+proj_hidden_kernel(const __grid_constant__ ProjHiddenParams P) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ uint32_t s_tmem;
+    unsigned char* sA = smem;
+    unsigned char* sB[2] = {smem + kTileM * K1 * 2, smem + kTileM * K1 * 2 + kChunkN * K1 * 2};
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int H = P.hidden, NC = H / kChunkN;
+
+    if (tid == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(2 * kChunkN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+    constexpr uint32_t kIdesc = idesc_bf16(kTileM, kChunkN, false, false);
+    uint32_t phase0 = 0u, phase1 = 0u;
+    const int row = tid;
+    const __nv_bfloat16* __restrict__ w1 = static_cast<const __nv_bfloat16*>(P.w1);
+
+    // W1 rows [c * 128, c * 128 + 128) -> canonical B tile
+    auto stage_chunk = [&](int c, unsigned char* dst) {
+        const __nv_bfloat16* src = w1 + static_cast<size_t>(c) * kChunkN * K1;
+        for (int e = tid; e < kChunkN * (K1 / 8); e += kMlpThreads) {
+            const int n = e / (K1 / 8), k8 = e % (K1 / 8);
+            *reinterpret_cast<uint4*>(dst + canon_chunk_offset(n, k8, K1)) = __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(n) * K1 + k8 * 8));
+        }
+    };
+    auto issue_chunk = [&](int g) {                    // g: running chunk number of this tile (0 .. 2 NC - 1)
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB[g & 1]);
+#pragma unroll
+        for (int k = 0; k < K1 / 16; ++k)
+            umma_bf16(tmem + (g & 1) * kChunkN, umma_desc(a0 + k * 256, 128, (K1 / 8) * 128), umma_desc(b0 + k * 256, 128, (K1 / 8) * 128),
+                      kIdesc, k > 0 ? 1u : 0u);
+        umma_commit(&s_bar[g & 1]);
+    };
+
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+        const long long p0 = static_cast<long long>(tile) * kTileM;
+        const int n_valid = static_cast<int>(P.n - p0 < kTileM ? P.n - p0 : kTileM);
+        const float* tile_base = P.x + p0 * P.x_stride;
+        const int xs = static_cast<int>(P.x_stride);
+        const bool a32 = ((reinterpret_cast<uintptr_t>(tile_base) | (static_cast<uintptr_t>(xs) << 2)) & 31) == 0;
+        // ---- features -> bf16 A tile (lane mapping of mlp_head.cu: conflict-free 16-byte shared stores) ----------------
+        constexpr int kIt = (4 * K1) / 32;
+        constexpr int kRound = kIt >= 2 ? kIt / 2 : kIt;
+#pragma unroll
+        for (int it0 = 0; it0 < kIt; it0 += kRound) {
+            float4 va[kRound], vb[kRound];
+#pragma unroll
+            for (int u = 0; u < kRound; ++u) {
+                const int c = lane + 32 * (it0 + u);
+                const int r = min(warp * 32 + (c / K1) * 8 + ((c % K1) & 7), n_valid - 1);     // tail rows re-read the last valid row
+                const int k8 = (c % K1) >> 3;
+                ld_stream_32B(tile_base + (static_cast<long long>(r) * xs + k8 * 8), va[u], vb[u], a32);
+            }
+#pragma unroll
+            for (int u = 0; u < kRound; ++u) {
+                const int c = lane + 32 * (it0 + u);
+                const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
+                const int k8 = (c % K1) >> 3;
+                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(r, k8, K1)) =
+                    make_uint4(pack_bf16(va[u].x, va[u].y), pack_bf16(va[u].z, va[u].w), pack_bf16(vb[u].x, vb[u].y), pack_bf16(vb[u].z, vb[u].w));
+            }
+        }
+        stage_chunk(0, sB[0]);
+        fence_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) issue_chunk(0);
+
+        float cnt = 0.0f, mean = 0.0f, m2 = 0.0f, rstd = 0.0f;
+        __nv_bfloat16* out_row = static_cast<__nv_bfloat16*>(P.hidden_out) + (p0 + row) * static_cast<long long>(P.hidden_stride);
+        for (int g = 0; g < 2 * NC; ++g) {
+            const int c = g < NC ? g : g - NC;
+            // next chunk's weights travel and its MMAs run while this chunk's epilogue executes
+            if (g + 1 < 2 * NC) {
+                stage_chunk(g + 1 < NC ? g + 1 : g + 1 - NC, sB[(g + 1) & 1]);
+                fence_async_smem();
+                tc_fence_before();
+                __syncthreads();                      // everyone is done reading TMEM buffer (g + 1) & 1 (chunk g - 1)
+                if (tid == 0) issue_chunk(g + 1);
+            }
+            if (g & 1) { mbar_wait(&s_bar[1], phase1); phase1 ^= 1u; }
+            else { mbar_wait(&s_bar[0], phase0); phase0 ^= 1u; }
+            tc_fence_after();
+            const uint32_t t_base = tmem + lane_off + (g & 1) * kChunkN;
+            if (g < NC) {
+                // ---- pass 1: row statistics ---------------------------------------------------------------------------
+#pragma unroll 1
+                for (int q = 0; q < kChunkN / 32; ++q) {
+                    float v[32];
+                    tmem_ld32(t_base + q * 32, v);
+                    const float* b1 = P.b1 + c * kChunkN + q * 32;
+                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        v[j] += __ldg(b1 + j); v[j + 1] += __ldg(b1 + j + 1); v[j + 2] += __ldg(b1 + j + 2); v[j + 3] += __ldg(b1 + j + 3);
+                        s0 += v[j]; s1 += v[j + 1]; s2 += v[j + 2]; s3 += v[j + 3];
+                    }
+                    const float mb = ((s0 + s1) + (s2 + s3)) * (1.0f / 32.0f);
+                    s0 = s1 = s2 = s3 = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const float d0 = v[j] - mb, d1 = v[j + 1] - mb, d2 = v[j + 2] - mb, d3 = v[j + 3] - mb;
+                        s0 = fmaf(d0, d0, s0); s1 = fmaf(d1, d1, s1); s2 = fmaf(d2, d2, s2); s3 = fmaf(d3, d3, s3);
+                    }
+                    chan_merge(cnt, mean, m2, 32.0f, mb, (s0 + s1) + (s2 + s3));
+                }
+                if (g == NC - 1) {
+                    rstd = rsqrtf(m2 / static_cast<float>(H) + P.ln_eps);
+                    if (P.stats_out && row < n_valid) {
+                        P.stats_out[2 * (p0 + row)] = mean;
+                        P.stats_out[2 * (p0 + row) + 1] = rstd;
+                    }
+                }
+            } else {
+                // ---- pass 2: normalise, GELU, bf16, store ---------------------------------------------------------------
+#pragma unroll 1
+                for (int q = 0; q < kChunkN / 32; ++q) {
+                    float v[32];
+                    tmem_ld32(t_base + q * 32, v);
+                    const int col0 = c * kChunkN + q * 32;
+                    uint32_t packed[16];
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {
+                        float a = v[j] + __ldg(P.b1 + col0 + j), b = v[j + 1] + __ldg(P.b1 + col0 + j + 1);
+                        a = fmaf((a - mean) * rstd, __ldg(P.ln_gamma + col0 + j), __ldg(P.ln_beta + col0 + j));
+                        b = fmaf((b - mean) * rstd, __ldg(P.ln_gamma + col0 + j + 1), __ldg(P.ln_beta + col0 + j + 1));
+                        packed[j >> 1] = pack_bf16(gelu_fwd(a), gelu_fwd(b));
+                    }
+                    if (row < n_valid) {
+                        uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) dst[u] = make_uint4(packed[4 * u], packed[4 * u + 1], packed[4 * u + 2], packed[4 * u + 3]);
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+        __syncthreads();          // the next tile overwrites sA / sB[0] and TMEM buffer 0
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * kChunkN) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// kernel 2: C = A . B^T (+ bias), bf16 operands by TMA, fp32 accumulation in TMEM
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 64, kGemmStages = 4;
+constexpr int kGemmThreads = 256;                      // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warps 4..7 epilogue
+constexpr uint32_t kGemmStageBytes = (kGemmBM + kGemmBN) * kGemmBK * 2;
+constexpr uint32_t kGemmSmemBytes = kGemmStages * kGemmStageBytes + 1024;   // + alignment slack
+
+template <int OUT_BF16>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                     const __grid_constant__ GemmParams P) {
+    extern __shared__ unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t s_full[kGemmStages], s_empty[kGemmStages], s_tfull[2], s_tempty[2];
+    __shared__ uint32_t s_tmem;
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_n = (P.N + kGemmBN - 1) / kGemmBN;
+    const long long tiles_m = (P.M + kGemmBM - 1) / kGemmBM;
+    const long long n_tiles = tiles_m * tiles_n;
+    const int k_blocks = (P.K + kGemmBK - 1) / kGemmBK;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kGemmStages; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp == 0 && lane == 0) {
+        // ===== TMA producer =====
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int m0 = static_cast<int>(tile / tiles_n) * kGemmBM, n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                mbar_wait(&s_empty[stage], phase ^ 1u);
+                unsigned char* sa = smem + stage * kGemmStageBytes;
+                unsigned char* sb = sa + kGemmBM * kGemmBK * 2;
+                mbar_expect_tx(&s_full[stage], kGemmStageBytes);
+                tma_load_2d(sa, &map_a, kb * kGemmBK, m0, &s_full[stage]);
+                tma_load_2d(sb, &map_b, kb * kGemmBK, n0, &s_full[stage]);
+                if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ===== MMA issuer =====
+        constexpr uint32_t kIdesc = idesc_bf16(kGemmBM, kGemmBN, false, false);
+        int stage = 0;
+        uint32_t phase = 0;
+        int as = 0;
+        uint32_t aphase = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            mbar_wait(&s_tempty[as], aphase ^ 1u);                  // epilogue has drained this accumulator
+            tc_fence_after();
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                mbar_wait(&s_full[stage], phase);
+                tc_fence_after();
+                const uint32_t a0 = smem_u32(smem + stage * kGemmStageBytes);
+                const uint32_t b0 = a0 + kGemmBM * kGemmBK * 2;
+#pragma unroll
+                for (int k = 0; k < kGemmBK / 16; ++k)
+                    umma_bf16(tmem + as * kGemmBN, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(b0 + k * 32, 16, 1024),
+                              kIdesc, (kb | k) ? 1u : 0u);
+                umma_commit(&s_empty[stage]);                        // frees the slot when these MMAs have read it
+                if (kb == k_blocks - 1) umma_commit(&s_tfull[as]);   // accumulator complete
+                if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
+            }
+            if (++as == 2) { as = 0; aphase ^= 1u; }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: TMEM -> registers -> global =====
+        const int quarter = warp & 3;                                // TMEM lanes this warp may read
+        int as = 0;
+        uint32_t aphase = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const long long m0 = (tile / tiles_n) * kGemmBM;
+            const int n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
+            mbar_wait(&s_tfull[as], aphase);
+            tc_fence_after();
+            const long long r = m0 + quarter * 32 + lane;
+            const uint32_t t_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + as * kGemmBN;
+#pragma unroll 1
+            for (int q = 0; q < kGemmBN / 32; ++q) {
+                const int col0 = n0 + q * 32;
+                if (col0 >= P.N) break;                              // warp-uniform
+                float v[32];
+                tmem_ld32(t_base + q * 32, v);
+                if (P.bias) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldg(P.bias + col0 + j) : 0.0f;
+                }
+                if (r < P.M) {
+                    if constexpr (OUT_BF16) {
+                        __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(P.c) + r * P.ldc + col0;
+                        if (col0 + 32 <= P.N && P.vec_ok) {
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                reinterpret_cast<uint4*>(dst)[u] = make_uint4(pack_bf16(v[8 * u], v[8 * u + 1]), pack_bf16(v[8 * u + 2], v[8 * u + 3]),
+                                                                              pack_bf16(v[8 * u + 4], v[8 * u + 5]), pack_bf16(v[8 * u + 6], v[8 * u + 7]));
+                        } else {
+                            #pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < P.N) dst[j] = __float2bfloat16_rn(v[j]);
+                        }
+                    } else {
+                        float* dst = static_cast<float*>(P.c) + r * P.ldc + col0;
+                        if (col0 + 32 <= P.N && P.vec_ok) {
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                st_stream_32B(dst + 8 * u, make_float4(v[8 * u], v[8 * u + 1], v[8 * u + 2], v[8 * u + 3]),
+                                              make_float4(v[8 * u + 4], v[8 * u + 5], v[8 * u + 6], v[8 * u + 7]), true);
+                        } else {
+                            #pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < P.N) dst[j] = v[j];
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_tempty[as]);
+            if (++as == 2) { as = 0; aphase ^= 1u; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// row-major bf16 matrix (rows, cols), leading dimension ld elements; box = {64 columns, box_rows}, 128 B swizzle
+bool make_map_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+    const cuuint32_t box[2] = {64u, static_cast<cuuint32_t>(box_rows)};
+    const cuuint32_t estr[2] = {1u, 1u};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+bool proj_hidden_supported(int in_dim, int hidden) {
+    const bool k_ok = in_dim == 32 || in_dim == 48 || in_dim == 64 || in_dim == 96 || in_dim == 128;
+    return k_ok && hidden >= kChunkN && hidden % kChunkN == 0 && hidden <= 4096;
+}
+
+template <int K1>
+static cudaError_t launch_hidden_k(const ProjHiddenParams& P, int n_sms, cudaStream_t s) {
+    const size_t smem = static_cast<size_t>(kTileM + 2 * kChunkN) * K1 * 2;
+    cudaError_t e = cudaFuncSetAttribute(proj_hidden_kernel<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
+    if (per_sm > 2) per_sm = 2;                                   // 2 x 256 TMEM columns
+    if (per_sm < 1) per_sm = 1;
+    int grid = n_sms * per_sm;
+    if (grid > P.n_tiles) grid = P.n_tiles;
+    proj_hidden_kernel<K1><<<grid, kMlpThreads, smem, s>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaStream_t s) {
+    P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
+    switch (in_dim) {
+        case 32: return launch_hidden_k<32>(P, n_sms, s);
+        case 48: return launch_hidden_k<48>(P, n_sms, s);
+        case 64: return launch_hidden_k<64>(P, n_sms, s);
+        case 96: return launch_hidden_k<96>(P, n_sms, s);
+        case 128: return launch_hidden_k<128>(P, n_sms, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+// C (M, N) = A (M, K) . B (N, K)^T + bias; A, B bf16 row-major (K contiguous), 16-byte aligned rows
+cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, GemmParams P, int out_bf16, int n_sms,
+                             cudaStream_t s) {
+    CUtensorMap map_a, map_b;
+    if (!make_map_bf16(&map_a, a, P.M, P.K, lda, kGemmBM) || !make_map_bf16(&map_b, b, P.N, P.K, ldb, kGemmBN))
+        return cudaErrorInvalidValue;
+    const long long tiles = ((P.M + kGemmBM - 1) / kGemmBM) * ((P.N + kGemmBN - 1) / kGemmBN);
+    const int grid = static_cast<int>(tiles < n_sms ? tiles : n_sms);
+    const size_t elem = out_bf16 ? 2 : 4;
+    P.vec_ok = (reinterpret_cast<uintptr_t>(P.c) % 32 == 0 && (P.ldc * elem) % 32 == 0) ? 1 : 0;
+    cudaError_t e;
+    if (out_bf16) {
+        e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGemmSmemBytes));
+        if (e != cudaSuccess) return e;
+        gemm_bf16_tma_kernel<1><<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
+    } else {
+        e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGemmSmemBytes));
+        if (e != cudaSuccess) return e;
+        gemm_bf16_tma_kernel<0><<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace de

@@ -90,6 +90,58 @@ def mlp_head_backward(x: torch.Tensor, grad_y: torch.Tensor, w1_bf16: torch.Tens
     return gx, gw1.view(hidden, in_dim), gb1, gg, gbeta, gw2.view(hidden, hidden), gb2
 
 
+def projection_supported(in_dim: int, hidden: int, out_dim: int) -> bool:
+    return bool(_lib.load().de_projection_supported(int(in_dim), int(hidden), int(out_dim)))
+
+
+def gemm_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, out_dtype=torch.float32,
+              out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """C (M, N) = A (M, K) @ B (N, K)^T + bias with the TMA / tcgen05 GEMM kernel (csrc/proj_kernels.cu); A, B bf16."""
+    _require_cuda(a, "a")
+    _require_cuda(b, "b")
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.dim() != 2 or b.dim() != 2 or a.shape[1] != b.shape[1]:
+        raise TypeError("gemm_bf16 expects bf16 matrices A (M, K), B (N, K)")
+    if a.stride(1) != 1 or a.stride(0) % 8 or a.data_ptr() % 16:
+        a = a.contiguous()
+    if b.stride(1) != 1 or b.stride(0) % 8 or b.data_ptr() % 16:
+        b = b.contiguous()
+    m, k = a.shape
+    n = b.shape[0]
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    code = {torch.float32: _lib.DE_F32, torch.bfloat16: _lib.DE_BF16}[out.dtype]
+    if m:
+        with torch.cuda.device(a.device):
+            rc = _lib.load().de_gemm_bf16(_ptr(a), a.stride(0), _ptr(b), b.stride(0), m, n, k,
+                                          _ptr(bias.float().contiguous() if bias is not None else None), _ptr(out),
+                                          out.stride(0), code, _stream_ptr(a.device))
+        _lib.check(rc, "de_gemm_bf16")
+    return out
+
+
+def projection_forward(x: torch.Tensor, w1_bf16: torch.Tensor, b1: torch.Tensor, ln_gamma: torch.Tensor,
+                       ln_beta: torch.Tensor, ln_eps: float, w2_bf16: torch.Tensor, b2: Optional[torch.Tensor],
+                       want_stats: bool = False):
+    """x (n, in_dim) fp32 -> (y (n, out) fp32, hidden (n, H) bf16 = GELU(LN(W1 x + b1)), stats (n, 2) | None)."""
+    _require_cuda(x, "x")
+    if x.dim() != 2 or x.dtype != torch.float32:
+        raise TypeError("x must be a 2-D float32 tensor")
+    if x.stride(1) != 1 or x.stride(0) % 4 or x.data_ptr() % 16:
+        x = x.contiguous()
+    n, in_dim = x.shape
+    hidden, out_dim = w1_bf16.shape[0], w2_bf16.shape[0]
+    y = torch.empty((n, out_dim), dtype=torch.float32, device=x.device)
+    hid = torch.empty((n, hidden), dtype=torch.bfloat16, device=x.device)
+    stats = torch.empty((n, 2), dtype=torch.float32, device=x.device) if want_stats else None
+    if n:
+        with torch.cuda.device(x.device):
+            rc = _lib.load().de_projection_forward(
+                _ptr(x), n, in_dim, x.stride(0), _ptr(w1_bf16), _ptr(b1), _ptr(ln_gamma), _ptr(ln_beta), float(ln_eps),
+                _ptr(w2_bf16), _ptr(b2), hidden, out_dim, _ptr(hid), _ptr(stats), _ptr(y), y.stride(0), _stream_ptr(x.device))
+        _lib.check(rc, "de_projection_forward")
+    return y, hid, stats
+
+
 # token -> (data_ptr, W) of a gradient buffer the head backward wrote group-major; consumed (popped) by
 # functional.Grid4DFunction.backward of the same Grid4DEncoder.forward call.  The features tensor between the two
 # autograd nodes is internal to that call, so the gradient reaches the consumer as the very buffer written here;
@@ -113,7 +165,7 @@ class _HeadFunction(torch.autograd.Function):
         (x,) = ctx.saved_tensors
         head = ctx.head
         params = list(head.seq.parameters())
-        if head.fused_backward:
+        if head.fused_backward and not head.wide:
             W = ctx.grouped[1] if (ctx.grouped and ctx.needs_input_grad[0]) else 0
             by_id = head.backward_fused(x, grad_y, group_width=W)
             gx = by_id.pop("x") if ctx.needs_input_grad[0] else None
@@ -160,8 +212,15 @@ class FusedProjection:
         self._key = None
         self._w1 = self._w2 = self._w1t = self._w2t = None
         self._grouped_next = None
+        # hidden widths other than 64 (768 by default, 2048 in the integrated model) take the two-kernel path of
+        # csrc/proj_kernels.cu; it needs the full Linear-LayerNorm-GELU-Linear structure with biases
+        self.wide = (self.lin1.out_features != 64 and self.norm is not None and self.activation == "gelu"
+                     and self.norm.elementwise_affine and self.lin1.bias is not None
+                     and self.lin2.in_features == self.lin1.out_features)
 
     def supported(self) -> bool:
+        if self.wide:
+            return projection_supported(self.lin1.in_features, self.lin1.out_features, self.lin2.out_features)
         return mlp_head_supported(self.lin1.in_features, self.lin1.out_features, self.lin2.out_features)
 
     def _weights(self):
@@ -196,6 +255,8 @@ class FusedProjection:
     def fused(self, x: torch.Tensor) -> torch.Tensor:
         w1, w2 = self._weights()
         n = self.norm
+        if self.wide:
+            return projection_forward(x, w1, self.lin1.bias, n.weight, n.bias, n.eps, w2, self.lin2.bias)[0]
         return mlp_head_forward(x, w1, self.lin1.bias, n.weight if n is not None else None,
                                 n.bias if n is not None else None, n.eps if n is not None else 1e-5,
                                 n is not None, self.activation, w2, self.lin2.bias)

@@ -48,6 +48,7 @@ extern "C" {
 #define DE_F16 1
 #define DE_F64 2
 #define DE_I32 3
+#define DE_BF16 4
 
 /* flags */
 #define DE_INTERP_NEAREST 0u /* floor cell only: models/hash_encoding.py:57-72     */
@@ -241,6 +242,27 @@ DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_p
                          int layernorm, int activation, int hidden, int out_dim,
                          float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1,
                          float* grad_gamma, float* grad_beta, float* grad_w2, float* grad_b2, void* stream);
+
+/*
+ * The projection at its real width -- replaces Grid4DEncoder.projection (models/encoders.py:47-52) for hidden_dim = 768
+ * (models/configs.py:44), 2048 (models/deepearth_integrated.py:69-74) or any multiple of 128:
+ *   a = GELU( LN( W1 x + b1 ) )   one tcgen05 kernel: x (n, in_dim) fp32 read once, a (n, hidden) bf16 written once; the
+ *                                 first Linear runs twice per 128-row tile in 128-column TMEM chunks (pass 1 = LayerNorm
+ *                                 statistics, pass 2 = normalise + GELU), so the pre-activation never exists in memory;
+ *   y = W2 a + b2                 persistent TMA (cp.async.bulk.tensor, 128 B swizzle) + tcgen05.mma GEMM, 128 x 256 tiles,
+ *                                 double-buffered TMEM accumulators, fp32 output.
+ * in_dim in {32, 48, 64, 96, 128}; out_dim a multiple of 8.  w1_bf16 (hidden, in_dim), w2_bf16 (out_dim, hidden): bf16 in
+ * nn.Linear.weight layout.  hidden_bf16: (n, hidden) bf16 device buffer (the activations the backward needs);
+ * row_stats: optional (n, 2) fp32 {mean, rstd} of the pre-LayerNorm rows.
+ */
+DE_API int de_projection_supported(int in_dim, int hidden, int out_dim);
+DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, int64_t x_stride,
+                          const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
+                          const void* w2_bf16, const float* b2, int hidden, int out_dim,
+                          void* hidden_bf16, float* row_stats, float* y, int64_t y_stride, void* stream);
+/* C (M, N) fp32 or bf16 (out_dtype DE_F32 / DE_BF16) = A (M, K) . B (N, K)^T + bias: the GEMM kernel on its own (tests, bench). */
+DE_API int de_gemm_bf16(const void* a_bf16, int64_t lda, const void* b_bf16, int64_t ldb, int64_t m, int n, int k,
+                 const float* bias, void* c, int64_t ldc, int out_dtype, void* stream);
 
 /*
  * Device-wide L2 fetch granularity hint (cudaLimitMaxL2FetchGranularity) of the current device: 32, 64 or

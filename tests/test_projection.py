@@ -1,0 +1,82 @@
+"""The projection at its real width (models/encoders.py:47-52, hidden_dim 768 / 2048): the
+TMA + tcgen05 GEMM kernel on its own, and the two-kernel forward against the fp32 nn.Sequential."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 256, 64), (1000, 768, 768), (4096 + 17, 768, 768), (300, 200, 72), (257, 2048, 2048),
+                                   (64, 8, 128)])
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_gemm_bf16_vs_torch(dev, m, n, k, out_dtype):
+    """C = A B^T + bias: bf16 operands are exact in the products, so an fp64 product of the SAME bf16 values differs
+    only by the kernel's fp32 accumulation (<= 2e-6 of max|C| per K = 2048) and, for bf16 output, the final rounding."""
+    from deepearth_b200.mlp_head import gemm_bf16
+    g = torch.Generator(device=dev).manual_seed(m * 7 + n)
+    a = torch.randn((m, k), device=dev, generator=g).to(torch.bfloat16)
+    b = torch.randn((n, k), device=dev, generator=g).to(torch.bfloat16)
+    bias = torch.randn(n, device=dev, generator=g)
+    c = gemm_bf16(a, b, bias, out_dtype=out_dtype)
+    want = a.double() @ b.double().t() + bias.double()
+    tol = 2e-5 if out_dtype == torch.float32 else 6e-3
+    err = float((c.double() - want).abs().max()) / float(want.abs().max())
+    assert err <= tol, err
+    c2 = gemm_bf16(a, b, None, out_dtype=out_dtype)
+    err2 = float((c2.double() - (want - bias.double())).abs().max()) / float(want.abs().max())
+    assert err2 <= tol, err2
+
+
+def same_rounding_reference(seq, x):
+    """fp64 evaluation with the kernel's roundings: bf16 x, W1, W2 and bf16 hidden activations."""
+    lin1, ln, _, lin2 = seq
+    bf = lambda t: t.detach().to(torch.bfloat16).double()      # noqa: E731
+    h = bf(x) @ bf(lin1.weight).t() + lin1.bias.double()
+    mu = h.mean(-1, keepdim=True)
+    var = ((h - mu) ** 2).mean(-1, keepdim=True)
+    v = (h - mu) / torch.sqrt(var + ln.eps) * ln.weight.double() + ln.bias.double()
+    a = torch.nn.functional.gelu(v)
+    return bf(a.float()) @ bf(lin2.weight).t() + lin2.bias.double(), a
+
+
+@pytest.mark.parametrize("in_dim,hidden,n", [(48, 768, 1000), (128, 768, 4096 + 5), (128, 2048, 513), (64, 128, 130), (32, 256, 1)])
+def test_projection_forward_vs_nn_sequential(dev, in_dim, hidden, n):
+    import torch.nn as nn
+    from deepearth_b200.mlp_head import FusedProjection, projection_forward
+    torch.manual_seed(hidden + in_dim)
+    seq = nn.Sequential(nn.Linear(in_dim, hidden), nn.LayerNorm(hidden), nn.GELU(), nn.Linear(hidden, hidden)).to(dev)
+    with torch.no_grad():
+        seq[1].weight.uniform_(0.5, 1.5)
+        seq[1].bias.uniform_(-0.5, 0.5)
+        seq[0].bias.uniform_(-1.0, 1.0)
+    g = torch.Generator(device=dev).manual_seed(n)
+    x = torch.randn((n, in_dim), device=dev, generator=g) * 2.0 + 0.3
+    fp = FusedProjection(seq)
+    assert fp.wide and fp.supported()
+    w1, w2 = fp._weights()
+    y, hid, stats = projection_forward(x, w1, seq[0].bias, seq[1].weight, seq[1].bias, seq[1].eps, w2, seq[3].bias, want_stats=True)
+    want_same, act = same_rounding_reference(seq, x)
+    scale = float(want_same.abs().max())
+    # hidden activations: bf16 rounding of the fp64 value computed from the same rounded operands (+ GELU approximation 3e-7)
+    herr = float((hid.double() - act).abs().max()) / float(act.abs().max())
+    assert herr <= 6e-3, herr
+    e_same = float((y.double() - want_same).abs().max()) / scale
+    assert e_same <= 2e-3, e_same
+    with torch.no_grad():
+        want = seq(x)
+    e_mod = float((y - want).abs().max()) / float(want.abs().max())
+    assert e_mod <= 3e-2, e_mod
+    # LayerNorm statistics of the pre-activation rows
+    h = x.to(torch.bfloat16).double() @ w1.double().t() + seq[0].bias.double()
+    assert float((stats[:, 0].double() - h.mean(-1)).abs().max()) <= 1e-4 * max(1.0, float(h.abs().max()))
+    rstd = 1.0 / torch.sqrt(h.var(-1, unbiased=False) + seq[1].eps)
+    assert float((stats[:, 1].double() / rstd - 1).abs().max()) <= 1e-4
+    assert torch.equal(fp(x), y)
+    print(f"projection K1={in_dim} H={hidden} n={n}: hidden {herr:.1e}, same-rounding {e_same:.1e}, vs fp32 module {e_mod:.1e}")
