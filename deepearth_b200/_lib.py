@@ -83,7 +83,12 @@ SIGNATURES = {
     "de_projection_supported": (c_int, [c_int, c_int, c_int]),
     "de_projection_forward": (c_int, [c_void_p, c_i64, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
                                       c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
-    "de_gemm_bf16": (c_int, [c_void_p, c_i64, c_void_p, c_i64, c_i64, c_int, c_int, c_void_p, c_void_p, c_i64, c_int, c_void_p]),
+    "de_projection_backward_workspace_bytes": (ctypes.c_size_t, [c_i64, c_int, c_int, c_int]),
+    "de_projection_backward": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_i64, c_i64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_size_t, c_void_p]),
+    "de_gemm_bf16": (c_int, [c_void_p, c_i64, c_void_p, c_i64, c_i64, c_int, c_i64, c_void_p, c_void_p, c_i64, c_int, c_int, c_int,
+                             c_void_p]),
     "de_geo_bbox": (c_int, [c_void_p, c_int, c_void_p, c_i64, c_void_p]),
     "de_set_l2_fetch_granularity": (c_int, [c_int]),
     "de_get_l2_fetch_granularity": (c_int, [ctypes.POINTER(c_int)]),

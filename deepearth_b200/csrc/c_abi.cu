@@ -953,19 +953,22 @@ static int device_sms() {
     return n_sms;
 }
 
-DE_API int de_gemm_bf16(const void* a_bf16, int64_t lda, const void* b_bf16, int64_t ldb, int64_t m, int n, int k,
-                 const float* bias, void* c, int64_t ldc, int out_dtype, void* stream) {
-    if (m < 0 || n < 1 || k < 1) return fail(DE_EINVAL, "gemm_bf16: m=%lld n=%d k=%d", (long long)m, n, k);
+DE_API int de_gemm_bf16(const void* a_bf16, int64_t lda, const void* b_bf16, int64_t ldb, int64_t m, int n, int64_t k,
+                 const float* bias, void* c, int64_t ldc, int out_dtype, int transposed, int accumulate, void* stream) {
+    if (m < 0 || n < 1 || k < 1) return fail(DE_EINVAL, "gemm_bf16: m=%lld n=%d k=%lld", (long long)m, n, (long long)k);
     if (m == 0) return DE_OK;
     if (!a_bf16 || !b_bf16 || !c) return fail(DE_EINVAL, "gemm_bf16: NULL pointer");
     if (out_dtype != DE_F32 && out_dtype != DE_BF16) return fail(DE_EUNSUPPORTED, "gemm_bf16: out_dtype=%d", out_dtype);
+    if (accumulate && (out_dtype != DE_F32 || bias)) return fail(DE_EUNSUPPORTED, "gemm_bf16: accumulation is fp32 and takes no bias");
     if (reinterpret_cast<uintptr_t>(a_bf16) % 16 || reinterpret_cast<uintptr_t>(b_bf16) % 16 || lda % 8 || ldb % 8)
         return fail(DE_EALIGN, "gemm_bf16: operand rows must be 16-byte aligned (TMA)");
-    if (lda < k || ldb < k || ldc < n) return fail(DE_EINVAL, "gemm_bf16: leading dimension shorter than the row");
-    if (m > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "gemm_bf16: m=%lld too large", (long long)m);
+    if (transposed ? (lda < m || ldb < n) : (lda < k || ldb < k)) return fail(DE_EINVAL, "gemm_bf16: leading dimension shorter than the row");
+    if (ldc < n) return fail(DE_EINVAL, "gemm_bf16: ldc shorter than the row");
+    if (m > 0x7fffffffll || k > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "gemm_bf16: m=%lld k=%lld too large", (long long)m, (long long)k);
     de::GemmParams P{};
     P.M = m; P.N = n; P.K = k; P.c = c; P.ldc = ldc; P.bias = bias;
-    cudaError_t e = de::launch_gemm_bf16(a_bf16, lda, b_bf16, ldb, P, out_dtype == DE_BF16, device_sms(), static_cast<cudaStream_t>(stream));
+    cudaError_t e = de::launch_gemm_bf16(a_bf16, lda, b_bf16, ldb, transposed ? 1 : 0, P, accumulate ? 2 : (out_dtype == DE_BF16 ? 1 : 0),
+                                         device_sms(), static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "gemm_bf16 launch (TMA descriptor or kernel)");
 }
 
@@ -997,8 +1000,84 @@ DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, i
     if (e != cudaSuccess) return cuda_fail(e, "projection hidden launch");
     de::GemmParams G{};
     G.M = n_points; G.N = out_dim; G.K = hidden; G.c = y; G.ldc = y_stride; G.bias = b2;
-    e = de::launch_gemm_bf16(hidden_bf16, hidden, w2_bf16, hidden, G, 0, n_sms, s);
+    e = de::launch_gemm_bf16(hidden_bf16, hidden, w2_bf16, hidden, 0, G, 0, n_sms, s);
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "projection GEMM launch");
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~static_cast<size_t>(255); }
+
+DE_API size_t de_projection_backward_workspace_bytes(int64_t n_points, int in_dim, int hidden, int out_dim) {
+    if (n_points <= 0 || in_dim <= 0 || hidden <= 0 || out_dim <= 0) return 0;
+    const size_t n = static_cast<size_t>(n_points);
+    return align256(n * out_dim * 2) + align256(n * hidden * 2) + align256(n * in_dim * 2);
+}
+
+DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n_points, int in_dim, int64_t x_stride,
+                           int64_t gy_stride, const void* w1_bf16, const void* w1t_bf16, const void* w2t_bf16,
+                           const float* b1, const float* ln_gamma, const float* ln_beta, int hidden, int out_dim,
+                           const void* hidden_bf16, const float* row_stats,
+                           float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1, float* grad_gamma,
+                           float* grad_beta, float* grad_w2, float* grad_b2,
+                           void* workspace, size_t workspace_bytes, void* stream) {
+    if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (n_points == 0) return DE_OK;
+    if (!x || !grad_y || !w1_bf16 || !w1t_bf16 || !w2t_bf16 || !b1 || !ln_gamma || !ln_beta || !hidden_bf16 || !row_stats ||
+        !grad_w1 || !grad_w2 || !workspace)
+        return fail(DE_EINVAL, "projection_backward: NULL pointer");
+    if (!de_projection_supported(in_dim, hidden, out_dim)) return fail(DE_EUNSUPPORTED, "projection_backward: in_dim=%d hidden=%d out_dim=%d", in_dim, hidden, out_dim);
+    if (workspace_bytes < de_projection_backward_workspace_bytes(n_points, in_dim, hidden, out_dim))
+        return fail(DE_EINVAL, "projection_backward: workspace of %zu bytes is too small", workspace_bytes);
+    if (x_stride < in_dim || gy_stride < out_dim || (grad_x && gx_stride < in_dim)) return fail(DE_EINVAL, "projection_backward: row stride shorter than the row");
+    const void* aligned[] = {x, grad_y, w1_bf16, w1t_bf16, w2t_bf16, hidden_bf16, workspace, grad_x};
+    for (const void* q : aligned)
+        if (reinterpret_cast<uintptr_t>(q) % 16) return fail(DE_EALIGN, "projection_backward: pointer not 16-byte aligned");
+    if (x_stride % 4 || gy_stride % 4) return fail(DE_EALIGN, "projection_backward: row strides must be multiples of 4 floats");
+    if (n_points > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "projection_backward: n_points too large");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int n_sms = device_sms();
+    const size_t n = static_cast<size_t>(n_points);
+    char* ws = static_cast<char*>(workspace);
+    void* gy16 = ws;
+    void* da = ws + align256(n * out_dim * 2);
+    void* x16 = ws + align256(n * out_dim * 2) + align256(n * hidden * 2);
+    // 1. bf16 copy of grad_y, db2 = column sums
+    cudaError_t e = de::launch_cast_colsum(grad_y, gy_stride, gy16, out_dim, n_points, out_dim, grad_b2, n_sms, s);
+    if (e != cudaSuccess) return cuda_fail(e, "projection_backward: cast launch");
+    // 2. da (n, hidden) = gy (n, out) . W2 (out, hidden)
+    {
+        de::GemmParams G{};
+        G.M = n_points; G.N = hidden; G.K = out_dim; G.c = da; G.ldc = hidden;
+        e = de::launch_gemm_bf16(gy16, out_dim, w2t_bf16, out_dim, 0, G, 1, n_sms, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: da GEMM launch");
+    }
+    // 3. dpre in place of da; dgamma, dbeta, db1; bf16 copy of x
+    {
+        de::ProjDpreParams D{};
+        D.x = x; D.n = n_points; D.x_stride = x_stride; D.w1 = w1_bf16; D.b1 = b1; D.ln_gamma = ln_gamma; D.ln_beta = ln_beta;
+        D.stats = row_stats; D.dact = da; D.dact_stride = hidden; D.dpre_out = da; D.x_bf16_out = x16;
+        D.dgamma = grad_gamma; D.dbeta = grad_beta; D.db1 = grad_b1; D.hidden = hidden;
+        e = de::launch_proj_dpre(D, in_dim, n_sms, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dpre launch");
+    }
+    // 4. dW2 (out, hidden) += gy^T . a ;  5. dW1 (hidden, in) += dpre^T . x   (contraction over the points)
+    {
+        de::GemmParams G{};
+        G.M = out_dim; G.N = hidden; G.K = n_points; G.c = grad_w2; G.ldc = hidden;
+        e = de::launch_gemm_bf16(gy16, out_dim, hidden_bf16, hidden, 1, G, 2, n_sms, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dW2 GEMM launch");
+        G = de::GemmParams{};
+        G.M = hidden; G.N = in_dim; G.K = n_points; G.c = grad_w1; G.ldc = in_dim;
+        e = de::launch_gemm_bf16(da, hidden, x16, in_dim, 1, G, 2, n_sms, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dW1 GEMM launch");
+    }
+    // 6. dx (n, in) = dpre (n, hidden) . W1 (hidden, in)
+    if (grad_x) {
+        de::GemmParams G{};
+        G.M = n_points; G.N = in_dim; G.K = hidden; G.c = grad_x; G.ldc = gx_stride;
+        e = de::launch_gemm_bf16(da, hidden, w1t_bf16, hidden, 0, G, 0, n_sms, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dx GEMM launch");
+    }
+    return DE_OK;
 }
 
 DE_API int de_set_l2_fetch_granularity(int bytes) {

@@ -121,17 +121,41 @@ struct ProjHiddenParams {
     int n_tiles;
 };
 struct GemmParams {
-    long long M;                  // rows of A and C
-    int N, K;
+    long long M;                  // rows of C
+    int N;
+    long long K;                  // contraction length
+    int k_splits;                 // filled by the launcher
     void* c;                      // (M, N) fp32 or bf16, rows ldc elements apart
     long long ldc;
     const float* bias;            // (N,) or NULL
     int vec_ok;
 };
+struct ProjDpreParams {
+    const float* x;               // (n, in_dim) fp32 features (forward input)
+    long long n;
+    long long x_stride;
+    const void* w1;               // (hidden, in_dim) bf16
+    const float* b1;
+    const float* ln_gamma;
+    const float* ln_beta;
+    const float* stats;           // (n, 2) {mean, rstd} saved by the forward
+    const void* dact;             // (n, hidden) bf16: d(loss)/d(activation) = gy . W2, rows dact_stride elements apart
+    long long dact_stride;
+    void* dpre_out;               // (n, hidden) bf16 contiguous; may alias dact (each thread reads its piece before writing it)
+    void* x_bf16_out;             // (n, in_dim) bf16 copy of the features, or NULL
+    float* dgamma;                // (hidden,) accumulated; any of the three may be NULL
+    float* dbeta;
+    float* db1;
+    int hidden;
+    int n_tiles;
+};
+cudaError_t launch_proj_dpre(ProjDpreParams P, int in_dim, int n_sms, cudaStream_t s);
+cudaError_t launch_cast_colsum(const float* src, long long ld_src, void* dst_bf16, long long ld_dst, long long n_rows, int n_cols,
+                               float* colsum, int n_sms, cudaStream_t s);
 bool proj_hidden_supported(int in_dim, int hidden);
 cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaStream_t s);
-cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, GemmParams P, int out_bf16, int n_sms,
-                             cudaStream_t s);
+cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int transposed, GemmParams P, int epi,
+                             int n_sms, cudaStream_t s);
 bool mlp_head_supported(int in_dim, int hidden, int out_dim);
 cudaError_t launch_mlp_head_bwd(MlpHeadBwdParams P, int in_dim, int n_sms, cudaStream_t s);        // mlp_head_bwd2.cu
 cudaError_t launch_mlp_head(MlpHeadParams P, int in_dim, int n_sms, cudaStream_t s);

@@ -39,6 +39,13 @@ __device__ __forceinline__ constexpr uint32_t umma_idesc(int n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(kTileM >> 4) << 24);
 }
 
+// general form: M x N tile, either operand K-major (0) or MN-major (1: bits 15 / 16)
+__host__ __device__ __forceinline__ constexpr uint32_t idesc_bf16(int m, int n, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn ? (1u << 15) : 0u) | (b_mn ? (1u << 16) : 0u) |
+           (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -168,6 +175,22 @@ __device__ __forceinline__ void gelu_fwd_bwd(float z, float& a, float& g) {
     g = fmaf(z * 0.3989422804014327f, e, cdf);
 }
 
+
+// Column sums over the 32 lanes of a warp for 32 register values each: afterwards lane l holds sum_over_lanes v[l].
+// Butterfly with halving payload: 16 + 8 + 4 + 2 + 1 = 31 shuffles (a per-column butterfly would take 160).
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+    for (int w = 16; w >= 1; w >>= 1) {
+        const bool up = (lane & w) != 0;
+#pragma unroll
+        for (int i = 0; i < w; ++i) {
+            const float send = up ? v[i] : v[i + w];
+            const float keep = up ? v[i + w] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+        }
+    }
+    return v[0];
+}
 
 // 2-byte element (row r, column c) of a K-major canonical tile with kt columns
 __device__ __forceinline__ uint32_t canon_elem_offset(int r, int c, int kt) {

@@ -1,0 +1,267 @@
+// proj_bwd_kernels.cu -- backward of the wide projection (proj_kernels.cu), sm_100a.
+//
+//   forward:   h = W1 x + b1;  xh = (h - mean) rstd;  v = gamma xh + beta;  a = GELU(v);  y = W2 a + b2
+//   backward:  da   = gy . W2                       TMA / tcgen05 GEMM (gemm_bf16_tma_kernel), bf16 out
+//              dv   = da * GELU'(v);  t = gamma dv
+//              dpre = rstd (t - mean_j t - xh mean_j (t xh))              <- proj_dpre_kernel (this file)
+//              dgamma = sum_p dv xh;  dbeta = sum_p dv;  db1 = sum_p dpre  <- same kernel (warp transpose sums)
+//              dW2 = gy^T a;  dW1 = dpre^T x                              GEMMs contracting over points (split-K, fp32 red)
+//              dx  = dpre . W1                                            GEMM, fp32 out: the gradient the hash grids consume
+//              db2 = sum_p gy                                             cast_colsum_kernel (also makes the bf16 copy of gy)
+//
+// proj_dpre_kernel mirrors proj_hidden_kernel: the first Linear is recomputed in 128-column TMEM chunks, twice per tile --
+// pass 1 for the two row sums the LayerNorm backward needs (and dgamma / dbeta), pass 2 for dpre itself (and db1).  The
+// pre-activation is never stored by the forward; the saved row statistics (mean, rstd) make the recompute exact.
+#include "launch.h"
+#include "mlp_common.cuh"
+
+namespace de {
+
+using namespace mlp;
+
+// ---- gy fp32 -> bf16 copy + column sums (db2) -----------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cast_colsum_kernel(const float* __restrict__ src, long long ld_src, __nv_bfloat16* __restrict__ dst,
+                                                          long long ld_dst, long long n_rows, int n_cols, float* colsum,
+                                                          long long rows_per_cta) {
+    __shared__ float s_part[8][128];
+    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+    const int c0 = blockIdx.x * 128 + cx * 4;
+    const long long r_begin = static_cast<long long>(blockIdx.y) * rows_per_cta;
+    const long long r_end = (r_begin + rows_per_cta < n_rows) ? r_begin + rows_per_cta : n_rows;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c0 < n_cols) {                                            // n_cols is a multiple of 4
+        for (long long r = r_begin + ry; r < r_end; r += 8) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(src + r * ld_src + c0));
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            if (dst) *reinterpret_cast<uint2*>(dst + r * ld_dst + c0) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+        }
+    }
+    if (!colsum) return;
+    *reinterpret_cast<float4*>(&s_part[ry][cx * 4]) = acc;
+    __syncthreads();
+    if (threadIdx.x < 128) {
+        float a = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a += s_part[i][threadIdx.x];
+        const int c = blockIdx.x * 128 + threadIdx.x;
+        if (c < n_cols) atomicAdd(colsum + c, a);
+    }
+}
+
+cudaError_t launch_cast_colsum(const float* src, long long ld_src, void* dst_bf16, long long ld_dst, long long n_rows, int n_cols,
+                               float* colsum, int n_sms, cudaStream_t s) {
+    if (n_rows == 0) return cudaSuccess;
+    const int bx = (n_cols + 127) / 128;
+    long long by = (static_cast<long long>(n_sms) * 8 + bx - 1) / bx;
+    long long rows = (n_rows + by - 1) / by;
+    if (rows < 64) rows = 64;
+    rows = (rows + 7) / 8 * 8;
+    by = (n_rows + rows - 1) / rows;
+    cast_colsum_kernel<<<dim3(bx, static_cast<unsigned>(by)), 256, 0, s>>>(src, ld_src, static_cast<__nv_bfloat16*>(dst_bf16), ld_dst,
+                                                                         n_rows, n_cols, colsum, rows);
+    return cudaGetLastError();
+}
+
+// ---- dpre ----------------------------------------------------------------------------------------------------------------
+constexpr int kBwdChunkN = 128;
+
+// dynamic shared memory: A [128 x K1] | B[2] [128 x K1] (bf16, canonical K-major) | acc[3][H] floats (dgamma, dbeta, db1)
+template <int K1>
+__global__ void __launch_bounds__(kMlpThreads)
+proj_dpre_kernel(const __grid_constant__ ProjDpreParams P) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ uint32_t s_tmem;
+    unsigned char* sA = smem;
+    unsigned char* sB[2] = {smem + kTileM * K1 * 2, smem + kTileM * K1 * 2 + kBwdChunkN * K1 * 2};
+    const int H = P.hidden, NC = H / kBwdChunkN;
+    float* s_acc = reinterpret_cast<float*>(smem + (kTileM + 2 * kBwdChunkN) * K1 * 2);     // [3][H]
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    for (int i = tid; i < 3 * H; i += kMlpThreads) s_acc[i] = 0.0f;
+    if (tid == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(2 * kBwdChunkN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+    constexpr uint32_t kIdesc = idesc_bf16(kTileM, kBwdChunkN, false, false);
+    uint32_t phase0 = 0u, phase1 = 0u;
+    const int row = tid;
+    const __nv_bfloat16* __restrict__ w1 = static_cast<const __nv_bfloat16*>(P.w1);
+    const float inv_h = 1.0f / static_cast<float>(H);
+
+    auto stage_chunk = [&](int c, unsigned char* dst) {
+        const __nv_bfloat16* src = w1 + static_cast<size_t>(c) * kBwdChunkN * K1;
+        for (int e = tid; e < kBwdChunkN * (K1 / 8); e += kMlpThreads) {
+            const int n = e / (K1 / 8), k8 = e % (K1 / 8);
+            *reinterpret_cast<uint4*>(dst + canon_chunk_offset(n, k8, K1)) = __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(n) * K1 + k8 * 8));
+        }
+    };
+    auto issue_chunk = [&](int g) {
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB[g & 1]);
+#pragma unroll
+        for (int k = 0; k < K1 / 16; ++k)
+            umma_bf16(tmem + (g & 1) * kBwdChunkN, umma_desc(a0 + k * 256, 128, (K1 / 8) * 128), umma_desc(b0 + k * 256, 128, (K1 / 8) * 128),
+                      kIdesc, k > 0 ? 1u : 0u);
+        umma_commit(&s_bar[g & 1]);
+    };
+
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+        const long long p0 = static_cast<long long>(tile) * kTileM;
+        const int n_valid = static_cast<int>(P.n - p0 < kTileM ? P.n - p0 : kTileM);
+        const float* tile_base = P.x + p0 * P.x_stride;
+        const int xs = static_cast<int>(P.x_stride);
+        const bool a32 = ((reinterpret_cast<uintptr_t>(tile_base) | (static_cast<uintptr_t>(xs) << 2)) & 31) == 0;
+        constexpr int kIt = (4 * K1) / 32;
+        constexpr int kRound = kIt >= 2 ? kIt / 2 : kIt;
+#pragma unroll
+        for (int it0 = 0; it0 < kIt; it0 += kRound) {
+            float4 va[kRound], vb[kRound];
+#pragma unroll
+            for (int u = 0; u < kRound; ++u) {
+                const int c = lane + 32 * (it0 + u);
+                const int r = min(warp * 32 + (c / K1) * 8 + ((c % K1) & 7), n_valid - 1);
+                const int k8 = (c % K1) >> 3;
+                ld_stream_32B(tile_base + (static_cast<long long>(r) * xs + k8 * 8), va[u], vb[u], a32);
+            }
+#pragma unroll
+            for (int u = 0; u < kRound; ++u) {
+                const int c = lane + 32 * (it0 + u);
+                const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
+                const int k8 = (c % K1) >> 3;
+                const uint4 pk = make_uint4(pack_bf16(va[u].x, va[u].y), pack_bf16(va[u].z, va[u].w), pack_bf16(vb[u].x, vb[u].y), pack_bf16(vb[u].z, vb[u].w));
+                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(r, k8, K1)) = pk;
+                // bf16 copy of the features for the dW1 GEMM (the contraction over points reads it as a (points, K1) matrix)
+                if (P.x_bf16_out && r < n_valid)
+                    *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(P.x_bf16_out) + (p0 + r) * K1 + k8 * 8) = pk;
+            }
+        }
+        stage_chunk(0, sB[0]);
+        fence_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) issue_chunk(0);
+
+        const bool live = row < n_valid;
+        const float mean = live ? __ldg(P.stats + 2 * (p0 + row)) : 0.0f;
+        const float rstd = live ? __ldg(P.stats + 2 * (p0 + row) + 1) : 0.0f;
+        const __nv_bfloat16* da_row = static_cast<const __nv_bfloat16*>(P.dact) + (p0 + row) * P.dact_stride;
+        __nv_bfloat16* out_row = static_cast<__nv_bfloat16*>(P.dpre_out) + (p0 + row) * static_cast<long long>(H);
+        float s1 = 0.0f, s2 = 0.0f;                       // sum_j t_j, sum_j t_j xh_j
+
+        for (int g = 0; g < 2 * NC; ++g) {
+            const int c = g < NC ? g : g - NC;
+            if (g + 1 < 2 * NC) {
+                stage_chunk(g + 1 < NC ? g + 1 : g + 1 - NC, sB[(g + 1) & 1]);
+                fence_async_smem();
+                tc_fence_before();
+                __syncthreads();
+                if (tid == 0) issue_chunk(g + 1);
+            }
+            if (g & 1) { mbar_wait(&s_bar[1], phase1); phase1 ^= 1u; }
+            else { mbar_wait(&s_bar[0], phase0); phase0 ^= 1u; }
+            tc_fence_after();
+            const uint32_t t_base = tmem + lane_off + (g & 1) * kBwdChunkN;
+#pragma unroll 1
+            for (int q = 0; q < kBwdChunkN / 32; ++q) {
+                const int col0 = c * kBwdChunkN + q * 32;
+                uint4 dq[4];                               // 32 bf16 of d(loss)/d(activation), this row
+#pragma unroll
+                for (int u = 0; u < 4; ++u) dq[u] = live ? __ldg(reinterpret_cast<const uint4*>(da_row + col0) + u) : make_uint4(0u, 0u, 0u, 0u);
+                float v[32];
+                tmem_ld32(t_base + q * 32, v);
+                const uint32_t* dw = reinterpret_cast<const uint32_t*>(dq);
+                float dvx[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float gam = __ldg(P.ln_gamma + col0 + j);
+                    const float xh = (v[j] + __ldg(P.b1 + col0 + j) - mean) * rstd;
+                    float act, gp;
+                    gelu_fwd_bwd(fmaf(gam, xh, __ldg(P.ln_beta + col0 + j)), act, gp);
+                    const uint32_t pr = dw[j >> 1];
+                    const float da = __uint_as_float((j & 1) ? (pr & 0xffff0000u) : (pr << 16));      // bf16 -> fp32
+                    const float dv = da * gp;
+                    const float t = gam * dv;
+                    if (g < NC) {
+                        s1 += t;
+                        s2 = fmaf(t, xh, s2);
+                        v[j] = dv;                          // column sums: dbeta
+                        dvx[j] = dv * xh;                   //              dgamma
+                    } else {
+                        v[j] = rstd * (t - s1 * inv_h - xh * (s2 * inv_h));     // dpre
+                    }
+                }
+                if (g < NC) {
+                    const float sb = warp_transpose_sum(v, lane);
+                    const float sg = warp_transpose_sum(dvx, lane);
+                    atomicAdd(&s_acc[H + col0 + lane], sb);
+                    atomicAdd(&s_acc[col0 + lane], sg);
+                } else {
+                    if (live) {
+                        uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            dst[u] = make_uint4(pack_bf16(v[8 * u], v[8 * u + 1]), pack_bf16(v[8 * u + 2], v[8 * u + 3]),
+                                                pack_bf16(v[8 * u + 4], v[8 * u + 5]), pack_bf16(v[8 * u + 6], v[8 * u + 7]));
+                    }
+                    // db1 sums the bf16-ROUNDED dpre, the values the dW1 / dx GEMMs consume
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = live ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.0f;
+                    const float sd = warp_transpose_sum(v, lane);
+                    atomicAdd(&s_acc[2 * H + col0 + lane], sd);
+                }
+            }
+        }
+        tc_fence_before();
+        __syncthreads();
+    }
+    // one flush per CTA
+    for (int i = tid; i < H; i += kMlpThreads) {
+        if (P.dgamma) atomicAdd(P.dgamma + i, s_acc[i]);
+        if (P.dbeta) atomicAdd(P.dbeta + i, s_acc[H + i]);
+        if (P.db1) atomicAdd(P.db1 + i, s_acc[2 * H + i]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * kBwdChunkN) : "memory");
+}
+
+template <int K1>
+static cudaError_t launch_dpre_k(const ProjDpreParams& P, int n_sms, cudaStream_t s) {
+    const size_t smem = static_cast<size_t>(kTileM + 2 * kBwdChunkN) * K1 * 2 + static_cast<size_t>(3) * P.hidden * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(proj_dpre_kernel<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
+    if (per_sm > 2) per_sm = 2;
+    if (per_sm < 1) per_sm = 1;
+    int grid = n_sms * per_sm;
+    if (grid > P.n_tiles) grid = P.n_tiles;
+    proj_dpre_kernel<K1><<<grid, kMlpThreads, smem, s>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_proj_dpre(ProjDpreParams P, int in_dim, int n_sms, cudaStream_t s) {
+    P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
+    switch (in_dim) {
+        case 32: return launch_dpre_k<32>(P, n_sms, s);
+        case 48: return launch_dpre_k<48>(P, n_sms, s);
+        case 64: return launch_dpre_k<64>(P, n_sms, s);
+        case 96: return launch_dpre_k<96>(P, n_sms, s);
+        case 128: return launch_dpre_k<128>(P, n_sms, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace de

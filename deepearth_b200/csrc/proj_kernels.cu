@@ -35,11 +35,6 @@ namespace {
 // ---------------------------------------------------------------------------------------------------------------------
 // shared pieces
 // ---------------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ constexpr uint32_t idesc_bf16(int m, int n, bool a_mn, bool b_mn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn ? (1u << 15) : 0u) | (b_mn ? (1u << 16) : 0u) |
-           (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
-}
-
 // K-major SWIZZLE_128B operand: start address, LBO (unused for swizzled K-major: 1), SBO = 1024 B between 8-row atoms
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
     uint64_t d = 0;
@@ -247,7 +242,10 @@ constexpr int kGemmThreads = 256;                      // warp 0 TMA, warp 1 MMA
 constexpr uint32_t kGemmStageBytes = (kGemmBM + kGemmBN) * kGemmBK * 2;
 constexpr uint32_t kGemmSmemBytes = kGemmStages * kGemmStageBytes + 1024;   // + alignment slack
 
-template <int OUT_BF16>
+// A_MN / B_MN = 1: the operand is stored with the contraction index as its ROW index ((K, M) resp. (K, N) row-major: a
+// "transposed" operand, MN-major in UMMA terms) and arrives as 64 x 64 boxes; 0: (M, K) resp. (N, K) row-major, K-major.
+// EPI 0: C fp32 = acc + bias; 1: C bf16 = acc + bias; 2: C fp32 += acc (red.global.add: split-K partial sums).
+template <int A_MN, int B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const __grid_constant__ GemmParams P) {
@@ -258,8 +256,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_n = (P.N + kGemmBN - 1) / kGemmBN;
     const long long tiles_m = (P.M + kGemmBM - 1) / kGemmBM;
-    const long long n_tiles = tiles_m * tiles_n;
-    const int k_blocks = (P.K + kGemmBK - 1) / kGemmBK;
+    const int k_blocks_all = static_cast<int>((P.K + kGemmBK - 1) / kGemmBK);
+    const int kb_per = (k_blocks_all + P.k_splits - 1) / P.k_splits;          // host guarantees every split is non-empty
+    const long long n_tiles = tiles_m * tiles_n * P.k_splits;                  // work items: (output tile, K split)
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kGemmStages; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 1); }
@@ -282,39 +281,58 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
         int stage = 0;
         uint32_t phase = 0;
-        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (long long work = blockIdx.x; work < n_tiles; work += gridDim.x) {
+            const long long tile = work / P.k_splits;
+            const int split = static_cast<int>(work - tile * P.k_splits);
             const int m0 = static_cast<int>(tile / tiles_n) * kGemmBM, n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
-            for (int kb = 0; kb < k_blocks; ++kb) {
+            const int kb_end = min(k_blocks_all, (split + 1) * kb_per);
+            for (int kb = split * kb_per; kb < kb_end; ++kb) {
                 mbar_wait(&s_empty[stage], phase ^ 1u);
                 unsigned char* sa = smem + stage * kGemmStageBytes;
                 unsigned char* sb = sa + kGemmBM * kGemmBK * 2;
                 mbar_expect_tx(&s_full[stage], kGemmStageBytes);
-                tma_load_2d(sa, &map_a, kb * kGemmBK, m0, &s_full[stage]);
-                tma_load_2d(sb, &map_b, kb * kGemmBK, n0, &s_full[stage]);
+                if constexpr (A_MN) {
+#pragma unroll
+                    for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d(sa + i * 8192, &map_a, m0 + 64 * i, kb * kGemmBK, &s_full[stage]);
+                } else {
+                    tma_load_2d(sa, &map_a, kb * kGemmBK, m0, &s_full[stage]);
+                }
+                if constexpr (B_MN) {
+#pragma unroll
+                    for (int i = 0; i < kGemmBN / 64; ++i) tma_load_2d(sb + i * 8192, &map_b, n0 + 64 * i, kb * kGemmBK, &s_full[stage]);
+                } else {
+                    tma_load_2d(sb, &map_b, kb * kGemmBK, n0, &s_full[stage]);
+                }
                 if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == 1 && lane == 0) {
         // ===== MMA issuer =====
-        constexpr uint32_t kIdesc = idesc_bf16(kGemmBM, kGemmBN, false, false);
+        constexpr uint32_t kIdesc = idesc_bf16(kGemmBM, kGemmBN, A_MN != 0, B_MN != 0);
         int stage = 0;
         uint32_t phase = 0;
         int as = 0;
         uint32_t aphase = 0;
-        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (long long work = blockIdx.x; work < n_tiles; work += gridDim.x) {
+            const int split = static_cast<int>(work % P.k_splits);
+            const int kb_begin = split * kb_per, kb_end = min(k_blocks_all, (split + 1) * kb_per);
             mbar_wait(&s_tempty[as], aphase ^ 1u);                  // epilogue has drained this accumulator
             tc_fence_after();
-            for (int kb = 0; kb < k_blocks; ++kb) {
+            for (int kb = kb_begin; kb < kb_end; ++kb) {
                 mbar_wait(&s_full[stage], phase);
                 tc_fence_after();
                 const uint32_t a0 = smem_u32(smem + stage * kGemmStageBytes);
                 const uint32_t b0 = a0 + kGemmBM * kGemmBK * 2;
 #pragma unroll
-                for (int k = 0; k < kGemmBK / 16; ++k)
-                    umma_bf16(tmem + as * kGemmBN, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(b0 + k * 32, 16, 1024),
-                              kIdesc, (kb | k) ? 1u : 0u);
+                for (int k = 0; k < kGemmBK / 16; ++k) {
+                    // K-major: 16 elements = 32 B further along the 128 B swizzled row; MN-major: 16 rows of 128 B = two
+                    // 1024 B atoms further (LBO = 8192 B between 64-wide MN blocks, SBO = 1024 B between 8-row K groups)
+                    const uint64_t da = A_MN ? umma_desc_sw128(a0 + k * 2048, 8192, 1024) : umma_desc_sw128(a0 + k * 32, 16, 1024);
+                    const uint64_t db = B_MN ? umma_desc_sw128(b0 + k * 2048, 8192, 1024) : umma_desc_sw128(b0 + k * 32, 16, 1024);
+                    umma_bf16(tmem + as * kGemmBN, da, db, kIdesc, (kb > kb_begin || k) ? 1u : 0u);
+                }
                 umma_commit(&s_empty[stage]);                        // frees the slot when these MMAs have read it
-                if (kb == k_blocks - 1) umma_commit(&s_tfull[as]);   // accumulator complete
+                if (kb == kb_end - 1) umma_commit(&s_tfull[as]);     // accumulator complete
                 if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
             }
             if (++as == 2) { as = 0; aphase ^= 1u; }
@@ -324,7 +342,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         const int quarter = warp & 3;                                // TMEM lanes this warp may read
         int as = 0;
         uint32_t aphase = 0;
-        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (long long work = blockIdx.x; work < n_tiles; work += gridDim.x) {
+            const long long tile = work / P.k_splits;
             const long long m0 = (tile / tiles_n) * kGemmBM;
             const int n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
             mbar_wait(&s_tfull[as], aphase);
@@ -342,7 +361,19 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                     for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldg(P.bias + col0 + j) : 0.0f;
                 }
                 if (r < P.M) {
-                    if constexpr (OUT_BF16) {
+                    if constexpr (EPI == 2) {
+                        float* dst = static_cast<float*>(P.c) + r * P.ldc + col0;
+                        if (col0 + 32 <= P.N && P.vec_ok) {
+#pragma unroll
+                            for (int u = 0; u < 8; ++u)
+                                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * u), "f"(v[4 * u]), "f"(v[4 * u + 1]),
+                                             "f"(v[4 * u + 2]), "f"(v[4 * u + 3]) : "memory");
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < P.N) atomicAdd(dst + j, v[j]);
+                        }
+                    } else if constexpr (EPI == 1) {
                         __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(P.c) + r * P.ldc + col0;
                         if (col0 + 32 <= P.N && P.vec_ok) {
 #pragma unroll
@@ -401,7 +432,8 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// row-major bf16 matrix (rows, cols), leading dimension ld elements; box = {64 columns, box_rows}, 128 B swizzle
+// row-major bf16 matrix (rows, cols), leading dimension ld elements; box = {64 columns, box_rows}, 128 B swizzle.
+// K-major operand (M or N rows, K columns): box_rows = the tile's MN extent; MN-major operand (K rows, MN columns): 64.
 bool make_map_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return false;
@@ -447,27 +479,52 @@ cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaSt
     }
 }
 
-// C (M, N) = A (M, K) . B (N, K)^T + bias; A, B bf16 row-major (K contiguous), 16-byte aligned rows
-cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, GemmParams P, int out_bf16, int n_sms,
-                             cudaStream_t s) {
-    CUtensorMap map_a, map_b;
-    if (!make_map_bf16(&map_a, a, P.M, P.K, lda, kGemmBM) || !make_map_bf16(&map_b, b, P.N, P.K, ldb, kGemmBN))
-        return cudaErrorInvalidValue;
-    const long long tiles = ((P.M + kGemmBM - 1) / kGemmBM) * ((P.N + kGemmBN - 1) / kGemmBN);
-    const int grid = static_cast<int>(tiles < n_sms ? tiles : n_sms);
-    const size_t elem = out_bf16 ? 2 : 4;
-    P.vec_ok = (reinterpret_cast<uintptr_t>(P.c) % 32 == 0 && (P.ldc * elem) % 32 == 0) ? 1 : 0;
-    cudaError_t e;
-    if (out_bf16) {
-        e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGemmSmemBytes));
-        if (e != cudaSuccess) return e;
-        gemm_bf16_tma_kernel<1><<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
-    } else {
-        e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGemmSmemBytes));
-        if (e != cudaSuccess) return e;
-        gemm_bf16_tma_kernel<0><<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
-    }
+template <int A_MN, int B_MN, int EPI>
+static cudaError_t launch_gemm_t(const CUtensorMap& map_a, const CUtensorMap& map_b, const GemmParams& P, int grid, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(kGemmSmemBytes));
+    if (e != cudaSuccess) return e;
+    gemm_bf16_tma_kernel<A_MN, B_MN, EPI><<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
     return cudaGetLastError();
+}
+
+// C (M, N) = A . B^T (+ bias | accumulated).  transposed = 0: A is (M, K), B is (N, K) row-major (K contiguous);
+// transposed = 1: A is (K, M), B is (K, N) row-major -- the contraction runs over ROWS (weight gradients: K = points).
+// epi: 0 fp32 store, 1 bf16 store, 2 fp32 atomic accumulation with the K range cut into `k_splits` work items per tile.
+cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int transposed, GemmParams P, int epi,
+                             int n_sms, cudaStream_t s) {
+    CUtensorMap map_a, map_b;
+    bool ok;
+    if (transposed) ok = make_map_bf16(&map_a, a, P.K, P.M, lda, 64) && make_map_bf16(&map_b, b, P.K, P.N, ldb, 64);
+    else ok = make_map_bf16(&map_a, a, P.M, P.K, lda, kGemmBM) && make_map_bf16(&map_b, b, P.N, P.K, ldb, kGemmBN);
+    if (!ok) return cudaErrorInvalidValue;
+    const long long tiles = ((P.M + kGemmBM - 1) / kGemmBM) * ((P.N + kGemmBN - 1) / kGemmBN);
+    const long long k_blocks = (P.K + kGemmBK - 1) / kGemmBK;
+    long long splits = 1;
+    if (epi == 2) {
+        splits = (n_sms + tiles - 1) / tiles;                       // fill the machine once
+        if (splits > k_blocks) splits = k_blocks;
+        if (splits < 1) splits = 1;
+        const long long per = (k_blocks + splits - 1) / splits;
+        splits = (k_blocks + per - 1) / per;                        // every split non-empty
+    }
+    P.k_splits = static_cast<int>(splits);
+    const long long work = tiles * splits;
+    const int grid = static_cast<int>(work < n_sms ? work : n_sms);
+    const size_t elem = epi == 1 ? 2 : 4;
+    P.vec_ok = (reinterpret_cast<uintptr_t>(P.c) % 32 == 0 && (P.ldc * elem) % 32 == 0) ? 1 : 0;
+    if (transposed) {
+        switch (epi) {
+            case 0: return launch_gemm_t<1, 1, 0>(map_a, map_b, P, grid, s);
+            case 1: return launch_gemm_t<1, 1, 1>(map_a, map_b, P, grid, s);
+            default: return launch_gemm_t<1, 1, 2>(map_a, map_b, P, grid, s);
+        }
+    }
+    switch (epi) {
+        case 0: return launch_gemm_t<0, 0, 0>(map_a, map_b, P, grid, s);
+        case 1: return launch_gemm_t<0, 0, 1>(map_a, map_b, P, grid, s);
+        default: return launch_gemm_t<0, 0, 2>(map_a, map_b, P, grid, s);
+    }
 }
 
 }  // namespace de

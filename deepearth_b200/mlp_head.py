@@ -95,26 +95,29 @@ def projection_supported(in_dim: int, hidden: int, out_dim: int) -> bool:
 
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, out_dtype=torch.float32,
-              out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """C (M, N) = A (M, K) @ B (N, K)^T + bias with the TMA / tcgen05 GEMM kernel (csrc/proj_kernels.cu); A, B bf16."""
+              out: Optional[torch.Tensor] = None, transposed: bool = False, accumulate: bool = False) -> torch.Tensor:
+    """TMA / tcgen05 GEMM kernel (csrc/proj_kernels.cu), bf16 operands, fp32 accumulation.
+    transposed=False: C (M, N) = A (M, K) @ B (N, K)^T + bias;  transposed=True: C (M, N) = A (K, M)^T @ B (K, N) (the
+    contraction runs over rows).  accumulate=True adds into ``out`` (fp32), the K range split over the CTAs."""
     _require_cuda(a, "a")
     _require_cuda(b, "b")
-    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.dim() != 2 or b.dim() != 2 or a.shape[1] != b.shape[1]:
-        raise TypeError("gemm_bf16 expects bf16 matrices A (M, K), B (N, K)")
+    kd = 0 if transposed else 1
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.dim() != 2 or b.dim() != 2 or a.shape[kd] != b.shape[kd]:
+        raise TypeError("gemm_bf16 expects bf16 matrices with a common contraction extent")
     if a.stride(1) != 1 or a.stride(0) % 8 or a.data_ptr() % 16:
         a = a.contiguous()
     if b.stride(1) != 1 or b.stride(0) % 8 or b.data_ptr() % 16:
         b = b.contiguous()
-    m, k = a.shape
-    n = b.shape[0]
+    k = a.shape[kd]
+    m, n = a.shape[1 - kd], b.shape[1 - kd]
     if out is None:
-        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+        out = (torch.zeros if accumulate else torch.empty)((m, n), dtype=out_dtype, device=a.device)
     code = {torch.float32: _lib.DE_F32, torch.bfloat16: _lib.DE_BF16}[out.dtype]
-    if m:
+    if m and k:
         with torch.cuda.device(a.device):
             rc = _lib.load().de_gemm_bf16(_ptr(a), a.stride(0), _ptr(b), b.stride(0), m, n, k,
                                           _ptr(bias.float().contiguous() if bias is not None else None), _ptr(out),
-                                          out.stride(0), code, _stream_ptr(a.device))
+                                          out.stride(0), code, int(transposed), int(accumulate), _stream_ptr(a.device))
         _lib.check(rc, "de_gemm_bf16")
     return out
 
@@ -142,6 +145,37 @@ def projection_forward(x: torch.Tensor, w1_bf16: torch.Tensor, b1: torch.Tensor,
     return y, hid, stats
 
 
+def projection_backward(x, grad_y, w1_bf16, w1t_bf16, w2t_bf16, b1, ln_gamma, ln_beta, hidden_bf16, stats,
+                        want_grad_x: bool = True):
+    """Backward of ``projection_forward``: (grad_x | None, grad_w1, grad_b1, grad_gamma, grad_beta, grad_w2, grad_b2), fp32."""
+    _require_cuda(x, "x")
+    _require_cuda(grad_y, "grad_y")
+    n, in_dim = x.shape
+    hidden, out_dim = w1_bf16.shape[0], w2t_bf16.shape[1]
+    if x.stride(1) != 1 or x.stride(0) % 4 or x.data_ptr() % 16:
+        x = x.contiguous()
+    grad_y = grad_y.float()
+    if grad_y.stride(1) != 1 or grad_y.stride(0) % 4 or grad_y.data_ptr() % 16:
+        grad_y = grad_y.contiguous()
+    dev = x.device
+    gx = torch.empty((n, in_dim), dtype=torch.float32, device=dev) if want_grad_x else None
+    sizes = [hidden * in_dim, out_dim * hidden, hidden, hidden, hidden, out_dim]
+    flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+    gw1, gw2, gb1, gg, gbeta, gb2 = torch.split(flat, sizes)
+    if n:
+        lib = _lib.load()
+        ws_bytes = int(lib.de_projection_backward_workspace_bytes(n, in_dim, hidden, out_dim))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.de_projection_backward(
+                _ptr(x), _ptr(grad_y), n, in_dim, x.stride(0), grad_y.stride(0), _ptr(w1_bf16), _ptr(w1t_bf16), _ptr(w2t_bf16),
+                _ptr(b1), _ptr(ln_gamma), _ptr(ln_beta), hidden, out_dim, _ptr(hidden_bf16), _ptr(stats),
+                _ptr(gx), gx.stride(0) if gx is not None else in_dim, _ptr(gw1), _ptr(gb1), _ptr(gg), _ptr(gbeta), _ptr(gw2),
+                _ptr(gb2), _ptr(ws), ws_bytes, _stream_ptr(dev))
+        _lib.check(rc, "de_projection_backward")
+    return gx, gw1.view(hidden, in_dim), gb1, gg, gbeta, gw2.view(out_dim, hidden), gb2
+
+
 # token -> (data_ptr, W) of a gradient buffer the head backward wrote group-major; consumed (popped) by
 # functional.Grid4DFunction.backward of the same Grid4DEncoder.forward call.  The features tensor between the two
 # autograd nodes is internal to that call, so the gradient reaches the consumer as the very buffer written here;
@@ -157,14 +191,23 @@ class _HeadFunction(torch.autograd.Function):
         ctx.head = head
         ctx.grouped = head._grouped_next     # (token, W) set by Grid4DEncoder.forward for this call, or None
         head._grouped_next = None
+        if head.wide and head.fused_backward:
+            y, hid, stats = head.fused_wide(x, want_stats=True)
+            ctx.save_for_backward(x, hid, stats)        # the bf16 activations and the LayerNorm row statistics
+            return y
         ctx.save_for_backward(x)
         return head.fused(x)
 
     @staticmethod
     def backward(ctx, grad_y):
-        (x,) = ctx.saved_tensors
+        x = ctx.saved_tensors[0]
         head = ctx.head
         params = list(head.seq.parameters())
+        if head.fused_backward and head.wide and len(ctx.saved_tensors) == 3:
+            by_id = head.backward_wide(x, ctx.saved_tensors[1], ctx.saved_tensors[2], grad_y, ctx.needs_input_grad[0])
+            gx = by_id.pop("x")
+            gp = [by_id.get(id(p)) if ctx.needs_input_grad[2 + i] else None for i, p in enumerate(params)]
+            return (gx, None, *gp)
         if head.fused_backward and not head.wide:
             W = ctx.grouped[1] if (ctx.grouped and ctx.needs_input_grad[0]) else 0
             by_id = head.backward_fused(x, grad_y, group_width=W)
@@ -250,6 +293,23 @@ class FusedProjection:
         if n is not None and n.weight is not None:
             out[id(n.weight)] = gg
             out[id(n.bias)] = gbeta
+        return out
+
+    def fused_wide(self, x: torch.Tensor, want_stats: bool = False):
+        w1, w2 = self._weights()
+        n = self.norm
+        return projection_forward(x, w1, self.lin1.bias, n.weight, n.bias, n.eps, w2, self.lin2.bias, want_stats=want_stats)
+
+    def backward_wide(self, x, hid, stats, grad_y, want_grad_x: bool = True) -> dict:
+        """Gradients of the wide projection by the tcgen05 kernels (csrc/proj_bwd_kernels.cu), keyed by id(parameter) (+ "x")."""
+        w1, _ = self._weights()
+        n = self.norm
+        gx, gw1, gb1, gg, gbeta, gw2, gb2 = projection_backward(x, grad_y, w1, self._w1t, self._w2t, self.lin1.bias, n.weight,
+                                                               n.bias, hid, stats, want_grad_x)
+        out = {"x": gx, id(self.lin1.weight): gw1, id(self.lin2.weight): gw2, id(self.lin1.bias): gb1,
+               id(n.weight): gg, id(n.bias): gbeta}
+        if self.lin2.bias is not None:
+            out[id(self.lin2.bias)] = gb2
         return out
 
     def fused(self, x: torch.Tensor) -> torch.Tensor:

@@ -260,9 +260,33 @@ DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, i
                           const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
                           const void* w2_bf16, const float* b2, int hidden, int out_dim,
                           void* hidden_bf16, float* row_stats, float* y, int64_t y_stride, void* stream);
-/* C (M, N) fp32 or bf16 (out_dtype DE_F32 / DE_BF16) = A (M, K) . B (N, K)^T + bias: the GEMM kernel on its own (tests, bench). */
-DE_API int de_gemm_bf16(const void* a_bf16, int64_t lda, const void* b_bf16, int64_t ldb, int64_t m, int n, int k,
-                 const float* bias, void* c, int64_t ldc, int out_dtype, void* stream);
+/*
+ * Backward of de_projection_forward -- replaces autograd's AddmmBackward / GeluBackward / NativeLayerNormBackward chain for
+ * models/encoders.py:47-52 at hidden_dim 768 / 2048.  grad_x (n, in_dim) fp32 is the gradient the hash grids consume; the
+ * parameter gradients are ACCUMULATED (caller zeroes them; any but the two weight gradients may be NULL).
+ * w1t_bf16 = W1 transposed (in_dim, hidden), w2t_bf16 = W2 transposed (hidden, out_dim); hidden_bf16 / row_stats are what the
+ * forward wrote.  workspace: de_projection_backward_workspace_bytes() bytes, 16-byte aligned (bf16 copies of grad_y and x, and
+ * d(loss)/d(activation), overwritten in place by d(loss)/d(pre-activation)).
+ * Kernels: cast + column sums (db2), GEMM da = gy W2, proj_dpre_kernel (GELU' and LayerNorm backward with the first Linear
+ * recomputed in tensor memory; dgamma, dbeta, db1), two split-K GEMMs over the points (dW2, dW1), GEMM dx = dpre W1.
+ */
+DE_API size_t de_projection_backward_workspace_bytes(int64_t n_points, int in_dim, int hidden, int out_dim);
+DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n_points, int in_dim, int64_t x_stride,
+                           int64_t gy_stride, const void* w1_bf16, const void* w1t_bf16, const void* w2t_bf16,
+                           const float* b1, const float* ln_gamma, const float* ln_beta, int hidden, int out_dim,
+                           const void* hidden_bf16, const float* row_stats,
+                           float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1, float* grad_gamma,
+                           float* grad_beta, float* grad_w2, float* grad_b2,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * The GEMM kernel on its own: C (M, N) = A . B^T + bias, bf16 operands, fp32 accumulation in tensor memory.
+ *   transposed = 0: A (M, K), B (N, K) row-major (K contiguous: nn.Linear layout);
+ *   transposed = 1: A (K, M), B (K, N) row-major -- the contraction runs over rows (weight gradients, K = points);
+ *   out_dtype DE_F32 / DE_BF16; accumulate = 1: C (fp32) += product, the K range split over CTAs (red.global.add).
+ */
+DE_API int de_gemm_bf16(const void* a_bf16, int64_t lda, const void* b_bf16, int64_t ldb, int64_t m, int n, int64_t k,
+                 const float* bias, void* c, int64_t ldc, int out_dtype, int transposed, int accumulate, void* stream);
 
 /*
  * Device-wide L2 fetch granularity hint (cudaLimitMaxL2FetchGranularity) of the current device: 32, 64 or

@@ -80,3 +80,88 @@ def test_projection_forward_vs_nn_sequential(dev, in_dim, hidden, n):
     assert float((stats[:, 1].double() / rstd - 1).abs().max()) <= 1e-4
     assert torch.equal(fp(x), y)
     print(f"projection K1={in_dim} H={hidden} n={n}: hidden {herr:.1e}, same-rounding {e_same:.1e}, vs fp32 module {e_mod:.1e}")
+
+
+@pytest.mark.parametrize("m,n,k", [(768, 768, 4096), (256, 128, 1000), (768, 48, 64 * 37 + 5), (130, 250, 70000)])
+def test_gemm_bf16_transposed_accumulate_vs_torch(dev, m, n, k):
+    """Weight-gradient form: C (M, N) += A (K, M)^T B (K, N), the contraction (points) split over the CTAs."""
+    from deepearth_b200.mlp_head import gemm_bf16
+    g = torch.Generator(device=dev).manual_seed(k)
+    a = torch.randn((k, m), device=dev, generator=g).to(torch.bfloat16)
+    b = torch.randn((k, n), device=dev, generator=g).to(torch.bfloat16)
+    want = a.double().t() @ b.double()
+    c = gemm_bf16(a, b, transposed=True, accumulate=True)
+    err = float((c.double() - want).abs().max()) / float(want.abs().max())
+    assert err <= 2e-5, err
+    c = gemm_bf16(a, b, transposed=True, accumulate=True, out=c)            # accumulates on top
+    err = float((c.double() - 2 * want).abs().max()) / float(want.abs().max())
+    assert err <= 4e-5, err
+    c1 = gemm_bf16(a, b, transposed=True)                                   # plain store, one K range
+    assert float((c1.double() - want).abs().max()) / float(want.abs().max()) <= 2e-5
+
+
+@pytest.mark.parametrize("in_dim,hidden,n", [(48, 768, 1000), (128, 768, 2048 + 5), (128, 2048, 300), (64, 128, 130)])
+def test_projection_backward_vs_autograd(dev, in_dim, hidden, n):
+    """Gradients against autograd through an fp32 evaluation that shares the kernel's operand roundings (bf16 x, W1, W2;
+    straight-through at the roundings).  The kernel additionally rounds the hidden activations, grad_y, da and dpre to
+    bf16 (2^-9 relative each): bounds are printed and set at ~2x what a B200 measures."""
+    import torch.nn as nn
+    from deepearth_b200.mlp_head import FusedProjection
+    torch.manual_seed(hidden * 3 + in_dim)
+    seq = nn.Sequential(nn.Linear(in_dim, hidden), nn.LayerNorm(hidden), nn.GELU(), nn.Linear(hidden, hidden)).to(dev)
+    with torch.no_grad():
+        seq[1].weight.uniform_(0.5, 1.5)
+        seq[1].bias.uniform_(-0.5, 0.5)
+    g = torch.Generator(device=dev).manual_seed(n + 1)
+    x = (torch.randn((n, in_dim), device=dev, generator=g) * 1.5).requires_grad_(True)
+    gy = torch.randn((n, hidden), device=dev, generator=g)
+    fp = FusedProjection(seq)
+    assert fp.wide and fp.supported() and fp.fused_backward
+    y = fp(x)
+    y.backward(gy)
+    got = {"x": x.grad.clone()}
+    got.update({name: p.grad.clone() for name, p in seq.named_parameters()})
+    x.grad = None
+    seq.zero_grad(set_to_none=True)
+
+    def ste_bf16(t):
+        return t + (t.to(torch.bfloat16).float() - t).detach()
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        h = torch.nn.functional.linear(ste_bf16(x), ste_bf16(seq[0].weight), seq[0].bias)
+        a = torch.nn.functional.gelu(seq[1](h))
+        y_ref = torch.nn.functional.linear(ste_bf16(a), ste_bf16(seq[3].weight), seq[3].bias)
+        y_ref.backward(gy)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    want = {"x": x.grad}
+    want.update({name: p.grad for name, p in seq.named_parameters()})
+    worst = {}
+    for k in want:
+        worst[k] = float((got[k] - want[k]).abs().max()) / max(float(want[k].abs().max()), 1e-30)
+    print(f"projection backward K1={in_dim} H={hidden} n={n}:", {k: f"{v:.1e}" for k, v in worst.items()})
+    for k, v in worst.items():
+        assert v <= 2e-2, (k, v)
+
+
+def test_grid4d_encoder_default_width_runs_on_our_kernels(dev):
+    """Grid4DEncoder(config) with the reference's default hidden_dim = 768 (models/configs.py:44) and grid4d_fused_head:
+    forward + backward through the wide projection kernels, checked against the fp32 nn.Sequential on the same features."""
+    import deepearth_b200 as de
+    torch.manual_seed(0)
+    cfg = de.DeepEarthConfig(hash_table_size=2 ** 14, grid4d_fused_head=True)
+    assert cfg.hidden_dim == 768
+    enc = de.Grid4DEncoder(cfg).to(dev)
+    with torch.no_grad():
+        for e in enc._encoders:
+            for t in e.hash_tables:
+                t.weight.uniform_(-1.0, 1.0)
+    xyzt = torch.rand((3000, 4), device=dev)
+    out = enc(xyzt)
+    assert enc._fused_head and enc._fused_head.wide
+    with torch.no_grad():
+        want = enc.projection(enc.encode_features(xyzt))
+    assert float((out - want).abs().max()) <= 3e-2 * float(want.abs().max())
+    out.sum().backward()
+    assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in enc.parameters())
