@@ -56,7 +56,10 @@ class DeepEarthConfig:
     grid4d_table_dtype: str = "float32"     # "float32" | "float16" working tables (fp32 masters kept)
     grid4d_table_scale: Optional[float] = None   # power-of-two scale of fp16 tables (None -> auto)
     grid4d_dense_fallback: Optional[bool] = None  # None -> on in decomposed mode
-    grid4d_fused_head: bool = False         # hidden_dim = 64: projection as one bf16 tcgen05 kernel (mlp_head.cu)
+    grid4d_fused_head: Optional[bool] = None  # projection on tcgen05 kernels (bf16 operands, fp32 accumulate).  None = auto:
+                                              # on for the widths the reference uses (hidden_dim a multiple of 128: 768,
+                                              # 2048 -> csrc/proj_kernels.cu), off otherwise; True also takes the 64-wide
+                                              # one-kernel head (csrc/mlp_head.cu); False = the fp32 nn.Sequential
     spacetime_resolutions: List[int] = None  # resolutions of the xyt/yzt/xzt grids (decomposed mode)
 
     def __post_init__(self):

@@ -204,10 +204,20 @@ class Grid4DEncoder(nn.Module):
                 enc._work_key = None          # a stand-alone call of one grid re-derives its own key
         return ptrs
 
+    def _head_wanted(self) -> bool:
+        """config.grid4d_fused_head: True = tcgen05 kernels whenever the shape is supported; None (default) = for the wide
+        projection the reference ships (hidden_dim a multiple of 128: 768, 2048); False = the fp32 nn.Sequential."""
+        want = getattr(self.config, "grid4d_fused_head", None)
+        if want is None:
+            return self.config.hidden_dim % 128 == 0
+        return bool(want)
+
     def _project(self, feats: torch.Tensor) -> torch.Tensor:
-        # opt-in (config.grid4d_fused_head = True): a hidden_dim = 64 head runs as one bf16 tcgen05 kernel
-        # (csrc/mlp_head.cu); the default and every other width is the reference's fp32 nn.Sequential (cuBLAS)
-        if not _cfg(self.config, "grid4d_fused_head", False) or torch.is_autocast_enabled():
+        # The projection runs on our tcgen05 kernels (bf16 operands, fp32 accumulation): csrc/proj_kernels.cu for the
+        # reference's widths, csrc/mlp_head.cu at hidden_dim = 64 (opt-in).  Unsupported shapes and
+        # grid4d_fused_head=False use the reference's fp32 nn.Sequential.  Under autocast the 64-wide head falls back (its
+        # autograd hand-off is fp32-only); the wide path runs as is and returns the autocast dtype, as nn.Linear would.
+        if not self._head_wanted():
             return self.projection(feats)
         if self._fused_head is None:
             try:
@@ -215,7 +225,16 @@ class Grid4DEncoder(nn.Module):
                 self._fused_head = fp if fp.supported() else False
             except TypeError:
                 self._fused_head = False
-        return self._fused_head(feats) if self._fused_head else self.projection(feats)
+        head = self._fused_head
+        if not head:
+            return self.projection(feats)
+        if torch.is_autocast_enabled():
+            if not head.wide:
+                return self.projection(feats)
+            with torch.autocast(device_type="cuda", enabled=False):
+                y = head(feats.float())
+            return y.to(torch.get_autocast_dtype("cuda"))
+        return head(feats)
 
     def forward(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,
                 temporal_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -233,11 +252,11 @@ class Grid4DEncoder(nn.Module):
         would first regroup.  The features tensor never leaves forward(), so its gradient has exactly one producer
         and one consumer; both sides share a per-call token."""
         head = self._fused_head
-        if head is None and _cfg(self.config, "grid4d_fused_head", False) and not torch.is_autocast_enabled():
+        if head is None and self._head_wanted() and not torch.is_autocast_enabled():
             self._project(feats[:0])                       # resolves self._fused_head
             head = self._fused_head
         fn = feats.grad_fn
-        if not head or not getattr(head, "fused_backward", False) or fn is None:
+        if not head or head.wide or not getattr(head, "fused_backward", False) or fn is None:
             return False
         if torch.is_autocast_enabled() or not hasattr(fn, "plan") or feats.shape[0] < (1 << 20):
             return False
