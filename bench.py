@@ -502,6 +502,75 @@ def st_embed_bench(device, n_tokens=1 << 16, dim=512):
                     "residual in one streaming pass (tokens read + out written = the streamed bytes), temporal MLP as an fp32 tile GEMM"}
 
 
+def projection_bench(device, log2_points=20, in_dim=128, hidden=768):
+    """Grid4DEncoder.projection at the reference's default width (models/configs.py:44) on the tcgen05 kernels,
+    forward + backward over 2^20 feature rows, beside the same nn.Sequential through cuBLAS (fp32, and bf16 autocast).
+    The GEMM fraction is the second Linear alone (2 n H^2 flop) against the measured dense bf16 peak."""
+    import torch.nn as nn
+    from deepearth_b200.mlp_head import FusedProjection, gemm_bf16
+    n = 2 ** log2_points
+    torch.manual_seed(11)
+    seq = nn.Sequential(nn.Linear(in_dim, hidden), nn.LayerNorm(hidden), nn.GELU(), nn.Linear(hidden, hidden)).to(device)
+    g = torch.Generator(device=device).manual_seed(5)
+    x = torch.randn((n, in_dim), device=device, generator=g).requires_grad_(True)
+    gy = torch.randn((n, hidden), device=device, generator=g)
+    fp = FusedProjection(seq)
+    assert fp.wide and fp.supported()
+
+    def ours():
+        x.grad = None
+        seq.zero_grad(set_to_none=True)
+        fp(x).backward(gy)
+
+    def torch_fp32():
+        x.grad = None
+        seq.zero_grad(set_to_none=True)
+        seq(x).backward(gy)
+
+    def torch_amp():
+        x.grad = None
+        seq.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            y = seq(x)
+        y.backward(gy.to(y.dtype))
+    with torch.no_grad():
+        ms_fwd = _time_cuda(lambda: fp(x))
+    ms_step = _time_cuda(ours)
+    hid = torch.randn((n, hidden), device=device, generator=g).to(torch.bfloat16)
+    w2 = seq[3].weight.detach().to(torch.bfloat16)
+    out = torch.empty((n, hidden), device=device)
+    ms_gemm = _time_cuda(lambda: gemm_bf16(hid, w2, seq[3].bias, out=out))
+    out16 = torch.empty((n, hidden), device=device, dtype=torch.bfloat16)
+    ms_gemm16 = _time_cuda(lambda: gemm_bf16(hid, w2, seq[3].bias, out=out16))
+    del hid, out, out16
+    ms_t32 = _time_cuda(torch_fp32, steps=3, warmup=1)
+    ms_amp = _time_cuda(torch_amp, steps=3, warmup=1)
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    burst, sustained = float(peaks.get("bf16_tflops", 1590.0)), float(peaks.get("bf16_tflops_sustained", 1400.0))
+    tf = 2.0 * n * hidden * hidden / (ms_gemm * 1e9)
+    tf16 = 2.0 * n * hidden * hidden / (ms_gemm16 * 1e9)
+    hbm, _ = measured_peaks()
+    gemm_bytes = n * hidden * (2 + 4)
+    return {"points": n, "in_dim": in_dim, "hidden": hidden, "forward_ms": ms_fwd, "fwd_bwd_ms": ms_step,
+            "mpoints_per_s_fwd_bwd": n / ms_step / 1e3,
+            "gemm2": {"ms_fp32_out": ms_gemm, "tflops_fp32_out": tf, "frac_of_bf16_burst": tf / burst, "frac_of_bf16_sustained": tf / sustained,
+                      "hbm_gbs_fp32_out": gemm_bytes / ms_gemm / 1e6, "hbm_frac_fp32_out": gemm_bytes / ms_gemm / 1e6 / hbm,
+                      "ms_bf16_out": ms_gemm16, "tflops_bf16_out": tf16, "frac_of_bf16_burst_bf16_out": tf16 / burst,
+                      "peak_source": "MEASURED_PEAKS.json bf16_tflops / bf16_tflops_sustained" if peaks else "fallback 1590 / 1400",
+                      "what": "y (n, H) = a (n, H) bf16 . W2^T + b2: persistent TMA + tcgen05 kernel, 128 x 256 tiles; with fp32 output the "
+                              "kernel writes 4 B per 2 H flop (H = 768: 3 KB per 1.18 MFLOP), so HBM binds before the tensor cores do"},
+            "torch_cublas_fp32_fwd_bwd_ms": ms_t32, "torch_cublas_bf16_autocast_fwd_bwd_ms": ms_amp,
+            "speedup_vs_cublas_fp32": ms_t32 / ms_step, "speedup_vs_cublas_bf16_autocast": ms_amp / ms_step,
+            "gpu_launches": 7 * 2 + 7 * 8 + 14,
+            "what": "FusedProjection (proj_hidden_kernel + gemm_bf16_tma_kernel forward; cast, da GEMM, proj_dpre_kernel, dW2 / dW1 "
+                    "split-K GEMMs, dx GEMM backward) vs the identical nn.Sequential through cuBLAS / ATen"}
+
+
 def cpu_sample_log2(wl, steps, warmup):
     """Bounded CPU sample: the decomposed mode runs ~0.03 Mpoints/s on 16 host threads, so 2^17 points x 13 steps is
     about a minute; more steps shrink the sample."""
@@ -884,6 +953,7 @@ def run_gpu_arm(args, wl):
                                                "roofline_packets", "e2e", "gpu_launches", "clocks")}
             extra["field"] = field_bench(ctx.device)
             extra["st_embed"] = st_embed_bench(ctx.device)
+            extra["projection_h768"] = projection_bench(ctx.device)
             torch.cuda.empty_cache()
             torch.cuda.reset_peak_memory_stats(ctx.device)
             extra["eager_cuda_baseline"] = {
