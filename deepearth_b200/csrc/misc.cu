@@ -11,6 +11,8 @@
 namespace de {
 
 // ---- tables -> fp16 ----------------------------------------------------------------------------
+__device__ __forceinline__ float sat_f16(float v) { return fminf(fmaxf(v, -65504.0f), 65504.0f); }   // NaN stays NaN
+
 __global__ void __launch_bounds__(256) cast_f16_kernel(const __grid_constant__ CastParams P) {
     const int level = blockIdx.y;
     const long long n = P.n_elems[level];
@@ -20,15 +22,16 @@ __global__ void __launch_bounds__(256) cast_f16_kernel(const __grid_constant__ C
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
         const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
-        __half2 a = __floats2half2_rn(v.x * P.scale, v.y * P.scale);
-        __half2 b = __floats2half2_rn(v.z * P.scale, v.w * P.scale);
+        // saturate: a parameter that outgrew the fp16 range (|w * scale| > 65504) clamps instead of becoming inf
+        __half2 a = __floats2half2_rn(sat_f16(v.x * P.scale), sat_f16(v.y * P.scale));
+        __half2 b = __floats2half2_rn(sat_f16(v.z * P.scale), sat_f16(v.w * P.scale));
         uint2 o;
         o.x = *reinterpret_cast<unsigned int*>(&a);
         o.y = *reinterpret_cast<unsigned int*>(&b);
         reinterpret_cast<uint2*>(dst)[i] = o;
     }
     for (long long i = n4 * 4 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
-        dst[i] = __float2half_rn(src[i] * P.scale);
+        dst[i] = __float2half_rn(sat_f16(src[i] * P.scale));
 }
 
 cudaError_t launch_cast_f16(const CastParams& P, cudaStream_t s) {

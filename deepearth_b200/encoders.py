@@ -182,6 +182,14 @@ class Grid4DEncoder(nn.Module):
         feats = self.encode_field(converter, lat_range, lon_range, n_lat, n_lon, altitude, time)
         return self._project(feats).reshape(int(n_lat), int(n_lon), -1)
 
+    def refresh_tables(self) -> None:
+        """Force the fp16 working tables to be re-derived on the next forward.  Needed only after the fp32 parameters were
+        rewritten through ``.data`` (``p.data.copy_(ema)`` does not bump ``Parameter._version``, which is what the cache
+        keys on outside training); optimiser steps, ``load_state_dict`` and ``.to()`` are tracked automatically."""
+        self.__dict__["_work_key_all"] = None
+        for enc in self._encoders:
+            enc._work_key = None
+
     def _working_ptrs(self, weights: List[torch.Tensor]) -> List[int]:
         """fp16 working tables of ALL grids, refreshed by ONE de_tables_to_f16 launch when the fp32 parameters may have
         changed (same rule as MultiResolutionHashEncoding.working_ptrs, without one launch + host round per grid)."""
@@ -256,6 +264,10 @@ class Grid4DEncoder(nn.Module):
             self._project(feats[:0])                       # resolves self._fused_head
             head = self._fused_head
         fn = feats.grad_fn
+        # the group-major hand-off is private to (head backward -> hash-grid backward): anything else that could look at
+        # d(loss)/d(features) -- tensor hooks, anomaly mode -- gets the ordinary row-major gradient instead
+        if torch.is_anomaly_enabled() or getattr(feats, "_backward_hooks", None):
+            return False
         if not head or head.wide or not getattr(head, "fused_backward", False) or fn is None:
             return False
         if torch.is_autocast_enabled() or not hasattr(fn, "plan") or feats.shape[0] < (1 << 20):

@@ -58,7 +58,15 @@ def _geo_arg(geo: torch.Tensor) -> torch.Tensor:
 
 
 class GeospatialConverter:
-    """geodetic (lat deg, lon deg, alt m) -> normalised fp32 xyzt, with the reference's bbox semantics."""
+    """geodetic (lat deg, lon deg, alt m) -> normalised fp32 xyzt.
+
+    Two deliberate differences from the reference's ``xyz_to_norm`` (geo2xyz.py:327-332), both in INTEGRATION.md:
+    * the reference always grows the bounding box with the batch; here that is ``update_bbox=True`` and the default is a
+      PRE-FITTED box (a training loop must not change its normalisation batch by batch);
+    * the reference returns fp64 whenever the span is large (``_norm_eff``); the encoder consumes fp32 coordinates
+      (models/hash_encoding.py:58 multiplies in the input dtype and every caller feeds fp32), so the normalised rows are
+      computed in fp64 and rounded ONCE to fp32 -- at R = 2^19 an fp32 coordinate in [0, 1] keeps ~5 fractional bits of
+      the cell position, exactly as in the reference's own fp32 pipeline."""
 
     def __init__(self, *, device: str = "cuda", bbox: Optional[BoundingBox] = None,
                  t_range: Optional[Tuple[float, float]] = None) -> None:

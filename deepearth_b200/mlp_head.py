@@ -213,7 +213,11 @@ class _HeadFunction(torch.autograd.Function):
             by_id = head.backward_fused(x, grad_y, group_width=W)
             gx = by_id.pop("x") if ctx.needs_input_grad[0] else None
             if W:
-                # tell the hash-grid backward (Grid4DFunction.backward, same token) that this buffer is group-major
+                # tell the hash-grid backward (Grid4DFunction.backward, same token) that this buffer is group-major.
+                # Entries are popped by their consumer; one whose consumer never ran (autograd.grad on the head's
+                # parameters only, an exception) must not outlive the next call
+                if len(GROUPED_GRADS) >= 4:
+                    GROUPED_GRADS.clear()
                 GROUPED_GRADS[ctx.grouped[0]] = (gx.data_ptr(), W)
             gp = [by_id.get(id(p)) if ctx.needs_input_grad[2 + i] else None for i, p in enumerate(params)]
             return (gx, None, *gp)
