@@ -62,6 +62,10 @@ WORKLOADS = {
     "c5": dict(mode="decomposed", T=2 ** 22, log2_points=24, coords="florida", table_dtype="float16", head=True,
                desc="configs[4]: geo2xyz prologue + 4 grids x 16 levels x 2 feat (T=2^22) + Linear-LayerNorm-GELU-Linear 64-wide head "
                     "(tcgen05 kernels forward and backward), 2^24 Florida-clustered geodetic points/GPU"),
+    "c5h768": dict(mode="decomposed", T=2 ** 19, log2_points=21, coords="florida", table_dtype="float16", head=True, hidden=768,
+                   desc="encoder step at the reference's default width: geo2xyz prologue + 4 grids x 16 levels x 2 feat (T=2^19) + "
+                        "Linear(128,768)-LayerNorm-GELU-Linear(768,768) projection (models/configs.py:44) on the tcgen05 / TMA kernels, "
+                        "forward and backward, 2^21 Florida-clustered geodetic points/GPU"),
     "c4": dict(mode="decomposed", T=2 ** 19, log2_points=26, total=True, coords="uniform", table_dtype="float16",
                desc="configs[3]: 2^26 points in total, sharded over the ranks (2^26 / N per GPU), 4 grids x 16 levels x 2 feat, "
                     "T=2^19/level, replicated tables, all-reduce of the table gradients"),
@@ -186,7 +190,7 @@ def build_config(wl):
     import deepearth_b200 as de
     res = [2 ** i for i in range(4, 20)]
     if wl["mode"] == "decomposed":
-        return de.DeepEarthConfig(hidden_dim=64, n_heads=4, n_layers=1, hash_table_size=wl["T"],
+        return de.DeepEarthConfig(hidden_dim=wl.get("hidden", 64), n_heads=4, n_layers=1, hash_table_size=wl["T"],
                                   n_spatial_levels=16, n_temporal_levels=16, spatial_resolutions=res,
                                   temporal_resolutions=res, grid4d_mode="decomposed",
                                   grid4d_table_dtype=wl["table_dtype"], grid4d_fused_head=bool(wl.get("head")))
@@ -249,6 +253,7 @@ class Job:
         self.flat_grad = torch.zeros(self.plan.grad_numel, dtype=torch.float32, device=device)
         self.grad_ptrs = [self.flat_grad.data_ptr() + 4 * o for o in self.plan.grad_offsets]
         self.head = None
+        self.hid = self.stats = None
         g = torch.Generator(device=device).manual_seed(seed + 1)
         if wl.get("head"):
             # configs[4]: the step starts from geodetic points (prologue kernel inside the timed region) and
@@ -257,9 +262,9 @@ class Job:
             self.geo, self.t, self.conv = make_geo(n_points, device, seed)
             self.coords = self.conv.geodetic_to_xyzt_norm(self.geo, self.t)
             self.head = FusedProjection(self.enc.projection)
-            assert self.head.supported(), "64-wide head expected"
+            assert self.head.supported(), "projection shape not served by the tcgen05 kernels"
             self.head_params = list(self.enc.projection.parameters())
-            self.gy = torch.randn((n_points, 64), device=device, generator=g)
+            self.gy = torch.randn((n_points, wl.get("hidden", 64)), device=device, generator=g)
             self.gout = None
         else:
             self.coords, self.gout = Job.inputs(wl, n_points, device, seed, self.plan.out_cols)
@@ -307,11 +312,19 @@ class Job:
         self.coords = self.conv.geodetic_to_xyzt_norm(self.geo, self.t)
 
     def head_forward(self):
+        if self.head.wide:
+            self.y, self.hid, self.stats = self.head.fused_wide(self.out, want_stats=True)
+            return
         self.y = self.head.fused(self.out)
 
     def head_backward(self):
         """Gradients of the head: the tcgen05 backward kernel (default) or, for A/B, a recompute through the fp32
         modules (cuBLAS + eager LayerNorm / GELU), which is what autograd does with fused_backward=False."""
+        if self.head_bwd == "tcgen05" and self.head.wide:
+            g = self.head.backward_wide(self.out, self.hid, self.stats, self.gy)
+            self.gout = g.pop("x")
+            self.head_grads = g
+            return
         if self.head_bwd == "tcgen05":
             g = self.head.backward_fused(self.out, self.gy, group_width=self.group_w)
             self.gout = g.pop("x")
@@ -345,7 +358,10 @@ class Job:
                 lv, len(self.plan.specs), self.F, self.n, lin | _lib.DE_FLAG_NO_REGROUP, self.plan.bwd_levels_per_group):
             extra += runs
         cast = 1 if self.plan.table_dtype == torch.float16 else 0            # de_tables_to_f16 refresh
-        return 2 * runs + extra + cast + (3 if self.head is not None else 0)     # + prologue + head forward + head backward kernels
+        head = 0
+        if self.head is not None:                 # prologue + head forward + head backward kernels
+            head = 1 + (2 + 6 if self.head.wide else 1 + 1)
+        return 2 * runs + extra + cast + head
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -663,7 +679,7 @@ def measure(args, name, wl, ctx, steps, want_clocks=True):
     job.head_bwd = args.head_bwd
     if job.head is not None:
         job.head.fused_backward = args.head_bwd == "tcgen05"
-        if args.head_bwd == "tcgen05" and not args.no_grouped_head:
+        if args.head_bwd == "tcgen05" and not args.no_grouped_head and not job.head.wide:
             job.group_w = Fn.backward_group_width(job.plan.specs, n, job.F, job.linear, job.plan.bwd_levels_per_group,
                                                   job.plan.extra_flags)
 
@@ -766,7 +782,7 @@ def measure(args, name, wl, ctx, steps, want_clocks=True):
         h2d_bytes = host_geo.numel() * 8 + host_t.numel() * 8
         params = job.weights + job.head_params
         api = "GeospatialConverter.geodetic_to_xyzt_norm + Grid4DEncoder.forward (tcgen05 head) + autograd backward; pinned host geodetic points -> device every step (copy of step i+1 overlaps step i); output checksum reduced + read back on a side stream during the backward"
-        job.gout = job.head_grads = job.y = None
+        job.gout = job.head_grads = job.y = job.hid = job.stats = None
     else:
         host = job.coords.cpu().pin_memory()
         h2d_bytes = host.numel() * 4
