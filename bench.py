@@ -868,8 +868,9 @@ def measure(args, name, wl, ctx, steps, want_clocks=True):
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
             with open(tpath) as f:
-                tj = json.load(f).get(name, {})
-            traffic, traffic_src = tj.get(dom), tj.get("source")
+                tfile = json.load(f)
+            tj = tfile.get(name, {})
+            traffic, traffic_src = tj.get(dom), (tfile.get("_source") if tj.get(dom) is not None else None)
         # where the dominant kernel's working set lives: one level group's tables (forward) / gradient tables (backward)
         lvl_bytes = wl["T"] * job.F * (4 if dom == "backward" else (2 if wl["table_dtype"] == "float16" else 4))
         resident = "l2" if lvl_bytes * 16 <= 64 * 2 ** 20 or wl["mode"] != "decomposed" else "hbm"
@@ -950,6 +951,51 @@ def grad_check(args, ctx, log2_points=16):
                     "ranks' points / world, max over ranks of max|diff| / max|ref| on the flat 256 MiB gradient buffer"}
 
 
+EXTRA_NAMES = ("c3", "c1r", "field", "st_embed", "projection_h768", "eager_cuda_baseline")
+
+
+def run_extra_child(name, steps, limit_s):
+    """One side measurement in a child process (`bench.py --extra-only NAME`), JSON on its last stdout line."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--extra-only", name, "--steps", str(steps)]
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE"):
+        env.pop(k, None)
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=limit_s, env=env)
+    except subprocess.TimeoutExpired:
+        return {"error": f"timed out after {limit_s} s"}
+    lines = [ln for ln in r.stdout.strip().splitlines() if ln.startswith("{")]
+    if r.returncode != 0 or not lines:
+        return {"error": f"exit code {r.returncode}: " + (r.stderr.strip().splitlines() or ["no output"])[-1][:300]}
+    try:
+        return json.loads(lines[-1])
+    except ValueError as e:
+        return {"error": f"unparsable output: {e}"}
+
+
+def run_extra_only(args):
+    """Child side of run_extra_child."""
+    ctx = Ctx()
+    name = args.extra_only
+    if name in ("c3", "c1r"):
+        r = measure(args, name, dict(WORKLOADS[name]), ctx, max(2, args.steps))
+        out = {k: r[k] for k in ("value", "unit", "steps", "ms_per_step", "config", "kernels_ms", "roofline", "roofline_packets",
+                                 "e2e", "gpu_launches", "clocks")}
+    elif name == "field":
+        out = field_bench(ctx.device)
+    elif name == "st_embed":
+        out = st_embed_bench(ctx.device)
+    elif name == "projection_h768":
+        out = projection_bench(ctx.device)
+    elif name == "eager_cuda_baseline":
+        out = {"c2": eager_cuda_baseline(dict(WORKLOADS["c2"]), 2 ** 22, ctx.device)}
+        torch.cuda.empty_cache()
+        out["c1r"] = eager_cuda_baseline(dict(WORKLOADS["c1r"]), 2 ** 22, ctx.device)
+    else:
+        raise SystemExit(f"unknown extra {name!r}")
+    print(json.dumps(out), flush=True)
+
+
 def run_gpu_arm(args, wl):
     ctx = Ctx()
     from deepearth_b200 import _lib as _L
@@ -963,19 +1009,12 @@ def run_gpu_arm(args, wl):
     if extras_on:
         side_steps = max(2, min(args.steps, 5))
         if ctx.world == 1:
-            for nm in ("c3", "c1r"):
-                r = measure(args, nm, dict(WORKLOADS[nm]), ctx, side_steps)
-                extra[nm] = {k: r[k] for k in ("value", "unit", "steps", "ms_per_step", "config", "kernels_ms", "roofline",
-                                               "roofline_packets", "e2e", "gpu_launches", "clocks")}
-            extra["field"] = field_bench(ctx.device)
-            extra["st_embed"] = st_embed_bench(ctx.device)
-            extra["projection_h768"] = projection_bench(ctx.device)
+            # Each side measurement runs in its own process with a time limit: a fault or a hang in one of them costs that
+            # entry (recorded as {"error": ...}), never the headline line.  This process keeps only its CUDA context.
             torch.cuda.empty_cache()
-            torch.cuda.reset_peak_memory_stats(ctx.device)
-            extra["eager_cuda_baseline"] = {
-                "c2": eager_cuda_baseline(dict(WORKLOADS["c2"]), 2 ** 22, ctx.device),
-                "c1r": eager_cuda_baseline(dict(WORKLOADS["c1r"]), 2 ** 22, ctx.device)}
-            torch.cuda.empty_cache()
+            for nm, limit in (("c3", 240), ("c1r", 120), ("field", 120), ("st_embed", 120), ("projection_h768", 180),
+                              ("eager_cuda_baseline", 240)):
+                extra[nm] = run_extra_child(nm, side_steps, limit)
         else:
             r = measure(args, "c4", dict(WORKLOADS["c4"]), ctx, side_steps, want_clocks=False)
             if ctx.rank == 0:
@@ -1003,6 +1042,7 @@ def main():
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--extras", default="auto", choices=["auto", "all", "none"],
                     help="side measurements in the same line: auto = on for the default workload, off for an explicit --workload")
+    ap.add_argument("--extra-only", default=None, choices=EXTRA_NAMES, help=argparse.SUPPRESS)
     ap.add_argument("--log2-points", type=int, default=0, help="override points per GPU (power of two)")
     ap.add_argument("--levels-per-group", type=int, default=0)
     ap.add_argument("--bwd-levels-per-group", type=int, default=0)
@@ -1028,7 +1068,9 @@ def main():
     if args.sort_points:
         wl["sort_points"] = True
         wl["desc"] += " [points Morton-sorted before timing]"
-    if args.impl == "reference":
+    if args.extra_only:
+        run_extra_only(args)
+    elif args.impl == "reference":
         run_reference_arm(args, wl)
     else:
         run_gpu_arm(args, wl)
