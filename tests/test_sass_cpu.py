@@ -102,3 +102,25 @@ def test_occupancy_the_measurements_were_taken_at(resources):
     assert all(resources[k][0] <= 32 for k in nearest_bwd)
     bwd_pair = _pick(resources, "grid4d_backward_pair_kernelILi3ELi2ELb1")
     assert all(resources[k][0] <= 48 and resources[k][1] == 0 for k in bwd_pair)
+
+
+def test_wide_projection_runs_on_tcgen05_and_tma(sass_by_function):
+    """the GEMM kernel loads its operands by TMA (UTMALDG = cp.async.bulk.tensor) and multiplies with
+    tcgen05.mma (UTCHMMA) out of tensor memory (LDTM); its split-K epilogue reduces with vector REDG; the hidden / dpre
+    kernels recompute the first Linear on tcgen05 as well."""
+    for k in _pick(sass_by_function, "gemm_bf16_tma_kernel"):
+        sass = sass_by_function[k]
+        assert "UTMALDG" in sass and "UTCHMMA" in sass and "LDTM" in sass and "UTCBAR" in sass, k
+    acc = [k for k in _pick(sass_by_function, "gemm_bf16_tma_kernel") if k.endswith("Li2EEv14CUtensorMap_stS0_NS_10GemmParamsE") or "Li2EE" in k]
+    assert any("REDG.E.ADD.F32" in sass_by_function[k] for k in acc)
+    for name in ("proj_hidden_kernel", "proj_dpre_kernel"):
+        for k in _pick(sass_by_function, name):
+            assert "UTCHMMA" in sass_by_function[k] and "LDTM" in sass_by_function[k], k
+
+
+def test_small1d_and_st_embed_accumulate_in_shared_memory(sass_by_function):
+    """grid4d_small1d / st_embed table-gradient kernels: shared-memory atomics (ATOMS) per point, global REDG only at the flush."""
+    for k in _pick(sass_by_function, "small1d_backward_kernel"):
+        assert "ATOMS" in sass_by_function[k] and "REDG.E.ADD.F32" in sass_by_function[k], k
+    for k in _pick(sass_by_function, "st_embed_table_grad_kernel"):
+        assert "ATOMS" in sass_by_function[k], k
