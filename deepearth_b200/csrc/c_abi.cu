@@ -677,6 +677,64 @@ DE_API int de_grid4d_backward(const de_level_desc* levels_host, int n_levels, co
     return run(a, Op::Backward, P, static_cast<cudaStream_t>(stream));
 }
 
+DE_API size_t de_grid4d_sort_workspace_bytes(int n_dims, int bits) {
+    if (n_dims < 1 || n_dims > 4 || bits < 1 || bits * n_dims > 16) return 0;
+    return static_cast<size_t>(4) << (bits * n_dims);
+}
+
+DE_API int de_grid4d_sort_points(const float* coords, int64_t n_points, int coord_stride, const uint8_t* dims_host, int n_dims,
+                          int bits, int32_t* perm, void* workspace, size_t workspace_bytes, void* stream) {
+    if (n_points < 0 || n_points > 0x7fffffffll) return fail(DE_EINVAL, "sort_points: n_points=%lld", (long long)n_points);
+    if (n_points == 0) return DE_OK;
+    if (!coords || !dims_host || !perm || !workspace) return fail(DE_EINVAL, "sort_points: NULL pointer");
+    const size_t need = de_grid4d_sort_workspace_bytes(n_dims, bits);
+    if (!need) return fail(DE_EUNSUPPORTED, "sort_points: n_dims=%d bits=%d (bits * n_dims must be in 1..16)", n_dims, bits);
+    if (workspace_bytes < need) return fail(DE_EINVAL, "sort_points: workspace of %zu bytes, %zu needed", workspace_bytes, need);
+    de::SortParams S{};
+    S.coords = coords; S.n = n_points; S.coord_stride = coord_stride; S.n_dims = n_dims; S.bits = bits;
+    for (int d = 0; d < n_dims; ++d) {
+        if (dims_host[d] >= coord_stride) return fail(DE_EINVAL, "sort_points: dim[%d]=%d >= coord_stride=%d", d, dims_host[d], coord_stride);
+        S.dim[d] = dims_host[d];
+    }
+    S.counts = static_cast<unsigned int*>(workspace);
+    S.perm = perm;
+    int dev = 0, n_sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = de::launch_sort_points(S, n_sms, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "sort_points launch");
+}
+
+DE_API int de_grid4d_backward_sorted(const de_level_desc* levels_host, int n_levels, const float* coords, int64_t n_points,
+                              int coord_stride, int n_features, const uint8_t* mask_a, const uint8_t* mask_b,
+                              const float* grad_out, int64_t grad_stride, uint32_t flags, const int32_t* perm, void* stream) {
+    CallArgs a{levels_host, n_levels, coords, n_points, coord_stride, DE_F32, n_features, flags, 0, false, true};
+    if (int rc = validate(a)) return rc;
+    if (n_points == 0) return DE_OK;
+    if (!grad_out || !perm) return fail(DE_EINVAL, "backward_sorted: NULL pointer");
+    if ((flags & DE_INTERP_MASK) != DE_INTERP_LINEAR) return fail(DE_EUNSUPPORTED, "backward_sorted: DE_INTERP_LINEAR levels only");
+    if (!(n_features == 1 || n_features == 2 || n_features == 4)) return fail(DE_EUNSUPPORTED, "backward_sorted: n_features=%d not in {1,2,4}", n_features);
+    if (n_levels > de::kMaxLaunchLevels) return fail(DE_EUNSUPPORTED, "backward_sorted: n_levels=%d > %d", n_levels, de::kMaxLaunchLevels);
+    de::EncodeParams P{};
+    P.coords = coords; P.mask_a = mask_a; P.mask_b = mask_b; P.grad_out = grad_out; P.n_points = n_points;
+    P.out_stride = grad_stride; P.coord_stride = coord_stride; P.n_features = n_features;
+    P.vec_coords = (coord_stride == 4 && reinterpret_cast<uintptr_t>(coords) % 16 == 0) ? 1 : 0;
+    P.vec_rows = rows_vectorisable(grad_out, grad_stride, levels_host, n_levels, n_features) ? 1 : 0;
+    P.out_scale = 1.0f;
+    P.n_levels = n_levels;
+    bool pow2_all = true;
+    for (int i = 0; i < n_levels; ++i) {
+        const de_level_desc& L = levels_host[i];
+        if (L.n_dims != 3) return fail(DE_EUNSUPPORTED, "backward_sorted: level %d has n_dims=%d (3-D grids only)", i, L.n_dims);
+        if ((int64_t)L.out_col + n_features > grad_stride) return fail(DE_EINVAL, "level %d: out_col %u + F %d exceeds grad_stride %lld", i, L.out_col, n_features, (long long)grad_stride);
+        fill_level(L, P.levels[i]);
+        pow2_all = pow2_all && is_pow2(L.table_size);
+    }
+    int dev = 0, n_sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = de::launch_backward_sorted(P, perm, n_features, pow2_all, n_sms, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "backward_sorted launch");
+}
+
 DE_API size_t de_grid4d_backward_workspace_bytes(const de_level_desc* levels_host, int n_levels, int n_features,
                                                  int64_t n_points, uint32_t flags) {
     return de_grid4d_backward_workspace_bytes_ex(levels_host, n_levels, n_features, n_points, flags, 0);

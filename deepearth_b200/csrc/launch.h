@@ -37,6 +37,19 @@ struct Small1dPlan {
 cudaError_t launch_small1d_forward(const EncodeParams& P, const Small1dPlan& S, bool half_tables, int F, int n_ctas, cudaStream_t s);
 cudaError_t launch_small1d_backward(const EncodeParams& P, const Small1dPlan& S, int F, int n_ctas, cudaStream_t s);
 
+// sort-by-cell + warp-aggregated backward (grid4d_sorted_kernels.cu; opt-in alternative to the gradient replicas)
+struct SortParams {
+    const float* coords;
+    long long n;
+    int coord_stride;
+    int n_dims, bits;             // key = cells on a 2^bits-per-axis grid over columns dim[0..n_dims), x-major
+    unsigned char dim[4];
+    unsigned int* counts;         // 2^(bits * n_dims) counters (workspace)
+    int* perm;                    // out: perm[i] = index of the i-th point in cell order
+};
+cudaError_t launch_sort_points(const SortParams& S, int n_sms, cudaStream_t s);
+cudaError_t launch_backward_sorted(const EncodeParams& P, const int* perm, int F, bool pow2, int n_sms, cudaStream_t s);
+
 struct CastParams {
     const float* src[64];
     void* dst[64];

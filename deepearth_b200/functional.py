@@ -228,6 +228,55 @@ def encode_backward(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: 
     _lib.check(rc, "de_grid4d_backward")
 
 
+def sort_points(coords: torch.Tensor, dims: Sequence[int], bits: int = 5) -> torch.Tensor:
+    """perm (int32, B): the points ordered by the cell they occupy on a 2^bits-per-axis grid over coordinate columns
+    ``dims`` (x-major) -- the pre-pass of the sort-by-cell backward (csrc/grid4d_sorted_kernels.cu)."""
+    _require_cuda(coords, "coords")
+    coords, stride = _coords_view(coords)
+    n = coords.shape[0]
+    perm = torch.empty(n, dtype=torch.int32, device=coords.device)
+    if n == 0:
+        return perm
+    lib = _lib.load()
+    ws_bytes = int(lib.de_grid4d_sort_workspace_bytes(len(dims), int(bits)))
+    if not ws_bytes:
+        raise ValueError(f"bits * len(dims) must be in 1..16, got bits={bits}, dims={tuple(dims)}")
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=coords.device)
+    d = (ctypes.c_uint8 * len(dims))(*[int(v) for v in dims])
+    with torch.cuda.device(coords.device):
+        rc = lib.de_grid4d_sort_points(_ptr(coords), n, stride, d, len(dims), int(bits), _ptr(perm), _ptr(ws), ws_bytes,
+                                       _stream_ptr(coords.device))
+    _lib.check(rc, "de_grid4d_sort_points")
+    return perm
+
+
+def encode_backward_sorted(specs: Sequence[LevelSpec], coords: torch.Tensor, grad_out: torch.Tensor,
+                           grad_ptrs: Sequence[int], n_features: int, perm: torch.Tensor,
+                           mask_a: Optional[torch.Tensor] = None, mask_b: Optional[torch.Tensor] = None) -> None:
+    """Warp-aggregated scatter of 3-D multilinear levels over the points in ``perm`` order (opt-in alternative to the
+    gradient replicas for densely colliding levels); accumulates into the fp32 buffers at ``grad_ptrs``."""
+    _require_cuda(coords, "coords")
+    _require_cuda(grad_out, "grad_out")
+    coords, stride = _coords_view(coords)
+    n = coords.shape[0]
+    if n == 0:
+        return
+    if perm.dtype != torch.int32 or perm.shape != (n,) or not perm.is_contiguous():
+        raise ValueError("perm must be a contiguous int32 tensor with one entry per point")
+    if grad_out.dtype != torch.float32:
+        grad_out = grad_out.float()
+    if grad_out.dim() != 2 or grad_out.shape[0] != n or grad_out.stride(1) != 1:
+        grad_out = grad_out.reshape(n, -1).contiguous()
+    ma = _mask_u8(mask_a, n, coords.device)
+    mb = _mask_u8(mask_b, n, coords.device)
+    with torch.cuda.device(coords.device):
+        rc = _lib.load().de_grid4d_backward_sorted(pack_levels(specs, None, grad_ptrs), len(specs), _ptr(coords), n, stride,
+                                                   n_features, _ptr(ma), _ptr(mb), _ptr(grad_out),
+                                                   grad_out.stride(0) if n > 1 else grad_out.shape[1], _lib.DE_INTERP_LINEAR,
+                                                   _ptr(perm), _stream_ptr(coords.device))
+    _lib.check(rc, "de_grid4d_backward_sorted")
+
+
 def backward_group_width(specs: Sequence[LevelSpec], n_points: int, n_features: int, linear: bool,
                          levels_per_group: int = 0, extra_flags: int = 0) -> int:
     """W > 0 when ``encode_backward`` for these arguments would regroup the gradient rows (large tables => few levels

@@ -166,6 +166,24 @@ DE_API int de_grid4d_backward_group_width(const de_level_desc* levels_host, int 
                                           int64_t n_points, uint32_t flags, int levels_per_group);
 
 /*
+ * Sort-by-cell + warp-aggregated scatter: the alternative backward for densely colliding (coarse) levels.  Opt-in; the
+ * default backward spreads such levels over gradient replicas instead (A/B in profiles/).
+ *   de_grid4d_sort_points: perm[i] = index of the i-th point when the points are ordered by the cell they occupy on a
+ *     2^bits-per-axis grid over coordinate columns dims_host[0 .. n_dims) (x-major; coordinates outside [0, 1) clamp to the
+ *     border cells).  Counting sort: bits * n_dims <= 16; workspace = de_grid4d_sort_workspace_bytes() bytes.
+ *   de_grid4d_backward_sorted: same contract as de_grid4d_backward for 3-D DE_INTERP_LINEAR levels, n_features in
+ *     {1, 2, 4}; a warp walks 32 consecutive points of `perm` for one level, the lanes of a run that shares a cell add their
+ *     contributions with a segmented shuffle scan and one lane issues the reduction.  Any permutation gives the same
+ *     gradients (up to fp32 summation order); only a cell-ordered one makes it fast.
+ */
+DE_API size_t de_grid4d_sort_workspace_bytes(int n_dims, int bits);
+DE_API int de_grid4d_sort_points(const float* coords, int64_t n_points, int coord_stride, const uint8_t* dims_host, int n_dims,
+                          int bits, int32_t* perm, void* workspace, size_t workspace_bytes, void* stream);
+DE_API int de_grid4d_backward_sorted(const de_level_desc* levels_host, int n_levels, const float* coords, int64_t n_points,
+                              int coord_stride, int n_features, const uint8_t* mask_a, const uint8_t* mask_b,
+                              const float* grad_out, int64_t grad_stride, uint32_t flags, const int32_t* perm, void* stream);
+
+/*
  * fp32 master tables -> fp16 working tables, dst = half(src * scale), one launch
  * for all levels (level i: src = levels_host[i].table (fp32), dst =
  * dst_tables[i]).  dst_tables_host: host array of n_levels device pointers.

@@ -846,3 +846,38 @@ def test_small1d_shared_memory_path_equals_general_kernels(dev):
         assert torch.equal(res[0][0], res[1][0])
         for a, b in zip(res[0][1], res[1][1]):
             assert float((a - b).abs().max()) <= 1e-5 * max(float(b.abs().max()), 1e-30)
+
+
+def test_sort_by_cell_and_warp_aggregated_backward(dev):
+    """The north_star's alternative for densely colliding levels: counting sort of the points by coarse cell, then a
+    backward whose warps aggregate runs of lanes that share a cell.  perm must be a cell-ordered permutation; the gradients
+    must equal the default (replica) path's on Florida-clustered points -- coarse dense and fine hashed levels, ragged tail."""
+    from bench import make_geo
+    from deepearth_b200 import functional as Fn
+    from deepearth_b200.functional import LevelSpec
+    n, T, F = (1 << 18) + 37, 2 ** 16, 2
+    geo, t, conv = make_geo(n, dev, 5)
+    xyzt = conv.geodetic_to_xyzt_norm(geo, t)
+    dims = (0, 1, 3)
+    perm = Fn.sort_points(xyzt, dims, bits=5)
+    assert torch.equal(torch.sort(perm.long()).values, torch.arange(n, device=dev))
+    cells = (xyzt[:, list(dims)].clamp(0, 1) * 32).clamp(max=31).floor().long()
+    key = (cells[:, 0] * 32 + cells[:, 1]) * 32 + cells[:, 2]
+    sk = key[perm.long()]
+    assert bool((sk[1:] >= sk[:-1]).all()), "perm is not in cell order"
+    res = [16, 32, 64, 1024]
+    specs = [LevelSpec(T, R, dims, l * F, dense=Fn.dense_fits(R, 3, T)) for l, R in enumerate(res)]
+    g = torch.Generator(device=dev).manual_seed(3)
+    gout = torch.randn((n, len(res) * F), device=dev, generator=g)
+    a = torch.zeros((len(res), T, F), device=dev)
+    b = torch.zeros_like(a)
+    Fn.encode_backward(specs, xyzt, gout, [a[l].data_ptr() for l in range(len(res))], F, True)
+    Fn.encode_backward_sorted(specs, xyzt, gout, [b[l].data_ptr() for l in range(len(res))], F, perm)
+    for l in range(len(res)):
+        err = float((a[l] - b[l]).abs().max()) / float(a[l].abs().max())
+        assert err <= 1e-4, (res[l], err)
+    # any permutation gives the same gradients
+    c = torch.zeros_like(a)
+    Fn.encode_backward_sorted(specs, xyzt, gout, [c[l].data_ptr() for l in range(len(res))], F,
+                              torch.randperm(n, device=dev, generator=g).int())
+    assert float((a - c).abs().max()) / float(a.abs().max()) <= 1e-4
