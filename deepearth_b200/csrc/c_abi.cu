@@ -1067,7 +1067,9 @@ static size_t align256(size_t v) { return (v + 255) & ~static_cast<size_t>(255);
 DE_API size_t de_projection_backward_workspace_bytes(int64_t n_points, int in_dim, int hidden, int out_dim) {
     if (n_points <= 0 || in_dim <= 0 || hidden <= 0 || out_dim <= 0) return 0;
     const size_t n = static_cast<size_t>(n_points);
-    return align256(n * out_dim * 2) + align256(n * hidden * 2) + align256(n * in_dim * 2);
+    const size_t nt = (n + 7) & ~static_cast<size_t>(7);      // leading dimension of the transposed copies (fallback path)
+    return align256(n * out_dim * 2) + align256(n * hidden * 2) + align256(n * in_dim * 2) +
+           align256(nt * out_dim * 2) + align256(nt * hidden * 2);
 }
 
 DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n_points, int in_dim, int64_t x_stride,
@@ -1118,7 +1120,26 @@ DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n
         if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dpre launch");
     }
     // 4. dW2 (out, hidden) += gy^T . a ;  5. dW1 (hidden, in) += dpre^T . x   (contraction over the points)
-    {
+    if (DE_KNOB("DE_PROJ_DW_TRANSPOSE", 0, 0, 1)) {
+        // fallback operand path: explicit transposes, then the K-major GEMM (K = points) -- same results, ~2x the bytes
+        const size_t nt = (n + 7) & ~static_cast<size_t>(7);
+        char* t0 = ws + align256(n * out_dim * 2) + align256(n * hidden * 2) + align256(n * in_dim * 2);
+        char* t1 = t0 + align256(nt * out_dim * 2);
+        e = de::launch_transpose_bf16(gy16, out_dim, t0, nt, n_points, out_dim, s);
+        if (e == cudaSuccess) e = de::launch_transpose_bf16(hidden_bf16, hidden, t1, nt, n_points, hidden, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: transpose launch");
+        de::GemmParams G{};
+        G.M = out_dim; G.N = hidden; G.K = n_points; G.c = grad_w2; G.ldc = hidden;
+        e = de::launch_gemm_bf16(t0, nt, t1, nt, 0, G, 2, n_sms, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dW2 GEMM launch");
+        e = de::launch_transpose_bf16(da, hidden, t1, nt, n_points, hidden, s);
+        if (e == cudaSuccess) e = de::launch_transpose_bf16(x16, in_dim, t0, nt, n_points, in_dim, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: transpose launch");
+        G = de::GemmParams{};
+        G.M = hidden; G.N = in_dim; G.K = n_points; G.c = grad_w1; G.ldc = in_dim;
+        e = de::launch_gemm_bf16(t1, nt, t0, nt, 0, G, 2, n_sms, s);
+        if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dW1 GEMM launch");
+    } else {
         de::GemmParams G{};
         G.M = out_dim; G.N = hidden; G.K = n_points; G.c = grad_w2; G.ldc = hidden;
         e = de::launch_gemm_bf16(gy16, out_dim, hidden_bf16, hidden, 1, G, 2, n_sms, s);

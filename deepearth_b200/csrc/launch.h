@@ -163,6 +163,8 @@ struct ProjDpreParams {
     int n_tiles;
 };
 cudaError_t launch_proj_dpre(ProjDpreParams P, int in_dim, int n_sms, cudaStream_t s);
+cudaError_t launch_transpose_bf16(const void* src, long long ld_src, void* dst, long long ld_dst, long long rows, int cols,
+                                  cudaStream_t s);
 cudaError_t launch_cast_colsum(const float* src, long long ld_src, void* dst_bf16, long long ld_dst, long long n_rows, int n_cols,
                                float* colsum, int n_sms, cudaStream_t s);
 bool proj_hidden_supported(int in_dim, int hidden);

@@ -62,6 +62,36 @@ cudaError_t launch_cast_colsum(const float* src, long long ld_src, void* dst_bf1
     return cudaGetLastError();
 }
 
+// ---- bf16 transpose (fallback operand path of the weight-gradient GEMMs, DE_PROJ_DW_TRANSPOSE=1) ----------------------
+// src (rows, cols) row-major -> dst (cols, ld_dst) row-major; 64 x 64 tiles through shared memory
+__global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src,
+                                                             __nv_bfloat16* __restrict__ dst, long long ld_dst, long long rows, int cols) {
+    __shared__ __nv_bfloat16 tile[64][66];
+    const long long r0 = static_cast<long long>(blockIdx.x) * 64;
+    const int c0 = blockIdx.y * 64;
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    for (int i = ty; i < 64; i += 4) {
+        const long long r = r0 + i;
+        const int c = c0 + tx;
+        tile[i][tx] = (r < rows && c < cols) ? src[r * ld_src + c] : __float2bfloat16_rn(0.0f);
+    }
+    __syncthreads();
+    for (int i = ty; i < 64; i += 4) {
+        const int c = c0 + i;
+        const long long r = r0 + tx;
+        if (c < cols && r < rows) dst[static_cast<long long>(c) * ld_dst + r] = tile[tx][i];
+    }
+}
+
+cudaError_t launch_transpose_bf16(const void* src, long long ld_src, void* dst, long long ld_dst, long long rows, int cols,
+                                  cudaStream_t s) {
+    if (rows == 0 || cols == 0) return cudaSuccess;
+    const dim3 grid(static_cast<unsigned>((rows + 63) / 64), static_cast<unsigned>((cols + 63) / 64));
+    transpose_bf16_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(src), ld_src, static_cast<__nv_bfloat16*>(dst), ld_dst,
+                                                rows, cols);
+    return cudaGetLastError();
+}
+
 // ---- dpre ----------------------------------------------------------------------------------------------------------------
 constexpr int kBwdChunkN = 128;
 
