@@ -63,16 +63,16 @@ def test_projection_forward_vs_nn_sequential(dev, in_dim, hidden, n):
     w1, w2 = fp._weights()
     y, hid, stats = projection_forward(x, w1, seq[0].bias, seq[1].weight, seq[1].bias, seq[1].eps, w2, seq[3].bias, want_stats=True)
     want_same, act = same_rounding_reference(seq, x)
-    scale = float(want_same.abs().max())
+    scale = float(want_same.detach().abs().max())
     # hidden activations: bf16 rounding of the fp64 value computed from the same rounded operands (+ GELU approximation 3e-7)
     herr = float((hid.double() - act).abs().max()) / float(act.abs().max())
-    assert herr <= 6e-3, herr
+    assert herr <= 6e-3, herr                    # one bf16 ulp of the largest activation (B200: 2.1e-3 .. 3.1e-3)
     e_same = float((y.double() - want_same).abs().max()) / scale
-    assert e_same <= 2e-3, e_same
+    assert e_same <= 1e-3, e_same                # B200: <= 2.6e-4
     with torch.no_grad():
         want = seq(x)
     e_mod = float((y - want).abs().max()) / float(want.abs().max())
-    assert e_mod <= 3e-2, e_mod
+    assert e_mod <= 1e-2, e_mod                  # B200: <= 3.7e-3
     # LayerNorm statistics of the pre-activation rows
     h = x.to(torch.bfloat16).double() @ w1.double().t() + seq[0].bias.double()
     assert float((stats[:, 0].double() - h.mean(-1)).abs().max()) <= 1e-4 * max(1.0, float(h.abs().max()))
@@ -82,7 +82,7 @@ def test_projection_forward_vs_nn_sequential(dev, in_dim, hidden, n):
     print(f"projection K1={in_dim} H={hidden} n={n}: hidden {herr:.1e}, same-rounding {e_same:.1e}, vs fp32 module {e_mod:.1e}")
 
 
-@pytest.mark.parametrize("m,n,k", [(768, 768, 4096), (256, 128, 1000), (768, 48, 64 * 37 + 5), (130, 250, 70000)])
+@pytest.mark.parametrize("m,n,k", [(768, 768, 4096), (256, 128, 1000), (768, 48, 64 * 37 + 5), (136, 248, 70000)])
 def test_gemm_bf16_transposed_accumulate_vs_torch(dev, m, n, k):
     """Weight-gradient form: C (M, N) += A (K, M)^T B (K, N), the contraction (points) split over the CTAs."""
     from deepearth_b200.mlp_head import gemm_bf16
@@ -142,7 +142,7 @@ def test_projection_backward_vs_autograd(dev, in_dim, hidden, n):
         worst[k] = float((got[k] - want[k]).abs().max()) / max(float(want[k].abs().max()), 1e-30)
     print(f"projection backward K1={in_dim} H={hidden} n={n}:", {k: f"{v:.1e}" for k, v in worst.items()})
     for k, v in worst.items():
-        assert v <= 2e-2, (k, v)
+        assert v <= 1e-2, (k, v)          # B200: <= 5e-3 on every shape (gpurun r02c)
 
 
 def test_grid4d_encoder_default_width_runs_on_our_kernels(dev):
@@ -162,6 +162,6 @@ def test_grid4d_encoder_default_width_runs_on_our_kernels(dev):
     assert enc._fused_head and enc._fused_head.wide
     with torch.no_grad():
         want = enc.projection(enc.encode_features(xyzt))
-    assert float((out - want).abs().max()) <= 3e-2 * float(want.abs().max())
+    assert float((out.detach() - want).abs().max()) <= 1e-2 * float(want.abs().max())
     out.sum().backward()
     assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in enc.parameters())
