@@ -14,6 +14,7 @@
 // pre-activation is never stored by the forward; the saved row statistics (mean, rstd) make the recompute exact.
 #include "launch.h"
 #include "mlp_common.cuh"
+#include "proj_common.cuh"
 
 namespace de {
 
@@ -95,29 +96,35 @@ cudaError_t launch_transpose_bf16(const void* src, long long ld_src, void* dst, 
 // ---- dpre ----------------------------------------------------------------------------------------------------------------
 constexpr int kBwdChunkN = 128;
 
-// dynamic shared memory: A [128 x K1] | B[2] [128 x K1] (bf16, canonical K-major) | acc[3][H] floats (dgamma, dbeta, db1)
+// W1 chunks arrive by TMA exactly as in proj_hidden_kernel (a continuous chunk stream, requested one epilogue ahead).
+// dynamic shared memory (1024 B aligned): B[2] [Kp / 64 boxes x 16 KB] | A [128 x Kp] bf16 canonical | acc[3][H] floats
 template <int K1>
 __global__ void __launch_bounds__(kMlpThreads)
-proj_dpre_kernel(const __grid_constant__ ProjDpreParams P) {
-    extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t s_bar[2];
+proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_constant__ ProjDpreParams P) {
+    constexpr int Kp = (K1 + 63) / 64 * 64;
+    constexpr uint32_t kChunkBytes = (Kp / 64) * 16384;
+    extern __shared__ unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t s_mma[2], s_tma[2];
     __shared__ uint32_t s_tmem;
-    unsigned char* sA = smem;
-    unsigned char* sB[2] = {smem + kTileM * K1 * 2, smem + kTileM * K1 * 2 + kBwdChunkN * K1 * 2};
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    unsigned char* sB[2] = {smem, smem + kChunkBytes};
+    unsigned char* sA = smem + 2 * kChunkBytes;
     const int H = P.hidden, NC = H / kBwdChunkN;
-    float* s_acc = reinterpret_cast<float*>(smem + (kTileM + 2 * kBwdChunkN) * K1 * 2);     // [3][H]
+    float* s_acc = reinterpret_cast<float*>(sA + kTileM * Kp * 2);     // [3][H]: dgamma, dbeta, db1
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     for (int i = tid; i < 3 * H; i += kMlpThreads) s_acc[i] = 0.0f;
     if (tid == 0) {
-        mbar_init(&s_bar[0], 1);
-        mbar_init(&s_bar[1], 1);
+        mbar_init(&s_mma[0], 1); mbar_init(&s_mma[1], 1);
+        mbar_init(&s_tma[0], 1); mbar_init(&s_tma[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(2 * kBwdChunkN) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    if (Kp != K1)
+        for (int i = tid; i < kTileM * Kp * 2 / 16; i += kMlpThreads) reinterpret_cast<uint4*>(sA)[i] = make_uint4(0u, 0u, 0u, 0u);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -125,29 +132,38 @@ proj_dpre_kernel(const __grid_constant__ ProjDpreParams P) {
     const uint32_t tmem = s_tmem;
     const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
     constexpr uint32_t kIdesc = idesc_bf16(kTileM, kBwdChunkN, false, false);
-    uint32_t phase0 = 0u, phase1 = 0u;
+    uint32_t mma_phase0 = 0u, mma_phase1 = 0u, tma_phase0 = 0u, tma_phase1 = 0u;
     const int row = tid;
-    const __nv_bfloat16* __restrict__ w1 = static_cast<const __nv_bfloat16*>(P.w1);
     const float inv_h = 1.0f / static_cast<float>(H);
+    const int my_tiles = (P.n_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const long long total_chunks = static_cast<long long>(my_tiles) * 2 * NC;
 
-    auto stage_chunk = [&](int c, unsigned char* dst) {
-        const __nv_bfloat16* src = w1 + static_cast<size_t>(c) * kBwdChunkN * K1;
-        for (int e = tid; e < kBwdChunkN * (K1 / 8); e += kMlpThreads) {
-            const int n = e / (K1 / 8), k8 = e % (K1 / 8);
-            *reinterpret_cast<uint4*>(dst + canon_chunk_offset(n, k8, K1)) = __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(n) * K1 + k8 * 8));
-        }
-    };
-    auto issue_chunk = [&](int g) {
-        tc_fence_after();
-        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB[g & 1]);
+    auto request_chunk = [&](long long q) {
+        const int c = static_cast<int>(q % (2 * NC)) % NC;
+        uint64_t* bar = &s_tma[q & 1];
+        mbar_expect_tx(bar, kChunkBytes);
 #pragma unroll
-        for (int k = 0; k < K1 / 16; ++k)
-            umma_bf16(tmem + (g & 1) * kBwdChunkN, umma_desc(a0 + k * 256, 128, (K1 / 8) * 128), umma_desc(b0 + k * 256, 128, (K1 / 8) * 128),
-                      kIdesc, k > 0 ? 1u : 0u);
-        umma_commit(&s_bar[g & 1]);
+        for (int b = 0; b < Kp / 64; ++b) tma_load_2d(sB[q & 1] + b * 16384, &map_w1, b * 64, c * kBwdChunkN, bar);
     };
+    auto issue_chunk = [&](long long q) {
+        if (q & 1) { mbar_wait(&s_tma[1], tma_phase1); tma_phase1 ^= 1u; }
+        else { mbar_wait(&s_tma[0], tma_phase0); tma_phase0 ^= 1u; }
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB[q & 1]);
+#pragma unroll
+        for (int k = 0; k < Kp / 16; ++k)
+            umma_bf16(tmem + static_cast<uint32_t>(q & 1) * kBwdChunkN, umma_desc(a0 + k * 256, 128, (Kp / 8) * 128),
+                      umma_desc_sw128(b0 + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), kIdesc, k > 0 ? 1u : 0u);
+        umma_commit(&s_mma[q & 1]);
+    };
+    if (tid == 0 && total_chunks > 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_w1)) : "memory");
+        request_chunk(0);
+        if (total_chunks > 1) request_chunk(1);
+    }
 
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+    long long q0 = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, q0 += 2 * NC) {
         const long long p0 = static_cast<long long>(tile) * kTileM;
         const int n_valid = static_cast<int>(P.n - p0 < kTileM ? P.n - p0 : kTileM);
         const float* tile_base = P.x + p0 * P.x_stride;
@@ -171,17 +187,16 @@ proj_dpre_kernel(const __grid_constant__ ProjDpreParams P) {
                 const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
                 const int k8 = (c % K1) >> 3;
                 const uint4 pk = make_uint4(pack_bf16(va[u].x, va[u].y), pack_bf16(va[u].z, va[u].w), pack_bf16(vb[u].x, vb[u].y), pack_bf16(vb[u].z, vb[u].w));
-                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(r, k8, K1)) = pk;
+                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(r, k8, Kp)) = pk;
                 // bf16 copy of the features for the dW1 GEMM (the contraction over points reads it as a (points, K1) matrix)
                 if (P.x_bf16_out && r < n_valid)
                     *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(P.x_bf16_out) + (p0 + r) * K1 + k8 * 8) = pk;
             }
         }
-        stage_chunk(0, sB[0]);
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
-        if (tid == 0) issue_chunk(0);
+        if (tid == 0) issue_chunk(q0);
 
         const bool live = row < n_valid;
         const float mean = live ? __ldg(P.stats + 2 * (p0 + row)) : 0.0f;
@@ -191,18 +206,18 @@ proj_dpre_kernel(const __grid_constant__ ProjDpreParams P) {
         float s1 = 0.0f, s2 = 0.0f;                       // sum_j t_j, sum_j t_j xh_j
 
         for (int g = 0; g < 2 * NC; ++g) {
+            const long long qs = q0 + g;
             const int c = g < NC ? g : g - NC;
             if (g + 1 < 2 * NC) {
-                stage_chunk(g + 1 < NC ? g + 1 : g + 1 - NC, sB[(g + 1) & 1]);
-                fence_async_smem();
                 tc_fence_before();
                 __syncthreads();
-                if (tid == 0) issue_chunk(g + 1);
+                if (tid == 0) issue_chunk(qs + 1);
             }
-            if (g & 1) { mbar_wait(&s_bar[1], phase1); phase1 ^= 1u; }
-            else { mbar_wait(&s_bar[0], phase0); phase0 ^= 1u; }
+            if (qs & 1) { mbar_wait(&s_mma[1], mma_phase1); mma_phase1 ^= 1u; }
+            else { mbar_wait(&s_mma[0], mma_phase0); mma_phase0 ^= 1u; }
             tc_fence_after();
-            const uint32_t t_base = tmem + lane_off + (g & 1) * kBwdChunkN;
+            if (tid == 0 && qs + 2 < total_chunks) request_chunk(qs + 2);
+            const uint32_t t_base = tmem + lane_off + static_cast<uint32_t>(qs & 1) * kBwdChunkN;
 #pragma unroll 1
             for (int q = 0; q < kBwdChunkN / 32; ++q) {
                 const int col0 = c * kBwdChunkN + q * 32;
@@ -270,15 +285,19 @@ proj_dpre_kernel(const __grid_constant__ ProjDpreParams P) {
 
 template <int K1>
 static cudaError_t launch_dpre_k(const ProjDpreParams& P, int n_sms, cudaStream_t s) {
-    const size_t smem = static_cast<size_t>(kTileM + 2 * kBwdChunkN) * K1 * 2 + static_cast<size_t>(3) * P.hidden * sizeof(float);
+    constexpr int Kp = (K1 + 63) / 64 * 64;
+    const size_t smem = static_cast<size_t>(2) * (Kp / 64) * 16384 + static_cast<size_t>(kTileM) * Kp * 2 +
+                        static_cast<size_t>(3) * P.hidden * sizeof(float) + 1024;
+    CUtensorMap map_w1;
+    if (!make_map_bf16(&map_w1, P.w1, P.hidden, K1, K1, kBwdChunkN)) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(proj_dpre_kernel<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
+    int per_sm = static_cast<int>(232448u / (smem + 2048));       // 227 KB of shared memory per SM, ~1 KB reserved per CTA
     if (per_sm > 2) per_sm = 2;
     if (per_sm < 1) per_sm = 1;
     int grid = n_sms * per_sm;
     if (grid > P.n_tiles) grid = P.n_tiles;
-    proj_dpre_kernel<K1><<<grid, kMlpThreads, smem, s>>>(P);
+    proj_dpre_kernel<K1><<<grid, kMlpThreads, smem, s>>>(map_w1, P);
     return cudaGetLastError();
 }
 

@@ -1,0 +1,51 @@
+// proj_common.cuh -- TMA / mbarrier / SWIZZLE_128B descriptor helpers shared by proj_kernels.cu and proj_bwd_kernels.cu.
+#pragma once
+#include <cuda.h>
+
+#include "mlp_common.cuh"
+
+namespace de {
+namespace mlp {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// shared pieces
+// ---------------------------------------------------------------------------------------------------------------------
+// K-major SWIZZLE_128B operand: start address, LBO (unused for swizzled K-major: 1), SBO = 1024 B between 8-row atoms
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFFu);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= 1ull << 46;                        // descriptor version 1 (Blackwell)
+    d |= 2ull << 61;                        // layout type SWIZZLE_128B
+    return d;
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+
+// Chan's parallel update: fold a block of `nb` values with mean mb and centred sum of squares m2b into (n, mean, m2)
+__device__ __forceinline__ void chan_merge(float& n, float& mean, float& m2, float nb, float mb, float m2b) {
+    const float tot = n + nb;
+    const float delta = mb - mean;
+    mean += delta * (nb / tot);
+    m2 += m2b + delta * delta * (n * nb / tot);
+    n = tot;
+}
+
+
+}  // namespace mlp
+
+// host: tensor map of a row-major bf16 matrix (rows, cols), leading dimension ld elements, box {64 columns, box_rows},
+// 128 B swizzle (proj_kernels.cu)
+bool make_map_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows);
+
+}  // namespace de

@@ -25,75 +25,47 @@
 
 #include "launch.h"
 #include "mlp_common.cuh"
+#include "proj_common.cuh"
 
 namespace de {
 
 using namespace mlp;
-
-namespace {
-
-// ---------------------------------------------------------------------------------------------------------------------
-// shared pieces
-// ---------------------------------------------------------------------------------------------------------------------
-// K-major SWIZZLE_128B operand: start address, LBO (unused for swizzled K-major: 1), SBO = 1024 B between 8-row atoms
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFFu);
-    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
-    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
-    d |= 1ull << 46;                        // descriptor version 1 (Blackwell)
-    d |= 2ull << 61;                        // layout type SWIZZLE_128B
-    return d;
-}
-
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
-}
-
-// Chan's parallel update: fold a block of `nb` values with mean mb and centred sum of squares m2b into (n, mean, m2)
-__device__ __forceinline__ void chan_merge(float& n, float& mean, float& m2, float nb, float mb, float m2b) {
-    const float tot = n + nb;
-    const float delta = mb - mean;
-    mean += delta * (nb / tot);
-    m2 += m2b + delta * delta * (n * nb / tot);
-    n = tot;
-}
-
-}  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------------
 // kernel 1: hidden activations
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kChunkN = 128;                                    // hidden columns per MMA chunk / TMEM buffer
 
-// dynamic shared memory: A [128 x K1] | B[2] [128 x K1]   (bf16, UMMA canonical K-major no-swizzle)
+// W1 chunks arrive by TMA: {64 k, 128 rows} boxes with the 128 B swizzle, Kp / 64 boxes per chunk (Kp = K1 rounded up to 64;
+// columns past K1 are zero-filled by the copy engine, and the A tile carries the same zero columns).  The chunk stream is
+// continuous across the CTA's tiles -- chunk q + 2 is requested as soon as the MMAs of chunk q have released its buffer,
+// i.e. one whole epilogue ahead of its use -- so no thread ever waits for weights.
+// dynamic shared memory (1024 B aligned): B[2] [Kp / 64 boxes x 16 KB] | A [128 x Kp] bf16, canonical K-major no-swizzle
 template <int K1>
 __global__ void __launch_bounds__(kMlpThreads)
-proj_hidden_kernel(const __grid_constant__ ProjHiddenParams P) {
-    extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t s_bar[2];
+proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_constant__ ProjHiddenParams P) {
+    constexpr int Kp = (K1 + 63) / 64 * 64;
+    constexpr uint32_t kChunkBytes = (Kp / 64) * 16384;
+    extern __shared__ unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t s_mma[2], s_tma[2];
     __shared__ uint32_t s_tmem;
-    unsigned char* sA = smem;
-    unsigned char* sB[2] = {smem + kTileM * K1 * 2, smem + kTileM * K1 * 2 + kChunkN * K1 * 2};
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    unsigned char* sB[2] = {smem, smem + kChunkBytes};
+    unsigned char* sA = smem + 2 * kChunkBytes;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int H = P.hidden, NC = H / kChunkN;
 
     if (tid == 0) {
-        mbar_init(&s_bar[0], 1);
-        mbar_init(&s_bar[1], 1);
+        mbar_init(&s_mma[0], 1); mbar_init(&s_mma[1], 1);
+        mbar_init(&s_tma[0], 1); mbar_init(&s_tma[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(2 * kChunkN) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    if (Kp != K1)                                               // the pad columns of the A tile stay zero for the CTA's life
+        for (int i = tid; i < kTileM * Kp * 2 / 16; i += kMlpThreads) reinterpret_cast<uint4*>(sA)[i] = make_uint4(0u, 0u, 0u, 0u);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -101,29 +73,38 @@ proj_hidden_kernel(const __grid_constant__ ProjHiddenParams P) {
     const uint32_t tmem = s_tmem;
     const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
     constexpr uint32_t kIdesc = idesc_bf16(kTileM, kChunkN, false, false);
-    uint32_t phase0 = 0u, phase1 = 0u;
+    uint32_t mma_phase0 = 0u, mma_phase1 = 0u;                  // every thread waits on the MMA barriers
+    uint32_t tma_phase0 = 0u, tma_phase1 = 0u;                  // thread 0 only
     const int row = tid;
-    const __nv_bfloat16* __restrict__ w1 = static_cast<const __nv_bfloat16*>(P.w1);
+    const int my_tiles = (P.n_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const long long total_chunks = static_cast<long long>(my_tiles) * 2 * NC;
 
-    // W1 rows [c * 128, c * 128 + 128) -> canonical B tile
-    auto stage_chunk = [&](int c, unsigned char* dst) {
-        const __nv_bfloat16* src = w1 + static_cast<size_t>(c) * kChunkN * K1;
-        for (int e = tid; e < kChunkN * (K1 / 8); e += kMlpThreads) {
-            const int n = e / (K1 / 8), k8 = e % (K1 / 8);
-            *reinterpret_cast<uint4*>(dst + canon_chunk_offset(n, k8, K1)) = __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(n) * K1 + k8 * 8));
-        }
-    };
-    auto issue_chunk = [&](int g) {                    // g: running chunk number of this tile (0 .. 2 NC - 1)
-        tc_fence_after();
-        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB[g & 1]);
+    auto request_chunk = [&](long long q) {                     // thread 0: W1 rows of stream position q -> buffer q & 1
+        const int c = static_cast<int>(q % (2 * NC)) % NC;
+        uint64_t* bar = &s_tma[q & 1];
+        mbar_expect_tx(bar, kChunkBytes);
 #pragma unroll
-        for (int k = 0; k < K1 / 16; ++k)
-            umma_bf16(tmem + (g & 1) * kChunkN, umma_desc(a0 + k * 256, 128, (K1 / 8) * 128), umma_desc(b0 + k * 256, 128, (K1 / 8) * 128),
-                      kIdesc, k > 0 ? 1u : 0u);
-        umma_commit(&s_bar[g & 1]);
+        for (int b = 0; b < Kp / 64; ++b) tma_load_2d(sB[q & 1] + b * 16384, &map_w1, b * 64, c * kChunkN, bar);
     };
+    auto issue_chunk = [&](long long q) {                       // thread 0: wait for the weights, then the chunk's MMAs
+        if (q & 1) { mbar_wait(&s_tma[1], tma_phase1); tma_phase1 ^= 1u; }
+        else { mbar_wait(&s_tma[0], tma_phase0); tma_phase0 ^= 1u; }
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB[q & 1]);
+#pragma unroll
+        for (int k = 0; k < Kp / 16; ++k)
+            umma_bf16(tmem + static_cast<uint32_t>(q & 1) * kChunkN, umma_desc(a0 + k * 256, 128, (Kp / 8) * 128),
+                      umma_desc_sw128(b0 + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024), kIdesc, k > 0 ? 1u : 0u);
+        umma_commit(&s_mma[q & 1]);
+    };
+    if (tid == 0 && total_chunks > 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_w1)) : "memory");
+        request_chunk(0);
+        if (total_chunks > 1) request_chunk(1);
+    }
 
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+    long long q0 = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, q0 += 2 * NC) {
         const long long p0 = static_cast<long long>(tile) * kTileM;
         const int n_valid = static_cast<int>(P.n - p0 < kTileM ? P.n - p0 : kTileM);
         const float* tile_base = P.x + p0 * P.x_stride;
@@ -147,32 +128,31 @@ proj_hidden_kernel(const __grid_constant__ ProjHiddenParams P) {
                 const int c = lane + 32 * (it0 + u);
                 const int r = warp * 32 + (c / K1) * 8 + ((c % K1) & 7);
                 const int k8 = (c % K1) >> 3;
-                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(r, k8, K1)) =
+                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(r, k8, Kp)) =
                     make_uint4(pack_bf16(va[u].x, va[u].y), pack_bf16(va[u].z, va[u].w), pack_bf16(vb[u].x, vb[u].y), pack_bf16(vb[u].z, vb[u].w));
             }
         }
-        stage_chunk(0, sB[0]);
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
-        if (tid == 0) issue_chunk(0);
+        if (tid == 0) issue_chunk(q0);
 
         float cnt = 0.0f, mean = 0.0f, m2 = 0.0f, rstd = 0.0f;
         __nv_bfloat16* out_row = static_cast<__nv_bfloat16*>(P.hidden_out) + (p0 + row) * static_cast<long long>(P.hidden_stride);
         for (int g = 0; g < 2 * NC; ++g) {
+            const long long q = q0 + g;
             const int c = g < NC ? g : g - NC;
-            // next chunk's weights travel and its MMAs run while this chunk's epilogue executes
+            // the next chunk's MMAs run while this chunk's epilogue executes
             if (g + 1 < 2 * NC) {
-                stage_chunk(g + 1 < NC ? g + 1 : g + 1 - NC, sB[(g + 1) & 1]);
-                fence_async_smem();
                 tc_fence_before();
-                __syncthreads();                      // everyone is done reading TMEM buffer (g + 1) & 1 (chunk g - 1)
-                if (tid == 0) issue_chunk(g + 1);
+                __syncthreads();                      // everyone is done reading TMEM buffer (q + 1) & 1 (chunk q - 1)
+                if (tid == 0) issue_chunk(q + 1);
             }
-            if (g & 1) { mbar_wait(&s_bar[1], phase1); phase1 ^= 1u; }
-            else { mbar_wait(&s_bar[0], phase0); phase0 ^= 1u; }
+            if (q & 1) { mbar_wait(&s_mma[1], mma_phase1); mma_phase1 ^= 1u; }
+            else { mbar_wait(&s_mma[0], mma_phase0); mma_phase0 ^= 1u; }
             tc_fence_after();
-            const uint32_t t_base = tmem + lane_off + (g & 1) * kChunkN;
+            if (tid == 0 && q + 2 < total_chunks) request_chunk(q + 2);      // buffer q & 1 is free again
+            const uint32_t t_base = tmem + lane_off + static_cast<uint32_t>(q & 1) * kChunkN;
             if (g < NC) {
                 // ---- pass 1: row statistics ---------------------------------------------------------------------------
 #pragma unroll 1
@@ -226,7 +206,7 @@ proj_hidden_kernel(const __grid_constant__ ProjHiddenParams P) {
             }
         }
         tc_fence_before();
-        __syncthreads();          // the next tile overwrites sA / sB[0] and TMEM buffer 0
+        __syncthreads();          // the next tile overwrites the A tile and TMEM buffer q0 & 1
     }
     tc_fence_before();
     __syncthreads();
@@ -432,6 +412,8 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
+}  // namespace
+
 // row-major bf16 matrix (rows, cols), leading dimension ld elements; box = {64 columns, box_rows}, 128 B swizzle.
 // K-major operand (M or N rows, K columns): box_rows = the tile's MN extent; MN-major operand (K rows, MN columns): 64.
 bool make_map_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows) {
@@ -446,8 +428,6 @@ bool make_map_bf16(CUtensorMap* map, const void* base, long long rows, long long
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-}  // namespace
-
 bool proj_hidden_supported(int in_dim, int hidden) {
     const bool k_ok = in_dim == 32 || in_dim == 48 || in_dim == 64 || in_dim == 96 || in_dim == 128;
     return k_ok && hidden >= kChunkN && hidden % kChunkN == 0 && hidden <= 4096;
@@ -455,15 +435,18 @@ bool proj_hidden_supported(int in_dim, int hidden) {
 
 template <int K1>
 static cudaError_t launch_hidden_k(const ProjHiddenParams& P, int n_sms, cudaStream_t s) {
-    const size_t smem = static_cast<size_t>(kTileM + 2 * kChunkN) * K1 * 2;
+    constexpr int Kp = (K1 + 63) / 64 * 64;
+    const size_t smem = static_cast<size_t>(2) * (Kp / 64) * 16384 + static_cast<size_t>(kTileM) * Kp * 2 + 1024;
+    CUtensorMap map_w1;
+    if (!make_map_bf16(&map_w1, P.w1, P.hidden, K1, K1, kChunkN)) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(proj_hidden_kernel<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
+    int per_sm = static_cast<int>(232448u / (smem + 2048));       // 227 KB of shared memory per SM, ~1 KB reserved per CTA
     if (per_sm > 2) per_sm = 2;                                   // 2 x 256 TMEM columns
     if (per_sm < 1) per_sm = 1;
     int grid = n_sms * per_sm;
     if (grid > P.n_tiles) grid = P.n_tiles;
-    proj_hidden_kernel<K1><<<grid, kMlpThreads, smem, s>>>(P);
+    proj_hidden_kernel<K1><<<grid, kMlpThreads, smem, s>>>(map_w1, P);
     return cudaGetLastError();
 }
 
