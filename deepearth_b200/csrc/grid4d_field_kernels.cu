@@ -57,13 +57,53 @@ __global__ void __launch_bounds__(256) field_xyzt_kernel(const FieldParams Fp, f
     reinterpret_cast<float4*>(xyzt)[p] = field_point(Fp, gi, gj);
 }
 
+// one (point, level) of the lane pair: cell, the lane's four corner indices, and -- after the gathers -- the feature sum
+template <int F, bool POW2>
+struct FieldLevel {
+    float w[3];
+    uint32_t idx[4];
+    __device__ __forceinline__ void prepare(const LevelParams& lv, const float4& c, int ox) {
+        float x[3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) x[d] = pick4(c, lv.dim[d]);
+        long long g[3];
+        cell_of<3>(lv, x, g, w);
+        CellTerms<3, POW2> ct;
+        ct.set(lv, g, ox);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) idx[j] = ct.index(lv, j);
+    }
+    __device__ __forceinline__ void finish(const float (&v)[4][F], int ox, unsigned pair_mask, float out_scale, float* dst) const {
+        float acc[F];
+#pragma unroll
+        for (int f = 0; f < F; ++f) acc[f] = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float wk = pair_weight<3>(w, ox, j);
+#pragma unroll
+            for (int f = 0; f < F; ++f) acc[f] = __fmaf_rn(wk, v[j][f], acc[f]);
+        }
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            acc[f] = __fadd_rn(acc[f], __shfl_xor_sync(pair_mask, acc[f], 1));
+            if (out_scale != 1.0f) acc[f] = __fmul_rn(acc[f], out_scale);
+        }
+        if constexpr (F == 1) {
+            if (ox == 0) dst[0] = acc[0];
+        } else {
+#pragma unroll
+            for (int f = 0; f < F / 2; ++f) dst[ox * (F / 2) + f] = ox ? acc[F / 2 + f] : acc[f];
+        }
+    }
+};
+
 template <typename TT, int F, bool POW2>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 3)
 grid4d_field_forward_kernel(const __grid_constant__ EncodeParams P, const __grid_constant__ FieldParams Fp) {
-    constexpr int D = 3, J = PairGeom<D>::kCombos;
     __shared__ LevelParams s_lv[kMaxGroup];
     __shared__ float4 s_xyzt[kFieldPoints];
-    extern __shared__ float s_out[];                               // [256 points][G * F]
+    __shared__ double s_lat[kFieldTile][2], s_lon[kFieldTile][2];
+    extern __shared__ float s_out[];                               // [256 points][G * F + F]: rows padded against bank conflicts
     const int G = P.group_size;
     const int group = blockIdx.x / P.n_tiles;
     const int tile = blockIdx.x - group * P.n_tiles;
@@ -73,11 +113,30 @@ grid4d_field_forward_kernel(const __grid_constant__ EncodeParams P, const __grid
 
     const int tiles_lon = (Fp.n_lon + kFieldTile - 1) / kFieldTile;
     const int ti = tile / tiles_lon, tj = tile - ti * tiles_lon;
+    // the trigonometry depends on the row (latitude) or the column (longitude) only: 16 + 16 evaluations per patch
+    if (threadIdx.x < kFieldTile) {
+        const int gi = min(ti * kFieldTile + static_cast<int>(threadIdx.x), Fp.n_lat - 1);
+        const LatTerms t = geodetic_lat_terms(linspace_at(Fp.lat_start, Fp.lat_stop, Fp.lat_step, Fp.n_lat, gi), Fp.altitude);
+        s_lat[threadIdx.x][0] = t.a1;
+        s_lat[threadIdx.x][1] = t.z;
+    } else if (threadIdx.x >= 32 && threadIdx.x < 32 + kFieldTile) {
+        const int j = threadIdx.x - 32;
+        const int gj = min(tj * kFieldTile + j, Fp.n_lon - 1);
+        const LonTerms t = geodetic_lon_terms(linspace_at(Fp.lon_start, Fp.lon_stop, Fp.lon_step, Fp.n_lon, gj));
+        s_lon[j][0] = t.co;
+        s_lon[j][1] = t.so;
+    }
+    __syncthreads();
     {
-        const int gi = ti * kFieldTile + (threadIdx.x >> 4), gj = tj * kFieldTile + (threadIdx.x & 15);
+        const int li = threadIdx.x >> 4, lj = threadIdx.x & 15;
+        const int gi = ti * kFieldTile + li, gj = tj * kFieldTile + lj;
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         if (gi < Fp.n_lat && gj < Fp.n_lon) {
-            c = field_point(Fp, gi, gj);
+            const double a1 = s_lat[li][0];
+            c.x = norm_coord(a1 * s_lon[lj][0], Fp.bbox_min[0], Fp.bbox_span[0]);      // ecef_from_geodetic, factored
+            c.y = norm_coord(a1 * s_lon[lj][1], Fp.bbox_min[1], Fp.bbox_span[1]);
+            c.z = norm_coord(s_lat[li][1], Fp.bbox_min[2], Fp.bbox_span[2]);
+            c.w = Fp.has_time ? norm_coord(Fp.time, Fp.t_min, Fp.t_span) : 0.0f;
             if (Fp.xyzt_out && group == 0) reinterpret_cast<float4*>(Fp.xyzt_out)[static_cast<long long>(gi) * Fp.n_lon + gj] = c;
         }
         s_xyzt[threadIdx.x] = c;
@@ -87,61 +146,43 @@ grid4d_field_forward_kernel(const __grid_constant__ EncodeParams P, const __grid
     const int ox = threadIdx.x & 1;
     const unsigned pair_mask = 3u << (threadIdx.x & 30);
     const L2Policies pol = make_l2_policies(P.l2_hints != 0);
-    const int row_floats = G * F;
+    const int row_floats = G * F + F;
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         const int pt = (threadIdx.x >> 1) + 128 * pass;           // a warp: 16 consecutive points of one patch row
         const float4 c = s_xyzt[pt];
-#pragma unroll 2
-        for (int l = 0; l < n_lv; ++l) {
-            const LevelParams& lv = s_lv[l];
-            float x[D];
+        float* row = s_out + pt * row_floats;
+        // two levels per trip: eight gathers in flight per lane
+#pragma unroll 1
+        for (int l = 0; l < n_lv; l += 2) {
+            const bool two = l + 1 < n_lv;
+            const LevelParams& lva = s_lv[l];
+            const LevelParams& lvb = s_lv[two ? l + 1 : l];
+            FieldLevel<F, POW2> A, B;
+            A.prepare(lva, c, ox);
+            B.prepare(lvb, c, ox);
+            float va[4][F], vb[4][F];
 #pragma unroll
-            for (int d = 0; d < D; ++d) x[d] = pick4(c, lv.dim[d]);
-            long long g[D];
-            float w[D];
-            cell_of<D>(lv, x, g, w);
-            CellTerms<D, POW2> ct;
-            ct.set(lv, g, ox);
-            uint32_t idx[J];
+            for (int j = 0; j < 4; ++j) load_entry_hint<TT, F>(lva.table, A.idx[j], va[j], pol.keep);
 #pragma unroll
-            for (int j = 0; j < J; ++j) idx[j] = ct.index(lv, j);
-            float v[J][F];
-#pragma unroll
-            for (int j = 0; j < J; ++j) load_entry_hint<TT, F>(lv.table, idx[j], v[j], pol.keep);
-            float acc[F];
-#pragma unroll
-            for (int f = 0; f < F; ++f) acc[f] = 0.0f;
-#pragma unroll
-            for (int j = 0; j < J; ++j) {
-                const float wk = pair_weight<D>(w, ox, j);
-#pragma unroll
-                for (int f = 0; f < F; ++f) acc[f] = __fmaf_rn(wk, v[j][f], acc[f]);
-            }
-#pragma unroll
-            for (int f = 0; f < F; ++f) {
-                acc[f] = __fadd_rn(acc[f], __shfl_xor_sync(pair_mask, acc[f], 1));
-                if (P.out_scale != 1.0f) acc[f] = __fmul_rn(acc[f], P.out_scale);
-            }
-            float* dst = s_out + pt * row_floats + l * F;
-            if constexpr (F == 1) {
-                if (ox == 0) dst[0] = acc[0];
-            } else {
-#pragma unroll
-                for (int f = 0; f < F / 2; ++f) dst[ox * (F / 2) + f] = ox ? acc[F / 2 + f] : acc[f];
-            }
+            for (int j = 0; j < 4; ++j) load_entry_hint<TT, F>(lvb.table, B.idx[j], vb[j], pol.keep);
+            A.finish(va, ox, pair_mask, P.out_scale, row + l * F);
+            if (two) B.finish(vb, ox, pair_mask, P.out_scale, row + (l + 1) * F);      // pair-uniform: both lanes share l
         }
     }
     __syncthreads();
-    // rows leave the CTA piecewise: consecutive threads write consecutive floats of a point's slice
+    // rows leave the CTA one point per warp trip: consecutive lanes write consecutive floats of the point's slice
     const int n_out = n_lv * F;
-    for (int e = threadIdx.x; e < kFieldPoints * n_out; e += kThreads) {
-        const int pt = e / n_out, c = e - pt * n_out;
-        const int gi = ti * kFieldTile + (pt >> 4), gj = tj * kFieldTile + (pt & 15);
-        if (gi >= Fp.n_lat || gj >= Fp.n_lon) continue;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int c0 = 0; c0 < n_out; c0 += 32) {
+        const int c = c0 + lane;
         const int l = c / F;
-        const long long p = static_cast<long long>(gi) * Fp.n_lon + gj;
-        __stcs(P.out + p * P.out_stride + s_lv[l].out_col + (c - l * F), s_out[pt * row_floats + c]);
+        const unsigned long long col = c < n_out ? s_lv[l].out_col + static_cast<unsigned>(c - l * F) : 0ull;
+        for (int pt = warp; pt < kFieldPoints; pt += kThreads / 32) {
+            const int gi = ti * kFieldTile + (pt >> 4), gj = tj * kFieldTile + (pt & 15);
+            if (c < n_out && gi < Fp.n_lat && gj < Fp.n_lon)
+                __stcs(P.out + (static_cast<long long>(gi) * Fp.n_lon + gj) * P.out_stride + col, s_out[pt * row_floats + c]);
+        }
     }
 }
 
@@ -156,14 +197,14 @@ static cudaError_t field_f(const EncodeParams& P, const FieldParams& Fp, int F, 
     return cudaGetLastError();
 }
 
-int field_max_group(int F) { return 32 / F; }           // 256 points x G x F floats = 32 KB of shared memory
+int field_max_group(int F) { return 32 / F; }           // 256 points x (G x F + F) floats <= 36 KB of shared memory
 
 cudaError_t launch_field_forward(EncodeParams P, const FieldParams& Fp, bool half_tables, int F, bool pow2, cudaStream_t s) {
     const long long tiles = static_cast<long long>((Fp.n_lat + kFieldTile - 1) / kFieldTile) * ((Fp.n_lon + kFieldTile - 1) / kFieldTile);
     if (tiles * P.n_groups >= (1ll << 31)) return cudaErrorInvalidValue;
     P.n_tiles = static_cast<int>(tiles);
     const unsigned blocks = static_cast<unsigned>(tiles * P.n_groups);
-    const size_t smem = static_cast<size_t>(kFieldPoints) * P.group_size * F * sizeof(float);
+    const size_t smem = static_cast<size_t>(kFieldPoints) * (P.group_size * F + F) * sizeof(float);
     if (half_tables) return pow2 ? field_f<__half, true>(P, Fp, F, blocks, smem, s) : field_f<__half, false>(P, Fp, F, blocks, smem, s);
     return pow2 ? field_f<float, true>(P, Fp, F, blocks, smem, s) : field_f<float, false>(P, Fp, F, blocks, smem, s);
 }

@@ -54,26 +54,35 @@ small1d_forward_kernel(const __grid_constant__ EncodeParams P, const __grid_cons
     const TT* s_tab = reinterpret_cast<const TT*>(s_raw + S.off[lane_level]);
     const int p_step = kThreads / G;
     const long long p_end = min(P.n_points, (static_cast<long long>(blockIdx.x) + 1) * P.points_per_cta);
-    for (long long p = static_cast<long long>(blockIdx.x) * P.points_per_cta + threadIdx.x / G; p < p_end; p += p_step) {
-        const uint32_t idx = index_1d(lv, coord_1d(P, lv, p));
-        bool has_mask;
-        const float m = row_mask(P, lv, p, has_mask);
-        float v[F];
-        if (idx < live) {
+    // four points per trip: the coordinate loads of all four are in flight before the first dependent shared-memory read
+    for (long long p = static_cast<long long>(blockIdx.x) * P.points_per_cta + threadIdx.x / G; p < p_end; p += 4 * p_step) {
+        float t[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) t[u] = (p + u * p_step < p_end) ? coord_1d(P, lv, p + u * p_step) : 0.0f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const long long pu = p + u * p_step;
+            if (pu >= p_end) break;
+            const uint32_t idx = index_1d(lv, t[u]);
+            bool has_mask;
+            const float m = row_mask(P, lv, pu, has_mask);
+            float v[F];
+            if (idx < live) {
+#pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    if constexpr (sizeof(TT) == 4) v[f] = reinterpret_cast<const float*>(s_tab)[idx * F + f];
+                    else v[f] = __half2float(reinterpret_cast<const __half*>(s_tab)[idx * F + f]);
+                }
+            } else {
+                EntryLoader<TT, F>::load(lv.table, idx, v);
+            }
 #pragma unroll
             for (int f = 0; f < F; ++f) {
-                if constexpr (sizeof(TT) == 4) v[f] = reinterpret_cast<const float*>(s_tab)[idx * F + f];
-                else v[f] = __half2float(reinterpret_cast<const __half*>(s_tab)[idx * F + f]);
+                if (P.out_scale != 1.0f) v[f] = __fmul_rn(v[f], P.out_scale);
+                if (has_mask) v[f] = __fmul_rn(v[f], m);           // encoders.py:73-79
             }
-        } else {
-            EntryLoader<TT, F>::load(lv.table, idx, v);
+            store_row<F>(P.out + pu * P.out_stride + lv.out_col, v, P.vec_rows != 0);
         }
-#pragma unroll
-        for (int f = 0; f < F; ++f) {
-            if (P.out_scale != 1.0f) v[f] = __fmul_rn(v[f], P.out_scale);
-            if (has_mask) v[f] = __fmul_rn(v[f], m);           // encoders.py:73-79
-        }
-        store_row<F>(P.out + p * P.out_stride + lv.out_col, v, P.vec_rows != 0);
     }
 }
 
@@ -96,18 +105,33 @@ small1d_backward_kernel(const __grid_constant__ EncodeParams P, const __grid_con
         // private copy of the level's live rows for this point slot: the lanes of one warp that share a level differ in slot
         float* mine = s_acc + S.off[lane_level] / 4 + static_cast<size_t>(slot & (S.copies[lane_level] - 1)) * live * F;
         const long long p_end = min(P.n_points, (static_cast<long long>(blockIdx.x) + 1) * P.points_per_cta);
-        for (long long p = static_cast<long long>(blockIdx.x) * P.points_per_cta + slot; p < p_end; p += p_step) {
-            bool has_mask;
-            const float m = row_mask(P, lv, p, has_mask);
-            if (has_mask && m == 0.0f) continue;
-            const uint32_t idx = index_1d(lv, coord_1d(P, lv, p));
-            float go[F];
-            load_row<F>(P.grad_out + p * P.out_stride + lv.out_col, go, P.vec_rows != 0);
-            if (idx < live) {
+        for (long long p = static_cast<long long>(blockIdx.x) * P.points_per_cta + slot; p < p_end; p += 4 * p_step) {
+            float t[4], go[4][F];
 #pragma unroll
-                for (int f = 0; f < F; ++f) atomicAdd(mine + idx * F + f, go[f]);
-            } else {
-                red_add_entry<F>(lv.grad, idx, go);
+            for (int u = 0; u < 4; ++u) {
+                const long long pu = p + u * p_step;
+                t[u] = 0.0f;
+#pragma unroll
+                for (int f = 0; f < F; ++f) go[u][f] = 0.0f;
+                if (pu < p_end) {
+                    t[u] = coord_1d(P, lv, pu);
+                    load_row<F>(P.grad_out + pu * P.out_stride + lv.out_col, go[u], P.vec_rows != 0);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long pu = p + u * p_step;
+                if (pu >= p_end) break;
+                bool has_mask;
+                const float m = row_mask(P, lv, pu, has_mask);
+                if (has_mask && m == 0.0f) continue;
+                const uint32_t idx = index_1d(lv, t[u]);
+                if (idx < live) {
+#pragma unroll
+                    for (int f = 0; f < F; ++f) atomicAdd(mine + idx * F + f, go[u][f]);
+                } else {
+                    red_add_entry<F>(lv.grad, idx, go[u]);
+                }
             }
         }
     }
