@@ -23,6 +23,8 @@
 // 128-byte atoms (stride byte offset 1024), exactly what a TMA box {64 bf16, rows} with CU_TENSOR_MAP_SWIZZLE_128B writes.
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "launch.h"
 #include "mlp_common.cuh"
 #include "proj_common.cuh"
@@ -221,11 +223,15 @@ constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 64, kGemmStages = 4;
 constexpr int kGemmThreads = 256;                      // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warps 4..7 epilogue
 constexpr uint32_t kGemmStageBytes = (kGemmBM + kGemmBN) * kGemmBK * 2;
 constexpr uint32_t kGemmSmemBytes = kGemmStages * kGemmStageBytes + 1024;   // + alignment slack
+constexpr int kGemmMulticastDefault = 0;              // flipped to 1 once the cluster path is validated on a B200
 
 // A_MN / B_MN = 1: the operand is stored with the contraction index as its ROW index ((K, M) resp. (K, N) row-major: a
 // "transposed" operand, MN-major in UMMA terms) and arrives as 64 x 64 boxes; 0: (M, K) resp. (N, K) row-major, K-major.
 // EPI 0: C fp32 = acc + bias; 1: C bf16 = acc + bias; 2: C fp32 += acc (red.global.add: split-K partial sums).
-template <int A_MN, int B_MN, int EPI>
+// MC = 2: thread-block clusters of two CTAs work on vertically adjacent output tiles; each loads its own A tile and HALF of
+// the shared B tile, multicast into both CTAs' shared memory -- 32 KB instead of 48 KB of L2 reads per CTA and k-block.  The
+// single-CTA kernel is L2-bandwidth bound (9.4 TB/s of operand traffic at 0.82 PFLOP/s against a ~12 TB/s fabric).
+template <int A_MN, int B_MN, int EPI, int MC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const __grid_constant__ GemmParams P) {
@@ -238,10 +244,13 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const long long tiles_m = (P.M + kGemmBM - 1) / kGemmBM;
     const int k_blocks_all = static_cast<int>((P.K + kGemmBK - 1) / kGemmBK);
     const int kb_per = (k_blocks_all + P.k_splits - 1) / P.k_splits;          // host guarantees every split is non-empty
-    const long long n_tiles = tiles_m * tiles_n * P.k_splits;                  // work items: (output tile, K split)
+    const long long tiles_mc = (tiles_m + MC - 1) / MC;                        // MC vertically adjacent tiles per cluster
+    const long long n_tiles = tiles_mc * tiles_n * P.k_splits;                 // work items: (output tile [pair], K split)
+    const uint32_t rank = MC > 1 ? cluster_rank() : 0u;
+    const long long unit = blockIdx.x / MC, n_units = gridDim.x / MC;          // the cluster is the scheduling unit
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kGemmStages; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 1); }
+        for (int i = 0; i < kGemmStages; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], MC); }
         for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -252,6 +261,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
+    if constexpr (MC > 1) cluster_sync_all();          // the peer's barriers exist before anything can arrive on them
     tc_fence_after();
     const uint32_t tmem = s_tmem;
 
@@ -261,10 +271,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
         int stage = 0;
         uint32_t phase = 0;
-        for (long long work = blockIdx.x; work < n_tiles; work += gridDim.x) {
+        for (long long work = unit; work < n_tiles; work += n_units) {
             const long long tile = work / P.k_splits;
             const int split = static_cast<int>(work - tile * P.k_splits);
-            const int m0 = static_cast<int>(tile / tiles_n) * kGemmBM, n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
+            const int m0 = static_cast<int>((tile / tiles_n) * MC + rank) * kGemmBM, n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
             const int kb_end = min(k_blocks_all, (split + 1) * kb_per);
             for (int kb = split * kb_per; kb < kb_end; ++kb) {
                 mbar_wait(&s_empty[stage], phase ^ 1u);
@@ -277,7 +287,19 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 } else {
                     tma_load_2d(sa, &map_a, kb * kGemmBK, m0, &s_full[stage]);
                 }
-                if constexpr (B_MN) {
+                if constexpr (MC > 1) {
+                    // this CTA's half of the B tile, delivered to both CTAs (each full barrier expects the whole stage)
+                    if constexpr (B_MN) {
+#pragma unroll
+                        for (int i = 0; i < kGemmBN / 128; ++i) {
+                            const int bi = static_cast<int>(rank) * (kGemmBN / 128) + i;
+                            tma_load_2d_mc(sb + bi * 8192, &map_b, n0 + 64 * bi, kb * kGemmBK, &s_full[stage], 3);
+                        }
+                    } else {
+                        tma_load_2d_mc(sb + rank * (kGemmBN / 2) * kGemmBK * 2, &map_b, kb * kGemmBK, n0 + static_cast<int>(rank) * (kGemmBN / 2),
+                                       &s_full[stage], 3);
+                    }
+                } else if constexpr (B_MN) {
 #pragma unroll
                     for (int i = 0; i < kGemmBN / 64; ++i) tma_load_2d(sb + i * 8192, &map_b, n0 + 64 * i, kb * kGemmBK, &s_full[stage]);
                 } else {
@@ -293,7 +315,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         uint32_t phase = 0;
         int as = 0;
         uint32_t aphase = 0;
-        for (long long work = blockIdx.x; work < n_tiles; work += gridDim.x) {
+        for (long long work = unit; work < n_tiles; work += n_units) {
             const int split = static_cast<int>(work % P.k_splits);
             const int kb_begin = split * kb_per, kb_end = min(k_blocks_all, (split + 1) * kb_per);
             mbar_wait(&s_tempty[as], aphase ^ 1u);                  // epilogue has drained this accumulator
@@ -311,7 +333,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                     const uint64_t db = B_MN ? umma_desc_sw128(b0 + k * 2048, 8192, 1024) : umma_desc_sw128(b0 + k * 32, 16, 1024);
                     umma_bf16(tmem + as * kGemmBN, da, db, kIdesc, (kb > kb_begin || k) ? 1u : 0u);
                 }
-                umma_commit(&s_empty[stage]);                        // frees the slot when these MMAs have read it
+                if constexpr (MC > 1) umma_commit_mc(&s_empty[stage], 3);   // the slot is refilled by BOTH producers: tell both
+                else umma_commit(&s_empty[stage]);                   // frees the slot when these MMAs have read it
                 if (kb == kb_end - 1) umma_commit(&s_tfull[as]);     // accumulator complete
                 if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
             }
@@ -322,9 +345,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         const int quarter = warp & 3;                                // TMEM lanes this warp may read
         int as = 0;
         uint32_t aphase = 0;
-        for (long long work = blockIdx.x; work < n_tiles; work += gridDim.x) {
+        for (long long work = unit; work < n_tiles; work += n_units) {
             const long long tile = work / P.k_splits;
-            const long long m0 = (tile / tiles_n) * kGemmBM;
+            const long long m0 = ((tile / tiles_n) * MC + rank) * kGemmBM;
             const int n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
             mbar_wait(&s_tfull[as], aphase);
             tc_fence_after();
@@ -388,6 +411,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (MC > 1) cluster_sync_all();          // no CTA leaves while its peer may still write into it or signal it
     if (warp == 2)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
 }
@@ -462,13 +486,46 @@ cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaSt
     }
 }
 
-template <int A_MN, int B_MN, int EPI>
+template <int A_MN, int B_MN, int EPI, int MC>
 static cudaError_t launch_gemm_t(const CUtensorMap& map_a, const CUtensorMap& map_b, const GemmParams& P, int grid, cudaStream_t s) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(kGemmSmemBytes));
+    auto kernel = gemm_bf16_tma_kernel<A_MN, B_MN, EPI, MC>;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGemmSmemBytes));
     if (e != cudaSuccess) return e;
-    gemm_bf16_tma_kernel<A_MN, B_MN, EPI><<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
-    return cudaGetLastError();
+    if (MC == 1) {
+        kernel<<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
+        return cudaGetLastError();
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(static_cast<unsigned>(grid));
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = kGemmSmemBytes;
+    cfg.stream = s;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = MC;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, P);
+}
+
+template <int A_MN, int B_MN, int MC>
+static cudaError_t launch_gemm_e(const CUtensorMap& map_a, const CUtensorMap& map_b, const GemmParams& P, int epi, int grid, cudaStream_t s) {
+    switch (epi) {
+        case 0: return launch_gemm_t<A_MN, B_MN, 0, MC>(map_a, map_b, P, grid, s);
+        case 1: return launch_gemm_t<A_MN, B_MN, 1, MC>(map_a, map_b, P, grid, s);
+        default: return launch_gemm_t<A_MN, B_MN, 2, MC>(map_a, map_b, P, grid, s);
+    }
+}
+
+// DE_GEMM_MULTICAST (read once per process): 1 = two-CTA clusters with the B tile multicast, 0 = single CTAs
+static int gemm_multicast() {
+    static const int v = []() {
+        const char* e = getenv("DE_GEMM_MULTICAST");
+        return (e && *e) ? (atoi(e) != 0 ? 1 : 0) : kGemmMulticastDefault;
+    }();
+    return v;
 }
 
 // C (M, N) = A . B^T (+ bias | accumulated).  transposed = 0: A is (M, K), B is (N, K) row-major (K contiguous);
@@ -476,38 +533,31 @@ static cudaError_t launch_gemm_t(const CUtensorMap& map_a, const CUtensorMap& ma
 // epi: 0 fp32 store, 1 bf16 store, 2 fp32 atomic accumulation with the K range cut into `k_splits` work items per tile.
 cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int transposed, GemmParams P, int epi,
                              int n_sms, cudaStream_t s) {
+    const long long tiles_m = (P.M + kGemmBM - 1) / kGemmBM, tiles_n = (P.N + kGemmBN - 1) / kGemmBN;
+    const int mc = (gemm_multicast() && tiles_m >= 2) ? 2 : 1;
     CUtensorMap map_a, map_b;
     bool ok;
     if (transposed) ok = make_map_bf16(&map_a, a, P.K, P.M, lda, 64) && make_map_bf16(&map_b, b, P.K, P.N, ldb, 64);
-    else ok = make_map_bf16(&map_a, a, P.M, P.K, lda, kGemmBM) && make_map_bf16(&map_b, b, P.N, P.K, ldb, kGemmBN);
+    else ok = make_map_bf16(&map_a, a, P.M, P.K, lda, kGemmBM) && make_map_bf16(&map_b, b, P.N, P.K, ldb, kGemmBN / mc);
     if (!ok) return cudaErrorInvalidValue;
-    const long long tiles = ((P.M + kGemmBM - 1) / kGemmBM) * ((P.N + kGemmBN - 1) / kGemmBN);
+    const long long units = ((tiles_m + mc - 1) / mc) * tiles_n;           // scheduling units: tiles or vertical tile pairs
+    const long long max_units = n_sms / mc;
     const long long k_blocks = (P.K + kGemmBK - 1) / kGemmBK;
     long long splits = 1;
     if (epi == 2) {
-        splits = (n_sms + tiles - 1) / tiles;                       // fill the machine once
+        splits = (max_units + units - 1) / units;                   // fill the machine once
         if (splits > k_blocks) splits = k_blocks;
         if (splits < 1) splits = 1;
         const long long per = (k_blocks + splits - 1) / splits;
         splits = (k_blocks + per - 1) / per;                        // every split non-empty
     }
     P.k_splits = static_cast<int>(splits);
-    const long long work = tiles * splits;
-    const int grid = static_cast<int>(work < n_sms ? work : n_sms);
+    const long long work = units * splits;
+    const int grid = static_cast<int>((work < max_units ? work : max_units) * mc);
     const size_t elem = epi == 1 ? 2 : 4;
     P.vec_ok = (reinterpret_cast<uintptr_t>(P.c) % 32 == 0 && (P.ldc * elem) % 32 == 0) ? 1 : 0;
-    if (transposed) {
-        switch (epi) {
-            case 0: return launch_gemm_t<1, 1, 0>(map_a, map_b, P, grid, s);
-            case 1: return launch_gemm_t<1, 1, 1>(map_a, map_b, P, grid, s);
-            default: return launch_gemm_t<1, 1, 2>(map_a, map_b, P, grid, s);
-        }
-    }
-    switch (epi) {
-        case 0: return launch_gemm_t<0, 0, 0>(map_a, map_b, P, grid, s);
-        case 1: return launch_gemm_t<0, 0, 1>(map_a, map_b, P, grid, s);
-        default: return launch_gemm_t<0, 0, 2>(map_a, map_b, P, grid, s);
-    }
+    if (mc == 2) return transposed ? launch_gemm_e<1, 1, 2>(map_a, map_b, P, epi, grid, s) : launch_gemm_e<0, 0, 2>(map_a, map_b, P, epi, grid, s);
+    return transposed ? launch_gemm_e<1, 1, 1>(map_a, map_b, P, epi, grid, s) : launch_gemm_e<0, 0, 1>(map_a, map_b, P, epi, grid, s);
 }
 
 }  // namespace de
