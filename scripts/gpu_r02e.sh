@@ -27,3 +27,8 @@ except Exception as e:
 PY
 bash scripts/gpu_r02d.sh proj field c1r > gpurun_out/r02e_prof.log 2>&1
 tail -5 gpurun_out/r02e_prof.log
+# last (a fault here must not cost the rest): the two-CTA multicast GEMM
+DE_GEMM_MULTICAST=1 timeout 240 python -m pytest tests/test_projection.py -m gpu -q -s -x 2>&1 | tail -15 > gpurun_out/r02e_mc_pytest.txt
+tail -4 gpurun_out/r02e_mc_pytest.txt
+DE_GEMM_MULTICAST=1 timeout 200 python bench.py --extra-only projection_h768 --steps 3 > gpurun_out/r02e_mc_projection.json 2> gpurun_out/r02e_mc_projection.err || tail -3 gpurun_out/r02e_mc_projection.err
+head -c 900 gpurun_out/r02e_mc_projection.json; echo
