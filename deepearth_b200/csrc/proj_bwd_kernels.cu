@@ -20,6 +20,9 @@ namespace de {
 
 using namespace mlp;
 
+// fire-and-forget reduction (the pointer arrives through a parameter struct, so atomicAdd would compile to a generic ATOM)
+__device__ __forceinline__ void red_f32(float* p, float v) { asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
+
 // ---- gy fp32 -> bf16 copy + column sums (db2) -----------------------------------------------------------------------
 __global__ void __launch_bounds__(256) cast_colsum_kernel(const float* __restrict__ src, long long ld_src, __nv_bfloat16* __restrict__ dst,
                                                           long long ld_dst, long long n_rows, int n_cols, float* colsum,
@@ -45,7 +48,7 @@ __global__ void __launch_bounds__(256) cast_colsum_kernel(const float* __restric
 #pragma unroll
         for (int i = 0; i < 8; ++i) a += s_part[i][threadIdx.x];
         const int c = blockIdx.x * 128 + threadIdx.x;
-        if (c < n_cols) atomicAdd(colsum + c, a);
+        if (c < n_cols) red_f32(colsum + c, a);
     }
 }
 
@@ -273,9 +276,9 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
     }
     // one flush per CTA
     for (int i = tid; i < H; i += kMlpThreads) {
-        if (P.dgamma) atomicAdd(P.dgamma + i, s_acc[i]);
-        if (P.dbeta) atomicAdd(P.dbeta + i, s_acc[H + i]);
-        if (P.db1) atomicAdd(P.db1 + i, s_acc[2 * H + i]);
+        if (P.dgamma) red_f32(P.dgamma + i, s_acc[i]);
+        if (P.dbeta) red_f32(P.dbeta + i, s_acc[H + i]);
+        if (P.db1) red_f32(P.db1 + i, s_acc[2 * H + i]);
     }
     tc_fence_before();
     __syncthreads();
