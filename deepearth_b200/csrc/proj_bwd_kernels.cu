@@ -23,6 +23,12 @@ using namespace mlp;
 // fire-and-forget reduction (the pointer arrives through a parameter struct, so atomicAdd would compile to a generic ATOM)
 __device__ __forceinline__ void red_f32(float* p, float v) { asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
 
+// shared-memory accumulation through an explicit shared address (s_acc is carved out of the aligned dynamic buffer, which
+// hides its address space from the compiler: atomicAdd would become a generic ATOM)
+__device__ __forceinline__ void red_shared_f32(float* p, float v) {
+    asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(v) : "memory");
+}
+
 // ---- gy fp32 -> bf16 copy + column sums (db2) -----------------------------------------------------------------------
 __global__ void __launch_bounds__(256) cast_colsum_kernel(const float* __restrict__ src, long long ld_src, __nv_bfloat16* __restrict__ dst,
                                                           long long ld_dst, long long n_rows, int n_cols, float* colsum,
@@ -253,8 +259,8 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                 if (g < NC) {
                     const float sb = warp_transpose_sum(v, lane);
                     const float sg = warp_transpose_sum(dvx, lane);
-                    atomicAdd(&s_acc[H + col0 + lane], sb);
-                    atomicAdd(&s_acc[col0 + lane], sg);
+                    red_shared_f32(&s_acc[H + col0 + lane], sb);
+                    red_shared_f32(&s_acc[col0 + lane], sg);
                 } else {
                     if (live) {
                         uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
@@ -267,7 +273,7 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = live ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.0f;
                     const float sd = warp_transpose_sum(v, lane);
-                    atomicAdd(&s_acc[2 * H + col0 + lane], sd);
+                    red_shared_f32(&s_acc[2 * H + col0 + lane], sd);
                 }
             }
         }
