@@ -37,15 +37,21 @@ using namespace mlp;
 // kernel 1: hidden activations
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kChunkN = 128;                                    // hidden columns per MMA chunk / TMEM buffer
+constexpr int kHiddenThreadsDefault = 128;
 
 // W1 chunks arrive by TMA: {64 k, 128 rows} boxes with the 128 B swizzle, Kp / 64 boxes per chunk (Kp = K1 rounded up to 64;
 // columns past K1 are zero-filled by the copy engine, and the A tile carries the same zero columns).  The chunk stream is
 // continuous across the CTA's tiles -- chunk q + 2 is requested as soon as the MMAs of chunk q have released its buffer,
 // i.e. one whole epilogue ahead of its use -- so no thread ever waits for weights.
 // dynamic shared memory (1024 B aligned): B[2] [Kp / 64 boxes x 16 KB] | A [128 x Kp] bf16, canonical K-major no-swizzle
-template <int K1>
-__global__ void __launch_bounds__(kMlpThreads)
+// NT = 128: one thread per row does the whole chunk; NT = 256: two threads per row, each takes half of a chunk's columns
+// (the LayerNorm / GELU epilogue is instruction-bound at 8 warps per SM) and the row statistics are merged once per tile.
+template <int K1, int NT>
+__global__ void __launch_bounds__(NT)
 proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_constant__ ProjHiddenParams P) {
+    constexpr int NH = NT / 128;                                // threads per row
+    constexpr int kPieces = kChunkN / 32 / NH;                  // 32-column pieces per thread and chunk
+    __shared__ float s_stat[NH][kTileM][3];
     constexpr int Kp = (K1 + 63) / 64 * 64;
     constexpr uint32_t kChunkBytes = (Kp / 64) * 16384;
     extern __shared__ unsigned char smem_raw[];
@@ -54,7 +60,7 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     unsigned char* sB[2] = {smem, smem + kChunkBytes};
     unsigned char* sA = smem + 2 * kChunkBytes;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = (tid >> 5) & 3, lane = tid & 31, half = tid >> 7;
     const int H = P.hidden, NC = H / kChunkN;
 
     if (tid == 0) {
@@ -62,12 +68,12 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
         mbar_init(&s_tma[0], 1); mbar_init(&s_tma[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 0) {
+    if (tid < 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(2 * kChunkN) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (Kp != K1)                                               // the pad columns of the A tile stay zero for the CTA's life
-        for (int i = tid; i < kTileM * Kp * 2 / 16; i += kMlpThreads) reinterpret_cast<uint4*>(sA)[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = tid; i < kTileM * Kp * 2 / 16; i += NT) reinterpret_cast<uint4*>(sA)[i] = make_uint4(0u, 0u, 0u, 0u);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -77,7 +83,7 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
     constexpr uint32_t kIdesc = idesc_bf16(kTileM, kChunkN, false, false);
     uint32_t mma_phase0 = 0u, mma_phase1 = 0u;                  // every thread waits on the MMA barriers
     uint32_t tma_phase0 = 0u, tma_phase1 = 0u;                  // thread 0 only
-    const int row = tid;
+    const int row = tid & 127;
     const int my_tiles = (P.n_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
     const long long total_chunks = static_cast<long long>(my_tiles) * 2 * NC;
 
@@ -116,7 +122,7 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
         constexpr int kIt = (4 * K1) / 32;
         constexpr int kRound = kIt >= 2 ? kIt / 2 : kIt;
 #pragma unroll
-        for (int it0 = 0; it0 < kIt; it0 += kRound) {
+        for (int it0 = 0; it0 < (half == 0 ? kIt : 0); it0 += kRound) {
             float4 va[kRound], vb[kRound];
 #pragma unroll
             for (int u = 0; u < kRound; ++u) {
@@ -158,7 +164,7 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
             if (g < NC) {
                 // ---- pass 1: row statistics ---------------------------------------------------------------------------
 #pragma unroll 1
-                for (int q = 0; q < kChunkN / 32; ++q) {
+                for (int q = half * kPieces; q < (half + 1) * kPieces; ++q) {
                     float v[32];
                     tmem_ld32(t_base + q * 32, v);
                     const float* b1 = P.b1 + c * kChunkN + q * 32;
@@ -178,8 +184,14 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
                     chan_merge(cnt, mean, m2, 32.0f, mb, (s0 + s1) + (s2 + s3));
                 }
                 if (g == NC - 1) {
+                    if constexpr (NH > 1) {                      // merge the two halves' statistics, in a fixed order
+                        s_stat[half][row][0] = cnt; s_stat[half][row][1] = mean; s_stat[half][row][2] = m2;
+                        __syncthreads();
+                        cnt = s_stat[0][row][0]; mean = s_stat[0][row][1]; m2 = s_stat[0][row][2];
+                        chan_merge(cnt, mean, m2, s_stat[1][row][0], s_stat[1][row][1], s_stat[1][row][2]);
+                    }
                     rstd = rsqrtf(m2 / static_cast<float>(H) + P.ln_eps);
-                    if (P.stats_out && row < n_valid) {
+                    if (P.stats_out && row < n_valid && half == 0) {
                         P.stats_out[2 * (p0 + row)] = mean;
                         P.stats_out[2 * (p0 + row) + 1] = rstd;
                     }
@@ -187,7 +199,7 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
             } else {
                 // ---- pass 2: normalise, GELU, bf16, store ---------------------------------------------------------------
 #pragma unroll 1
-                for (int q = 0; q < kChunkN / 32; ++q) {
+                for (int q = half * kPieces; q < (half + 1) * kPieces; ++q) {
                     float v[32];
                     tmem_ld32(t_base + q * 32, v);
                     const int col0 = c * kChunkN + q * 32;
@@ -457,33 +469,39 @@ bool proj_hidden_supported(int in_dim, int hidden) {
     return k_ok && hidden >= kChunkN && hidden % kChunkN == 0 && hidden <= 4096;
 }
 
-template <int K1>
+template <int K1, int NT>
 static cudaError_t launch_hidden_k(const ProjHiddenParams& P, int n_sms, cudaStream_t s) {
     constexpr int Kp = (K1 + 63) / 64 * 64;
     const size_t smem = static_cast<size_t>(2) * (Kp / 64) * 16384 + static_cast<size_t>(kTileM) * Kp * 2 + 1024;
     CUtensorMap map_w1;
     if (!make_map_bf16(&map_w1, P.w1, P.hidden, K1, K1, kChunkN)) return cudaErrorInvalidValue;
-    cudaError_t e = cudaFuncSetAttribute(proj_hidden_kernel<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    cudaError_t e = cudaFuncSetAttribute(proj_hidden_kernel<K1, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
     int per_sm = static_cast<int>(232448u / (smem + 2048));       // 227 KB of shared memory per SM, ~1 KB reserved per CTA
     if (per_sm > 2) per_sm = 2;                                   // 2 x 256 TMEM columns
     if (per_sm < 1) per_sm = 1;
     int grid = n_sms * per_sm;
     if (grid > P.n_tiles) grid = P.n_tiles;
-    proj_hidden_kernel<K1><<<grid, kMlpThreads, smem, s>>>(map_w1, P);
+    proj_hidden_kernel<K1, NT><<<grid, NT, smem, s>>>(map_w1, P);
     return cudaGetLastError();
 }
 
 cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaStream_t s) {
     P.n_tiles = static_cast<int>((P.n + kTileM - 1) / kTileM);
+    static const int threads = []() {                    // DE_PROJ_HIDDEN_THREADS (read once): 128 or 256 threads per CTA
+        const char* e = getenv("DE_PROJ_HIDDEN_THREADS");
+        return (e && atoi(e) == 128) ? 128 : ((e && atoi(e) == 256) ? 256 : kHiddenThreadsDefault);
+    }();
+#define DE_HID(K) (threads == 256 ? launch_hidden_k<K, 256>(P, n_sms, s) : launch_hidden_k<K, 128>(P, n_sms, s))
     switch (in_dim) {
-        case 32: return launch_hidden_k<32>(P, n_sms, s);
-        case 48: return launch_hidden_k<48>(P, n_sms, s);
-        case 64: return launch_hidden_k<64>(P, n_sms, s);
-        case 96: return launch_hidden_k<96>(P, n_sms, s);
-        case 128: return launch_hidden_k<128>(P, n_sms, s);
+        case 32: return DE_HID(32);
+        case 48: return DE_HID(48);
+        case 64: return DE_HID(64);
+        case 96: return DE_HID(96);
+        case 128: return DE_HID(128);
         default: return cudaErrorInvalidValue;
     }
+#undef DE_HID
 }
 
 template <int A_MN, int B_MN, int EPI, int MC>

@@ -32,3 +32,8 @@ DE_GEMM_MULTICAST=1 timeout 240 python -m pytest tests/test_projection.py -m gpu
 tail -4 gpurun_out/r02e_mc_pytest.txt
 DE_GEMM_MULTICAST=1 timeout 200 python bench.py --extra-only projection_h768 --steps 3 > gpurun_out/r02e_mc_projection.json 2> gpurun_out/r02e_mc_projection.err || tail -3 gpurun_out/r02e_mc_projection.err
 head -c 900 gpurun_out/r02e_mc_projection.json; echo
+# two threads per row in the hidden kernel
+DE_PROJ_HIDDEN_THREADS=256 timeout 240 python -m pytest tests/test_projection.py -m gpu -q -s -x -k "projection_forward or default_width" 2>&1 | tail -12 > gpurun_out/r02e_h256_pytest.txt
+tail -3 gpurun_out/r02e_h256_pytest.txt
+DE_PROJ_HIDDEN_THREADS=256 timeout 200 python bench.py --extra-only projection_h768 --steps 3 > gpurun_out/r02e_h256_projection.json 2> gpurun_out/r02e_h256_projection.err || tail -3 gpurun_out/r02e_h256_projection.err
+head -c 300 gpurun_out/r02e_h256_projection.json; echo
