@@ -9,7 +9,8 @@
 //     (x, y, z, t) rows in shared memory;
 //   * a warp holds 16 NEIGHBOURING points of ONE level (the general kernel: 16 levels of one point), so at the coarse
 //     and middle levels -- where neighbouring grid points fall into the same or adjacent cells -- the lanes of a gather
-//     instruction land in the same 128 B lines and the L1 pipeline is charged one wavefront instead of sixteen;
+//     instruction land in the same 128 B lines and the L1 pipeline is charged one wavefront instead of sixteen
+//     (ncu r02e: 233 M load wavefronts per 2^22 points against 1208 M for the general kernel);
 //   * feature rows are assembled in shared memory and leave the CTA as whole G*F*4-byte pieces.
 // Per-corner index, weight and summation order are those of the pair kernel, so the features are bit-identical to
 // de_grid4d_forward over the same points (tests/test_field.py).
@@ -147,33 +148,32 @@ grid4d_field_forward_kernel(const __grid_constant__ EncodeParams P, const __grid
     const unsigned pair_mask = 3u << (threadIdx.x & 30);
     const L2Policies pol = make_l2_policies(P.l2_hints != 0);
     const int row_floats = G * F + F;
+    // A warp owns LEVELS (warp, warp + 8, ...) and walks the patch's 256 points for each: the level's parameters stay in
+    // registers (the first version re-read them from shared memory for every point: 153 instructions per lane and level,
+    // ncu r02e), its 32 lanes are 16 neighbouring points x the x-pair, two such point rows per trip (8 gathers in flight).
+    const int warp = threadIdx.x >> 5, lane_pt = (threadIdx.x & 31) >> 1;
 #pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
-        const int pt = (threadIdx.x >> 1) + 128 * pass;           // a warp: 16 consecutive points of one patch row
-        const float4 c = s_xyzt[pt];
-        float* row = s_out + pt * row_floats;
-        // two levels per trip: eight gathers in flight per lane
+    for (int l = warp; l < n_lv; l += kThreads / 32) {
+        const LevelParams lv = s_lv[l];
 #pragma unroll 1
-        for (int l = 0; l < n_lv; l += 2) {
-            const bool two = l + 1 < n_lv;
-            const LevelParams& lva = s_lv[l];
-            const LevelParams& lvb = s_lv[two ? l + 1 : l];
+        for (int pt0 = 0; pt0 < kFieldPoints; pt0 += 32) {
+            const int pa = pt0 + lane_pt, pb = pt0 + 16 + lane_pt;
             FieldLevel<F, POW2> A, B;
-            A.prepare(lva, c, ox);
-            B.prepare(lvb, c, ox);
+            A.prepare(lv, s_xyzt[pa], ox);
+            B.prepare(lv, s_xyzt[pb], ox);
             float va[4][F], vb[4][F];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) load_entry_hint<TT, F>(lva.table, A.idx[j], va[j], pol.keep);
+            for (int j = 0; j < 4; ++j) load_entry_hint<TT, F>(lv.table, A.idx[j], va[j], pol.keep);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) load_entry_hint<TT, F>(lvb.table, B.idx[j], vb[j], pol.keep);
-            A.finish(va, ox, pair_mask, P.out_scale, row + l * F);
-            if (two) B.finish(vb, ox, pair_mask, P.out_scale, row + (l + 1) * F);      // pair-uniform: both lanes share l
+            for (int j = 0; j < 4; ++j) load_entry_hint<TT, F>(lv.table, B.idx[j], vb[j], pol.keep);
+            A.finish(va, ox, pair_mask, P.out_scale, s_out + pa * row_floats + l * F);
+            B.finish(vb, ox, pair_mask, P.out_scale, s_out + pb * row_floats + l * F);
         }
     }
     __syncthreads();
     // rows leave the CTA one point per warp trip: consecutive lanes write consecutive floats of the point's slice
     const int n_out = n_lv * F;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31;
     for (int c0 = 0; c0 < n_out; c0 += 32) {
         const int c = c0 + lane;
         const int l = c / F;

@@ -178,7 +178,7 @@ def test_c3_geometry_florida_vs_device_restatement(dev):
     # the clustered inputs really are clustered: a handful of coarse (R = 16) cells holds most of the points
     cells = (xyzt[:, 0] * 16).floor() * 1000 + (xyzt[:, 1] * 16).floor()
     _, counts = torch.unique(cells, return_counts=True)
-    assert float(counts.sort(descending=True).values[:32].sum()) >= 0.5 * n
+    assert float(counts.sort(descending=True).values[:32].sum()) >= 0.25 * n      # uniform points: 32 / 4913 of them
     g = torch.Generator(device=dev).manual_seed(77)
     gout = torch.randn((n, 128), device=dev, generator=g)
     plan = enc._plan()
