@@ -1045,7 +1045,7 @@ DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, i
         return fail(DE_EUNSUPPORTED, "projection: in_dim=%d hidden=%d out_dim=%d (in_dim in {32,48,64,96,128}, hidden a multiple of 128, out_dim of 8)", in_dim, hidden, out_dim);
     if (x_stride < in_dim || y_stride < out_dim) return fail(DE_EINVAL, "projection: row stride shorter than the row");
     if (reinterpret_cast<uintptr_t>(x) % 16 || x_stride % 4) return fail(DE_EALIGN, "projection: x rows not 16-byte aligned");
-    const void* aligned[] = {w1_bf16, w2_bf16, hidden_bf16, y};
+    const void* aligned[] = {w1_bf16, w2_bf16, hidden_bf16, y, b1, ln_gamma, ln_beta};
     for (const void* q : aligned)
         if (reinterpret_cast<uintptr_t>(q) % 16) return fail(DE_EALIGN, "projection: pointer not 16-byte aligned");
     if (n_points > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "projection: n_points too large");
@@ -1088,7 +1088,7 @@ DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n
     if (workspace_bytes < de_projection_backward_workspace_bytes(n_points, in_dim, hidden, out_dim))
         return fail(DE_EINVAL, "projection_backward: workspace of %zu bytes is too small", workspace_bytes);
     if (x_stride < in_dim || gy_stride < out_dim || (grad_x && gx_stride < in_dim)) return fail(DE_EINVAL, "projection_backward: row stride shorter than the row");
-    const void* aligned[] = {x, grad_y, w1_bf16, w1t_bf16, w2t_bf16, hidden_bf16, workspace, grad_x};
+    const void* aligned[] = {x, grad_y, w1_bf16, w1t_bf16, w2t_bf16, hidden_bf16, workspace, grad_x, b1, ln_gamma, ln_beta};
     for (const void* q : aligned)
         if (reinterpret_cast<uintptr_t>(q) % 16) return fail(DE_EALIGN, "projection_backward: pointer not 16-byte aligned");
     if (x_stride % 4 || gy_stride % 4) return fail(DE_EALIGN, "projection_backward: row strides must be multiples of 4 floats");

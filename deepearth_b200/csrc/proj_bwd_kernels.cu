@@ -230,48 +230,86 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
 #pragma unroll 1
             for (int q = 0; q < kBwdChunkN / 32; ++q) {
                 const int col0 = c * kBwdChunkN + q * 32;
-                uint4 dq[4];                               // 32 bf16 of d(loss)/d(activation), this row
-#pragma unroll
-                for (int u = 0; u < 4; ++u) dq[u] = live ? __ldg(reinterpret_cast<const uint4*>(da_row + col0) + u) : make_uint4(0u, 0u, 0u, 0u);
-                float v[32];
-                tmem_ld32(t_base + q * 32, v);
-                const uint32_t* dw = reinterpret_cast<const uint32_t*>(dq);
-                float dvx[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const float gam = __ldg(P.ln_gamma + col0 + j);
-                    const float xh = (v[j] + __ldg(P.b1 + col0 + j) - mean) * rstd;
-                    float act, gp;
-                    gelu_fwd_bwd(fmaf(gam, xh, __ldg(P.ln_beta + col0 + j)), act, gp);
-                    const uint32_t pr = dw[j >> 1];
-                    const float da = __uint_as_float((j & 1) ? (pr & 0xffff0000u) : (pr << 16));      // bf16 -> fp32
-                    const float dv = da * gp;
-                    const float t = gam * dv;
-                    if (g < NC) {
-                        s1 += t;
-                        s2 = fmaf(t, xh, s2);
-                        v[j] = dv;                          // column sums: dbeta
-                        dvx[j] = dv * xh;                   //              dgamma
-                    } else {
-                        v[j] = rstd * (t - s1 * inv_h - xh * (s2 * inv_h));     // dpre
-                    }
-                }
+                const float4* b1v = reinterpret_cast<const float4*>(P.b1 + col0);           // 16-byte aligned (C ABI)
+                uint4* piece = reinterpret_cast<uint4*>(out_row + col0);                    // this row's 32 columns of dpre_out
                 if (g < NC) {
+                    // ---- pass 1: dv = da GELU'(v), t = gamma dv; row sums of t and t xh; dgamma, dbeta.  t is parked (bf16)
+                    //      in dpre_out so that pass 2 needs neither da nor the GELU derivative again
+                    uint4 dq[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) dq[u] = live ? __ldg(reinterpret_cast<const uint4*>(da_row + col0) + u) : make_uint4(0u, 0u, 0u, 0u);
+                    float v[32];
+                    tmem_ld32(t_base + q * 32, v);
+                    const uint32_t* dw = reinterpret_cast<const uint32_t*>(dq);
+                    const float4* gav = reinterpret_cast<const float4*>(P.ln_gamma + col0);
+                    const float4* bev = reinterpret_cast<const float4*>(P.ln_beta + col0);
+                    float dvx[32];
+                    uint32_t tp[16];
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 b4 = __ldg(b1v + j4), g4 = __ldg(gav + j4), e4 = __ldg(bev + j4);
+                        const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, gg[4] = {g4.x, g4.y, g4.z, g4.w}, ee[4] = {e4.x, e4.y, e4.z, e4.w};
+                        float tt[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int j = 4 * j4 + u;
+                            const float xh = (v[j] + bb[u] - mean) * rstd;
+                            float act, gp;
+                            gelu_fwd_bwd(fmaf(gg[u], xh, ee[u]), act, gp);
+                            const uint32_t pr = dw[j >> 1];
+                            const float da = __uint_as_float((j & 1) ? (pr & 0xffff0000u) : (pr << 16));      // bf16 -> fp32
+                            const float dv = da * gp;
+                            tt[u] = gg[u] * dv;
+                            s1 += tt[u];
+                            s2 = fmaf(tt[u], xh, s2);
+                            v[j] = dv;                          // column sums: dbeta
+                            dvx[j] = dv * xh;                   //              dgamma
+                        }
+                        tp[2 * j4] = pack_bf16(tt[0], tt[1]);
+                        tp[2 * j4 + 1] = pack_bf16(tt[2], tt[3]);
+                    }
+                    if (live) {
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) piece[u] = make_uint4(tp[4 * u], tp[4 * u + 1], tp[4 * u + 2], tp[4 * u + 3]);
+                    }
                     const float sb = warp_transpose_sum(v, lane);
                     const float sg = warp_transpose_sum(dvx, lane);
                     red_shared_f32(&s_acc[H + col0 + lane], sb);
                     red_shared_f32(&s_acc[col0 + lane], sg);
                 } else {
-                    if (live) {
-                        uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
+                    // ---- pass 2: dpre = rstd (t - mean t - xh mean(t xh)); db1 ---------------------------------------------
+                    uint4 tq[4];
 #pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            dst[u] = make_uint4(pack_bf16(v[8 * u], v[8 * u + 1]), pack_bf16(v[8 * u + 2], v[8 * u + 3]),
-                                                pack_bf16(v[8 * u + 4], v[8 * u + 5]), pack_bf16(v[8 * u + 6], v[8 * u + 7]));
+                    for (int u = 0; u < 4; ++u) tq[u] = live ? piece[u] : make_uint4(0u, 0u, 0u, 0u);    // written by this thread in pass 1
+                    float v[32];
+                    tmem_ld32(t_base + q * 32, v);
+                    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tq);
+                    const float m1 = s1 * inv_h, m2 = s2 * inv_h;
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 b4 = __ldg(b1v + j4);
+                        const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int j = 4 * j4 + u;
+                            const float xh = (v[j] + bb[u] - mean) * rstd;
+                            const uint32_t pr = tw[j >> 1];
+                            const float t = __uint_as_float((j & 1) ? (pr & 0xffff0000u) : (pr << 16));
+                            v[j] = rstd * (t - m1 - xh * m2);
+                        }
                     }
-                    // db1 sums the bf16-ROUNDED dpre, the values the dW1 / dx GEMMs consume
+                    uint32_t pk[16];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = live ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.0f;
+                    for (int j = 0; j < 32; j += 2) {
+                        pk[j >> 1] = pack_bf16(v[j], v[j + 1]);
+                        // db1 sums the bf16-ROUNDED dpre, the values the dW1 / dx GEMMs consume
+                        v[j] = live ? __uint_as_float(pk[j >> 1] << 16) : 0.0f;
+                        v[j + 1] = live ? __uint_as_float(pk[j >> 1] & 0xffff0000u) : 0.0f;
+                    }
+                    if (live) {
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) piece[u] = make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
+                    }
                     const float sd = warp_transpose_sum(v, lane);
                     red_shared_f32(&s_acc[2 * H + col0 + lane], sd);
                 }

@@ -37,7 +37,7 @@ using namespace mlp;
 // kernel 1: hidden activations
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kChunkN = 128;                                    // hidden columns per MMA chunk / TMEM buffer
-constexpr int kHiddenThreadsDefault = 128;
+constexpr int kHiddenThreadsDefault = 256;            // B200 (r02e): forward 4.13 -> 3.42 ms per 2^20 rows against 128 threads
 
 // W1 chunks arrive by TMA: {64 k, 128 rows} boxes with the 128 B swizzle, Kp / 64 boxes per chunk (Kp = K1 rounded up to 64;
 // columns past K1 are zero-filled by the copy engine, and the A tile carries the same zero columns).  The chunk stream is
@@ -167,11 +167,12 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
                 for (int q = half * kPieces; q < (half + 1) * kPieces; ++q) {
                     float v[32];
                     tmem_ld32(t_base + q * 32, v);
-                    const float* b1 = P.b1 + c * kChunkN + q * 32;
+                    const float4* b1 = reinterpret_cast<const float4*>(P.b1 + c * kChunkN + q * 32);      // 16-byte aligned (C ABI)
                     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) {
-                        v[j] += __ldg(b1 + j); v[j + 1] += __ldg(b1 + j + 1); v[j + 2] += __ldg(b1 + j + 2); v[j + 3] += __ldg(b1 + j + 3);
+                        const float4 b = __ldg(b1 + (j >> 2));
+                        v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
                         s0 += v[j]; s1 += v[j + 1]; s2 += v[j + 2]; s3 += v[j + 3];
                     }
                     const float mb = ((s0 + s1) + (s2 + s3)) * (1.0f / 32.0f);
@@ -204,12 +205,18 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
                     tmem_ld32(t_base + q * 32, v);
                     const int col0 = c * kChunkN + q * 32;
                     uint32_t packed[16];
+                    const float4* b1 = reinterpret_cast<const float4*>(P.b1 + col0);
+                    const float4* ga = reinterpret_cast<const float4*>(P.ln_gamma + col0);
+                    const float4* be = reinterpret_cast<const float4*>(P.ln_beta + col0);
 #pragma unroll
-                    for (int j = 0; j < 32; j += 2) {
-                        float a = v[j] + __ldg(P.b1 + col0 + j), b = v[j + 1] + __ldg(P.b1 + col0 + j + 1);
-                        a = fmaf((a - mean) * rstd, __ldg(P.ln_gamma + col0 + j), __ldg(P.ln_beta + col0 + j));
-                        b = fmaf((b - mean) * rstd, __ldg(P.ln_gamma + col0 + j + 1), __ldg(P.ln_beta + col0 + j + 1));
-                        packed[j >> 1] = pack_bf16(gelu_fwd(a), gelu_fwd(b));
+                    for (int j = 0; j < 32; j += 4) {
+                        const float4 b = __ldg(b1 + (j >> 2)), g4 = __ldg(ga + (j >> 2)), e4 = __ldg(be + (j >> 2));
+                        const float a0 = fmaf((v[j] + b.x - mean) * rstd, g4.x, e4.x);
+                        const float a1 = fmaf((v[j + 1] + b.y - mean) * rstd, g4.y, e4.y);
+                        const float a2 = fmaf((v[j + 2] + b.z - mean) * rstd, g4.z, e4.z);
+                        const float a3 = fmaf((v[j + 3] + b.w - mean) * rstd, g4.w, e4.w);
+                        packed[j >> 1] = pack_bf16(gelu_fwd(a0), gelu_fwd(a1));
+                        packed[(j >> 1) + 1] = pack_bf16(gelu_fwd(a2), gelu_fwd(a3));
                     }
                     if (row < n_valid) {
                         uint4* dst = reinterpret_cast<uint4*>(out_row + col0);

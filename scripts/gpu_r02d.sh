@@ -11,7 +11,7 @@ prof() {   # tag, kernel regex, skip, count, command...
 }
 for what in "$@"; do
   case $what in
-    proj)   prof proj "proj_|gemm_bf16|cast_colsum" 9 9 python bench.py --extra-only projection_h768 --steps 2 ;;
+    proj)   prof proj "proj_|gemm_bf16|cast_colsum" 9 16 python bench.py --extra-only projection_h768 --steps 2 ;;
     field)  prof field "field" 2 2 python bench.py --extra-only field --steps 2 ;;
     c1r)    prof c1r "grid4d_|small1d" 8 4 python bench.py --workload c1r --steps 2 --warmup 3 --no-cpu-baseline ;;
     c3)     prof c3 "grid4d_|regroup" 12 6 python bench.py --workload c3 --steps 2 --warmup 3 --no-cpu-baseline ;;

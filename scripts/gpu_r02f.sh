@@ -1,0 +1,38 @@
+#!/bin/bash
+# round-2 GPU pass 3: tests, then the reworked projection / field kernels (bench lines + launch list + full ncu set)
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests -m gpu -q -s 2>&1 | tail -40 > gpurun_out/r02f_pytest.txt
+tail -4 gpurun_out/r02f_pytest.txt
+for x in field projection_h768; do
+  timeout 200 python bench.py --extra-only $x --steps 3 > gpurun_out/r02f_$x.json 2> gpurun_out/r02f_$x.err || tail -3 gpurun_out/r02f_$x.err
+  head -c 420 gpurun_out/r02f_$x.json; echo
+done
+DE_PROJ_HIDDEN_THREADS=128 timeout 200 python bench.py --extra-only projection_h768 --steps 3 > gpurun_out/r02f_projection_h768_t128.json 2>/dev/null
+head -c 200 gpurun_out/r02f_projection_h768_t128.json; echo
+timeout 300 python bench.py --workload c5h768 --steps 5 --no-cpu-baseline > gpurun_out/r02f_c5h768.json 2> gpurun_out/r02f_c5h768.err || tail -3 gpurun_out/r02f_c5h768.err
+python - <<'PY'
+import json
+try:
+    d = json.load(open("gpurun_out/r02f_c5h768.json"))
+    print("c5h768", round(d["value"], 1), d["kernels_ms"], "e2e", round(d["e2e"]["value"], 1))
+except Exception as e:
+    print("c5h768 failed", e)
+PY
+sed -i 's/r02d_/r02f_/g' scripts/gpu_r02d.sh
+bash scripts/gpu_r02d.sh proj field > gpurun_out/r02f_prof.log 2>&1
+tail -3 gpurun_out/r02f_prof.log
+timeout 900 python bench.py > gpurun_out/r02f_bench.json 2> gpurun_out/r02f_bench.err
+tail -2 gpurun_out/r02f_bench.err
+python - <<'PY'
+import json
+try:
+    d = json.load(open('gpurun_out/r02f_bench.json'))
+    print('c2', d['value'], d['kernels_ms'], 'e2e', d['e2e']['value'])
+    for k, v in d.get('extra', {}).items():
+        if k in ('c3', 'c1r') and 'value' in v:
+            print(k, v['value'], v['kernels_ms'])
+        else:
+            print(k, str({a: b for a, b in v.items() if a not in ('what', 'gemm2')})[:300] if isinstance(v, dict) else v)
+except Exception as e:
+    print('bench parse failed', e)
+PY
