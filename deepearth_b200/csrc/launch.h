@@ -138,6 +138,7 @@ struct GemmParams {
     int N;
     long long K;                  // contraction length
     int k_splits;                 // filled by the launcher
+    int prefetch;                 // filled by the launcher: L2 prefetch cursor on (DE_GEMM_PREFETCH, default 1)
     void* c;                      // (M, N) fp32 or bf16, rows ldc elements apart
     long long ldc;
     const float* bias;            // (N,) or NULL

@@ -242,6 +242,7 @@ constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 64, kGemmStages = 4;
 constexpr int kGemmThreads = 256;                      // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warps 4..7 epilogue
 constexpr uint32_t kGemmStageBytes = (kGemmBM + kGemmBN) * kGemmBK * 2;
 constexpr uint32_t kGemmSmemBytes = kGemmStages * kGemmStageBytes + 1024;   // + alignment slack
+constexpr int kGemmPrefetch = 12;                    // k-blocks the L2 prefetch cursor runs ahead of the loads
 constexpr int kGemmMulticastDefault = 0;              // flipped to 1 once the cluster path is validated on a B200
 
 // A_MN / B_MN = 1: the operand is stored with the contraction index as its ROW index ((K, M) resp. (K, N) row-major: a
@@ -290,12 +291,43 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
         int stage = 0;
         uint32_t phase = 0;
+        // The ring holds 4 k-blocks (192 KB): ~2000 clocks of tensor work, about one HBM round trip -- ncu r02e showed the
+        // tensor pipe 42 % active, waiting for operands that stream from HBM.  A second cursor therefore runs kGemmPrefetch
+        // k-blocks ahead of the loads (across tile boundaries) and asks L2 for the streamed operand boxes, so the loads
+        // themselves find their data in L2.
+        long long pf_work = unit;
+        int pf_kb = 0, pf_end = 0;
+        auto pf_range = [&]() {
+            const int sp = static_cast<int>(pf_work % P.k_splits);
+            pf_kb = sp * kb_per;
+            pf_end = min(k_blocks_all, (sp + 1) * kb_per);
+        };
+        auto pf_step = [&]() {
+            if (pf_work >= n_tiles || !P.prefetch) return;
+            const long long t = pf_work / P.k_splits;
+            const int pm0 = static_cast<int>((t / tiles_n) * MC + rank) * kGemmBM, pn0 = static_cast<int>(t % tiles_n) * kGemmBN;
+            if constexpr (A_MN) {
+#pragma unroll
+                for (int i = 0; i < kGemmBM / 64; ++i) tma_prefetch_2d(&map_a, pm0 + 64 * i, pf_kb * kGemmBK);
+            } else {
+                tma_prefetch_2d(&map_a, pf_kb * kGemmBK, pm0);
+            }
+            if constexpr (B_MN) {                                  // weight-gradient form: B streams from HBM as well
+#pragma unroll
+                for (int i = 0; i < kGemmBN / 64; ++i)
+                    if (MC == 1 || (i >> 1) == static_cast<int>(rank)) tma_prefetch_2d(&map_b, pn0 + 64 * i, pf_kb * kGemmBK);
+            }
+            if (++pf_kb == pf_end) { pf_work += n_units; if (pf_work < n_tiles) pf_range(); }
+        };
+        if (pf_work < n_tiles) pf_range();
+        for (int i = 0; i < kGemmPrefetch; ++i) pf_step();
         for (long long work = unit; work < n_tiles; work += n_units) {
             const long long tile = work / P.k_splits;
             const int split = static_cast<int>(work - tile * P.k_splits);
             const int m0 = static_cast<int>((tile / tiles_n) * MC + rank) * kGemmBM, n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
             const int kb_end = min(k_blocks_all, (split + 1) * kb_per);
             for (int kb = split * kb_per; kb < kb_end; ++kb) {
+                pf_step();
                 mbar_wait(&s_empty[stage], phase ^ 1u);
                 unsigned char* sa = smem + stage * kGemmStageBytes;
                 unsigned char* sb = sa + kGemmBM * kGemmBK * 2;
@@ -577,6 +609,8 @@ cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long l
         splits = (k_blocks + per - 1) / per;                        // every split non-empty
     }
     P.k_splits = static_cast<int>(splits);
+    static const int prefetch = []() { const char* e = getenv("DE_GEMM_PREFETCH"); return (e && *e) ? (atoi(e) != 0) : 1; }();
+    P.prefetch = prefetch;
     const long long work = units * splits;
     const int grid = static_cast<int>((work < max_units ? work : max_units) * mc);
     const size_t elem = epi == 1 ? 2 : 4;

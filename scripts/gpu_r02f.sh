@@ -36,3 +36,13 @@ try:
 except Exception as e:
     print('bench parse failed', e)
 PY
+DE_GEMM_PREFETCH=0 timeout 200 python bench.py --extra-only projection_h768 --steps 3 > gpurun_out/r02f_projection_h768_nopf.json 2>/dev/null
+python - <<'PY'
+import json
+for f in ("projection_h768", "projection_h768_nopf", "projection_h768_t128"):
+    try:
+        d = json.load(open(f"gpurun_out/r02f_{f}.json"))
+        print(f, "fwd", round(d["forward_ms"], 3), "fwd+bwd", round(d["fwd_bwd_ms"], 3), "gemm2 fp32", round(d["gemm2"]["ms_fp32_out"], 3), "bf16", round(d["gemm2"]["ms_bf16_out"], 3))
+    except Exception as e:
+        print(f, "failed", e)
+PY
