@@ -430,10 +430,14 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                     } else if constexpr (EPI == 1) {
                         __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(P.c) + r * P.ldc + col0;
                         if (col0 + 32 <= P.N && P.vec_ok) {
+                            // two 32-byte stores: whole sectors (four 16-byte stores left every sector half written per instruction)
 #pragma unroll
-                            for (int u = 0; u < 4; ++u)
-                                reinterpret_cast<uint4*>(dst)[u] = make_uint4(pack_bf16(v[8 * u], v[8 * u + 1]), pack_bf16(v[8 * u + 2], v[8 * u + 3]),
-                                                                              pack_bf16(v[8 * u + 4], v[8 * u + 5]), pack_bf16(v[8 * u + 6], v[8 * u + 7]));
+                            for (int u = 0; u < 2; ++u)
+                                asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * u),
+                                             "r"(pack_bf16(v[16 * u], v[16 * u + 1])), "r"(pack_bf16(v[16 * u + 2], v[16 * u + 3])),
+                                             "r"(pack_bf16(v[16 * u + 4], v[16 * u + 5])), "r"(pack_bf16(v[16 * u + 6], v[16 * u + 7])),
+                                             "r"(pack_bf16(v[16 * u + 8], v[16 * u + 9])), "r"(pack_bf16(v[16 * u + 10], v[16 * u + 11])),
+                                             "r"(pack_bf16(v[16 * u + 12], v[16 * u + 13])), "r"(pack_bf16(v[16 * u + 14], v[16 * u + 15])) : "memory");
                         } else {
                             #pragma unroll
                             for (int j = 0; j < 32; ++j)
