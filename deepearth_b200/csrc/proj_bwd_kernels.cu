@@ -107,9 +107,15 @@ constexpr int kBwdChunkN = 128;
 
 // W1 chunks arrive by TMA exactly as in proj_hidden_kernel (a continuous chunk stream, requested one epilogue ahead).
 // dynamic shared memory (1024 B aligned): B[2] [Kp / 64 boxes x 16 KB] | A [128 x Kp] bf16 canonical | acc[3][H] floats
+// Two threads per row (256 per CTA, each takes half of a chunk's columns; the two row sums are merged once per tile): the
+// epilogue is instruction- and latency-bound, and 2 x 4 warps per SM issued 27 % of the time (ncu r02f).
+constexpr int kDpreThreads = 256;
 template <int K1>
-__global__ void __launch_bounds__(kMlpThreads)
+__global__ void __launch_bounds__(kDpreThreads, 2)
 proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_constant__ ProjDpreParams P) {
+    constexpr int NT = kDpreThreads;
+    constexpr int kPieces = kBwdChunkN / 32 / (NT / 128);
+    __shared__ float s_part[2][kTileM][2];
     constexpr int Kp = (K1 + 63) / 64 * 64;
     constexpr uint32_t kChunkBytes = (Kp / 64) * 16384;
     extern __shared__ unsigned char smem_raw[];
@@ -120,20 +126,20 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
     unsigned char* sA = smem + 2 * kChunkBytes;
     const int H = P.hidden, NC = H / kBwdChunkN;
     float* s_acc = reinterpret_cast<float*>(sA + kTileM * Kp * 2);     // [3][H]: dgamma, dbeta, db1
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = (tid >> 5) & 3, lane = tid & 31, half = tid >> 7;
 
-    for (int i = tid; i < 3 * H; i += kMlpThreads) s_acc[i] = 0.0f;
+    for (int i = tid; i < 3 * H; i += NT) s_acc[i] = 0.0f;
     if (tid == 0) {
         mbar_init(&s_mma[0], 1); mbar_init(&s_mma[1], 1);
         mbar_init(&s_tma[0], 1); mbar_init(&s_tma[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 0) {
+    if (tid < 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(2 * kBwdChunkN) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (Kp != K1)
-        for (int i = tid; i < kTileM * Kp * 2 / 16; i += kMlpThreads) reinterpret_cast<uint4*>(sA)[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = tid; i < kTileM * Kp * 2 / 16; i += NT) reinterpret_cast<uint4*>(sA)[i] = make_uint4(0u, 0u, 0u, 0u);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -142,7 +148,7 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
     const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
     constexpr uint32_t kIdesc = idesc_bf16(kTileM, kBwdChunkN, false, false);
     uint32_t mma_phase0 = 0u, mma_phase1 = 0u, tma_phase0 = 0u, tma_phase1 = 0u;
-    const int row = tid;
+    const int row = tid & 127;
     const float inv_h = 1.0f / static_cast<float>(H);
     const int my_tiles = (P.n_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
     const long long total_chunks = static_cast<long long>(my_tiles) * 2 * NC;
@@ -181,7 +187,7 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
         constexpr int kIt = (4 * K1) / 32;
         constexpr int kRound = kIt >= 2 ? kIt / 2 : kIt;
 #pragma unroll
-        for (int it0 = 0; it0 < kIt; it0 += kRound) {
+        for (int it0 = 0; it0 < (half == 0 ? kIt : 0); it0 += kRound) {       // the first 128 threads fill the A tile
             float4 va[kRound], vb[kRound];
 #pragma unroll
             for (int u = 0; u < kRound; ++u) {
@@ -228,7 +234,7 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
             if (tid == 0 && qs + 2 < total_chunks) request_chunk(qs + 2);
             const uint32_t t_base = tmem + lane_off + static_cast<uint32_t>(qs & 1) * kBwdChunkN;
 #pragma unroll 1
-            for (int q = 0; q < kBwdChunkN / 32; ++q) {
+            for (int q = half * kPieces; q < (half + 1) * kPieces; ++q) {
                 const int col0 = c * kBwdChunkN + q * 32;
                 const float4* b1v = reinterpret_cast<const float4*>(P.b1 + col0);           // 16-byte aligned (C ABI)
                 uint4* piece = reinterpret_cast<uint4*>(out_row + col0);                    // this row's 32 columns of dpre_out
@@ -314,12 +320,19 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                     red_shared_f32(&s_acc[2 * H + col0 + lane], sd);
                 }
             }
+            if (g == NC - 1) {                                    // both halves of a row need the row's full sums for pass 2
+                s_part[half][row][0] = s1;
+                s_part[half][row][1] = s2;
+                __syncthreads();
+                s1 = s_part[0][row][0] + s_part[1][row][0];
+                s2 = s_part[0][row][1] + s_part[1][row][1];
+            }
         }
         tc_fence_before();
         __syncthreads();
     }
     // one flush per CTA
-    for (int i = tid; i < H; i += kMlpThreads) {
+    for (int i = tid; i < H; i += NT) {
         if (P.dgamma) red_f32(P.dgamma + i, s_acc[i]);
         if (P.dbeta) red_f32(P.dbeta + i, s_acc[H + i]);
         if (P.db1) red_f32(P.db1 + i, s_acc[2 * H + i]);
@@ -344,7 +357,7 @@ static cudaError_t launch_dpre_k(const ProjDpreParams& P, int n_sms, cudaStream_
     if (per_sm < 1) per_sm = 1;
     int grid = n_sms * per_sm;
     if (grid > P.n_tiles) grid = P.n_tiles;
-    proj_dpre_kernel<K1><<<grid, kMlpThreads, smem, s>>>(map_w1, P);
+    proj_dpre_kernel<K1><<<grid, kDpreThreads, smem, s>>>(map_w1, P);
     return cudaGetLastError();
 }
 
