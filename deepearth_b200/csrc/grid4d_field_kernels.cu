@@ -63,9 +63,20 @@ template <int F, bool POW2>
 struct FieldLevel {
     float w[3];
     uint32_t idx[4];
-    // c: the point's (x, y, z, t) row in shared memory; the level's three columns are picked by address, not by branches
-    __device__ __forceinline__ void prepare(const LevelParams& lv, const float* c, int d0, int d1, int d2, int ox) {
-        const float x[3] = {c[d0], c[d1], c[d2]};
+    // c: the point's (x, y, z, t) row; the level's three columns are picked with selects on loop-invariant predicates
+    // (pick4's nested conditionals compiled to branches: ~50 of 153 instructions per lane and level, ncu r02e; picking by
+    // shared-memory address instead put the load latency on the index arithmetic's critical path, r02g)
+    __device__ __forceinline__ void prepare(const LevelParams& lv, const float4& c, int d0, int d1, int d2, int ox) {
+        const int dd[3] = {d0, d1, d2};
+        float x[3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            float r = c.x;
+            r = dd[d] == 1 ? c.y : r;
+            r = dd[d] == 2 ? c.z : r;
+            r = dd[d] == 3 ? c.w : r;
+            x[d] = r;
+        }
         long long g[3];
         cell_of<3>(lv, x, g, w);
         CellTerms<3, POW2> ct;
@@ -98,7 +109,7 @@ struct FieldLevel {
 };
 
 template <typename TT, int F, bool POW2>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 3)
 grid4d_field_forward_kernel(const __grid_constant__ EncodeParams P, const __grid_constant__ FieldParams Fp) {
     __shared__ LevelParams s_lv[kMaxGroup];
     __shared__ float4 s_xyzt[kFieldPoints];
@@ -155,13 +166,12 @@ grid4d_field_forward_kernel(const __grid_constant__ EncodeParams P, const __grid
     for (int l = warp; l < n_lv; l += kThreads / 32) {
         const LevelParams lv = s_lv[l];
         const int d0 = lv.dim[0], d1 = lv.dim[1], d2 = lv.dim[2];
-        const float* xyzt = reinterpret_cast<const float*>(s_xyzt);
 #pragma unroll 1
         for (int pt0 = 0; pt0 < kFieldPoints; pt0 += 32) {
             const int pa = pt0 + lane_pt, pb = pt0 + 16 + lane_pt;
             FieldLevel<F, POW2> A, B;
-            A.prepare(lv, xyzt + 4 * pa, d0, d1, d2, ox);
-            B.prepare(lv, xyzt + 4 * pb, d0, d1, d2, ox);
+            A.prepare(lv, s_xyzt[pa], d0, d1, d2, ox);
+            B.prepare(lv, s_xyzt[pb], d0, d1, d2, ox);
             float va[4][F], vb[4][F];
 #pragma unroll
             for (int j = 0; j < 4; ++j) load_entry_hint<TT, F>(lv.table, A.idx[j], va[j], pol.keep);

@@ -138,11 +138,12 @@ struct GemmParams {
     int N;
     long long K;                  // contraction length
     int k_splits;                 // filled by the launcher
-    int prefetch;                 // filled by the launcher: L2 prefetch cursor on (DE_GEMM_PREFETCH, default 1)
+    int prefetch;                 // filled by the launcher: L2 prefetch cursor (DE_GEMM_PREFETCH=1; measured slower, off by default)
     void* c;                      // (M, N) fp32 or bf16, rows ldc elements apart
     long long ldc;
     const float* bias;            // (N,) or NULL
     int vec_ok;
+    int bias_vec;                 // filled by the launcher: bias is 16-byte aligned
 };
 struct ProjDpreParams {
     const float* x;               // (n, in_dim) fp32 features (forward input)

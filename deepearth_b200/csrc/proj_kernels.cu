@@ -239,7 +239,7 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
 // kernel 2: C = A . B^T (+ bias), bf16 operands by TMA, fp32 accumulation in TMEM
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 64, kGemmStages = 4;
-constexpr int kGemmThreads = 256;                      // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warps 4..7 epilogue
+constexpr int kGemmThreads = 384;                      // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warps 4..11 epilogue
 constexpr uint32_t kGemmStageBytes = (kGemmBM + kGemmBN) * kGemmBK * 2;
 constexpr uint32_t kGemmSmemBytes = kGemmStages * kGemmStageBytes + 1024;   // + alignment slack
 constexpr int kGemmPrefetch = 12;                    // k-blocks the L2 prefetch cursor runs ahead of the loads
@@ -271,7 +271,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kGemmStages; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], MC); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 4); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 8); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -393,7 +393,12 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         }
     } else if (warp >= 4) {
         // ===== epilogue: TMEM -> registers -> global =====
+        // eight warps: two per TMEM lane quarter, each draining half of the accumulator's columns.  With four, the drain of a
+        // 128 x 256 fp32 tile (8 dependent tcgen05.ld -> bias -> store rounds per thread) took about as long as the next
+        // tile's mainloop and the MMA warp waited for a free accumulator (tensor pipe 42 % active with fp32 output, 57 % with
+        // bf16, ncu r02e).
         const int quarter = warp & 3;                                // TMEM lanes this warp may read
+        const int col_half = (warp - 4) >> 2;
         int as = 0;
         uint32_t aphase = 0;
         for (long long work = unit; work < n_tiles; work += n_units) {
@@ -405,14 +410,23 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             const long long r = m0 + quarter * 32 + lane;
             const uint32_t t_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + as * kGemmBN;
 #pragma unroll 1
-            for (int q = 0; q < kGemmBN / 32; ++q) {
+            for (int q = col_half * (kGemmBN / 64); q < (col_half + 1) * (kGemmBN / 64); ++q) {
                 const int col0 = n0 + q * 32;
                 if (col0 >= P.N) break;                              // warp-uniform
                 float v[32];
                 tmem_ld32(t_base + q * 32, v);
                 if (P.bias) {
+                    if (col0 + 32 <= P.N && P.bias_vec) {
+                        const float4* b4 = reinterpret_cast<const float4*>(P.bias + col0);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldg(P.bias + col0 + j) : 0.0f;
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 b = __ldg(b4 + j);
+                            v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldg(P.bias + col0 + j) : 0.0f;
+                    }
                 }
                 if (r < P.M) {
                     if constexpr (EPI == 2) {
@@ -613,12 +627,13 @@ cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long l
         splits = (k_blocks + per - 1) / per;                        // every split non-empty
     }
     P.k_splits = static_cast<int>(splits);
-    static const int prefetch = []() { const char* e = getenv("DE_GEMM_PREFETCH"); return (e && *e) ? (atoi(e) != 0) : 1; }();
+    static const int prefetch = []() { const char* e = getenv("DE_GEMM_PREFETCH"); return (e && *e) ? (atoi(e) != 0) : 0; }();   // B200 r02g: 13.7 ms with, 11.9 ms without
     P.prefetch = prefetch;
     const long long work = units * splits;
     const int grid = static_cast<int>((work < max_units ? work : max_units) * mc);
     const size_t elem = epi == 1 ? 2 : 4;
     P.vec_ok = (reinterpret_cast<uintptr_t>(P.c) % 32 == 0 && (P.ldc * elem) % 32 == 0) ? 1 : 0;
+    P.bias_vec = (P.bias && reinterpret_cast<uintptr_t>(P.bias) % 16 == 0) ? 1 : 0;
     if (mc == 2) return transposed ? launch_gemm_e<1, 1, 2>(map_a, map_b, P, epi, grid, s) : launch_gemm_e<0, 0, 2>(map_a, map_b, P, epi, grid, s);
     return transposed ? launch_gemm_e<1, 1, 1>(map_a, map_b, P, epi, grid, s) : launch_gemm_e<0, 0, 1>(map_a, map_b, P, epi, grid, s);
 }
