@@ -587,6 +587,34 @@ def projection_bench(device, log2_points=20, in_dim=128, hidden=768):
                     "split-K GEMMs, dx GEMM backward) vs the identical nn.Sequential through cuBLAS / ATen"}
 
 
+def small_batch_bench(device, log2_points=12):
+    """The reference's own batch sizes (a few thousand points, tests/run_tests.py:265-324): one c2 training step at 4096
+    points through the module API -- eager (host-bound: Python, ctypes and autograd bookkeeping for 64 table parameters) and
+    with forward + backward replayed as CUDA graphs (Grid4DEncoder.graphed_features)."""
+    n = 2 ** log2_points
+    job = Job(dict(WORKLOADS["c2"]), device, seed=1234, n_points=n)
+    params = job.weights
+    enc = job.enc.train()
+
+    def eager():
+        for p in params:
+            p.grad = None
+        enc.encode_features(job.coords).backward(job.gout)
+    ms_eager = _time_cuda(eager, steps=200, warmup=20)
+    graphed = enc.graphed_features(job.coords)
+
+    def replay():
+        for p in params:
+            p.grad = None
+        graphed(job.coords).backward(job.gout)
+    ms_graph = _time_cuda(replay, steps=200, warmup=20)
+    return {"points": n, "eager_ms_per_step": ms_eager, "graphed_ms_per_step": ms_graph, "speedup": ms_eager / ms_graph,
+            "eager_mpoints_per_s": n / ms_eager / 1e3, "graphed_mpoints_per_s": n / ms_graph / 1e3, "gpu_launches": 4 * 440,
+            "what": "c2 grids (64 table parameters), 4096 uniform points, Grid4DEncoder.encode_features + autograd backward, CUDA events "
+                    "over 200 steps; graphed = torch.cuda.make_graphed_callables over the same kernels (fp16 table refresh, forward, "
+                    "gradient zeroing, backward)"}
+
+
 def cpu_sample_log2(wl, steps, warmup):
     """Bounded CPU sample: the decomposed mode runs ~0.03 Mpoints/s on 16 host threads, so 2^17 points x 13 steps is
     about a minute; more steps shrink the sample."""
@@ -951,7 +979,7 @@ def grad_check(args, ctx, log2_points=16):
                     "ranks' points / world, max over ranks of max|diff| / max|ref| on the flat 256 MiB gradient buffer"}
 
 
-EXTRA_NAMES = ("c3", "c1r", "field", "st_embed", "projection_h768", "eager_cuda_baseline")
+EXTRA_NAMES = ("c3", "c1r", "field", "st_embed", "projection_h768", "small_batch", "eager_cuda_baseline")
 
 
 def run_extra_child(name, steps, limit_s):
@@ -987,6 +1015,8 @@ def run_extra_only(args):
         out = st_embed_bench(ctx.device)
     elif name == "projection_h768":
         out = projection_bench(ctx.device)
+    elif name == "small_batch":
+        out = small_batch_bench(ctx.device)
     elif name == "eager_cuda_baseline":
         out = {"c2": eager_cuda_baseline(dict(WORKLOADS["c2"]), 2 ** 22, ctx.device)}
         torch.cuda.empty_cache()
@@ -1013,7 +1043,7 @@ def run_gpu_arm(args, wl):
             # entry (recorded as {"error": ...}), never the headline line.  This process keeps only its CUDA context.
             torch.cuda.empty_cache()
             for nm, limit in (("c3", 240), ("c1r", 120), ("field", 120), ("st_embed", 120), ("projection_h768", 180),
-                              ("eager_cuda_baseline", 240)):
+                              ("small_batch", 120), ("eager_cuda_baseline", 240)):
                 extra[nm] = run_extra_child(nm, side_steps, limit)
         else:
             r = measure(args, "c4", dict(WORKLOADS["c4"]), ctx, side_steps, want_clocks=False)
