@@ -50,7 +50,6 @@ template <int K1, int NT>
 __global__ void __launch_bounds__(NT)
 proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_constant__ ProjHiddenParams P) {
     constexpr int NH = NT / 128;                                // threads per row
-    constexpr int kPieces = kChunkN / 32 / NH;                  // 32-column pieces per thread and chunk
     __shared__ float s_stat[NH][kTileM][3];
     constexpr int Kp = (K1 + 63) / 64 * 64;
     constexpr uint32_t kChunkBytes = (Kp / 64) * 16384;
@@ -161,28 +160,42 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
             tc_fence_after();
             if (tid == 0 && q + 2 < total_chunks) request_chunk(q + 2);      // buffer q & 1 is free again
             const uint32_t t_base = tmem + lane_off + static_cast<uint32_t>(q & 1) * kChunkN;
+            // The thread's columns of the chunk come in 16-column pieces; piece i + 1 is requested from tensor memory as soon
+            // as piece i has arrived, and the constants of a piece are requested before its wait (ncu r02g: a third of the
+            // stall samples sat on the first FADD after each 32-column tcgen05.ld).
+            constexpr int NP = kChunkN / NH / 16;
+            const uint32_t t_mine = t_base + half * (kChunkN / NH);
+            const int col_mine = c * kChunkN + half * (kChunkN / NH);
+            uint32_t rb[2][16];
+            tmem_ld16_issue(t_mine, rb[0]);
             if (g < NC) {
                 // ---- pass 1: row statistics ---------------------------------------------------------------------------
-#pragma unroll 1
-                for (int q = half * kPieces; q < (half + 1) * kPieces; ++q) {
-                    float v[32];
-                    tmem_ld32(t_base + q * 32, v);
-                    const float4* b1 = reinterpret_cast<const float4*>(P.b1 + c * kChunkN + q * 32);      // 16-byte aligned (C ABI)
+#pragma unroll
+                for (int i = 0; i < NP; ++i) {
+                    const float4* b1 = reinterpret_cast<const float4*>(P.b1 + col_mine + i * 16);      // 16-byte aligned (C ABI)
+                    float4 bb[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) bb[u] = __ldg(b1 + u);
+                    tmem_ld16_wait(rb[i & 1]);
+                    if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
+                    float v[16];
                     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        const float4 b = __ldg(b1 + (j >> 2));
-                        v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-                        s0 += v[j]; s1 += v[j + 1]; s2 += v[j + 2]; s3 += v[j + 3];
+                    for (int u = 0; u < 4; ++u) {
+                        v[4 * u] = __uint_as_float(rb[i & 1][4 * u]) + bb[u].x;
+                        v[4 * u + 1] = __uint_as_float(rb[i & 1][4 * u + 1]) + bb[u].y;
+                        v[4 * u + 2] = __uint_as_float(rb[i & 1][4 * u + 2]) + bb[u].z;
+                        v[4 * u + 3] = __uint_as_float(rb[i & 1][4 * u + 3]) + bb[u].w;
+                        s0 += v[4 * u]; s1 += v[4 * u + 1]; s2 += v[4 * u + 2]; s3 += v[4 * u + 3];
                     }
-                    const float mb = ((s0 + s1) + (s2 + s3)) * (1.0f / 32.0f);
+                    const float mb = ((s0 + s1) + (s2 + s3)) * (1.0f / 16.0f);
                     s0 = s1 = s2 = s3 = 0.f;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
+                    for (int j = 0; j < 16; j += 4) {
                         const float d0 = v[j] - mb, d1 = v[j + 1] - mb, d2 = v[j + 2] - mb, d3 = v[j + 3] - mb;
                         s0 = fmaf(d0, d0, s0); s1 = fmaf(d1, d1, s1); s2 = fmaf(d2, d2, s2); s3 = fmaf(d3, d3, s3);
                     }
-                    chan_merge(cnt, mean, m2, 32.0f, mb, (s0 + s1) + (s2 + s3));
+                    chan_merge(cnt, mean, m2, 16.0f, mb, (s0 + s1) + (s2 + s3));
                 }
                 if (g == NC - 1) {
                     if constexpr (NH > 1) {                      // merge the two halves' statistics, in a fixed order
@@ -199,29 +212,31 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
                 }
             } else {
                 // ---- pass 2: normalise, GELU, bf16, store ---------------------------------------------------------------
-#pragma unroll 1
-                for (int q = half * kPieces; q < (half + 1) * kPieces; ++q) {
-                    float v[32];
-                    tmem_ld32(t_base + q * 32, v);
-                    const int col0 = c * kChunkN + q * 32;
-                    uint32_t packed[16];
+#pragma unroll
+                for (int i = 0; i < NP; ++i) {
+                    const int col0 = col_mine + i * 16;
                     const float4* b1 = reinterpret_cast<const float4*>(P.b1 + col0);
                     const float4* ga = reinterpret_cast<const float4*>(P.ln_gamma + col0);
                     const float4* be = reinterpret_cast<const float4*>(P.ln_beta + col0);
+                    float4 bb[4], gg[4], ee[4];
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        const float4 b = __ldg(b1 + (j >> 2)), g4 = __ldg(ga + (j >> 2)), e4 = __ldg(be + (j >> 2));
-                        const float a0 = fmaf((v[j] + b.x - mean) * rstd, g4.x, e4.x);
-                        const float a1 = fmaf((v[j + 1] + b.y - mean) * rstd, g4.y, e4.y);
-                        const float a2 = fmaf((v[j + 2] + b.z - mean) * rstd, g4.z, e4.z);
-                        const float a3 = fmaf((v[j + 3] + b.w - mean) * rstd, g4.w, e4.w);
-                        packed[j >> 1] = pack_bf16(gelu_fwd(a0), gelu_fwd(a1));
-                        packed[(j >> 1) + 1] = pack_bf16(gelu_fwd(a2), gelu_fwd(a3));
+                    for (int u = 0; u < 4; ++u) { bb[u] = __ldg(b1 + u); gg[u] = __ldg(ga + u); ee[u] = __ldg(be + u); }
+                    tmem_ld16_wait(rb[i & 1]);
+                    if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
+                    uint32_t packed[8];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const float a0 = fmaf((__uint_as_float(rb[i & 1][4 * u]) + bb[u].x - mean) * rstd, gg[u].x, ee[u].x);
+                        const float a1 = fmaf((__uint_as_float(rb[i & 1][4 * u + 1]) + bb[u].y - mean) * rstd, gg[u].y, ee[u].y);
+                        const float a2 = fmaf((__uint_as_float(rb[i & 1][4 * u + 2]) + bb[u].z - mean) * rstd, gg[u].z, ee[u].z);
+                        const float a3 = fmaf((__uint_as_float(rb[i & 1][4 * u + 3]) + bb[u].w - mean) * rstd, gg[u].w, ee[u].w);
+                        packed[2 * u] = pack_bf16(gelu_fwd(a0), gelu_fwd(a1));
+                        packed[2 * u + 1] = pack_bf16(gelu_fwd(a2), gelu_fwd(a3));
                     }
                     if (row < n_valid) {
                         uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) dst[u] = make_uint4(packed[4 * u], packed[4 * u + 1], packed[4 * u + 2], packed[4 * u + 3]);
+                        dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                        dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
                     }
                 }
             }
