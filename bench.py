@@ -626,8 +626,13 @@ def cpu_sample_log2(wl, steps, warmup):
     return log2
 
 
+L2_POLICY = "inputs larger than L2 (coords + grad_out + out > 4 GiB per step at the workload's size); no flush"
+
+
 def describe_config(name, wl, n_points, world=1):
-    return {"workload": name, "description": wl["desc"], "points_per_gpu": n_points, "coords": wl["coords"],
+    """The workload, identically worded by both arms (the driver compares the two `config` objects); what is specific to a
+    run -- the reference arm's bounded sample, the GPU arm's L2 limits and overlap -- lives outside it."""
+    return {"workload": name, "l2_policy": L2_POLICY, "description": wl["desc"], "points_per_gpu": n_points, "coords": wl["coords"],
             "levels": 64 if wl["mode"] == "decomposed" else 24, "features_per_level": 2, "table_size": wl["T"],
             "interpolation": "linear" if wl["mode"] == "decomposed" else "nearest",
             "parallelism": f"points-sharded x{world}, replicated tables, NCCL all-reduce of table grads"}
@@ -640,7 +645,6 @@ def run_reference_arm(args, wl):
     log2_sample = cpu_sample_log2(wl, max(1, args.steps), max(1, args.warmup))
     cb = cpu_baseline_run(wl, log2_sample, max(1, args.steps), max(1, args.warmup))
     cfg = describe_config(args.workload, wl, 2 ** wl["log2_points"], args.gpus)
-    cfg["sample"] = cb["sample"]
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
             "scaling": "strong" if wl.get("total") else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -903,12 +907,11 @@ def measure(args, name, wl, ctx, steps, want_clocks=True):
         lvl_bytes = wl["T"] * job.F * (4 if dom == "backward" else (2 if wl["table_dtype"] == "float16" else 4))
         resident = "l2" if lvl_bytes * 16 <= 64 * 2 ** 20 or wl["mode"] != "decomposed" else "hbm"
         cfg = describe_config(name, wl, n, world)
-        if sync is not None:
-            cfg["parallelism"] += f" overlapped with the backward in {args.sync_chunks} level runs"
-        cfg.update({"l2_policy": "inputs larger than L2 (coords + grad_out + out > 4 GiB per step); no flush",
-                    "l2_fetch_granularity": _gran.value, "head_grad_group_width": job.group_w,
-                    "l2_persisting_bytes": _pl2.value, "l2_persisting_max_bytes": _pl2max.value,
-                    "step": "zero grad buffer + fp32->fp16 table refresh + forward + backward" + (" + all-reduce" if world > 1 else "")})
+        run_detail = {"l2_fetch_granularity": _gran.value, "head_grad_group_width": job.group_w,
+                      "l2_persisting_bytes": _pl2.value, "l2_persisting_max_bytes": _pl2max.value,
+                      "allreduce": (f"overlapped with the backward in {args.sync_chunks} level runs" if sync is not None
+                                    else ("one collective after the backward" if world > 1 else "none")),
+                      "step": "zero grad buffer + fp32->fp16 table refresh + forward + backward" + (" + all-reduce" if world > 1 else "")}
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -916,6 +919,7 @@ def measure(args, name, wl, ctx, steps, want_clocks=True):
             "vs_baseline": None, "dtype": "f16 tables / f32 accumulate" if wl["table_dtype"] == "float16" else "f32",
             "data": "synthetic",
             "config": cfg,
+            "run": run_detail,
             "kernels_ms": {"forward": fwd_ms, "backward": bwd_ms, "allreduce": ar_ms, **(head_ms or {})},
             "roofline": {"bound": "hbm", "kernel": f"grid4d_{dom}_kernel", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,

@@ -1,13 +1,13 @@
 #!/bin/bash
 # round-2 profiling pass (one gpurun call): plain run of each command first, then the launch list / full capture of it.
-#   usage: scripts/gpu_r02d.sh [proj] [field] [c1r] [c3] [c5h768]
+#   usage: TAG=r02x scripts/gpu_profile.sh [proj] [field] [c1r] [c3] [c5h768]
 mkdir -p gpurun_out
 prof() {   # tag, kernel regex, skip, count, command...
   local tag=$1 rx=$2 skip=$3 cnt=$4; shift 4
-  "$@" > gpurun_out/r02d_plain_$tag.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02d_launches_$tag.csv "$@" > gpurun_out/r02d_ncu1_$tag.log 2>&1
-  ncu --set full --clock-control none --import-source on -k regex:"$rx" -s $skip -c $cnt -o gpurun_out/r02d_prof_$tag "$@" > gpurun_out/r02d_ncu2_$tag.log 2>&1
-  ls -la gpurun_out/r02d_prof_$tag* 2>/dev/null
+  "$@" > gpurun_out/${TAG:-r02}_plain_$tag.log 2>&1 &&
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${TAG:-r02}_launches_$tag.csv "$@" > gpurun_out/${TAG:-r02}_ncu1_$tag.log 2>&1
+  ncu --set full --clock-control none --import-source on -k regex:"$rx" -s $skip -c $cnt -o gpurun_out/${TAG:-r02}_prof_$tag "$@" > gpurun_out/${TAG:-r02}_ncu2_$tag.log 2>&1
+  ls -la gpurun_out/${TAG:-r02}_prof_$tag* 2>/dev/null
 }
 for what in "$@"; do
   case $what in

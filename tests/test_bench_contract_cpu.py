@@ -35,7 +35,9 @@ def test_reference_arm_prints_the_contract_line():
     assert e2e["h2d_bytes_per_step"] == 0 and e2e["d2h_bytes_per_step"] == 0
     assert d["gpu_launches"] == 0
     # same config keys as the GPU arm's line (the driver compares them), plus what the bounded sample was
-    assert {"workload", "description", "points_per_gpu", "coords", "levels", "table_size", "interpolation", "sample"} <= set(d["config"])
+    assert {"workload", "description", "points_per_gpu", "coords", "levels", "table_size", "interpolation", "l2_policy"} <= set(d["config"])
+    import bench
+    assert d["config"] == bench.describe_config("c2", dict(bench.WORKLOADS["c2"]), 2 ** 22, 1)      # word for word the GPU arm's
 
 
 def test_reference_arm_at_the_reference_geometry_runs_the_reference_or_its_port():
