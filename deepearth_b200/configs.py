@@ -60,6 +60,8 @@ class DeepEarthConfig:
                                               # on for the widths the reference uses (hidden_dim a multiple of 128: 768,
                                               # 2048 -> csrc/proj_kernels.cu), off otherwise; True also takes the 64-wide
                                               # one-kernel head (csrc/mlp_head.cu); False = the fp32 nn.Sequential
+    grid4d_flat_tables: bool = False        # one (L, T, F) parameter per grid instead of L (T, F) parameters; state dicts
+                                            # keep the reference's keys hash_tables.{l}.weight
     spacetime_resolutions: List[int] = None  # resolutions of the xyt/yzt/xzt grids (decomposed mode)
 
     def __post_init__(self):

@@ -51,6 +51,7 @@ class Grid4DEncoder(nn.Module):
         F = config.n_features_per_level
         table_dtype = _cfg(config, "grid4d_table_dtype", "float32")
         table_scale = getattr(config, "grid4d_table_scale", None)
+        flat = bool(_cfg(config, "grid4d_flat_tables", False))
 
         if self.mode == "reference":
             interp = _cfg(config, "grid4d_interpolation", "nearest")
@@ -59,12 +60,12 @@ class Grid4DEncoder(nn.Module):
                 n_levels=config.n_spatial_levels, n_features_per_level=F,
                 resolutions=config.spatial_resolutions, hash_table_size=config.hash_table_size, coords_dim=3,
                 interpolation=interp, dense_fallback=dense, table_dtype=table_dtype, table_scale=table_scale,
-                dims=(0, 1, 2))
+                dims=(0, 1, 2), flat_tables=flat)
             self.temporal_encoder = MultiResolutionHashEncoding(
                 n_levels=config.n_temporal_levels, n_features_per_level=F,
                 resolutions=config.temporal_resolutions, hash_table_size=config.hash_table_size // 4,
                 coords_dim=1, interpolation=interp, dense_fallback=dense, table_dtype=table_dtype,
-                table_scale=table_scale, dims=(3,))
+                table_scale=table_scale, dims=(3,), flat_tables=flat)
             self._encoders = [self.spatial_encoder, self.temporal_encoder]
             self._mask_ids = [1, 2]
         elif self.mode == "decomposed":
@@ -72,7 +73,8 @@ class Grid4DEncoder(nn.Module):
             dense = bool(_cfg(config, "grid4d_dense_fallback", True))
             st_res = _cfg(config, "spacetime_resolutions", config.temporal_resolutions)
             kw = dict(n_features_per_level=F, hash_table_size=config.hash_table_size, coords_dim=3,
-                      interpolation=interp, dense_fallback=dense, table_dtype=table_dtype, table_scale=table_scale)
+                      interpolation=interp, dense_fallback=dense, table_dtype=table_dtype, table_scale=table_scale,
+                      flat_tables=flat)
             self.xyz_encoder = MultiResolutionHashEncoding(
                 n_levels=config.n_spatial_levels, resolutions=config.spatial_resolutions, dims=GRID_DIMS["xyz"], **kw)
             self.xyt_encoder = MultiResolutionHashEncoding(
@@ -135,10 +137,13 @@ class Grid4DEncoder(nn.Module):
             raise ValueError(f"xyzt must be (B, 4), got {tuple(xyzt.shape)}")
         Fn._require_cuda(xyzt, "xyzt")
         weights: List[torch.Tensor] = []
+        leaves: List[torch.Tensor] = []
         for enc in self._encoders:
             weights += enc.weights()
+            leaves += enc.autograd_tensors()
         Fn._require_cuda(weights[0], "hash table weights")
-        ptrs = self._working_ptrs(weights) if self._encoders[0].table_dtype == torch.float16 else None
+        ptrs = (self._working_ptrs(weights) if self._encoders[0].table_dtype == torch.float16
+                else [w.data_ptr() for w in weights])
         if self.mode == "decomposed" and (spatial_mask is not None or temporal_mask is not None):
             xyzt = xyzt.clone()                       # SPECIFICATIONS.MD:1159-1164: mask coordinates
             if spatial_mask is not None:
@@ -146,7 +151,7 @@ class Grid4DEncoder(nn.Module):
             if temporal_mask is not None:
                 xyzt[~temporal_mask.bool(), 3] = 0
             spatial_mask = temporal_mask = None
-        return Grid4DFunction.apply(xyzt, spatial_mask, temporal_mask, self._plan(), ptrs, *weights)
+        return Grid4DFunction.apply(xyzt, spatial_mask, temporal_mask, self._plan(), ptrs, *leaves)
 
     @torch.no_grad()
     def encode_field(self, converter, lat_range, lon_range, n_lat: int, n_lon: int, altitude: float = 0.0,

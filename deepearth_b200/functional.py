@@ -345,7 +345,12 @@ class Grid4DFunction(torch.autograd.Function):
     @staticmethod
     @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
     def forward(ctx, coords, mask_a, mask_b, plan: EncodePlan, working_ptrs, *weights):
+        # weights: the autograd leaves -- one (T, F) parameter per level, or one flat (L, T, F) parameter per encoder; in
+        # plan order either way, so the flat gradient buffer splits by numel.  working_ptrs: per-LEVEL device pointers of
+        # the tables the kernel reads (required with flat parameters)
         ptrs = working_ptrs if working_ptrs is not None else [w.data_ptr() for w in weights]
+        if len(ptrs) != len(plan.specs):
+            raise ValueError("Grid4DFunction: one table pointer per level is required")
         out = encode_forward(plan.specs, coords, ptrs, plan.table_dtype, plan.n_features, plan.out_cols,
                              plan.linear, 1.0 / plan.table_scale if plan.table_scale != 1.0 else 1.0,
                              mask_a, mask_b, levels_per_group=plan.levels_per_group, extra_flags=plan.extra_flags)
@@ -383,18 +388,23 @@ class Grid4DFunction(torch.autograd.Function):
             encode_backward(plan.specs, coords, grad_out, [base + 4 * o for o in plan.grad_offsets],
                             plan.n_features, plan.linear, mask_a, mask_b,
                             levels_per_group=plan.bwd_levels_per_group, extra_flags=plan.extra_flags, group_width=W)
-        # per-table views of the flat buffer: one view + unbind per run of equally shaped tables (64 slice + view
-        # calls were ~0.2 ms of host time per step, a visible share of a small-batch step)
+        # gradients as views of the flat buffer, split by numel in plan order: one view + unbind per run of equally shaped
+        # (T, F) tables (64 slice + view calls were ~0.2 ms of host time per step), one view per flat (L, T, F) parameter
         grads: list = []
         shapes = ctx.weight_shapes
-        i = 0
+        i, o = 0, 0
         while i < n_w:
             j = i + 1
-            while j < n_w and shapes[j] == shapes[i]:
+            while j < n_w and shapes[j] == shapes[i] and len(shapes[i]) == 2:
                 j += 1
-            o = plan.grad_offsets[i]
-            numel = plan.specs[i].table_size * plan.n_features
-            grads.extend(flat[o:o + (j - i) * numel].view(j - i, *shapes[i]).unbind(0))
+            numel = 1
+            for d in shapes[i]:
+                numel *= d
+            if j - i > 1:
+                grads.extend(flat[o:o + (j - i) * numel].view(j - i, *shapes[i]).unbind(0))
+            else:
+                grads.append(flat[o:o + numel].view(*shapes[i]))
+            o += (j - i) * numel
             i = j
         if not all(ctx.needs_input_grad[5:]):
             grads = [g if ctx.needs_input_grad[5 + k] else None for k, g in enumerate(grads)]

@@ -29,12 +29,48 @@ _DTYPES = {"float32": torch.float32, "fp32": torch.float32, "float16": torch.flo
 DEFAULT_F16_TABLE_SCALE = 4096.0  # 2^12: lifts the U(-1e-4,1e-4) init out of the fp16 subnormal range
 
 
+class _LevelView:
+    """`hash_tables[l]` of a flat-table encoder: exposes `.weight` (a (T, F) view of the flat parameter) and the
+    nn.Embedding attributes callers read."""
+
+    def __init__(self, owner, level: int):
+        self._owner, self._level = owner, level
+
+    @property
+    def weight(self) -> torch.Tensor:
+        return self._owner.tables[self._level]
+
+    @property
+    def num_embeddings(self) -> int:
+        return self._owner.hash_table_size
+
+    @property
+    def embedding_dim(self) -> int:
+        return self._owner.n_features_per_level
+
+
+class _TableViews:
+    def __init__(self, owner):
+        self._owner = owner
+
+    def __len__(self) -> int:
+        return self._owner.n_levels
+
+    def __getitem__(self, l: int) -> _LevelView:
+        if not -len(self) <= l < len(self):
+            raise IndexError(l)
+        return _LevelView(self._owner, l % len(self))
+
+    def __iter__(self):
+        return (_LevelView(self._owner, l) for l in range(len(self)))
+
+
 class MultiResolutionHashEncoding(nn.Module):
     def __init__(self, n_levels: int, n_features_per_level: int, resolutions: List[int],
                  hash_table_size: int, coords_dim: int, *, interpolation: str = "nearest",
                  dense_fallback: bool = False, table_dtype="float32", table_scale: Optional[float] = None,
                  dims: Optional[Sequence[int]] = None, levels_per_group: int = 0,
-                 bwd_levels_per_group: int = 0):
+                 bwd_levels_per_group: int = 0, flat_tables: bool = False):
         super().__init__()
         if not 1 <= coords_dim <= 4:
             raise ValueError(f"coords_dim must be in 1..4 (the reference has 4 primes, hash_encoding.py:64), got {coords_dim}")
@@ -66,10 +102,19 @@ class MultiResolutionHashEncoding(nn.Module):
         self.bwd_levels_per_group = bwd_levels_per_group
         self.extra_flags = 0   # DE_FLAG_* A/B switches (include/de_grid4d.h); 0 = every optimisation on
 
-        self.hash_tables = nn.ModuleList(
-            [nn.Embedding(hash_table_size, n_features_per_level) for _ in range(n_levels)])
-        for table in self.hash_tables:
+        # the reference's construction (and RNG consumption): n_levels nn.Embedding, then uniform init (hash_encoding.py:38-45)
+        tables = nn.ModuleList([nn.Embedding(hash_table_size, n_features_per_level) for _ in range(n_levels)])
+        for table in tables:
             nn.init.uniform_(table.weight, -1e-4, 1e-4)
+        self.flat_tables = bool(flat_tables)
+        if self.flat_tables:
+            # ONE (L, T, F) parameter: autograd, optimisers and DDP see one tensor per encoder instead of L (the per-level
+            # bookkeeping is ~0.3 ms of a small-batch step).  `hash_tables[l].weight` stays readable (a view) and state dicts
+            # keep the reference's keys `hash_tables.{l}.weight` (_save_to_state_dict / _load_from_state_dict below).
+            self.tables = nn.Parameter(torch.stack([t.weight.detach() for t in tables]))
+            object.__setattr__(self, "hash_tables", _TableViews(self))
+        else:
+            self.hash_tables = tables
 
         self._work: Optional[torch.Tensor] = None   # flat fp16 working copy (L, T, F)
         self._work_key = None
@@ -101,7 +146,40 @@ class MultiResolutionHashEncoding(nn.Module):
         return specs
 
     def weights(self) -> List[torch.Tensor]:
+        """Per-level (T, F) tensors (parameters, or views of the flat parameter): what the kernels take pointers of."""
+        if self.flat_tables:
+            return list(self.tables.unbind(0))
         return [t.weight for t in self.hash_tables]
+
+    def autograd_tensors(self) -> List[torch.Tensor]:
+        """The leaves autograd differentiates: the L level parameters, or the one flat parameter."""
+        return [self.tables] if self.flat_tables else [t.weight for t in self.hash_tables]
+
+    # ---- state dict: the reference's keys in both layouts -----------------------------------------------------
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        if not self.flat_tables:
+            return super()._save_to_state_dict(destination, prefix, keep_vars)
+        for l in range(self.n_levels):
+            t = self.tables[l]
+            destination[f"{prefix}hash_tables.{l}.weight"] = t if keep_vars else t.detach()
+
+    def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs):
+        if not self.flat_tables:
+            return super()._load_from_state_dict(state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
+                                                 error_msgs)
+        with torch.no_grad():
+            for l in range(self.n_levels):
+                key = f"{prefix}hash_tables.{l}.weight"
+                if key not in state_dict:
+                    missing_keys.append(key)
+                    continue
+                src = state_dict[key]
+                if tuple(src.shape) != tuple(self.tables.shape[1:]):
+                    error_msgs.append(f"size mismatch for {key}: copying a param with shape {tuple(src.shape)} from checkpoint, "
+                                      f"the shape in current model is {tuple(self.tables.shape[1:])}.")
+                    continue
+                self.tables[l].copy_(src)
+        self._work_key = None
 
     # ---- fp16 working tables ----------------------------------------------------------------------
     def working_ptrs(self) -> Optional[List[int]]:
@@ -180,8 +258,10 @@ class MultiResolutionHashEncoding(nn.Module):
         # 0..D-1; a wider row (e.g. xyzt) is read through self.dims
         dims = self.dims if coords.shape[1] > max(self.dims) else tuple(range(self.coords_dim))
         Fn._require_cuda(coords, "coords")
-        Fn._require_cuda(self.hash_tables[0].weight, "hash table weights")
-        return Grid4DFunction.apply(coords, None, None, self.plan(dims), self.working_ptrs(), *self.weights())
+        ws = self.weights()
+        Fn._require_cuda(ws[0], "hash table weights")
+        ptrs = self.working_ptrs() if self.table_dtype == torch.float16 else [w.data_ptr() for w in ws]
+        return Grid4DFunction.apply(coords, None, None, self.plan(dims), ptrs, *self.autograd_tensors())
 
     def extra_repr(self) -> str:
         return (f"levels={self.n_levels}, F={self.n_features_per_level}, T={self.hash_table_size}, D={self.coords_dim}, "

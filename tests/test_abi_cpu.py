@@ -176,3 +176,34 @@ def test_import_shim_serves_the_reference_import_lines():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stderr[-2000:]
+
+
+def test_flat_table_parameter_keeps_the_reference_state_dict():
+    """flat_tables=True: one (L, T, F) parameter per encoder, same initial values as the per-level layout under the same
+    seed, state dicts interchangeable in both directions with the reference's keys hash_tables.{l}.weight."""
+    import torch
+    import deepearth_b200 as de
+    torch.manual_seed(5)
+    a = de.MultiResolutionHashEncoding(4, 2, [4, 8, 16, 32], 64, 3)
+    torch.manual_seed(5)
+    b = de.MultiResolutionHashEncoding(4, 2, [4, 8, 16, 32], 64, 3, flat_tables=True)
+    sa, sb = a.state_dict(), b.state_dict()
+    assert list(sa.keys()) == list(sb.keys()) == [f"hash_tables.{l}.weight" for l in range(4)]
+    assert all(torch.equal(sa[k], sb[k]) for k in sa)
+    assert [n for n, _ in b.named_parameters()] == ["tables"] and b.tables.shape == (4, 64, 2)
+    assert len(b.hash_tables) == 4 and b.hash_tables[2].weight.shape == (64, 2)
+    torch.manual_seed(6)
+    c = de.MultiResolutionHashEncoding(4, 2, [4, 8, 16, 32], 64, 3, flat_tables=True)
+    res = c.load_state_dict(sa)
+    assert not res.missing_keys and not res.unexpected_keys
+    assert all(torch.equal(c.tables[l], sa[f"hash_tables.{l}.weight"]) for l in range(4))
+    d = de.MultiResolutionHashEncoding(4, 2, [4, 8, 16, 32], 64, 3)
+    d.load_state_dict(c.state_dict())
+    assert all(torch.equal(d.hash_tables[l].weight, c.tables[l]) for l in range(4))
+    import pytest
+    with pytest.raises(RuntimeError):
+        c.load_state_dict({k: v for k, v in sa.items() if not k.endswith("3.weight")})      # strict: missing key
+    g = de.Grid4DEncoder(de.DeepEarthConfig(hidden_dim=16, hash_table_size=64, grid4d_flat_tables=True))
+    names = [n for n, _ in g.named_parameters()]
+    assert names[:2] == ["spatial_encoder.tables", "temporal_encoder.tables"]
+    assert "spatial_encoder.hash_tables.0.weight" in g.state_dict() and "temporal_encoder.hash_tables.7.weight" in g.state_dict()

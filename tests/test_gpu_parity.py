@@ -913,3 +913,49 @@ def test_graphed_features_match_eager_and_follow_optimiser_steps(dev):
         with torch.no_grad():                                  # an "optimiser step": the next replay must see the new tables
             for w in tables:
                 w.add_(torch.randn_like(w) * 1e-4)
+
+
+@pytest.mark.parametrize("mode", ["reference", "decomposed"])
+def test_flat_table_parameter_matches_per_level_layout(dev, mode):
+    """config.grid4d_flat_tables: identical features, the flat gradient equals the stacked per-level gradients, optimiser
+    step + state-dict round trip through the reference's keys, and the CUDA-graph path on top of it."""
+    import deepearth_b200 as de
+    kw = dict(hidden_dim=32, n_heads=4, n_layers=1, hash_table_size=2 ** 14)
+    if mode == "decomposed":
+        res = [2 ** i for i in range(4, 12)]
+        kw.update(n_spatial_levels=8, n_temporal_levels=8, spatial_resolutions=res, temporal_resolutions=res,
+                  grid4d_mode="decomposed", grid4d_table_dtype="float16")
+    torch.manual_seed(11)
+    a = de.Grid4DEncoder(de.DeepEarthConfig(**kw)).to(dev).train()
+    torch.manual_seed(11)
+    b = de.Grid4DEncoder(de.DeepEarthConfig(grid4d_flat_tables=True, **kw)).to(dev).train()
+    assert len(list(b.parameters())) == len(a._encoders) + 6
+    g = torch.Generator(device=dev).manual_seed(2)
+    n = 5000
+    xyzt = torch.rand((n, 4), device=dev, generator=g) * 1.2 - 0.1
+    gout = torch.randn((n, a.feature_dim), device=dev, generator=g)
+    fa = a.encode_features(xyzt)
+    fb = b.encode_features(xyzt)
+    assert torch.equal(fa, fb)
+    fa.backward(gout)
+    fb.backward(gout)
+    for ea, eb in zip(a._encoders, b._encoders):
+        want = torch.stack([w.grad for w in ea.weights()])
+        assert eb.tables.grad.shape == want.shape
+        assert float((eb.tables.grad - want).abs().max()) <= 1e-5 * max(float(want.abs().max()), 1e-30)
+    opt = torch.optim.AdamW(b.parameters(), lr=1e-3)
+    opt.step()
+    a.load_state_dict(b.state_dict())                          # reference keys in, per-level layout
+    with torch.no_grad():
+        assert torch.equal(a.encode_features(xyzt), b.encode_features(xyzt))
+    graphed = b.graphed_features(xyzt)
+    b.zero_grad(set_to_none=True)
+    fg = graphed(xyzt)
+    fg.backward(gout)
+    a.zero_grad(set_to_none=True)
+    fe = a.encode_features(xyzt)
+    fe.backward(gout)
+    assert torch.equal(fg, fe)
+    for ea, eb in zip(a._encoders, b._encoders):
+        want = torch.stack([w.grad for w in ea.weights()])
+        assert float((eb.tables.grad - want).abs().max()) <= 1e-5 * max(float(want.abs().max()), 1e-30)
