@@ -208,7 +208,10 @@ class Grid4DEncoder(nn.Module):
         parameters).  Replays cost two graph launches.  Every kernel of the path is capture-safe (no synchronisation, no
         host-side state, scratch from the caching allocator); the fp32 -> fp16 table refresh is part of the forward graph,
         so optimiser steps between replays are seen.  Usual CUDA-graph rules apply: fixed shape, no masks, gradients are
-        written into static buffers (set ``p.grad = None`` or step the optimiser before the next replay)."""
+        written into static buffers (set ``p.grad = None`` or step the optimiser before the next replay), and the call must
+        come BEFORE the module's first eager backward (autograd binds a parameter's AccumulateGrad node to the stream of its
+        first backward; one bound to the default stream cannot run inside a capture).  With ``grid4d_flat_tables`` a c2 step
+        at 4096 points takes 0.18 ms (0.76 ms eager, per-level parameters)."""
         Fn._require_cuda(sample_xyzt, "sample_xyzt")
         feats = _GraphedFeatures(self)
         return torch.cuda.make_graphed_callables(feats, (sample_xyzt,), num_warmup_iters=num_warmup_iters)

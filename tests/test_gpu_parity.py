@@ -948,14 +948,19 @@ def test_flat_table_parameter_matches_per_level_layout(dev, mode):
     a.load_state_dict(b.state_dict())                          # reference keys in, per-level layout
     with torch.no_grad():
         assert torch.equal(a.encode_features(xyzt), b.encode_features(xyzt))
-    graphed = b.graphed_features(xyzt)
-    b.zero_grad(set_to_none=True)
+    # CUDA graphs on top of the flat layout.  Captured on a FRESH module: autograd ties a parameter's AccumulateGrad node to
+    # the stream of its first backward, so graphed_features must be called before the module's first eager backward
+    torch.manual_seed(11)
+    c = de.Grid4DEncoder(de.DeepEarthConfig(grid4d_flat_tables=True, **kw)).to(dev).train()
+    c.load_state_dict(b.state_dict())
+    graphed = c.graphed_features(xyzt)
+    c.zero_grad(set_to_none=True)
     fg = graphed(xyzt)
     fg.backward(gout)
     a.zero_grad(set_to_none=True)
     fe = a.encode_features(xyzt)
     fe.backward(gout)
     assert torch.equal(fg, fe)
-    for ea, eb in zip(a._encoders, b._encoders):
+    for ea, ec in zip(a._encoders, c._encoders):
         want = torch.stack([w.grad for w in ea.weights()])
-        assert float((eb.tables.grad - want).abs().max()) <= 1e-5 * max(float(want.abs().max()), 1e-30)
+        assert float((ec.tables.grad - want).abs().max()) <= 1e-5 * max(float(want.abs().max()), 1e-30)
