@@ -737,6 +737,9 @@ def _head_reference(x, seq):
     return bf(h) @ bf(mods[-1].weight).t() + mods[-1].bias
 
 
+HEAD_BWD_TOL = 8e-3          # B200 (gpurun r02p): worst 3.7e-3 over every shape and gradient; 2x that
+
+
 @pytest.mark.parametrize("in_dim,layernorm,act", [(128, True, "gelu"), (48, True, "gelu"), (64, False, "relu"),
                                                   (32, False, "none"), (96, True, "relu")])
 def test_mlp_head_vs_torch(dev, in_dim, layernorm, act):
@@ -787,6 +790,7 @@ def test_mlp_head_vs_torch(dev, in_dim, layernorm, act):
             h = m(h)
         return torch.nn.functional.linear(ste(h), ste(seq[-1].weight), seq[-1].bias)
 
+    worst = {}
     for n in (777, 128 * 148 * 3 + 5):
         x = torch.randn((n, in_dim), device=dev, generator=g, requires_grad=True)
         gy = torch.randn((n, 64), device=dev, generator=g)
@@ -800,7 +804,9 @@ def test_mlp_head_vs_torch(dev, in_dim, layernorm, act):
         for k, w in want.items():
             assert got[k] is not None, k
             err = float((got[k] - w).abs().max()) / max(float(w.abs().max()), 1e-20)
-            assert err <= 4e-2, (n, k, err)
+            worst[k] = max(worst.get(k, 0.0), err)
+            assert err <= HEAD_BWD_TOL, (n, k, err)
+    print(f"head backward in_dim={in_dim} ln={layernorm} act={act}:", {k: f"{v:.1e}" for k, v in worst.items()})
 
 
 def test_grid4d_encoder_fused_head(dev):
