@@ -209,6 +209,83 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
     return v[0];
 }
 
+// ---- packed fp32 x 2 arithmetic (sm_100: FFMA2 / FADD2 / FMUL2, one issue slot for two lanes' worth of flops) ----------
+// The LayerNorm / GELU epilogues of the wide projection are instruction-issue bound; three quarters of their instructions
+// are fp32 pipe operations.  Each half of a pair is an ordinary IEEE operation: results equal the scalar code's bit for bit.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+    f32x2 v;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "f"(lo), "f"(hi));
+    return v;
+}
+__device__ __forceinline__ f32x2 pk2u(uint32_t lo, uint32_t hi) {
+    f32x2 v;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "r"(lo), "r"(hi));
+    return v;
+}
+__device__ __forceinline__ void upk2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 splat2(float x) { return pk2(x, x); }
+
+// GELU on a pair.  q = 1 - Phi(|z|) with the polynomial of gelu_parts (its 0.5 folded into the coefficients: exact), the
+// exponential as one ex2.approx.ftz of -z^2/2 * log2 e (the non-ftz __expf wraps MUFU.EX2 in a range test and two FMULs
+// per element; flushing exp(-z^2/2) < 2^-126 to zero changes nothing at the bf16 precision of the outputs).
+__device__ __forceinline__ void gelu_tail2(f32x2 z, f32x2& az, f32x2& q, f32x2& e) {
+    float zl, zh;
+    upk2(z, zl, zh);
+    az = pk2(fabsf(zl), fabsf(zh));
+    const f32x2 x = mul2(az, splat2(0.70710678118654752f));
+    float dl, dh;
+    upk2(fma2(splat2(0.3275911f), x, splat2(1.0f)), dl, dh);
+    float tl, th;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(tl) : "f"(dl));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(th) : "f"(dh));
+    const f32x2 t = pk2(tl, th);
+    float al, ah, el, eh;
+    upk2(mul2(mul2(x, x), splat2(-1.4426950408889634f)), al, ah);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(el) : "f"(al));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(eh) : "f"(ah));
+    e = pk2(el, eh);
+    f32x2 p = fma2(t, splat2(0.5f * 1.061405429f), splat2(0.5f * -1.453152027f));
+    p = fma2(t, p, splat2(0.5f * 1.421413741f));
+    p = fma2(t, p, splat2(0.5f * -0.284496736f));
+    p = fma2(t, p, splat2(0.5f * 0.254829592f));
+    q = mul2(mul2(p, t), e);
+}
+// gelu(z) = z Phi(z) = max(z, 0) - |z| q   (z >= 0: z - z q;  z < 0: z q)
+__device__ __forceinline__ f32x2 gelu_fwd2(f32x2 z) {
+    f32x2 az, q, e;
+    gelu_tail2(z, az, q, e);
+    float zl, zh;
+    upk2(z, zl, zh);
+    return fma2(az, mul2(q, splat2(-1.0f)), pk2(fmaxf(zl, 0.0f), fmaxf(zh, 0.0f)));
+}
+// a = gelu(z), g = d gelu / dz = Phi(z) + z phi(z), Phi(z) = 0.5 + copysign(0.5 - q, z)
+__device__ __forceinline__ void gelu_fwd_bwd2(f32x2 z, f32x2& a, f32x2& g) {
+    f32x2 az, q, e;
+    gelu_tail2(z, az, q, e);
+    float zl, zh, hl, hh;
+    upk2(z, zl, zh);
+    upk2(fma2(q, splat2(-1.0f), splat2(0.5f)), hl, hh);
+    const f32x2 cdf = add2(splat2(0.5f), pk2(copysignf(hl, zl), copysignf(hh, zh)));
+    a = mul2(z, cdf);
+    g = fma2(mul2(z, splat2(0.3989422804014327f)), e, cdf);
+}
+
 // 2-byte element (row r, column c) of a K-major canonical tile with kt columns
 __device__ __forceinline__ uint32_t canon_elem_offset(int r, int c, int kt) {
     return static_cast<uint32_t>((r >> 3) * (kt >> 3) * 128 + (c >> 3) * 128 + (r & 7) * 16 + (c & 7) * 2);

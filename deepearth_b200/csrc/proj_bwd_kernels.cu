@@ -251,28 +251,39 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                     const float4* bev = reinterpret_cast<const float4*>(P.ln_beta + col0);
                     float dvx[32];
                     uint32_t tp[16];
+                    // packed pairs (mlp_common.cuh): columns (2k, 2k + 1) of the piece share one FFMA2 / FMUL2 / FADD2
+                    const f32x2 nmean2 = splat2(-mean), rstd2 = splat2(rstd);
+                    f32x2 s1p = 0ull, s2p = 0ull;
 #pragma unroll
                     for (int j4 = 0; j4 < 8; ++j4) {
                         const float4 b4 = __ldg(b1v + j4), g4 = __ldg(gav + j4), e4 = __ldg(bev + j4);
-                        const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, gg[4] = {g4.x, g4.y, g4.z, g4.w}, ee[4] = {e4.x, e4.y, e4.z, e4.w};
-                        float tt[4];
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const int j = 4 * j4 + u;
-                            const float xh = (v[j] + bb[u] - mean) * rstd;
-                            float act, gp;
-                            gelu_fwd_bwd(fmaf(gg[u], xh, ee[u]), act, gp);
+                        for (int u = 0; u < 2; ++u) {
+                            const int j = 4 * j4 + 2 * u;
+                            const f32x2 b2 = u ? pk2(b4.z, b4.w) : pk2(b4.x, b4.y);
+                            const f32x2 g2 = u ? pk2(g4.z, g4.w) : pk2(g4.x, g4.y);
+                            const f32x2 e2 = u ? pk2(e4.z, e4.w) : pk2(e4.x, e4.y);
+                            const f32x2 xh = mul2(add2(add2(pk2(v[j], v[j + 1]), b2), nmean2), rstd2);
+                            f32x2 act, gp;
+                            gelu_fwd_bwd2(fma2(g2, xh, e2), act, gp);
                             const uint32_t pr = dw[j >> 1];
-                            const float da = __uint_as_float((j & 1) ? (pr & 0xffff0000u) : (pr << 16));      // bf16 -> fp32
-                            const float dv = da * gp;
-                            tt[u] = gg[u] * dv;
-                            s1 += tt[u];
-                            s2 = fmaf(tt[u], xh, s2);
-                            v[j] = dv;                          // column sums: dbeta
-                            dvx[j] = dv * xh;                   //              dgamma
+                            const f32x2 dv = mul2(pk2u(pr << 16, pr & 0xffff0000u), gp);               // bf16 -> fp32, times GELU'
+                            const f32x2 tt = mul2(g2, dv);
+                            s1p = add2(s1p, tt);
+                            s2p = fma2(tt, xh, s2p);
+                            upk2(dv, v[j], v[j + 1]);                                // column sums: dbeta
+                            upk2(mul2(dv, xh), dvx[j], dvx[j + 1]);                  //              dgamma
+                            float t0, t1;
+                            upk2(tt, t0, t1);
+                            tp[j >> 1] = pack_bf16(t0, t1);
                         }
-                        tp[2 * j4] = pack_bf16(tt[0], tt[1]);
-                        tp[2 * j4 + 1] = pack_bf16(tt[2], tt[3]);
+                    }
+                    {
+                        float a0, a1, c0, c1;
+                        upk2(s1p, a0, a1);
+                        upk2(s2p, c0, c1);
+                        s1 += a0 + a1;
+                        s2 += c0 + c1;
                     }
                     if (live) {
 #pragma unroll
@@ -291,17 +302,18 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                     tmem_ld32(t_base + q * 32, v);
                     const uint32_t* tw = reinterpret_cast<const uint32_t*>(tq);
                     const float m1 = s1 * inv_h, m2 = s2 * inv_h;
+                    const f32x2 nmean2 = splat2(-mean), rstd2 = splat2(rstd), nm1 = splat2(-m1), nm2 = splat2(-m2);
 #pragma unroll
                     for (int j4 = 0; j4 < 8; ++j4) {
                         const float4 b4 = __ldg(b1v + j4);
-                        const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const int j = 4 * j4 + u;
-                            const float xh = (v[j] + bb[u] - mean) * rstd;
+                        for (int u = 0; u < 2; ++u) {
+                            const int j = 4 * j4 + 2 * u;
+                            const f32x2 b2 = u ? pk2(b4.z, b4.w) : pk2(b4.x, b4.y);
+                            const f32x2 xh = mul2(add2(add2(pk2(v[j], v[j + 1]), b2), nmean2), rstd2);
                             const uint32_t pr = tw[j >> 1];
-                            const float t = __uint_as_float((j & 1) ? (pr & 0xffff0000u) : (pr << 16));
-                            v[j] = rstd * (t - m1 - xh * m2);
+                            const f32x2 t = pk2u(pr << 16, pr & 0xffff0000u);
+                            upk2(mul2(rstd2, fma2(xh, nm2, add2(t, nm1))), v[j], v[j + 1]);
                         }
                     }
                     uint32_t pk[16];
@@ -339,7 +351,8 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0)
+    if (tid < 32)                     // ONE warp: with 256 threads "warp" (the TMEM lane quarter) is 0 for warps 0 and 4, and a second
+                                      // dealloc of the same columns traps (intermittently: only when it sees the first one's update)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * kBwdChunkN) : "memory");
 }
 

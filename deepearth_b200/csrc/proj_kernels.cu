@@ -178,23 +178,30 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
                     for (int u = 0; u < 4; ++u) bb[u] = __ldg(b1 + u);
                     tmem_ld16_wait(rb[i & 1]);
                     if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
-                    float v[16];
-                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+                    // packed pairs (FADD2 / FFMA2): half the fp32-pipe instructions of the scalar form
+                    f32x2 v[8];
+                    f32x2 sa = 0ull, sb = 0ull;                     // (+0, +0)
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        v[4 * u] = __uint_as_float(rb[i & 1][4 * u]) + bb[u].x;
-                        v[4 * u + 1] = __uint_as_float(rb[i & 1][4 * u + 1]) + bb[u].y;
-                        v[4 * u + 2] = __uint_as_float(rb[i & 1][4 * u + 2]) + bb[u].z;
-                        v[4 * u + 3] = __uint_as_float(rb[i & 1][4 * u + 3]) + bb[u].w;
-                        s0 += v[4 * u]; s1 += v[4 * u + 1]; s2 += v[4 * u + 2]; s3 += v[4 * u + 3];
+                        v[2 * u] = add2(pk2u(rb[i & 1][4 * u], rb[i & 1][4 * u + 1]), pk2(bb[u].x, bb[u].y));
+                        v[2 * u + 1] = add2(pk2u(rb[i & 1][4 * u + 2], rb[i & 1][4 * u + 3]), pk2(bb[u].z, bb[u].w));
+                        sa = add2(sa, v[2 * u]);
+                        sb = add2(sb, v[2 * u + 1]);
                     }
+                    float s0, s1, s2, s3;
+                    upk2(sa, s0, s1);
+                    upk2(sb, s2, s3);
                     const float mb = ((s0 + s1) + (s2 + s3)) * (1.0f / 16.0f);
-                    s0 = s1 = s2 = s3 = 0.f;
+                    const f32x2 nmb = splat2(-mb);
+                    sa = sb = 0ull;
 #pragma unroll
-                    for (int j = 0; j < 16; j += 4) {
-                        const float d0 = v[j] - mb, d1 = v[j + 1] - mb, d2 = v[j + 2] - mb, d3 = v[j + 3] - mb;
-                        s0 = fmaf(d0, d0, s0); s1 = fmaf(d1, d1, s1); s2 = fmaf(d2, d2, s2); s3 = fmaf(d3, d3, s3);
+                    for (int j = 0; j < 8; j += 2) {
+                        const f32x2 d0 = add2(v[j], nmb), d1 = add2(v[j + 1], nmb);
+                        sa = fma2(d0, d0, sa);
+                        sb = fma2(d1, d1, sb);
                     }
+                    upk2(sa, s0, s1);
+                    upk2(sb, s2, s3);
                     chan_merge(cnt, mean, m2, 16.0f, mb, (s0 + s1) + (s2 + s3));
                 }
                 if (g == NC - 1) {
@@ -224,14 +231,18 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
                     tmem_ld16_wait(rb[i & 1]);
                     if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
                     uint32_t packed[8];
+                    const f32x2 nmean = splat2(-mean), rstd2 = splat2(rstd);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const float a0 = fmaf((__uint_as_float(rb[i & 1][4 * u]) + bb[u].x - mean) * rstd, gg[u].x, ee[u].x);
-                        const float a1 = fmaf((__uint_as_float(rb[i & 1][4 * u + 1]) + bb[u].y - mean) * rstd, gg[u].y, ee[u].y);
-                        const float a2 = fmaf((__uint_as_float(rb[i & 1][4 * u + 2]) + bb[u].z - mean) * rstd, gg[u].z, ee[u].z);
-                        const float a3 = fmaf((__uint_as_float(rb[i & 1][4 * u + 3]) + bb[u].w - mean) * rstd, gg[u].w, ee[u].w);
-                        packed[2 * u] = pack_bf16(gelu_fwd(a0), gelu_fwd(a1));
-                        packed[2 * u + 1] = pack_bf16(gelu_fwd(a2), gelu_fwd(a3));
+                    for (int u = 0; u < 8; ++u) {
+                        const int q4 = u >> 1;
+                        const f32x2 b = (u & 1) ? pk2(bb[q4].z, bb[q4].w) : pk2(bb[q4].x, bb[q4].y);
+                        const f32x2 ga2 = (u & 1) ? pk2(gg[q4].z, gg[q4].w) : pk2(gg[q4].x, gg[q4].y);
+                        const f32x2 be2 = (u & 1) ? pk2(ee[q4].z, ee[q4].w) : pk2(ee[q4].x, ee[q4].y);
+                        const f32x2 pre = add2(add2(pk2u(rb[i & 1][2 * u], rb[i & 1][2 * u + 1]), b), nmean);
+                        const f32x2 act = gelu_fwd2(fma2(mul2(pre, rstd2), ga2, be2));
+                        float lo, hi;
+                        upk2(act, lo, hi);
+                        packed[u] = pack_bf16(lo, hi);
                     }
                     if (row < n_valid) {
                         uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
@@ -246,7 +257,8 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0)
+    if (tid < 32)                     // ONE warp: with 256 threads "warp" (the TMEM lane quarter) is 0 for warps 0 and 4, and a second
+                                      // dealloc of the same columns traps (intermittently: only when it sees the first one's update)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * kChunkN) : "memory");
 }
 

@@ -166,3 +166,18 @@ def test_grid4d_encoder_default_width_runs_on_our_kernels(dev):
     assert float((out.detach() - want).abs().max()) <= 1e-2 * float(want.abs().max())
     out.sum().backward()
     assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in enc.parameters())
+
+
+def test_projection_repeats_bit_for_bit_in_fresh_processes():
+    """scripts/stress_projection.py in three fresh processes: hidden / grad_x repeat bit for bit and no launch fails.
+    (Round 2 found a double tcgen05.dealloc here that trapped in ~1 process of 3 at 2^20 rows -- a fault only a
+    repeated, full-size run shows; a fresh process per run keeps a failure from poisoning this one's CUDA context.)"""
+    import os
+    import subprocess
+    import sys
+    script = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts", "stress_projection.py")
+    for _ in range(3):
+        r = subprocess.run([sys.executable, script, "--n", str(1 << 20), "--reps", "6"], capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        assert "mismatches=0" in r.stdout
