@@ -209,6 +209,21 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
     return v[0];
 }
 
+// The same for 16 values: lane l returns the sum over all 32 lanes of v[l & 15] (15 + 1 shuffles).
+__device__ __forceinline__ float warp_transpose_sum16(float (&v)[16], int lane) {
+#pragma unroll
+    for (int w = 8; w >= 1; w >>= 1) {
+        const bool up = (lane & w) != 0;
+#pragma unroll
+        for (int i = 0; i < w; ++i) {
+            const float send = up ? v[i] : v[i + w];
+            const float keep = up ? v[i + w] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
+}
+
 // ---- packed fp32 x 2 arithmetic (sm_100: FFMA2 / FADD2 / FMUL2, one issue slot for two lanes' worth of flops) ----------
 // The LayerNorm / GELU epilogues of the wide projection are instruction-issue bound; three quarters of their instructions
 // are fp32 pipe operations.  Each half of a pair is an ordinary IEEE operation: results equal the scalar code's bit for bit.

@@ -114,7 +114,6 @@ template <int K1>
 __global__ void __launch_bounds__(kDpreThreads, 2)
 proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_constant__ ProjDpreParams P) {
     constexpr int NT = kDpreThreads;
-    constexpr int kPieces = kBwdChunkN / 32 / (NT / 128);
     __shared__ float s_part[2][kTileM][2];
     constexpr int Kp = (K1 + 63) / 64 * 64;
     constexpr uint32_t kChunkBytes = (Kp / 64) * 16384;
@@ -219,6 +218,7 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
         const __nv_bfloat16* da_row = static_cast<const __nv_bfloat16*>(P.dact) + (p0 + row) * P.dact_stride;
         __nv_bfloat16* out_row = static_cast<__nv_bfloat16*>(P.dpre_out) + (p0 + row) * static_cast<long long>(H);
         float s1 = 0.0f, s2 = 0.0f;                       // sum_j t_j, sum_j t_j xh_j
+        f32x2 s1p = 0ull, s2p = 0ull;                     // their running pairs (even / odd columns) during pass 1
 
         for (int g = 0; g < 2 * NC; ++g) {
             const long long qs = q0 + g;
@@ -233,106 +233,111 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
             tc_fence_after();
             if (tid == 0 && qs + 2 < total_chunks) request_chunk(qs + 2);
             const uint32_t t_base = tmem + lane_off + static_cast<uint32_t>(qs & 1) * kBwdChunkN;
-#pragma unroll 1
-            for (int q = half * kPieces; q < (half + 1) * kPieces; ++q) {
-                const int col0 = c * kBwdChunkN + q * 32;
+            // The thread's 64 columns of the chunk come as four 16-column pieces (ncu r02n: with 32-column pieces the kernel sat
+            // at the 128-register cap, and the reloads of its spilled loop state were ~12 % of the stall samples); piece i + 1
+            // is requested from tensor memory as soon as piece i has arrived, and a piece's global loads go out before its wait.
+            constexpr int NP = kBwdChunkN / (NT / 128) / 16;
+            const uint32_t t_mine = t_base + half * (kBwdChunkN / 2);
+            const int col_mine = c * kBwdChunkN + half * (kBwdChunkN / 2);
+            uint32_t rb[2][16];
+            tmem_ld16_issue(t_mine, rb[0]);
+            const f32x2 nmean2 = splat2(-mean), rstd2 = splat2(rstd);
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                const int col0 = col_mine + i * 16;
                 const float4* b1v = reinterpret_cast<const float4*>(P.b1 + col0);           // 16-byte aligned (C ABI)
-                uint4* piece = reinterpret_cast<uint4*>(out_row + col0);                    // this row's 32 columns of dpre_out
+                uint4* piece = reinterpret_cast<uint4*>(out_row + col0);                    // this row's 16 columns of dpre_out
+                float4 bb[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) bb[u] = __ldg(b1v + u);
                 if (g < NC) {
                     // ---- pass 1: dv = da GELU'(v), t = gamma dv; row sums of t and t xh; dgamma, dbeta.  t is parked (bf16)
                     //      in dpre_out so that pass 2 needs neither da nor the GELU derivative again
-                    uint4 dq[4];
+                    uint4 dq[2];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) dq[u] = live ? __ldg(reinterpret_cast<const uint4*>(da_row + col0) + u) : make_uint4(0u, 0u, 0u, 0u);
-                    float v[32];
-                    tmem_ld32(t_base + q * 32, v);
-                    const uint32_t* dw = reinterpret_cast<const uint32_t*>(dq);
+                    for (int u = 0; u < 2; ++u) dq[u] = live ? __ldg(reinterpret_cast<const uint4*>(da_row + col0) + u) : make_uint4(0u, 0u, 0u, 0u);
                     const float4* gav = reinterpret_cast<const float4*>(P.ln_gamma + col0);
                     const float4* bev = reinterpret_cast<const float4*>(P.ln_beta + col0);
-                    float dvx[32];
-                    uint32_t tp[16];
-                    // packed pairs (mlp_common.cuh): columns (2k, 2k + 1) of the piece share one FFMA2 / FMUL2 / FADD2
-                    const f32x2 nmean2 = splat2(-mean), rstd2 = splat2(rstd);
-                    f32x2 s1p = 0ull, s2p = 0ull;
+                    float4 gg[4], ee[4];
 #pragma unroll
-                    for (int j4 = 0; j4 < 8; ++j4) {
-                        const float4 b4 = __ldg(b1v + j4), g4 = __ldg(gav + j4), e4 = __ldg(bev + j4);
+                    for (int u = 0; u < 4; ++u) { gg[u] = __ldg(gav + u); ee[u] = __ldg(bev + u); }
+                    tmem_ld16_wait(rb[i & 1]);
+                    if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
+                    const uint32_t* dw = reinterpret_cast<const uint32_t*>(dq);
+                    float dvv[16], dvx[16];
+                    uint32_t tp[8];
+                    // packed pairs (mlp_common.cuh): columns (2u, 2u + 1) of the piece share one FFMA2 / FMUL2 / FADD2
 #pragma unroll
-                        for (int u = 0; u < 2; ++u) {
-                            const int j = 4 * j4 + 2 * u;
-                            const f32x2 b2 = u ? pk2(b4.z, b4.w) : pk2(b4.x, b4.y);
-                            const f32x2 g2 = u ? pk2(g4.z, g4.w) : pk2(g4.x, g4.y);
-                            const f32x2 e2 = u ? pk2(e4.z, e4.w) : pk2(e4.x, e4.y);
-                            const f32x2 xh = mul2(add2(add2(pk2(v[j], v[j + 1]), b2), nmean2), rstd2);
-                            f32x2 act, gp;
-                            gelu_fwd_bwd2(fma2(g2, xh, e2), act, gp);
-                            const uint32_t pr = dw[j >> 1];
-                            const f32x2 dv = mul2(pk2u(pr << 16, pr & 0xffff0000u), gp);               // bf16 -> fp32, times GELU'
-                            const f32x2 tt = mul2(g2, dv);
-                            s1p = add2(s1p, tt);
-                            s2p = fma2(tt, xh, s2p);
-                            upk2(dv, v[j], v[j + 1]);                                // column sums: dbeta
-                            upk2(mul2(dv, xh), dvx[j], dvx[j + 1]);                  //              dgamma
-                            float t0, t1;
-                            upk2(tt, t0, t1);
-                            tp[j >> 1] = pack_bf16(t0, t1);
-                        }
-                    }
-                    {
-                        float a0, a1, c0, c1;
-                        upk2(s1p, a0, a1);
-                        upk2(s2p, c0, c1);
-                        s1 += a0 + a1;
-                        s2 += c0 + c1;
+                    for (int u = 0; u < 8; ++u) {
+                        const int q4 = u >> 1;
+                        const f32x2 b2 = (u & 1) ? pk2(bb[q4].z, bb[q4].w) : pk2(bb[q4].x, bb[q4].y);
+                        const f32x2 g2 = (u & 1) ? pk2(gg[q4].z, gg[q4].w) : pk2(gg[q4].x, gg[q4].y);
+                        const f32x2 e2 = (u & 1) ? pk2(ee[q4].z, ee[q4].w) : pk2(ee[q4].x, ee[q4].y);
+                        const f32x2 xh = mul2(add2(add2(pk2u(rb[i & 1][2 * u], rb[i & 1][2 * u + 1]), b2), nmean2), rstd2);
+                        f32x2 act, gp;
+                        gelu_fwd_bwd2(fma2(g2, xh, e2), act, gp);
+                        const uint32_t pr = dw[u];
+                        const f32x2 dv = mul2(pk2u(pr << 16, pr & 0xffff0000u), gp);               // bf16 -> fp32, times GELU'
+                        const f32x2 tt = mul2(g2, dv);
+                        s1p = add2(s1p, tt);
+                        s2p = fma2(tt, xh, s2p);
+                        upk2(dv, dvv[2 * u], dvv[2 * u + 1]);                        // column sums: dbeta
+                        upk2(mul2(dv, xh), dvx[2 * u], dvx[2 * u + 1]);              //              dgamma
+                        float t0, t1;
+                        upk2(tt, t0, t1);
+                        tp[u] = pack_bf16(t0, t1);
                     }
                     if (live) {
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) piece[u] = make_uint4(tp[4 * u], tp[4 * u + 1], tp[4 * u + 2], tp[4 * u + 3]);
+                        piece[0] = make_uint4(tp[0], tp[1], tp[2], tp[3]);
+                        piece[1] = make_uint4(tp[4], tp[5], tp[6], tp[7]);
                     }
-                    const float sb = warp_transpose_sum(v, lane);
-                    const float sg = warp_transpose_sum(dvx, lane);
-                    red_shared_f32(&s_acc[H + col0 + lane], sb);
-                    red_shared_f32(&s_acc[col0 + lane], sg);
+                    const float sb = warp_transpose_sum16(dvv, lane);
+                    const float sg = warp_transpose_sum16(dvx, lane);
+                    if (lane < 16) {
+                        red_shared_f32(&s_acc[H + col0 + lane], sb);
+                        red_shared_f32(&s_acc[col0 + lane], sg);
+                    }
                 } else {
                     // ---- pass 2: dpre = rstd (t - mean t - xh mean(t xh)); db1 ---------------------------------------------
-                    uint4 tq[4];
+                    uint4 tq[2];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) tq[u] = live ? piece[u] : make_uint4(0u, 0u, 0u, 0u);    // written by this thread in pass 1
-                    float v[32];
-                    tmem_ld32(t_base + q * 32, v);
+                    for (int u = 0; u < 2; ++u) tq[u] = live ? piece[u] : make_uint4(0u, 0u, 0u, 0u);    // written by this thread in pass 1
+                    tmem_ld16_wait(rb[i & 1]);
+                    if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
                     const uint32_t* tw = reinterpret_cast<const uint32_t*>(tq);
-                    const float m1 = s1 * inv_h, m2 = s2 * inv_h;
-                    const f32x2 nmean2 = splat2(-mean), rstd2 = splat2(rstd), nm1 = splat2(-m1), nm2 = splat2(-m2);
+                    const f32x2 nm1 = splat2(-(s1 * inv_h)), nm2 = splat2(-(s2 * inv_h));
+                    float dd[16];
+                    uint32_t pk[8];
 #pragma unroll
-                    for (int j4 = 0; j4 < 8; ++j4) {
-                        const float4 b4 = __ldg(b1v + j4);
-#pragma unroll
-                        for (int u = 0; u < 2; ++u) {
-                            const int j = 4 * j4 + 2 * u;
-                            const f32x2 b2 = u ? pk2(b4.z, b4.w) : pk2(b4.x, b4.y);
-                            const f32x2 xh = mul2(add2(add2(pk2(v[j], v[j + 1]), b2), nmean2), rstd2);
-                            const uint32_t pr = tw[j >> 1];
-                            const f32x2 t = pk2u(pr << 16, pr & 0xffff0000u);
-                            upk2(mul2(rstd2, fma2(xh, nm2, add2(t, nm1))), v[j], v[j + 1]);
-                        }
-                    }
-                    uint32_t pk[16];
-#pragma unroll
-                    for (int j = 0; j < 32; j += 2) {
-                        pk[j >> 1] = pack_bf16(v[j], v[j + 1]);
+                    for (int u = 0; u < 8; ++u) {
+                        const int q4 = u >> 1;
+                        const f32x2 b2 = (u & 1) ? pk2(bb[q4].z, bb[q4].w) : pk2(bb[q4].x, bb[q4].y);
+                        const f32x2 xh = mul2(add2(add2(pk2u(rb[i & 1][2 * u], rb[i & 1][2 * u + 1]), b2), nmean2), rstd2);
+                        const uint32_t pr = tw[u];
+                        const f32x2 t = pk2u(pr << 16, pr & 0xffff0000u);
+                        float d0, d1;
+                        upk2(mul2(rstd2, fma2(xh, nm2, add2(t, nm1))), d0, d1);
+                        pk[u] = pack_bf16(d0, d1);
                         // db1 sums the bf16-ROUNDED dpre, the values the dW1 / dx GEMMs consume
-                        v[j] = live ? __uint_as_float(pk[j >> 1] << 16) : 0.0f;
-                        v[j + 1] = live ? __uint_as_float(pk[j >> 1] & 0xffff0000u) : 0.0f;
+                        dd[2 * u] = live ? __uint_as_float(pk[u] << 16) : 0.0f;
+                        dd[2 * u + 1] = live ? __uint_as_float(pk[u] & 0xffff0000u) : 0.0f;
                     }
                     if (live) {
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) piece[u] = make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
+                        piece[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        piece[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                     }
-                    const float sd = warp_transpose_sum(v, lane);
-                    red_shared_f32(&s_acc[2 * H + col0 + lane], sd);
+                    const float sd = warp_transpose_sum16(dd, lane);
+                    if (lane < 16) red_shared_f32(&s_acc[2 * H + col0 + lane], sd);
                 }
             }
             if (g == NC - 1) {                                    // both halves of a row need the row's full sums for pass 2
+                {
+                    float a0, a1, c0, c1;
+                    upk2(s1p, a0, a1);
+                    upk2(s2p, c0, c1);
+                    s1 = a0 + a1;
+                    s2 = c0 + c1;
+                }
                 s_part[half][row][0] = s1;
                 s_part[half][row][1] = s2;
                 __syncthreads();
