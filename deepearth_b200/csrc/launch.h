@@ -144,6 +144,8 @@ struct GemmParams {
     const float* bias;            // (N,) or NULL
     int vec_ok;
     int bias_vec;                 // filled by the launcher: bias is 16-byte aligned
+    int tma_store;                // filled by the launcher: fp32 C leaves through shared memory and TMA tensor stores
+    int full_n;                   // filled by the launcher: DE_GEMM_FULL_N=1 keeps every MMA 256 columns wide (A/B switch)
 };
 struct ProjDpreParams {
     const float* x;               // (n, in_dim) fp32 features (forward input)

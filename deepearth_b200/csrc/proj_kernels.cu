@@ -265,25 +265,41 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
 // ---------------------------------------------------------------------------------------------------------------------
 // kernel 2: C = A . B^T (+ bias), bf16 operands by TMA, fp32 accumulation in TMEM
 // ---------------------------------------------------------------------------------------------------------------------
-constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 64, kGemmStages = 4;
+constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 64;
+constexpr int kGemmMaxStages = 6;
 constexpr int kGemmThreads = 384;                      // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warps 4..11 epilogue
-constexpr uint32_t kGemmStageBytes = (kGemmBM + kGemmBN) * kGemmBK * 2;
-constexpr uint32_t kGemmSmemBytes = kGemmStages * kGemmStageBytes + 1024;   // + alignment slack
+constexpr uint32_t kGemmRingBytes = 192 * 1024;
+constexpr uint32_t kGemmStoreBytes = 8 * 4096;               // one 32 x 32 fp32 staging tile per epilogue warp (TMA stores)
+constexpr uint32_t kGemmSmemBytes = kGemmRingBytes + kGemmStoreBytes + 1024;      // + alignment slack
 constexpr int kGemmPrefetch = 12;                    // k-blocks the L2 prefetch cursor runs ahead of the loads
-constexpr int kGemmMulticastDefault = 0;              // flipped to 1 once the cluster path is validated on a B200
+constexpr int kGemmPairDefault = 1;                   // B200 r02p: fwd+bwd 11.06 -> 10.58 ms at 2^20 x 768 against single CTAs
 
 // A_MN / B_MN = 1: the operand is stored with the contraction index as its ROW index ((K, M) resp. (K, N) row-major: a
 // "transposed" operand, MN-major in UMMA terms) and arrives as 64 x 64 boxes; 0: (M, K) resp. (N, K) row-major, K-major.
 // EPI 0: C fp32 = acc + bias; 1: C bf16 = acc + bias; 2: C fp32 += acc (red.global.add: split-K partial sums).
-// MC = 2: thread-block clusters of two CTAs work on vertically adjacent output tiles; each loads its own A tile and HALF of
-// the shared B tile, multicast into both CTAs' shared memory -- 32 KB instead of 48 KB of L2 reads per CTA and k-block.  The
-// single-CTA kernel is L2-bandwidth bound (9.4 TB/s of operand traffic at 0.82 PFLOP/s against a ~12 TB/s fabric).
+// MC = 2: CTA PAIRS (tcgen05 cta_group::2).  The two CTAs of a cluster (the two SMs of a TPC) run one M = 256 MMA on a
+// 256 x 256 output tile: each CTA loads its own 128 rows of A and HALF of the B tile (128 of the 256 N rows) into its own
+// shared memory and holds the accumulator rows of its A half in its own TMEM; the leader (rank 0) issues every MMA and its
+// commits are multicast to both CTAs' barriers.  Per CTA and k-block that is 32 KB of L2 reads and 8 KB of shared-memory
+// operand reads per MMA instruction instead of 48 KB and 12 KB: the single-CTA kernel keeps the shared-memory pipe busy
+// 3/4 of the time with operand reads alone (ncu r02m: l1tex the busiest unit at 68 %, tensor pipe 55 %), which is why the
+// vendor's kernels for these shapes are all 2-CTA ones.  Ring: 6 stages of 32 KB (MC = 1: 4 of 48 KB).
+// live MMA width of a tile with n_left columns to its right edge: a multiple of 16 per CTA's share
+template <int MC>
+__device__ __forceinline__ int gemm_n_eff(int n_left) {
+    const int n = n_left < kGemmBN ? n_left : kGemmBN;
+    return (n + 16 * MC - 1) / (16 * MC) * (16 * MC);
+}
+
 template <int A_MN, int B_MN, int EPI, int MC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                     const __grid_constant__ GemmParams P) {
+                     const __grid_constant__ CUtensorMap map_c, const __grid_constant__ GemmParams P) {
+    constexpr int kGemmStages = MC == 2 ? 6 : 4;
+    constexpr uint32_t kGemmStageBytes = (kGemmBM + kGemmBN / MC) * kGemmBK * 2;         // this CTA's share of a k-block
+    static_assert(kGemmStages <= kGemmMaxStages && kGemmStages * kGemmStageBytes <= kGemmRingBytes, "operand ring");
     extern __shared__ unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t s_full[kGemmStages], s_empty[kGemmStages], s_tfull[2], s_tempty[2];
+    __shared__ __align__(8) uint64_t s_full[kGemmMaxStages], s_empty[kGemmMaxStages], s_tfull[2], s_tempty[2];
     __shared__ uint32_t s_tmem;
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -297,13 +313,18 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const long long unit = blockIdx.x / MC, n_units = gridDim.x / MC;          // the cluster is the scheduling unit
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kGemmStages; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], MC); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 8); }
+        for (int i = 0; i < kGemmStages; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 8 * MC); }   // MC = 2: the leader's counts both CTAs' epilogue warps
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (warp == 2) {                                   // MC = 2: the same warp of both CTAs, collectively
+        if constexpr (MC == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     fence_async_smem();
     tc_fence_before();
@@ -358,37 +379,44 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 mbar_wait(&s_empty[stage], phase ^ 1u);
                 unsigned char* sa = smem + stage * kGemmStageBytes;
                 unsigned char* sb = sa + kGemmBM * kGemmBK * 2;
-                mbar_expect_tx(&s_full[stage], kGemmStageBytes);
-                if constexpr (A_MN) {
+                if constexpr (MC == 2) {
+                    // both CTAs' boxes report to the LEADER's full barrier, which the leader arms for the pair's bytes
+                    if (rank == 0) mbar_expect_tx(&s_full[stage], 2 * kGemmStageBytes);
+                    const uint32_t full = mapa_u32(smem_u32(&s_full[stage]), 0);
+                    // this CTA's half of the B tile: the MMA reads the first n_eff / 2 rows of each CTA's B buffer
+                    const int nb = n0 + static_cast<int>(rank) * (gemm_n_eff<MC>(P.full_n ? kGemmBN : P.N - n0) / 2);
+                    if constexpr (A_MN) {
 #pragma unroll
-                    for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d(sa + i * 8192, &map_a, m0 + 64 * i, kb * kGemmBK, &s_full[stage]);
-                } else {
-                    tma_load_2d(sa, &map_a, kb * kGemmBK, m0, &s_full[stage]);
-                }
-                if constexpr (MC > 1) {
-                    // this CTA's half of the B tile, delivered to both CTAs (each full barrier expects the whole stage)
+                        for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d_pair(sa + i * 8192, &map_a, m0 + 64 * i, kb * kGemmBK, full);
+                    } else {
+                        tma_load_2d_pair(sa, &map_a, kb * kGemmBK, m0, full);
+                    }
                     if constexpr (B_MN) {
 #pragma unroll
-                        for (int i = 0; i < kGemmBN / 128; ++i) {
-                            const int bi = static_cast<int>(rank) * (kGemmBN / 128) + i;
-                            tma_load_2d_mc(sb + bi * 8192, &map_b, n0 + 64 * bi, kb * kGemmBK, &s_full[stage], 3);
-                        }
+                        for (int i = 0; i < kGemmBN / 128; ++i) tma_load_2d_pair(sb + i * 8192, &map_b, nb + 64 * i, kb * kGemmBK, full);
                     } else {
-                        tma_load_2d_mc(sb + rank * (kGemmBN / 2) * kGemmBK * 2, &map_b, kb * kGemmBK, n0 + static_cast<int>(rank) * (kGemmBN / 2),
-                                       &s_full[stage], 3);
+                        tma_load_2d_pair(sb, &map_b, kb * kGemmBK, nb, full);
                     }
-                } else if constexpr (B_MN) {
-#pragma unroll
-                    for (int i = 0; i < kGemmBN / 64; ++i) tma_load_2d(sb + i * 8192, &map_b, n0 + 64 * i, kb * kGemmBK, &s_full[stage]);
                 } else {
-                    tma_load_2d(sb, &map_b, kb * kGemmBK, n0, &s_full[stage]);
+                    mbar_expect_tx(&s_full[stage], kGemmStageBytes);
+                    if constexpr (A_MN) {
+#pragma unroll
+                        for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d(sa + i * 8192, &map_a, m0 + 64 * i, kb * kGemmBK, &s_full[stage]);
+                    } else {
+                        tma_load_2d(sa, &map_a, kb * kGemmBK, m0, &s_full[stage]);
+                    }
+                    if constexpr (B_MN) {
+#pragma unroll
+                        for (int i = 0; i < kGemmBN / 64; ++i) tma_load_2d(sb + i * 8192, &map_b, n0 + 64 * i, kb * kGemmBK, &s_full[stage]);
+                    } else {
+                        tma_load_2d(sb, &map_b, kb * kGemmBK, n0, &s_full[stage]);
+                    }
                 }
                 if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
             }
         }
-    } else if (warp == 1 && lane == 0) {
-        // ===== MMA issuer =====
-        constexpr uint32_t kIdesc = idesc_bf16(kGemmBM, kGemmBN, A_MN != 0, B_MN != 0);
+    } else if (warp == 1 && lane == 0 && rank == 0) {
+        // ===== MMA issuer (MC = 2: the pair's leader) =====
         int stage = 0;
         uint32_t phase = 0;
         int as = 0;
@@ -396,6 +424,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         for (long long work = unit; work < n_tiles; work += n_units) {
             const int split = static_cast<int>(work % P.k_splits);
             const int kb_begin = split * kb_per, kb_end = min(k_blocks_all, (split + 1) * kb_per);
+            // the MMA's N is the tile's live width (a multiple of 16): a 128-column matrix (dx, dW1 at in_dim 128) costs half
+            // the tensor time of a full 256-column tile instead of multiplying zero-filled rows
+            const int n_left = P.N - static_cast<int>((work / P.k_splits) % tiles_n) * kGemmBN;
+            const uint32_t kIdesc = idesc_bf16(kGemmBM * MC, gemm_n_eff<MC>(P.full_n ? kGemmBN : n_left), A_MN != 0, B_MN != 0);
             mbar_wait(&s_tempty[as], aphase ^ 1u);                  // epilogue has drained this accumulator
             tc_fence_after();
             for (int kb = kb_begin; kb < kb_end; ++kb) {
@@ -409,11 +441,16 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                     // 1024 B atoms further (LBO = 8192 B between 64-wide MN blocks, SBO = 1024 B between 8-row K groups)
                     const uint64_t da = A_MN ? umma_desc_sw128(a0 + k * 2048, 8192, 1024) : umma_desc_sw128(a0 + k * 32, 16, 1024);
                     const uint64_t db = B_MN ? umma_desc_sw128(b0 + k * 2048, 8192, 1024) : umma_desc_sw128(b0 + k * 32, 16, 1024);
-                    umma_bf16(tmem + as * kGemmBN, da, db, kIdesc, (kb > kb_begin || k) ? 1u : 0u);
+                    if constexpr (MC == 2) umma_bf16_pair(tmem + as * kGemmBN, da, db, kIdesc, (kb > kb_begin || k) ? 1u : 0u);
+                    else umma_bf16(tmem + as * kGemmBN, da, db, kIdesc, (kb > kb_begin || k) ? 1u : 0u);
                 }
-                if constexpr (MC > 1) umma_commit_mc(&s_empty[stage], 3);   // the slot is refilled by BOTH producers: tell both
-                else umma_commit(&s_empty[stage]);                   // frees the slot when these MMAs have read it
-                if (kb == kb_end - 1) umma_commit(&s_tfull[as]);     // accumulator complete
+                if constexpr (MC == 2) {
+                    umma_commit_pair(&s_empty[stage], 3);            // the slot is refilled by BOTH producers: tell both
+                    if (kb == kb_end - 1) umma_commit_pair(&s_tfull[as], 3);       // each CTA drains its own half
+                } else {
+                    umma_commit(&s_empty[stage]);                    // frees the slot when these MMAs have read it
+                    if (kb == kb_end - 1) umma_commit(&s_tfull[as]); // accumulator complete
+                }
                 if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
             }
             if (++as == 2) { as = 0; aphase ^= 1u; }
@@ -455,7 +492,29 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                         for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldg(P.bias + col0 + j) : 0.0f;
                     }
                 }
-                if (r < P.M) {
+                if (EPI == 0 && P.tma_store) {
+                    // fp32 rows through shared memory and a tensor store: the 32 lanes' 32 x 128 B leave as one box of whole
+                    // lines (ncu r02p: with per-lane 32 B stores the fp32 epilogue, not the tensor pipe (58 % active) or HBM
+                    // (45 %), set the pace).  128 B swizzle: lane r keeps 16-byte chunk c at chunk c ^ (r & 7) -- conflict-free
+                    // stores, and the layout the tensor map (SWIZZLE_128B, box 32 x 32) expects.  The copy engine clips the box
+                    // at the matrix edge.
+                    unsigned char* stg = smem + kGemmRingBytes + (warp - 4) * 4096;
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");      // the previous box has left
+                    __syncwarp();
+                    const uint32_t row_addr = smem_u32(stg) + lane * 128;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_addr + ((c ^ (lane & 7)) << 4)), "f"(v[4 * c]),
+                                     "f"(v[4 * c + 1]), "f"(v[4 * c + 2]), "f"(v[4 * c + 3]) : "memory");
+                    fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];"
+                                     ::"l"(reinterpret_cast<uint64_t>(&map_c)), "r"(col0), "r"(static_cast<int>(m0) + quarter * 32),
+                                       "r"(smem_u32(stg)) : "memory");
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                } else if (r < P.M) {
                     if constexpr (EPI == 2) {
                         float* dst = static_cast<float*>(P.c) + r * P.ldc + col0;
                         if (col0 + 32 <= P.N && P.vec_ok) {
@@ -501,15 +560,21 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&s_tempty[as]);
+            if (lane == 0) {
+                if constexpr (MC == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&s_tempty[as]), 0));     // the leader issues the MMAs
+                else mbar_arrive(&s_tempty[as]);
+            }
             if (++as == 2) { as = 0; aphase ^= 1u; }
         }
     }
+    if (EPI == 0 && warp >= 4 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // tensor stores complete
     tc_fence_before();
     __syncthreads();
     if constexpr (MC > 1) cluster_sync_all();          // no CTA leaves while its peer may still write into it or signal it
-    if (warp == 2)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    if (warp == 2) {
+        if constexpr (MC == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -588,13 +653,26 @@ cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaSt
 #undef DE_HID
 }
 
+// fp32 matrix (rows, cols), rows ld elements apart: box {32 columns, 32 rows}, 128 B swizzle -- the epilogue's tensor stores
+static bool make_map_f32_store(CUtensorMap* map, void* base, long long rows, long long cols, long long ld) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
+    const cuuint32_t box[2] = {32u, 32u};
+    const cuuint32_t estr[2] = {1u, 1u};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int A_MN, int B_MN, int EPI, int MC>
-static cudaError_t launch_gemm_t(const CUtensorMap& map_a, const CUtensorMap& map_b, const GemmParams& P, int grid, cudaStream_t s) {
+static cudaError_t launch_gemm_t(const CUtensorMap& map_a, const CUtensorMap& map_b, const CUtensorMap& map_c, const GemmParams& P, int grid,
+                                 cudaStream_t s) {
     auto kernel = gemm_bf16_tma_kernel<A_MN, B_MN, EPI, MC>;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGemmSmemBytes));
     if (e != cudaSuccess) return e;
     if (MC == 1) {
-        kernel<<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, P);
+        kernel<<<grid, kGemmThreads, kGemmSmemBytes, s>>>(map_a, map_b, map_c, P);
         return cudaGetLastError();
     }
     cudaLaunchConfig_t cfg{};
@@ -609,23 +687,24 @@ static cudaError_t launch_gemm_t(const CUtensorMap& map_a, const CUtensorMap& ma
     attr.val.clusterDim.z = 1;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, P);
+    return cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, map_c, P);
 }
 
 template <int A_MN, int B_MN, int MC>
-static cudaError_t launch_gemm_e(const CUtensorMap& map_a, const CUtensorMap& map_b, const GemmParams& P, int epi, int grid, cudaStream_t s) {
+static cudaError_t launch_gemm_e(const CUtensorMap& map_a, const CUtensorMap& map_b, const CUtensorMap& map_c, const GemmParams& P, int epi,
+                                 int grid, cudaStream_t s) {
     switch (epi) {
-        case 0: return launch_gemm_t<A_MN, B_MN, 0, MC>(map_a, map_b, P, grid, s);
-        case 1: return launch_gemm_t<A_MN, B_MN, 1, MC>(map_a, map_b, P, grid, s);
-        default: return launch_gemm_t<A_MN, B_MN, 2, MC>(map_a, map_b, P, grid, s);
+        case 0: return launch_gemm_t<A_MN, B_MN, 0, MC>(map_a, map_b, map_c, P, grid, s);
+        case 1: return launch_gemm_t<A_MN, B_MN, 1, MC>(map_a, map_b, map_c, P, grid, s);
+        default: return launch_gemm_t<A_MN, B_MN, 2, MC>(map_a, map_b, map_c, P, grid, s);
     }
 }
 
-// DE_GEMM_MULTICAST (read once per process): 1 = two-CTA clusters with the B tile multicast, 0 = single CTAs
-static int gemm_multicast() {
+// DE_GEMM_PAIR (read once per process): 1 = CTA pairs (cta_group::2, 256 x 256 tiles), 0 = single CTAs (128 x 256)
+static int gemm_pair() {
     static const int v = []() {
-        const char* e = getenv("DE_GEMM_MULTICAST");
-        return (e && *e) ? (atoi(e) != 0 ? 1 : 0) : kGemmMulticastDefault;
+        const char* e = getenv("DE_GEMM_PAIR");
+        return (e && *e) ? (atoi(e) != 0 ? 1 : 0) : kGemmPairDefault;
     }();
     return v;
 }
@@ -636,7 +715,7 @@ static int gemm_multicast() {
 cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int transposed, GemmParams P, int epi,
                              int n_sms, cudaStream_t s) {
     const long long tiles_m = (P.M + kGemmBM - 1) / kGemmBM, tiles_n = (P.N + kGemmBN - 1) / kGemmBN;
-    const int mc = (gemm_multicast() && tiles_m >= 2) ? 2 : 1;
+    const int mc = (gemm_pair() && tiles_m >= 2) ? 2 : 1;
     CUtensorMap map_a, map_b;
     bool ok;
     if (transposed) ok = make_map_bf16(&map_a, a, P.K, P.M, lda, 64) && make_map_bf16(&map_b, b, P.K, P.N, ldb, 64);
@@ -656,13 +735,23 @@ cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long l
     P.k_splits = static_cast<int>(splits);
     static const int prefetch = []() { const char* e = getenv("DE_GEMM_PREFETCH"); return (e && *e) ? (atoi(e) != 0) : 0; }();   // B200 r02g: 13.7 ms with, 11.9 ms without
     P.prefetch = prefetch;
+    static const int full_n = []() { const char* e = getenv("DE_GEMM_FULL_N"); return (e && *e) ? (atoi(e) != 0) : 0; }();
+    P.full_n = full_n;
     const long long work = units * splits;
     const int grid = static_cast<int>((work < max_units ? work : max_units) * mc);
     const size_t elem = epi == 1 ? 2 : 4;
     P.vec_ok = (reinterpret_cast<uintptr_t>(P.c) % 32 == 0 && (P.ldc * elem) % 32 == 0) ? 1 : 0;
     P.bias_vec = (P.bias && reinterpret_cast<uintptr_t>(P.bias) % 16 == 0) ? 1 : 0;
-    if (mc == 2) return transposed ? launch_gemm_e<1, 1, 2>(map_a, map_b, P, epi, grid, s) : launch_gemm_e<0, 0, 2>(map_a, map_b, P, epi, grid, s);
-    return transposed ? launch_gemm_e<1, 1, 1>(map_a, map_b, P, epi, grid, s) : launch_gemm_e<0, 0, 1>(map_a, map_b, P, epi, grid, s);
+    // fp32 output through tensor stores when the matrix allows a tensor map (16-byte aligned base and row pitch)
+    static const int tma_store = []() { const char* e = getenv("DE_GEMM_TMA_STORE"); return (e && *e) ? (atoi(e) != 0) : 1; }();
+    CUtensorMap map_c = map_a;                             // placeholder when unused
+    P.tma_store = 0;
+    if (epi == 0 && tma_store && reinterpret_cast<uintptr_t>(P.c) % 16 == 0 && (P.ldc * 4) % 16 == 0 &&
+        make_map_f32_store(&map_c, P.c, P.M, P.N, P.ldc))
+        P.tma_store = 1;
+    if (mc == 2)
+        return transposed ? launch_gemm_e<1, 1, 2>(map_a, map_b, map_c, P, epi, grid, s) : launch_gemm_e<0, 0, 2>(map_a, map_b, map_c, P, epi, grid, s);
+    return transposed ? launch_gemm_e<1, 1, 1>(map_a, map_b, map_c, P, epi, grid, s) : launch_gemm_e<0, 0, 1>(map_a, map_b, map_c, P, epi, grid, s);
 }
 
 }  // namespace de

@@ -8,7 +8,7 @@ timeout 300 python __graft_entry__.py smoke 2>&1 | tail -3
 for x in field projection_h768; do
   timeout 200 python bench.py --extra-only $x --steps 3 > gpurun_out/${T}_$x.json 2> gpurun_out/${T}_$x.err || tail -3 gpurun_out/${T}_$x.err
 done
-DE_GEMM_MULTICAST=1 timeout 200 python bench.py --extra-only projection_h768 --steps 3 > gpurun_out/${T}_projection_h768_mc.json 2>/dev/null
+DE_GEMM_PAIR=0 timeout 200 python bench.py --extra-only projection_h768 --steps 3 > gpurun_out/${T}_projection_h768_single_cta.json 2>/dev/null
 timeout 300 python bench.py --workload c5h768 --steps 5 --no-cpu-baseline > gpurun_out/${T}_c5h768.json 2> gpurun_out/${T}_c5h768.err || tail -3 gpurun_out/${T}_c5h768.err
 python - $T <<'PY'
 import json, sys
