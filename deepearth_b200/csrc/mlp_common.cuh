@@ -132,6 +132,19 @@ __device__ __forceinline__ void st_stream_32B(float* p, const float4& a, const f
     }
 }
 
+// 32 contiguous, 32-byte aligned bytes as ONE request per lane (a whole sector): the projection kernels move their bf16
+// rows 16 columns at a time per thread, and two 16-byte accesses per piece doubled the L1 wavefronts of that traffic
+// (B200 r02s: hidden kernel 1.63 -> 1.35 ms, dpre kernel 3.63 -> 2.72 ms per 2^20 x 768).  Loads bypass L1 allocation
+// (streamed once; the per-column constants are what should stay there).
+__device__ __forceinline__ void ld_nc_32B(const void* p, uint32_t (&r)[8]) {
+    asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p));
+}
+__device__ __forceinline__ void st_32B(void* p, const uint32_t (&r)[8]) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<const uint32_t*>(&h);

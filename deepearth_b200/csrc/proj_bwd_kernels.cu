@@ -105,6 +105,24 @@ cudaError_t launch_transpose_bf16(const void* src, long long ld_src, void* dst, 
 // ---- dpre ----------------------------------------------------------------------------------------------------------------
 constexpr int kBwdChunkN = 128;
 
+// 16 bf16 columns of a row: one 32-byte request (not allocated in L1), or two 16-byte ones when the rows are only 16-byte aligned
+__device__ __forceinline__ void load_piece(const void* p, uint32_t (&r)[8], bool v32) {
+    if (v32) {
+        ld_nc_32B(p, r);
+    } else {
+        const uint4 a = *reinterpret_cast<const uint4*>(p), b = *(reinterpret_cast<const uint4*>(p) + 1);
+        r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w; r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+    }
+}
+__device__ __forceinline__ void store_piece(void* p, const uint32_t (&r)[8], bool v32) {
+    if (v32) {
+        st_32B(p, r);
+    } else {
+        reinterpret_cast<uint4*>(p)[0] = make_uint4(r[0], r[1], r[2], r[3]);
+        reinterpret_cast<uint4*>(p)[1] = make_uint4(r[4], r[5], r[6], r[7]);
+    }
+}
+
 // W1 chunks arrive by TMA exactly as in proj_hidden_kernel (a continuous chunk stream, requested one epilogue ahead).
 // dynamic shared memory (1024 B aligned): B[2] [Kp / 64 boxes x 16 KB] | A [128 x Kp] bf16 canonical | acc[3][H] floats
 // Two threads per row (256 per CTA, each takes half of a chunk's columns; the two row sums are merged once per tile): the
@@ -126,6 +144,8 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
     const int H = P.hidden, NC = H / kBwdChunkN;
     float* s_acc = reinterpret_cast<float*>(sA + kTileM * Kp * 2);     // [3][H]: dgamma, dbeta, db1
     const int tid = threadIdx.x, warp = (tid >> 5) & 3, lane = tid & 31, half = tid >> 7;
+    // the bf16 rows move as one 32-byte request per piece and lane when everything is 32-byte aligned
+    const bool v32 = ((reinterpret_cast<uintptr_t>(P.dact) | reinterpret_cast<uintptr_t>(P.dpre_out)) & 31) == 0 && P.dact_stride % 16 == 0;
 
     for (int i = tid; i < 3 * H; i += NT) s_acc[i] = 0.0f;
     if (tid == 0) {
@@ -253,9 +273,8 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                 if (g < NC) {
                     // ---- pass 1: dv = da GELU'(v), t = gamma dv; row sums of t and t xh; dgamma, dbeta.  t is parked (bf16)
                     //      in dpre_out so that pass 2 needs neither da nor the GELU derivative again
-                    uint4 dq[2];
-#pragma unroll
-                    for (int u = 0; u < 2; ++u) dq[u] = live ? __ldg(reinterpret_cast<const uint4*>(da_row + col0) + u) : make_uint4(0u, 0u, 0u, 0u);
+                    uint32_t dw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                    if (live) load_piece(da_row + col0, dw, v32);
                     const float4* gav = reinterpret_cast<const float4*>(P.ln_gamma + col0);
                     const float4* bev = reinterpret_cast<const float4*>(P.ln_beta + col0);
                     float4 gg[4], ee[4];
@@ -263,7 +282,6 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                     for (int u = 0; u < 4; ++u) { gg[u] = __ldg(gav + u); ee[u] = __ldg(bev + u); }
                     tmem_ld16_wait(rb[i & 1]);
                     if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
-                    const uint32_t* dw = reinterpret_cast<const uint32_t*>(dq);
                     float dvv[16], dvx[16];
                     uint32_t tp[8];
                     // packed pairs (mlp_common.cuh): columns (2u, 2u + 1) of the piece share one FFMA2 / FMUL2 / FADD2
@@ -287,10 +305,7 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                         upk2(tt, t0, t1);
                         tp[u] = pack_bf16(t0, t1);
                     }
-                    if (live) {
-                        piece[0] = make_uint4(tp[0], tp[1], tp[2], tp[3]);
-                        piece[1] = make_uint4(tp[4], tp[5], tp[6], tp[7]);
-                    }
+                    if (live) store_piece(piece, tp, v32);
                     const float sb = warp_transpose_sum16(dvv, lane);
                     const float sg = warp_transpose_sum16(dvx, lane);
                     if (lane < 16) {
@@ -299,12 +314,10 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                     }
                 } else {
                     // ---- pass 2: dpre = rstd (t - mean t - xh mean(t xh)); db1 ---------------------------------------------
-                    uint4 tq[2];
-#pragma unroll
-                    for (int u = 0; u < 2; ++u) tq[u] = live ? piece[u] : make_uint4(0u, 0u, 0u, 0u);    // written by this thread in pass 1
+                    uint32_t tw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                    if (live) load_piece(piece, tw, v32);                                             // written by this thread in pass 1
                     tmem_ld16_wait(rb[i & 1]);
                     if (i + 1 < NP) tmem_ld16_issue(t_mine + (i + 1) * 16, rb[(i + 1) & 1]);
-                    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tq);
                     const f32x2 nm1 = splat2(-(s1 * inv_h)), nm2 = splat2(-(s2 * inv_h));
                     float dd[16];
                     uint32_t pk[8];
@@ -322,10 +335,7 @@ proj_dpre_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_consta
                         dd[2 * u] = live ? __uint_as_float(pk[u] << 16) : 0.0f;
                         dd[2 * u + 1] = live ? __uint_as_float(pk[u] & 0xffff0000u) : 0.0f;
                     }
-                    if (live) {
-                        piece[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                        piece[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                    }
+                    if (live) store_piece(piece, pk, v32);
                     const float sd = warp_transpose_sum16(dd, lane);
                     if (lane < 16) red_shared_f32(&s_acc[2 * H + col0 + lane], sd);
                 }

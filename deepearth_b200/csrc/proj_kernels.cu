@@ -61,6 +61,7 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
     unsigned char* sA = smem + 2 * kChunkBytes;
     const int tid = threadIdx.x, warp = (tid >> 5) & 3, lane = tid & 31, half = tid >> 7;
     const int H = P.hidden, NC = H / kChunkN;
+    const bool st32 = (reinterpret_cast<uintptr_t>(P.hidden_out) & 31) == 0 && P.hidden_stride % 16 == 0;
 
     if (tid == 0) {
         mbar_init(&s_mma[0], 1); mbar_init(&s_mma[1], 1);
@@ -245,9 +246,13 @@ proj_hidden_kernel(const __grid_constant__ CUtensorMap map_w1, const __grid_cons
                         packed[u] = pack_bf16(lo, hi);
                     }
                     if (row < n_valid) {
-                        uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
-                        dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-                        dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+                        if (st32) {                                 // rows 32-byte aligned: one whole-sector store per piece
+                            st_32B(out_row + col0, packed);
+                        } else {
+                            uint4* dst = reinterpret_cast<uint4*>(out_row + col0);
+                            dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                            dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+                        }
                     }
                 }
             }
