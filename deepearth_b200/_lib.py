@@ -68,6 +68,8 @@ SIGNATURES = {
     "de_grid4d_backward_workspace_bytes_ex": (ctypes.c_size_t, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32, c_int]),
     "de_grid4d_backward_group_width": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32, c_int]),
     "de_grid4d_sort_workspace_bytes": (ctypes.c_size_t, [c_int, c_int]),
+    "de_grid4d_sort_points_noalloc_max_buckets": (ctypes.c_size_t, []),
+    "de_grid4d_sort_points_noalloc": (c_int, [c_void_p, c_i64, c_int, ctypes.POINTER(ctypes.c_uint8), c_int, c_int, c_void_p, c_void_p]),
     "de_grid4d_sort_points": (c_int, [c_void_p, c_i64, c_int, ctypes.POINTER(ctypes.c_uint8), c_int, c_int, c_void_p, c_void_p,
                                       ctypes.c_size_t, c_void_p]),
     "de_grid4d_backward_sorted": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_void_p, c_i64, c_int, c_int, c_void_p, c_void_p,

@@ -704,6 +704,65 @@ DE_API int de_grid4d_sort_points(const float* coords, int64_t n_points, int coor
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "sort_points launch");
 }
 
+// ---- de_grid4d_sort_points without any allocation on the caller's side ---------------------------------------------------
+// The counting sort's bucket counters live in a file-scope device array instead of a caller-provided workspace: 2^16 buckets
+// (the entry point's own limit, bits * n_dims <= 16) x 4 bytes = 256 KiB, held by every GPU that loads the library until the
+// process exits.  `g_sort_counters` is, in host code, only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current, and is what the kernels receive.  The one piece of
+// mutable global state in this file (the rest of the surface is re-entrant): calls share the array, see the header.
+namespace {
+
+constexpr int kNoAllocSortMaxBuckets = 1 << 16;
+static __device__ __align__(256) unsigned int g_sort_counters[kNoAllocSortMaxBuckets];
+
+constexpr int kNoAllocMaxDevices = 64;
+unsigned int* g_sort_counters_addr[kNoAllocMaxDevices];           // [device ordinal] -> device address of g_sort_counters there
+
+int sort_counters_for_current_device(unsigned int** out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "sort_points_noalloc: cudaGetDevice");
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(DE_EUNSUPPORTED, "sort_points_noalloc: device ordinal %d >= %d", dev, kNoAllocMaxDevices);
+    unsigned int* p = __atomic_load_n(&g_sort_counters_addr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        // set-up, once per device (two threads racing here obtain the same address)
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_sort_counters);
+        if (e != cudaSuccess) return cuda_fail(e, "sort_points_noalloc: cudaGetSymbolAddress");
+        if (!p) return fail(DE_EINVAL, "sort_points_noalloc: cudaGetSymbolAddress returned a null address");
+        __atomic_store_n(&g_sort_counters_addr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return DE_OK;
+}
+
+}  // namespace
+
+DE_API size_t de_grid4d_sort_points_noalloc_max_buckets(void) { return static_cast<size_t>(kNoAllocSortMaxBuckets); }
+
+DE_API int de_grid4d_sort_points_noalloc(const float* coords, int64_t n_points, int coord_stride, const uint8_t* dims_host, int n_dims,
+                                  int bits, int32_t* perm, void* stream) {
+    if (n_points < 0 || n_points > 0x7fffffffll) return fail(DE_EINVAL, "sort_points_noalloc: n_points=%lld", (long long)n_points);
+    if (n_dims < 1 || n_dims > 4 || bits < 1 || bits * n_dims > 16 || (1ll << (bits * n_dims)) > kNoAllocSortMaxBuckets)
+        return fail(DE_EUNSUPPORTED, "sort_points_noalloc: n_dims=%d bits=%d needs 2^%d buckets; the built-in scratch holds %d (bits * n_dims must be in 1..16)",
+                    n_dims, bits, bits * n_dims, kNoAllocSortMaxBuckets);
+    unsigned int* counters = nullptr;
+    if (int rc = sort_counters_for_current_device(&counters)) return rc;      // also with n_points = 0: a caller's warm-up call
+    if (n_points == 0) return DE_OK;
+    if (!coords || !dims_host || !perm) return fail(DE_EINVAL, "sort_points_noalloc: NULL pointer");
+    de::SortParams S{};
+    S.coords = coords; S.n = n_points; S.coord_stride = coord_stride; S.n_dims = n_dims; S.bits = bits;
+    for (int d = 0; d < n_dims; ++d) {
+        if (dims_host[d] >= coord_stride) return fail(DE_EINVAL, "sort_points_noalloc: dim[%d]=%d >= coord_stride=%d", d, dims_host[d], coord_stride);
+        S.dim[d] = dims_host[d];
+    }
+    S.counts = counters;          // launch_sort_points zeroes the 2^(bits * n_dims) counters it uses (cudaMemsetAsync on `stream`)
+    S.perm = perm;
+    int dev = 0, n_sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = de::launch_sort_points(S, n_sms, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "sort_points_noalloc launch");
+}
+
 DE_API int de_grid4d_backward_sorted(const de_level_desc* levels_host, int n_levels, const float* coords, int64_t n_points,
                               int coord_stride, int n_features, const uint8_t* mask_a, const uint8_t* mask_b,
                               const float* grad_out, int64_t grad_stride, uint32_t flags, const int32_t* perm, void* stream) {

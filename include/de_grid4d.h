@@ -184,6 +184,23 @@ DE_API int de_grid4d_backward_sorted(const de_level_desc* levels_host, int n_lev
                               const float* grad_out, int64_t grad_stride, uint32_t flags, const int32_t* perm, void* stream);
 
 /*
+ * de_grid4d_sort_points for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments and result as de_grid4d_sort_points minus the workspace: the bucket counters live in a 256 KiB static
+ * device array inside the library (2^16 buckets x 4 B, i.e. the full bits * n_dims <= 16 range of the sort; held by every GPU
+ * that loads the library until the process exits).  Sizes beyond de_grid4d_sort_points_noalloc_max_buckets() buckets return
+ * DE_EUNSUPPORTED.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); the first call per
+ * device looks the array's address up (cudaGetSymbolAddress with that device current) -- a call with n_points = 0 does just
+ * that and can serve as warm-up.  ALL calls on a device share the array (it is zeroed at the start of each call, on `stream`,
+ * and keeps the last call's counters afterwards): two calls whose kernels overlap on the GPU -- different streams, or
+ * several host threads -- race; order them on one stream or with events.  perm: as for de_grid4d_sort_points (the order of
+ * points inside one cell is unspecified in both).
+ */
+DE_API size_t de_grid4d_sort_points_noalloc_max_buckets(void);
+DE_API int de_grid4d_sort_points_noalloc(const float* coords, int64_t n_points, int coord_stride, const uint8_t* dims_host, int n_dims,
+                                  int bits, int32_t* perm, void* stream);
+
+/*
  * fp32 master tables -> fp16 working tables, dst = half(src * scale), one launch
  * for all levels (level i: src = levels_host[i].table (fp32), dst =
  * dst_tables[i]).  dst_tables_host: host array of n_levels device pointers.
