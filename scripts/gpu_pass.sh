@@ -1,7 +1,7 @@
 #!/bin/bash
-# round-2 GPU pass 5: tests + smoke, then the bench lines of the reworked kernels and a launch list of the projection
+# round-2 GPU pass: tests + smoke, then the bench lines of the reworked kernels and a launch list of the projection
 mkdir -p gpurun_out
-T=${1:-r02h}
+T=${1:-r02t}
 timeout 1200 python -m pytest tests -m gpu -q -s 2>&1 | tail -30 > gpurun_out/${T}_pytest.txt
 tail -3 gpurun_out/${T}_pytest.txt
 timeout 300 python __graft_entry__.py smoke 2>&1 | tail -3
@@ -13,7 +13,7 @@ timeout 300 python bench.py --workload c5h768 --steps 5 --no-cpu-baseline > gpur
 python - $T <<'PY'
 import json, sys
 T = sys.argv[1]
-for f in ("projection_h768", "projection_h768_mc"):
+for f in ("projection_h768", "projection_h768_single_cta"):
     try:
         d = json.load(open(f"gpurun_out/{T}_{f}.json"))
         print(f, "fwd", round(d["forward_ms"], 3), "fwd+bwd", round(d["fwd_bwd_ms"], 3), "gemm2 fp32", round(d["gemm2"]["ms_fp32_out"], 3),
