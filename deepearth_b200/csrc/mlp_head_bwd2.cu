@@ -174,7 +174,7 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
     constexpr uint32_t kXaGroup = (NB / 8) * 128;     // bytes between 8-point groups of XA
     constexpr uint32_t kGdGroup = (128 / 8) * 128;    // ... of GD
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ float s_vec[3][kH];                    // b1, ln gamma, ln beta
+    __shared__ __align__(16) float s_vec[3][kH];      // b1, ln gamma, ln beta (read as packed pairs)
     __shared__ __align__(8) uint64_t s_in_full[2], s_d12[2], s_mid_full[2], s_d34[2];
     __shared__ uint32_t s_tmem;
 
@@ -340,22 +340,49 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
 
             // ---- epilogue A: one point per thread (LayerNorm statistics, activation and its derivative,
             //      LayerNorm backward, all in registers) -----------------------------------------------
+            //      The arithmetic runs on packed fp32 pairs (mlp_common.cuh: FFMA2 / FADD2 / FMUL2, columns 2k and 2k + 1 in
+            //      one issue slot; each half an ordinary IEEE operation, sums in the scalar version's order): the consumers
+            //      are latency-bound at two warps per scheduler, and this epilogue was ~60 % of the kernel's instructions.
             {
-                float v[kH];      // h, then xhat (LayerNorm) or h (no LayerNorm)
-                float d[kH];      // dz = da * act'(z), then dh
+                f32x2 v[kH / 2];      // h, then xhat (LayerNorm) or h (no LayerNorm)
+                f32x2 d[kH / 2];      // dz = da * act'(z), then dh
+                const f32x2* vb1 = reinterpret_cast<const f32x2*>(s_vec[0]);
+                const f32x2* vga = reinterpret_cast<const f32x2*>(s_vec[1]);
+                const f32x2* vbe = reinterpret_cast<const f32x2*>(s_vec[2]);
                 {
                     float lo[32], hi[32];
                     tmem_ld32(tmem_row, lo);
                     tmem_ld32(tmem_row + 32, hi);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) { v[j] = lo[j] + s_vec[0][j]; v[32 + j] = hi[j] + s_vec[0][32 + j]; }
+                    for (int j = 0; j < 16; ++j) {
+                        v[j] = add2(pk2(lo[2 * j], lo[2 * j + 1]), vb1[j]);
+                        v[16 + j] = add2(pk2(hi[2 * j], hi[2 * j + 1]), vb1[16 + j]);
+                    }
                 }
                 float rstd = 1.0f;
                 if (P.layernorm) {
-                    const float mean = sum64(v) * (1.0f / kH);
-                    rstd = rsqrtf(sumsq_centered64(v, mean) * (1.0f / kH) + P.ln_eps);
+                    f32x2 sa = 0ull, sb = 0ull;                         // (+0, +0); the four chains of sum64
 #pragma unroll
-                    for (int j = 0; j < kH; ++j) v[j] = (v[j] - mean) * rstd;
+                    for (int j = 0; j < kH / 2; j += 2) { sa = add2(sa, v[j]); sb = add2(sb, v[j + 1]); }
+                    float a0, a1, a2, a3;
+                    upk2(sa, a0, a1);
+                    upk2(sb, a2, a3);
+                    const float mean = ((a0 + a1) + (a2 + a3)) * (1.0f / kH);
+                    const f32x2 nmean = splat2(-mean);
+                    sa = sb = 0ull;
+#pragma unroll
+                    for (int j = 0; j < kH / 2; j += 2) {
+                        v[j] = add2(v[j], nmean);
+                        v[j + 1] = add2(v[j + 1], nmean);
+                        sa = fma2(v[j], v[j], sa);
+                        sb = fma2(v[j + 1], v[j + 1], sb);
+                    }
+                    upk2(sa, a0, a1);
+                    upk2(sb, a2, a3);
+                    rstd = rsqrtf(((a0 + a1) + (a2 + a3)) * (1.0f / kH) + P.ln_eps);
+                    const f32x2 r2 = splat2(rstd);
+#pragma unroll
+                    for (int j = 0; j < kH / 2; ++j) v[j] = mul2(v[j], r2);
                 }
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
@@ -363,24 +390,27 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                     tmem_ld32(tmem_row + 64 + 32 * half, da);
 #pragma unroll
                     for (int c8 = 0; c8 < 4; ++c8) {
-                        float a8[8];
+                        uint32_t a8[4];
 #pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            const int i = 8 * c8 + u, j = 32 * half + i;
-                            const float z = P.layernorm ? fmaf(v[j], s_vec[1][j], s_vec[2][j]) : v[j];
-                            float a = z, g = 1.0f;
-                            if (P.activation == 1) {
-                                a = fmaxf(z, 0.0f);
-                                g = z > 0.0f ? 1.0f : 0.0f;
-                            } else if (P.activation == 2) {
-                                gelu_fwd_bwd(z, a, g);
+                        for (int u = 0; u < 4; ++u) {
+                            const int i = 8 * c8 + 2 * u, jp = 16 * half + 4 * c8 + u;       // column in this half, pair index
+                            const f32x2 z = P.layernorm ? fma2(v[jp], vga[jp], vbe[jp]) : v[jp];
+                            f32x2 a = z, g = splat2(1.0f);
+                            if (P.activation == 2) {
+                                gelu_fwd_bwd2(z, a, g);
+                            } else if (P.activation == 1) {
+                                float z0, z1;
+                                upk2(z, z0, z1);
+                                a = pk2(fmaxf(z0, 0.0f), fmaxf(z1, 0.0f));
+                                g = pk2(z0 > 0.0f ? 1.0f : 0.0f, z1 > 0.0f ? 1.0f : 0.0f);
                             }
-                            a8[u] = a;
-                            d[j] = da[i] * g;
+                            float a0, a1;
+                            upk2(a, a0, a1);
+                            a8[u] = pack_bf16(a0, a1);
+                            d[jp] = mul2(pk2(da[i], da[i + 1]), g);
                         }
                         // A: columns 0..63 of XA (B operand of GEMM 4)
-                        *reinterpret_cast<uint4*>(sXA + canon_chunk_offset(row, 4 * half + c8, NB)) =
-                            make_uint4(pack_bf16(a8[0], a8[1]), pack_bf16(a8[2], a8[3]), pack_bf16(a8[4], a8[5]), pack_bf16(a8[6], a8[7]));
+                        *reinterpret_cast<uint4*>(sXA + canon_chunk_offset(row, 4 * half + c8, NB)) = make_uint4(a8[0], a8[1], a8[2], a8[3]);
                     }
                 }
                 if (P.layernorm) {
@@ -389,25 +419,44 @@ mlp_head_bwd_pp_kernel(const __grid_constant__ MlpHeadBwdParams P) {
                     for (int half = 0; half < 2; ++half) {
                         float t[32];
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) t[i] = d[32 * half + i];
+                        for (int i = 0; i < 16; ++i) upk2(d[16 * half + i], t[2 * i], t[2 * i + 1]);
                         acc_beta[half] += colsum32(t, lane);
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) t[i] = d[32 * half + i] * v[32 * half + i];
+                        for (int i = 0; i < 16; ++i) upk2(mul2(d[16 * half + i], v[16 * half + i]), t[2 * i], t[2 * i + 1]);
                         acc_gamma[half] += colsum32(t, lane);
                     }
+                    f32x2 sa = 0ull, sb = 0ull, da2 = 0ull, db2 = 0ull;            // sum64(d), dot64(d, v): four chains each
 #pragma unroll
-                    for (int j = 0; j < kH; ++j) d[j] *= s_vec[1][j];      // dxhat
-                    const float m1 = sum64(d) * (1.0f / kH);
-                    const float m2 = dot64(d, v) * (1.0f / kH);
+                    for (int j = 0; j < kH / 2; j += 2) {
+                        d[j] = mul2(d[j], vga[j]);                                  // dxhat
+                        d[j + 1] = mul2(d[j + 1], vga[j + 1]);
+                        sa = add2(sa, d[j]);
+                        sb = add2(sb, d[j + 1]);
+                        da2 = fma2(d[j], v[j], da2);
+                        db2 = fma2(d[j + 1], v[j + 1], db2);
+                    }
+                    float a0, a1, a2, a3;
+                    upk2(sa, a0, a1);
+                    upk2(sb, a2, a3);
+                    const f32x2 nm1 = splat2(-(((a0 + a1) + (a2 + a3)) * (1.0f / kH)));
+                    upk2(da2, a0, a1);
+                    upk2(db2, a2, a3);
+                    const f32x2 nm2 = splat2(-(((a0 + a1) + (a2 + a3)) * (1.0f / kH)));
+                    const f32x2 r2 = splat2(rstd);
 #pragma unroll
-                    for (int j = 0; j < kH; ++j) d[j] = rstd * (d[j] - m1 - v[j] * m2);
+                    for (int j = 0; j < kH / 2; ++j) d[j] = mul2(r2, fma2(v[j], nm2, add2(d[j], nm1)));
                 }
                 // DH: columns 64..127 of GD (A operand of GEMM 3, rows 64..127 of GEMM 4's A)
 #pragma unroll
                 for (int k8 = 0; k8 < kH / 8; ++k8) {
-                    *reinterpret_cast<uint4*>(sGD + canon_chunk_offset(row, kH / 8 + k8, 128)) =
-                        make_uint4(pack_bf16(d[8 * k8], d[8 * k8 + 1]), pack_bf16(d[8 * k8 + 2], d[8 * k8 + 3]),
-                                   pack_bf16(d[8 * k8 + 4], d[8 * k8 + 5]), pack_bf16(d[8 * k8 + 6], d[8 * k8 + 7]));
+                    uint32_t q[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        float d0, d1;
+                        upk2(d[4 * k8 + u], d0, d1);
+                        q[u] = pack_bf16(d0, d1);
+                    }
+                    *reinterpret_cast<uint4*>(sGD + canon_chunk_offset(row, kH / 8 + k8, 128)) = make_uint4(q[0], q[1], q[2], q[3]);
                 }
             }
             fence_async_smem();
