@@ -549,9 +549,16 @@ def projection_bench(device, log2_points=20, in_dim=128, hidden=768):
         with torch.autocast("cuda", dtype=torch.bfloat16):
             y = seq(x)
         y.backward(gy.to(y.dtype))
+    def ours_amp():                     # the same call sequence as torch_amp: bf16 y, its gradient cast to bf16 by the caller
+        x.grad = None
+        seq.zero_grad(set_to_none=True)
+        y = fp(x, out_dtype=torch.bfloat16)
+        y.backward(gy.to(y.dtype))
     with torch.no_grad():
         ms_fwd = _time_cuda(lambda: fp(x))
+        ms_fwd16 = _time_cuda(lambda: fp(x, out_dtype=torch.bfloat16))
     ms_step = _time_cuda(ours)
+    ms_step16 = _time_cuda(ours_amp)
     hid = torch.randn((n, hidden), device=device, generator=g).to(torch.bfloat16)
     w2 = seq[3].weight.detach().to(torch.bfloat16)
     out = torch.empty((n, hidden), device=device)
@@ -574,6 +581,9 @@ def projection_bench(device, log2_points=20, in_dim=128, hidden=768):
     gemm_bytes = n * hidden * (2 + 4)
     return {"points": n, "in_dim": in_dim, "hidden": hidden, "forward_ms": ms_fwd, "fwd_bwd_ms": ms_step,
             "mpoints_per_s_fwd_bwd": n / ms_step / 1e3,
+            "bf16_io": {"forward_ms": ms_fwd16, "fwd_bwd_ms": ms_step16, "speedup_vs_cublas_bf16_autocast": ms_amp / ms_step16,
+                        "what": "bf16 y out of the GEMM epilogue and bf16 grad_y consumed in place (de_projection_forward_ex / "
+                                "_backward_ex): what Grid4DEncoder does under torch.autocast(bfloat16), the reference's training mode"},
             "gemm2": {"ms_fp32_out": ms_gemm, "tflops_fp32_out": tf, "frac_of_bf16_burst": tf / burst, "frac_of_bf16_sustained": tf / sustained,
                       "hbm_gbs_fp32_out": gemm_bytes / ms_gemm / 1e6, "hbm_frac_fp32_out": gemm_bytes / ms_gemm / 1e6 / hbm,
                       "ms_bf16_out": ms_gemm16, "tflops_bf16_out": tf16, "frac_of_bf16_burst_bf16_out": tf16 / burst,

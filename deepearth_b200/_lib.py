@@ -13,7 +13,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libde_grid4d.so")
 
 DE_OK = 0
-ABI_VERSION = 4
+ABI_VERSION = 5
 DE_F32, DE_F16, DE_F64, DE_I32, DE_BF16 = 0, 1, 2, 3, 4
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS, DE_FLAG_NO_REGROUP = 0x100, 0x200, 0x400, 0x800
@@ -90,6 +90,11 @@ SIGNATURES = {
     "de_projection_supported": (c_int, [c_int, c_int, c_int]),
     "de_projection_forward": (c_int, [c_void_p, c_i64, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
                                       c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "de_projection_forward_ex": (c_int, [c_void_p, c_i64, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                         c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_i64, c_void_p]),
+    "de_projection_backward_ex": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_int, c_i64, c_i64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p,
+                                          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_size_t, c_void_p]),
     "de_projection_backward_workspace_bytes": (ctypes.c_size_t, [c_i64, c_int, c_int, c_int]),
     "de_projection_backward": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_i64, c_i64, c_void_p, c_void_p, c_void_p, c_void_p,
                                        c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p,

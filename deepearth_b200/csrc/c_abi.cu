@@ -1097,7 +1097,16 @@ DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, i
                           const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
                           const void* w2_bf16, const float* b2, int hidden, int out_dim,
                           void* hidden_bf16, float* row_stats, float* y, int64_t y_stride, void* stream) {
+    return de_projection_forward_ex(x, n_points, in_dim, x_stride, w1_bf16, b1, ln_gamma, ln_beta, ln_eps, w2_bf16, b2, hidden, out_dim,
+                                    hidden_bf16, row_stats, y, DE_F32, y_stride, stream);
+}
+
+DE_API int de_projection_forward_ex(const float* x, int64_t n_points, int in_dim, int64_t x_stride,
+                             const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
+                             const void* w2_bf16, const float* b2, int hidden, int out_dim,
+                             void* hidden_bf16, float* row_stats, void* y, int y_dtype, int64_t y_stride, void* stream) {
     if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (y_dtype != DE_F32 && y_dtype != DE_BF16) return fail(DE_EUNSUPPORTED, "projection: y_dtype %d (DE_F32 or DE_BF16)", y_dtype);
     if (n_points == 0) return DE_OK;
     if (!x || !w1_bf16 || !b1 || !ln_gamma || !ln_beta || !w2_bf16 || !hidden_bf16 || !y) return fail(DE_EINVAL, "projection: NULL pointer");
     if (!de_projection_supported(in_dim, hidden, out_dim))
@@ -1117,7 +1126,7 @@ DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, i
     if (e != cudaSuccess) return cuda_fail(e, "projection hidden launch");
     de::GemmParams G{};
     G.M = n_points; G.N = out_dim; G.K = hidden; G.c = y; G.ldc = y_stride; G.bias = b2;
-    e = de::launch_gemm_bf16(hidden_bf16, hidden, w2_bf16, hidden, 0, G, 0, n_sms, s);
+    e = de::launch_gemm_bf16(hidden_bf16, hidden, w2_bf16, hidden, 0, G, y_dtype == DE_BF16 ? 1 : 0, n_sms, s);
     return e == cudaSuccess ? DE_OK : cuda_fail(e, "projection GEMM launch");
 }
 
@@ -1138,7 +1147,20 @@ DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n
                            float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1, float* grad_gamma,
                            float* grad_beta, float* grad_w2, float* grad_b2,
                            void* workspace, size_t workspace_bytes, void* stream) {
+    return de_projection_backward_ex(x, grad_y, DE_F32, n_points, in_dim, x_stride, gy_stride, w1_bf16, w1t_bf16, w2t_bf16, b1, ln_gamma,
+                                     ln_beta, hidden, out_dim, hidden_bf16, row_stats, grad_x, gx_stride, grad_w1, grad_b1, grad_gamma,
+                                     grad_beta, grad_w2, grad_b2, workspace, workspace_bytes, stream);
+}
+
+DE_API int de_projection_backward_ex(const float* x, const void* grad_y, int gy_dtype, int64_t n_points, int in_dim, int64_t x_stride,
+                              int64_t gy_stride, const void* w1_bf16, const void* w1t_bf16, const void* w2t_bf16,
+                              const float* b1, const float* ln_gamma, const float* ln_beta, int hidden, int out_dim,
+                              const void* hidden_bf16, const float* row_stats,
+                              float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1, float* grad_gamma,
+                              float* grad_beta, float* grad_w2, float* grad_b2,
+                              void* workspace, size_t workspace_bytes, void* stream) {
     if (n_points < 0) return fail(DE_EINVAL, "n_points < 0");
+    if (gy_dtype != DE_F32 && gy_dtype != DE_BF16) return fail(DE_EUNSUPPORTED, "projection_backward: gy_dtype %d (DE_F32 or DE_BF16)", gy_dtype);
     if (n_points == 0) return DE_OK;
     if (!x || !grad_y || !w1_bf16 || !w1t_bf16 || !w2t_bf16 || !b1 || !ln_gamma || !ln_beta || !hidden_bf16 || !row_stats ||
         !grad_w1 || !grad_w2 || !workspace)
@@ -1150,23 +1172,30 @@ DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n
     const void* aligned[] = {x, grad_y, w1_bf16, w1t_bf16, w2t_bf16, hidden_bf16, workspace, grad_x, b1, ln_gamma, ln_beta};
     for (const void* q : aligned)
         if (reinterpret_cast<uintptr_t>(q) % 16) return fail(DE_EALIGN, "projection_backward: pointer not 16-byte aligned");
-    if (x_stride % 4 || gy_stride % 4) return fail(DE_EALIGN, "projection_backward: row strides must be multiples of 4 floats");
+    if (x_stride % 4 || gy_stride % (gy_dtype == DE_BF16 ? 8 : 4))
+        return fail(DE_EALIGN, "projection_backward: row strides must be multiples of 16 bytes");
     if (n_points > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "projection_backward: n_points too large");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int n_sms = device_sms();
     const size_t n = static_cast<size_t>(n_points);
     char* ws = static_cast<char*>(workspace);
-    void* gy16 = ws;
+    const void* gy16 = gy_dtype == DE_BF16 ? grad_y : ws;      // bf16 gradients are consumed where they lie (TMA: any 16-byte row pitch)
+    const int64_t gy16_ld = gy_dtype == DE_BF16 ? gy_stride : out_dim;
     void* da = ws + align256(n * out_dim * 2);
     void* x16 = ws + align256(n * out_dim * 2) + align256(n * hidden * 2);
-    // 1. bf16 copy of grad_y, db2 = column sums
-    cudaError_t e = de::launch_cast_colsum(grad_y, gy_stride, gy16, out_dim, n_points, out_dim, grad_b2, n_sms, s);
-    if (e != cudaSuccess) return cuda_fail(e, "projection_backward: cast launch");
+    // 1. bf16 copy of grad_y (fp32 input only), db2 = column sums
+    cudaError_t e = cudaSuccess;
+    if (gy_dtype == DE_BF16) {
+        if (grad_b2) e = de::launch_colsum_bf16(grad_y, gy_stride, n_points, out_dim, grad_b2, n_sms, s);
+    } else {
+        e = de::launch_cast_colsum(static_cast<const float*>(grad_y), gy_stride, ws, out_dim, n_points, out_dim, grad_b2, n_sms, s);
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "projection_backward: cast / column-sum launch");
     // 2. da (n, hidden) = gy (n, out) . W2 (out, hidden)
     {
         de::GemmParams G{};
         G.M = n_points; G.N = hidden; G.K = out_dim; G.c = da; G.ldc = hidden;
-        e = de::launch_gemm_bf16(gy16, out_dim, w2t_bf16, out_dim, 0, G, 1, n_sms, s);
+        e = de::launch_gemm_bf16(gy16, gy16_ld, w2t_bf16, out_dim, 0, G, 1, n_sms, s);
         if (e != cudaSuccess) return cuda_fail(e, "projection_backward: da GEMM launch");
     }
     // 3. dpre in place of da; dgamma, dbeta, db1; bf16 copy of x
@@ -1184,7 +1213,7 @@ DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n
         const size_t nt = (n + 7) & ~static_cast<size_t>(7);
         char* t0 = ws + align256(n * out_dim * 2) + align256(n * hidden * 2) + align256(n * in_dim * 2);
         char* t1 = t0 + align256(nt * out_dim * 2);
-        e = de::launch_transpose_bf16(gy16, out_dim, t0, nt, n_points, out_dim, s);
+        e = de::launch_transpose_bf16(gy16, gy16_ld, t0, nt, n_points, out_dim, s);
         if (e == cudaSuccess) e = de::launch_transpose_bf16(hidden_bf16, hidden, t1, nt, n_points, hidden, s);
         if (e != cudaSuccess) return cuda_fail(e, "projection_backward: transpose launch");
         de::GemmParams G{};
@@ -1201,7 +1230,7 @@ DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n
     } else {
         de::GemmParams G{};
         G.M = out_dim; G.N = hidden; G.K = n_points; G.c = grad_w2; G.ldc = hidden;
-        e = de::launch_gemm_bf16(gy16, out_dim, hidden_bf16, hidden, 1, G, 2, n_sms, s);
+        e = de::launch_gemm_bf16(gy16, gy16_ld, hidden_bf16, hidden, 1, G, 2, n_sms, s);
         if (e != cudaSuccess) return cuda_fail(e, "projection_backward: dW2 GEMM launch");
         G = de::GemmParams{};
         G.M = hidden; G.N = in_dim; G.K = n_points; G.c = grad_w1; G.ldc = in_dim;

@@ -171,6 +171,8 @@ cudaError_t launch_transpose_bf16(const void* src, long long ld_src, void* dst, 
                                   cudaStream_t s);
 cudaError_t launch_cast_colsum(const float* src, long long ld_src, void* dst_bf16, long long ld_dst, long long n_rows, int n_cols,
                                float* colsum, int n_sms, cudaStream_t s);
+cudaError_t launch_colsum_bf16(const void* src_bf16, long long ld_src, long long n_rows, int n_cols, float* colsum, int n_sms,
+                               cudaStream_t s);
 bool proj_hidden_supported(int in_dim, int hidden);
 cudaError_t launch_proj_hidden(ProjHiddenParams P, int in_dim, int n_sms, cudaStream_t s);
 cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long long ldb, int transposed, GemmParams P, int epi,

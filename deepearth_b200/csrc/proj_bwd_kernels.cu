@@ -72,6 +72,51 @@ cudaError_t launch_cast_colsum(const float* src, long long ld_src, void* dst_bf1
     return cudaGetLastError();
 }
 
+// ---- column sums of a bf16 matrix (db2 when grad_y arrives in bf16: autocast) --------------------------------------------
+// 32 lanes x 8 columns (one 16-byte load each) = 256 columns per CTA column, 8 row phases per CTA; n_cols is a multiple of 8.
+__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src, long long n_rows,
+                                                          int n_cols, float* colsum, long long rows_per_cta) {
+    __shared__ float s_part[8][256];
+    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+    const int c0 = blockIdx.x * 256 + cx * 8;
+    const long long r_begin = static_cast<long long>(blockIdx.y) * rows_per_cta;
+    const long long r_end = (r_begin + rows_per_cta < n_rows) ? r_begin + rows_per_cta : n_rows;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (c0 < n_cols) {
+        for (long long r = r_begin + ry; r < r_end; r += 8) {
+            const uint4 v = __ldcs(reinterpret_cast<const uint4*>(src + r * ld_src + c0));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                acc[2 * i] += __uint_as_float(w[i] << 16);
+                acc[2 * i + 1] += __uint_as_float(w[i] & 0xffff0000u);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s_part[ry][cx * 8 + i] = acc[i];
+    __syncthreads();
+    float a = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a += s_part[i][threadIdx.x];
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c < n_cols) red_f32(colsum + c, a);
+}
+
+cudaError_t launch_colsum_bf16(const void* src_bf16, long long ld_src, long long n_rows, int n_cols, float* colsum, int n_sms,
+                               cudaStream_t s) {
+    if (n_rows == 0 || !colsum) return cudaSuccess;
+    const int bx = (n_cols + 255) / 256;
+    long long by = (static_cast<long long>(n_sms) * 8 + bx - 1) / bx;
+    long long rows = (n_rows + by - 1) / by;
+    if (rows < 64) rows = 64;
+    rows = (rows + 7) / 8 * 8;
+    by = (n_rows + rows - 1) / rows;
+    colsum_bf16_kernel<<<dim3(bx, static_cast<unsigned>(by)), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(src_bf16), ld_src, n_rows,
+                                                                         n_cols, colsum, rows);
+    return cudaGetLastError();
+}
+
 // ---- bf16 transpose (fallback operand path of the weight-gradient GEMMs, DE_PROJ_DW_TRANSPOSE=1) ----------------------
 // src (rows, cols) row-major -> dst (cols, ld_dst) row-major; 64 x 64 tiles through shared memory
 __global__ void __launch_bounds__(256) transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src,

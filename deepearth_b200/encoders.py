@@ -273,9 +273,12 @@ class Grid4DEncoder(nn.Module):
         if torch.is_autocast_enabled():
             if not head.wide:
                 return self.projection(feats)
+            dt = torch.get_autocast_dtype("cuda")
             with torch.autocast(device_type="cuda", enabled=False):
+                if dt == torch.bfloat16:          # y leaves the GEMM in bf16, its gradient arrives in bf16: no cast passes
+                    return head(feats.float(), out_dtype=torch.bfloat16)
                 y = head(feats.float())
-            return y.to(torch.get_autocast_dtype("cuda"))
+            return y.to(dt)
         return head(feats)
 
     def forward(self, xyzt: torch.Tensor, spatial_mask: Optional[torch.Tensor] = None,

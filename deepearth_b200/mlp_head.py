@@ -124,8 +124,9 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = N
 
 def projection_forward(x: torch.Tensor, w1_bf16: torch.Tensor, b1: torch.Tensor, ln_gamma: torch.Tensor,
                        ln_beta: torch.Tensor, ln_eps: float, w2_bf16: torch.Tensor, b2: Optional[torch.Tensor],
-                       want_stats: bool = False):
-    """x (n, in_dim) fp32 -> (y (n, out) fp32, hidden (n, H) bf16 = GELU(LN(W1 x + b1)), stats (n, 2) | None)."""
+                       want_stats: bool = False, out_dtype: torch.dtype = torch.float32):
+    """x (n, in_dim) fp32 -> (y (n, out) fp32 | bf16, hidden (n, H) bf16 = GELU(LN(W1 x + b1)), stats (n, 2) | None).
+    ``out_dtype=torch.bfloat16``: y rounded once in the GEMM epilogue (what nn.Linear returns under autocast)."""
     _require_cuda(x, "x")
     if x.dim() != 2 or x.dtype != torch.float32:
         raise TypeError("x must be a 2-D float32 tensor")
@@ -133,29 +134,34 @@ def projection_forward(x: torch.Tensor, w1_bf16: torch.Tensor, b1: torch.Tensor,
         x = x.contiguous()
     n, in_dim = x.shape
     hidden, out_dim = w1_bf16.shape[0], w2_bf16.shape[0]
-    y = torch.empty((n, out_dim), dtype=torch.float32, device=x.device)
+    if out_dtype not in (torch.float32, torch.bfloat16):
+        raise TypeError("out_dtype must be torch.float32 or torch.bfloat16")
+    y = torch.empty((n, out_dim), dtype=out_dtype, device=x.device)
     hid = torch.empty((n, hidden), dtype=torch.bfloat16, device=x.device)
     stats = torch.empty((n, 2), dtype=torch.float32, device=x.device) if want_stats else None
     if n:
         with torch.cuda.device(x.device):
-            rc = _lib.load().de_projection_forward(
+            rc = _lib.load().de_projection_forward_ex(
                 _ptr(x), n, in_dim, x.stride(0), _ptr(w1_bf16), _ptr(b1), _ptr(ln_gamma), _ptr(ln_beta), float(ln_eps),
-                _ptr(w2_bf16), _ptr(b2), hidden, out_dim, _ptr(hid), _ptr(stats), _ptr(y), y.stride(0), _stream_ptr(x.device))
-        _lib.check(rc, "de_projection_forward")
+                _ptr(w2_bf16), _ptr(b2), hidden, out_dim, _ptr(hid), _ptr(stats), _ptr(y),
+                _lib.DE_BF16 if out_dtype == torch.bfloat16 else _lib.DE_F32, y.stride(0), _stream_ptr(x.device))
+        _lib.check(rc, "de_projection_forward_ex")
     return y, hid, stats
 
 
 def projection_backward(x, grad_y, w1_bf16, w1t_bf16, w2t_bf16, b1, ln_gamma, ln_beta, hidden_bf16, stats,
                         want_grad_x: bool = True):
-    """Backward of ``projection_forward``: (grad_x | None, grad_w1, grad_b1, grad_gamma, grad_beta, grad_w2, grad_b2), fp32."""
+    """Backward of ``projection_forward``: (grad_x | None, grad_w1, grad_b1, grad_gamma, grad_beta, grad_w2, grad_b2), fp32.
+    ``grad_y`` fp32, or bf16 (the gradient of a bf16 output: consumed in place, no cast pass)."""
     _require_cuda(x, "x")
     _require_cuda(grad_y, "grad_y")
     n, in_dim = x.shape
     hidden, out_dim = w1_bf16.shape[0], w2t_bf16.shape[1]
     if x.stride(1) != 1 or x.stride(0) % 4 or x.data_ptr() % 16:
         x = x.contiguous()
-    grad_y = grad_y.float()
-    if grad_y.stride(1) != 1 or grad_y.stride(0) % 4 or grad_y.data_ptr() % 16:
+    if grad_y.dtype != torch.bfloat16:
+        grad_y = grad_y.float()
+    if grad_y.stride(1) != 1 or grad_y.stride(0) % (8 if grad_y.dtype == torch.bfloat16 else 4) or grad_y.data_ptr() % 16:
         grad_y = grad_y.contiguous()
     dev = x.device
     gx = torch.empty((n, in_dim), dtype=torch.float32, device=dev) if want_grad_x else None
@@ -167,12 +173,13 @@ def projection_backward(x, grad_y, w1_bf16, w1t_bf16, w2t_bf16, b1, ln_gamma, ln
         ws_bytes = int(lib.de_projection_backward_workspace_bytes(n, in_dim, hidden, out_dim))
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
-            rc = lib.de_projection_backward(
-                _ptr(x), _ptr(grad_y), n, in_dim, x.stride(0), grad_y.stride(0), _ptr(w1_bf16), _ptr(w1t_bf16), _ptr(w2t_bf16),
+            rc = lib.de_projection_backward_ex(
+                _ptr(x), _ptr(grad_y), _lib.DE_BF16 if grad_y.dtype == torch.bfloat16 else _lib.DE_F32, n, in_dim, x.stride(0),
+                grad_y.stride(0), _ptr(w1_bf16), _ptr(w1t_bf16), _ptr(w2t_bf16),
                 _ptr(b1), _ptr(ln_gamma), _ptr(ln_beta), hidden, out_dim, _ptr(hidden_bf16), _ptr(stats),
                 _ptr(gx), gx.stride(0) if gx is not None else in_dim, _ptr(gw1), _ptr(gb1), _ptr(gg), _ptr(gbeta), _ptr(gw2),
                 _ptr(gb2), _ptr(ws), ws_bytes, _stream_ptr(dev))
-        _lib.check(rc, "de_projection_backward")
+        _lib.check(rc, "de_projection_backward_ex")
     return gx, gw1.view(hidden, in_dim), gb1, gg, gbeta, gw2.view(out_dim, hidden), gb2
 
 
@@ -192,7 +199,7 @@ class _HeadFunction(torch.autograd.Function):
         ctx.grouped = head._grouped_next     # (token, W) set by Grid4DEncoder.forward for this call, or None
         head._grouped_next = None
         if head.wide and head.fused_backward:
-            y, hid, stats = head.fused_wide(x, want_stats=True)
+            y, hid, stats = head.fused_wide(x, want_stats=True, out_dtype=head._out_dtype_next)
             ctx.save_for_backward(x, hid, stats)        # the bf16 activations and the LayerNorm row statistics
             return y
         ctx.save_for_backward(x)
@@ -259,6 +266,7 @@ class FusedProjection:
         self._key = None
         self._w1 = self._w2 = self._w1t = self._w2t = None
         self._grouped_next = None
+        self._out_dtype_next = torch.float32
         # hidden widths other than 64 (768 by default, 2048 in the integrated model) take the two-kernel path of
         # csrc/proj_kernels.cu; it needs the full Linear-LayerNorm-GELU-Linear structure with biases
         self.wide = (self.lin1.out_features != 64 and self.norm is not None and self.activation == "gelu"
@@ -299,10 +307,11 @@ class FusedProjection:
             out[id(n.bias)] = gbeta
         return out
 
-    def fused_wide(self, x: torch.Tensor, want_stats: bool = False):
+    def fused_wide(self, x: torch.Tensor, want_stats: bool = False, out_dtype: torch.dtype = torch.float32):
         w1, w2 = self._weights()
         n = self.norm
-        return projection_forward(x, w1, self.lin1.bias, n.weight, n.bias, n.eps, w2, self.lin2.bias, want_stats=want_stats)
+        return projection_forward(x, w1, self.lin1.bias, n.weight, n.bias, n.eps, w2, self.lin2.bias, want_stats=want_stats,
+                                  out_dtype=out_dtype)
 
     def backward_wide(self, x, hid, stats, grad_y, want_grad_x: bool = True) -> dict:
         """Gradients of the wide projection by the tcgen05 kernels (csrc/proj_bwd_kernels.cu), keyed by id(parameter) (+ "x")."""
@@ -320,12 +329,23 @@ class FusedProjection:
         w1, w2 = self._weights()
         n = self.norm
         if self.wide:
-            return projection_forward(x, w1, self.lin1.bias, n.weight, n.bias, n.eps, w2, self.lin2.bias)[0]
+            return projection_forward(x, w1, self.lin1.bias, n.weight, n.bias, n.eps, w2, self.lin2.bias, out_dtype=self._out_dtype_next)[0]
         return mlp_head_forward(x, w1, self.lin1.bias, n.weight if n is not None else None,
                                 n.bias if n is not None else None, n.eps if n is not None else 1e-5,
                                 n is not None, self.activation, w2, self.lin2.bias)
 
-    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+    def __call__(self, x: torch.Tensor, out_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+        """``out_dtype=torch.bfloat16`` (wide path only): y leaves the second GEMM in bf16 and its gradient is taken in bf16 --
+        nn.Linear's behaviour under ``torch.autocast(bfloat16)``, without a cast pass on either side."""
+        if out_dtype != torch.float32 and not self.wide:
+            raise TypeError("out_dtype other than float32 needs the wide projection path")
+        self._out_dtype_next = out_dtype
+        try:
+            return self._call(x)
+        finally:
+            self._out_dtype_next = torch.float32
+
+    def _call(self, x: torch.Tensor) -> torch.Tensor:
         needs_grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.seq.parameters()))
         if needs_grad:
             return _HeadFunction.apply(x, self, *self.seq.parameters())

@@ -35,7 +35,7 @@ extern "C" {
 #define DE_API
 #endif
 
-#define DE_ABI_VERSION 4
+#define DE_ABI_VERSION 5
 
 /* status codes (negative = caller error) */
 #define DE_OK 0
@@ -295,6 +295,13 @@ DE_API int de_projection_forward(const float* x, int64_t n_points, int in_dim, i
                           const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
                           const void* w2_bf16, const float* b2, int hidden, int out_dim,
                           void* hidden_bf16, float* row_stats, float* y, int64_t y_stride, void* stream);
+/* Same, with the output dtype stated: y_dtype DE_F32 or DE_BF16 (y_stride in elements).  DE_BF16 is what nn.Linear returns
+ * under torch.autocast(bfloat16) -- the mode the reference trains in (hpc/train_distrbuted.py:284): the GEMM's epilogue rounds
+ * acc + b2 once, so the result equals the fp32 output rounded to bf16, without the 6 bytes per element of a separate cast. */
+DE_API int de_projection_forward_ex(const float* x, int64_t n_points, int in_dim, int64_t x_stride,
+                             const void* w1_bf16, const float* b1, const float* ln_gamma, const float* ln_beta, float ln_eps,
+                             const void* w2_bf16, const float* b2, int hidden, int out_dim,
+                             void* hidden_bf16, float* row_stats, void* y, int y_dtype, int64_t y_stride, void* stream);
 /*
  * Backward of de_projection_forward -- replaces autograd's AddmmBackward / GeluBackward / NativeLayerNormBackward chain for
  * models/encoders.py:47-52 at hidden_dim 768 / 2048.  grad_x (n, in_dim) fp32 is the gradient the hash grids consume; the
@@ -313,6 +320,16 @@ DE_API int de_projection_backward(const float* x, const float* grad_y, int64_t n
                            float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1, float* grad_gamma,
                            float* grad_beta, float* grad_w2, float* grad_b2,
                            void* workspace, size_t workspace_bytes, void* stream);
+/* Same, with the dtype of grad_y stated: DE_F32, or DE_BF16 (autocast: the gradient of a bf16 y) -- then grad_y (rows
+ * gy_stride elements apart, a multiple of 8) is consumed in place by the GEMMs: no fp32 -> bf16 copy pass, db2 by a column-sum
+ * kernel over the bf16 rows.  Same workspace size. */
+DE_API int de_projection_backward_ex(const float* x, const void* grad_y, int gy_dtype, int64_t n_points, int in_dim, int64_t x_stride,
+                              int64_t gy_stride, const void* w1_bf16, const void* w1t_bf16, const void* w2t_bf16,
+                              const float* b1, const float* ln_gamma, const float* ln_beta, int hidden, int out_dim,
+                              const void* hidden_bf16, const float* row_stats,
+                              float* grad_x, int64_t gx_stride, float* grad_w1, float* grad_b1, float* grad_gamma,
+                              float* grad_beta, float* grad_w2, float* grad_b2,
+                              void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * The GEMM kernel on its own: C (M, N) = A . B^T + bias, bf16 operands, fp32 accumulation in tensor memory.

@@ -30,7 +30,7 @@ def test_header_symbols_exported(lib):
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/de_grid4d.h but not exported"
         assert s in _lib.SIGNATURES, f"{s} has no ctypes signature in deepearth_b200/_lib.py"
-    assert lib.de_abi_version() == _lib.ABI_VERSION == 4
+    assert lib.de_abi_version() == _lib.ABI_VERSION == 5
     assert lib.de_corners(1, 3) == 8 and lib.de_corners(0, 3) == 1 and lib.de_corners(1, 4) == 16
 
 

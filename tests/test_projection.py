@@ -146,6 +146,74 @@ def test_projection_backward_vs_autograd(dev, in_dim, hidden, n):
         assert v <= 1e-2, (k, v)          # B200: <= 5e-3 on every shape (gpurun r02c)
 
 
+@pytest.mark.parametrize("in_dim,hidden,n", [(128, 768, 2048 + 5), (48, 256, 300)])
+def test_projection_bf16_output_and_bf16_grad_y(dev, in_dim, hidden, n):
+    """The autocast form (de_projection_forward_ex / _backward_ex with DE_BF16): y leaves the GEMM rounded once -- equal to
+    the fp32 output rounded to bf16 -- and a bf16 grad_y is consumed in place: every gradient equals the one computed from
+    grad_y.float() through the fp32 entry point (same operands, same kernels), db2 up to the order of its column sums."""
+    import torch.nn as nn
+    from deepearth_b200.mlp_head import FusedProjection, projection_backward, projection_forward
+    torch.manual_seed(in_dim + hidden)
+    seq = nn.Sequential(nn.Linear(in_dim, hidden), nn.LayerNorm(hidden), nn.GELU(), nn.Linear(hidden, hidden)).to(dev)
+    g = torch.Generator(device=dev).manual_seed(n)
+    x = torch.randn((n, in_dim), device=dev, generator=g)
+    gy16 = torch.randn((n, hidden), device=dev, generator=g).to(torch.bfloat16)
+    fp = FusedProjection(seq)
+    w1, w2 = fp._weights()
+    args = (x, w1, seq[0].bias, seq[1].weight, seq[1].bias, seq[1].eps, w2, seq[3].bias)
+    y32, hid, stats = projection_forward(*args, want_stats=True)
+    y16, hid16, stats16 = projection_forward(*args, want_stats=True, out_dtype=torch.bfloat16)
+    assert y16.dtype == torch.bfloat16
+    assert torch.equal(y16, y32.to(torch.bfloat16)) and torch.equal(hid, hid16) and torch.equal(stats, stats16)
+    bargs = (w1, fp._w1t, fp._w2t, seq[0].bias, seq[1].weight, seq[1].bias, hid, stats)
+    want = projection_backward(x, gy16.float(), *bargs)
+    got = projection_backward(x, gy16, *bargs)
+    names = ["grad_x", "grad_w1", "grad_b1", "grad_gamma", "grad_beta", "grad_w2", "grad_b2"]
+    for name, a, b in zip(names, got, want):
+        scale = float(b.abs().max())
+        if name == "grad_x":
+            assert torch.equal(a, b), name                       # no atomics on its path
+        else:
+            assert float((a - b).abs().max()) <= 2e-4 * scale, (name, float((a - b).abs().max()) / scale)
+    # a row pitch that is not the row length: grad_y as a column slice of a wider bf16 buffer
+    wide = torch.zeros((n, hidden + 16), device=dev, dtype=torch.bfloat16)
+    wide[:, 8:8 + hidden] = gy16
+    got2 = projection_backward(x, wide[:, 8:8 + hidden], *bargs)
+    assert torch.equal(got2[0], want[0])
+    assert float((got2[5] - want[5]).abs().max()) <= 2e-4 * float(want[5].abs().max())
+
+
+def test_grid4d_encoder_under_autocast_bf16(dev):
+    """Under torch.autocast(bfloat16) -- how the reference trains (hpc/train_distrbuted.py:284) -- the encoder returns bf16
+    like the reference's nn.Linear would, through the bf16-output GEMM, and its backward takes the bf16 gradient directly."""
+    import deepearth_b200 as de
+    torch.manual_seed(1)
+    cfg = de.DeepEarthConfig(hash_table_size=2 ** 14)
+    enc = de.Grid4DEncoder(cfg).to(dev)
+    with torch.no_grad():
+        for e in enc._encoders:
+            for t in e.hash_tables:
+                t.weight.uniform_(-1.0, 1.0)
+    xyzt = torch.rand((2500, 4), device=dev)
+    out32 = enc(xyzt)
+    out32.square().mean().backward()
+    ref = {k: p.grad.clone() for k, p in enc.named_parameters()}
+    enc.zero_grad(set_to_none=True)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out16 = enc(xyzt)
+    assert out16.dtype == torch.bfloat16
+    assert torch.equal(out16, out32.detach().to(torch.bfloat16))
+    out16.float().square().mean().backward()
+    worst = 0.0
+    for k, p in enc.named_parameters():
+        assert p.grad is not None and p.grad.dtype == torch.float32, k
+        scale = float(ref[k].abs().max())
+        if scale > 0:
+            worst = max(worst, float((p.grad - ref[k]).abs().max()) / scale)
+    print(f"autocast bf16 vs fp32 output: worst relative gradient difference {worst:.2e}")
+    assert worst <= 1e-2, worst              # y and grad_y rounded to bf16 (2^-9 each); B200: 4.8e-3
+
+
 def test_grid4d_encoder_default_width_runs_on_our_kernels(dev):
     """Grid4DEncoder(config) with the reference's default hidden_dim = 768 (models/configs.py:44) and grid4d_fused_head:
     forward + backward through the wide projection kernels, checked against the fp32 nn.Sequential on the same features."""
