@@ -118,6 +118,33 @@ def test_wide_projection_runs_on_tcgen05_and_tma(sass_by_function):
             assert "UTCHMMA" in sass_by_function[k] and "LDTM" in sass_by_function[k], k
 
 
+def test_projection_round2_mechanisms_are_in_the_binary(sass_by_function):
+    """DESIGN.md 2.8, round 2: CTA-pair MMAs (tcgen05 cta_group::2 = UTCHMMA.2CTA, operands by UTMALDG...2CTA, commits multicast to
+    both CTAs), fp32 output through TMA tensor stores (UTMASTG), LayerNorm / GELU epilogues on packed fp32 pairs
+    (FFMA2 / FADD2 / FMUL2) with whole-sector 256-bit row accesses."""
+    def is_pair(k):                                    # template arguments <A_MN, B_MN, EPI, MC>: MC = 2
+        return re.search(r"gemm_bf16_tma_kernelILi\dELi\dELi\dELi2EE", k) is not None
+    pair = [k for k in _pick(sass_by_function, "gemm_bf16_tma_kernel") if is_pair(k)]
+    single = [k for k in _pick(sass_by_function, "gemm_bf16_tma_kernel") if not is_pair(k)]
+    assert pair and single
+    for k in pair:
+        sass = sass_by_function[k]
+        assert "UTCHMMA.2CTA" in sass and "UTMALDG.2D.2CTA" in sass and "UTCBAR.2CTA.MULTICAST" in sass, k
+    for k in single:
+        assert "UTCHMMA.2CTA" not in sass_by_function[k], k
+    fp32_store = [k for k in pair + single if re.search(r"ILi\dELi\dELi0ELi\dEE", k)]
+    assert fp32_store and all("UTMASTG" in sass_by_function[k] for k in fp32_store)
+    for name in ("proj_hidden_kernel", "proj_dpre_kernel", "mlp_head_bwd_pp_kernel"):
+        for k in _pick(sass_by_function, name):
+            sass = sass_by_function[k]
+            assert "FFMA2" in sass and "FADD2" in sass and "FMUL2" in sass, k
+    for name in ("proj_hidden_kernel", "proj_dpre_kernel"):
+        for k in _pick(sass_by_function, name):
+            assert re.search(r"STG\.E\.(ENL2\.)?256", sass_by_function[k]), k
+    for k in _pick(sass_by_function, "proj_dpre_kernel"):
+        assert re.search(r"LDG\.E\.[A-Z0-9.]*256", sass_by_function[k]), k
+
+
 def test_small1d_and_st_embed_accumulate_in_shared_memory(sass_by_function):
     """grid4d_small1d / st_embed table-gradient kernels: shared-memory atomics (ATOMS) per point, global REDG only at the flush."""
     for k in _pick(sass_by_function, "small1d_backward_kernel"):
