@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_PKG, "libde_grid4d.so")
 DE_OK = 0
 ABI_VERSION = 5
 DE_F32, DE_F16, DE_F64, DE_I32, DE_BF16 = 0, 1, 2, 3, 4
+DE_SORT_NOALLOC_MAX_BUCKETS = 65536
 DE_INTERP_NEAREST, DE_INTERP_LINEAR = 0, 1
 DE_FLAG_STAGED_BWD, DE_FLAG_SMEM_COARSE, DE_FLAG_NO_L2_HINTS, DE_FLAG_NO_REGROUP = 0x100, 0x200, 0x400, 0x800
 DE_FLAG_GRAD_GROUPED = 0x1000
@@ -68,7 +69,6 @@ SIGNATURES = {
     "de_grid4d_backward_workspace_bytes_ex": (ctypes.c_size_t, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32, c_int]),
     "de_grid4d_backward_group_width": (c_int, [ctypes.POINTER(DeLevelDesc), c_int, c_int, c_i64, c_u32, c_int]),
     "de_grid4d_sort_workspace_bytes": (ctypes.c_size_t, [c_int, c_int]),
-    "de_grid4d_sort_points_noalloc_max_buckets": (ctypes.c_size_t, []),
     "de_grid4d_sort_points_noalloc": (c_int, [c_void_p, c_i64, c_int, ctypes.POINTER(ctypes.c_uint8), c_int, c_int, c_void_p, c_void_p]),
     "de_grid4d_sort_points": (c_int, [c_void_p, c_i64, c_int, ctypes.POINTER(ctypes.c_uint8), c_int, c_int, c_void_p, c_void_p,
                                       ctypes.c_size_t, c_void_p]),

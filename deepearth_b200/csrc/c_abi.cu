@@ -712,7 +712,7 @@ DE_API int de_grid4d_sort_points(const float* coords, int64_t n_points, int coor
 // mutable global state in this file (the rest of the surface is re-entrant): calls share the array, see the header.
 namespace {
 
-constexpr int kNoAllocSortMaxBuckets = 1 << 16;
+constexpr int kNoAllocSortMaxBuckets = DE_SORT_NOALLOC_MAX_BUCKETS;
 static __device__ __align__(256) unsigned int g_sort_counters[kNoAllocSortMaxBuckets];
 
 constexpr int kNoAllocMaxDevices = 64;
@@ -736,8 +736,6 @@ int sort_counters_for_current_device(unsigned int** out) {
 }
 
 }  // namespace
-
-DE_API size_t de_grid4d_sort_points_noalloc_max_buckets(void) { return static_cast<size_t>(kNoAllocSortMaxBuckets); }
 
 DE_API int de_grid4d_sort_points_noalloc(const float* coords, int64_t n_points, int coord_stride, const uint8_t* dims_host, int n_dims,
                                   int bits, int32_t* perm, void* stream) {

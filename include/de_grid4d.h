@@ -188,7 +188,7 @@ DE_API int de_grid4d_backward_sorted(const de_level_desc* levels_host, int n_lev
  * forbid cudaMalloc).  No counterpart in the reference.
  * Same arguments and result as de_grid4d_sort_points minus the workspace: the bucket counters live in a 256 KiB static
  * device array inside the library (2^16 buckets x 4 B, i.e. the full bits * n_dims <= 16 range of the sort; held by every GPU
- * that loads the library until the process exits).  Sizes beyond de_grid4d_sort_points_noalloc_max_buckets() buckets return
+ * that loads the library until the process exits).  Sizes beyond DE_SORT_NOALLOC_MAX_BUCKETS buckets return
  * DE_EUNSUPPORTED.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); the first call per
  * device looks the array's address up (cudaGetSymbolAddress with that device current) -- a call with n_points = 0 does just
  * that and can serve as warm-up.  ALL calls on a device share the array (it is zeroed at the start of each call, on `stream`,
@@ -196,7 +196,7 @@ DE_API int de_grid4d_backward_sorted(const de_level_desc* levels_host, int n_lev
  * several host threads -- race; order them on one stream or with events.  perm: as for de_grid4d_sort_points (the order of
  * points inside one cell is unspecified in both).
  */
-DE_API size_t de_grid4d_sort_points_noalloc_max_buckets(void);
+#define DE_SORT_NOALLOC_MAX_BUCKETS 65536
 DE_API int de_grid4d_sort_points_noalloc(const float* coords, int64_t n_points, int coord_stride, const uint8_t* dims_host, int n_dims,
                                   int bits, int32_t* perm, void* stream);
 

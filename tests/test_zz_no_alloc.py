@@ -53,7 +53,7 @@ def _sort_both(lib, coords, dims, bits):
 def test_sort_points_noalloc_matches_sort_points_twice_in_a_row(dev):
     from deepearth_b200 import _lib
     lib = _lib.load()
-    assert int(lib.de_grid4d_sort_points_noalloc_max_buckets()) == 1 << 16
+    assert _lib.DE_SORT_NOALLOC_MAX_BUCKETS == 1 << 16
     # warm-up / set-up call: n_points = 0 looks the scratch address up for this device and launches nothing
     with torch.cuda.device(dev):
         d0 = (ctypes.c_uint8 * 1)(0)
