@@ -30,7 +30,7 @@ template <int K1>
 __global__ void __launch_bounds__(kMlpThreads)
 mlp_head_kernel(const __grid_constant__ MlpHeadParams P) {
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ float s_vec[4][kH];            // b1, ln gamma, ln beta, b2
+    __shared__ __align__(16) float s_vec[4][kH];   // b1, ln gamma, ln beta, b2
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ uint32_t s_tmem;
 
@@ -214,7 +214,7 @@ template <int K1>
 __global__ void __launch_bounds__(2 * kMlpThreads, 2)
 mlp_head_dual_kernel(const __grid_constant__ MlpHeadParams P) {
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ float s_vec[4][kH];            // b1, ln gamma, ln beta, b2
+    __shared__ __align__(16) float s_vec[4][kH];   // b1, ln gamma, ln beta, b2
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ uint32_t s_tmem;
 
@@ -309,35 +309,66 @@ mlp_head_dual_kernel(const __grid_constant__ MlpHeadParams P) {
         tc_fence_after();
 
         // ---- 3. epilogue 1: bias + LayerNorm + activation; the bf16 hidden row overwrites the consumed A1 tile
+        //         (packed fp32 pairs, mlp_common.cuh: half the fp32-pipe instructions and half the shared-memory reads of the
+        //         per-column constants; sums in the scalar version's order)
         {
-            float h[kH];
+            f32x2 h[kH / 2];
+            const f32x2* vb1 = reinterpret_cast<const f32x2*>(s_vec[0]);
+            const f32x2* vga = reinterpret_cast<const f32x2*>(s_vec[1]);
+            const f32x2* vbe = reinterpret_cast<const f32x2*>(s_vec[2]);
             {
                 float lo[32];
                 tmem_ld32(tmem_row, lo);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) h[j] = lo[j] + s_vec[0][j];
+                for (int j = 0; j < 16; ++j) h[j] = add2(pk2(lo[2 * j], lo[2 * j + 1]), vb1[j]);
                 tmem_ld32(tmem_row + 32, lo);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) h[32 + j] = lo[j] + s_vec[0][32 + j];
+                for (int j = 0; j < 16; ++j) h[16 + j] = add2(pk2(lo[2 * j], lo[2 * j + 1]), vb1[16 + j]);
             }
             if (P.layernorm) {
-                const float mean = sum64(h) * (1.0f / kH);
-                const float rstd = rsqrtf(sumsq_centered64(h, mean) * (1.0f / kH) + P.ln_eps);
+                f32x2 sa = 0ull, sb = 0ull;                             // the four chains of sum64
 #pragma unroll
-                for (int j = 0; j < kH; ++j) h[j] = fmaf((h[j] - mean) * rstd, s_vec[1][j], s_vec[2][j]);
+                for (int j = 0; j < kH / 2; j += 2) { sa = add2(sa, h[j]); sb = add2(sb, h[j + 1]); }
+                float a0, a1, a2, a3;
+                upk2(sa, a0, a1);
+                upk2(sb, a2, a3);
+                const float mean = ((a0 + a1) + (a2 + a3)) * (1.0f / kH);
+                const f32x2 nmean = splat2(-mean);
+                sa = sb = 0ull;
+#pragma unroll
+                for (int j = 0; j < kH / 2; j += 2) {
+                    h[j] = add2(h[j], nmean);
+                    h[j + 1] = add2(h[j + 1], nmean);
+                    sa = fma2(h[j], h[j], sa);
+                    sb = fma2(h[j + 1], h[j + 1], sb);
+                }
+                upk2(sa, a0, a1);
+                upk2(sb, a2, a3);
+                const f32x2 r2 = splat2(rsqrtf(((a0 + a1) + (a2 + a3)) * (1.0f / kH) + P.ln_eps));
+#pragma unroll
+                for (int j = 0; j < kH / 2; ++j) h[j] = fma2(mul2(h[j], r2), vga[j], vbe[j]);
             }
             if (P.activation == 1) {
 #pragma unroll
-                for (int j = 0; j < kH; ++j) h[j] = fmaxf(h[j], 0.0f);
+                for (int j = 0; j < kH / 2; ++j) {
+                    float z0, z1;
+                    upk2(h[j], z0, z1);
+                    h[j] = pk2(fmaxf(z0, 0.0f), fmaxf(z1, 0.0f));
+                }
             } else if (P.activation == 2) {
 #pragma unroll
-                for (int j = 0; j < kH; ++j) h[j] = gelu_fwd(h[j]);   // nn.GELU() (erf form)
+                for (int j = 0; j < kH / 2; ++j) h[j] = gelu_fwd2(h[j]);   // nn.GELU() (erf form)
             }
 #pragma unroll
             for (int k8 = 0; k8 < kH / 8; ++k8) {
-                const uint4 v = make_uint4(pack_bf16(h[8 * k8], h[8 * k8 + 1]), pack_bf16(h[8 * k8 + 2], h[8 * k8 + 3]),
-                                           pack_bf16(h[8 * k8 + 4], h[8 * k8 + 5]), pack_bf16(h[8 * k8 + 6], h[8 * k8 + 7]));
-                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(row, k8, kH)) = v;
+                uint32_t q[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    float d0, d1;
+                    upk2(h[4 * k8 + u], d0, d1);
+                    q[u] = pack_bf16(d0, d1);
+                }
+                *reinterpret_cast<uint4*>(sA + canon_chunk_offset(row, k8, kH)) = make_uint4(q[0], q[1], q[2], q[3]);
             }
         }
         fence_async_smem();
