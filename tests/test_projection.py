@@ -249,3 +249,19 @@ def test_projection_repeats_bit_for_bit_in_fresh_processes():
                            timeout=600)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         assert "mismatches=0" in r.stdout
+
+
+def test_single_cta_gemm_path_still_matches(dev):
+    """DE_GEMM_PAIR=0 (read once per process) selects the single-CTA form of the GEMM kernel (M = 128 tiles, 4-stage ring) that
+    the CTA-pair default replaced; it stays in the library as the A/B arm and the fallback, so its parity is kept green: the
+    GEMM and projection-backward tests of this file again, in a child process with the switch set."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, DE_GEMM_PAIR="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-k",
+                        "gemm_bf16 or backward_vs_autograd", "-p", "no:cacheprovider"],
+                       capture_output=True, text=True, timeout=900, env=env,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout and "failed" not in r.stdout
