@@ -117,6 +117,14 @@ SIGNATURES = {
     "de_st_embedding_backward": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i64, c_void_p, c_int, c_void_p, c_void_p,
                                          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                          c_void_p, c_void_p]),
+    "de_st_embedding_tc_supported": (c_int, [c_int]),
+    "de_st_embedding_tc_workspace_bytes": (ctypes.c_size_t, [c_i64, c_int, c_int]),
+    "de_st_embedding_forward_tc": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_int,
+                                           c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                           ctypes.c_size_t, c_void_p]),
+    "de_st_embedding_backward_tc": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i64, c_void_p, c_int, c_void_p, c_void_p,
+                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                            c_void_p, ctypes.c_size_t, c_void_p]),
     "de_sum_f32": (c_int, [c_void_p, c_i64, c_void_p, c_void_p]),
     "de_probe_gather": (c_int, [c_void_p, c_i64, c_int, c_int, c_i64, c_int, c_int, c_void_p, c_void_p]),
 }

@@ -28,7 +28,7 @@ EXTRA = {
     "geo2xyz.cu": ["-fmad=false"],   # one IEEE rounding per fp64 op, reference order
     "grid4d_field_kernels.cu": ["-fmad=false"],   # same prologue arithmetic, generated in place
 }
-SOURCES = ["c_abi.cu", "grid4d_kernels.cu", "grid4d_pair_kernels.cu", "grid4d_staged_kernels.cu", "grid4d_smem_kernels.cu", "geo2xyz.cu", "misc.cu", "mlp_head.cu", "mlp_head_bwd2.cu", "st_embed.cu", "grid4d_field_kernels.cu", "grid4d_small1d_kernels.cu", "proj_kernels.cu", "proj_bwd_kernels.cu", "grid4d_sorted_kernels.cu"]
+SOURCES = ["c_abi.cu", "grid4d_kernels.cu", "grid4d_pair_kernels.cu", "grid4d_staged_kernels.cu", "grid4d_smem_kernels.cu", "geo2xyz.cu", "misc.cu", "mlp_head.cu", "mlp_head_bwd2.cu", "st_embed.cu", "st_embed_tc.cu", "grid4d_field_kernels.cu", "grid4d_small1d_kernels.cu", "proj_kernels.cu", "proj_bwd_kernels.cu", "grid4d_sorted_kernels.cu"]
 
 
 def _nvcc() -> str:

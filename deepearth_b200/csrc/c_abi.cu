@@ -1068,6 +1068,64 @@ static int device_sms() {
     return n_sms;
 }
 
+DE_API int de_st_embedding_tc_supported(int dim) { return de::st_embed_tc_supported(dim) ? 1 : 0; }
+
+DE_API size_t de_st_embedding_tc_workspace_bytes(int64_t n_tokens, int dim, int backward) {
+    return de::st_embed_tc_workspace_bytes(n_tokens, dim, backward != 0);
+}
+
+DE_API int de_st_embedding_forward_tc(const float* tokens, int64_t n_tokens, int dim, const float* pos, int64_t pos_stride,
+                               const float* t, const float* embed_x, const float* embed_y, int resolution,
+                               const float* t_w1, const float* t_b1, const float* t_w2, const float* t_b2,
+                               const float* modality, float* out, int* error_flag, void* workspace, size_t workspace_bytes,
+                               void* stream) {
+    if (n_tokens < 0) return fail(DE_EINVAL, "n_tokens < 0");
+    if (n_tokens == 0) return DE_OK;
+    if (!tokens || !out) return fail(DE_EINVAL, "st_embedding_tc: tokens / out is NULL");
+    if (!de::st_embed_tc_supported(dim)) return fail(DE_EUNSUPPORTED, "st_embedding_tc: dim=%d must be a multiple of 128", dim);
+    if (pos && (!embed_x || !embed_y || resolution < 1)) return fail(DE_EINVAL, "st_embedding_tc: spatial positions without tables");
+    if (pos && pos_stride < 2) return fail(DE_EINVAL, "st_embedding_tc: pos_stride=%lld < 2", (long long)pos_stride);
+    if (t && (!t_w1 || !t_b1 || !t_w2 || !t_b2)) return fail(DE_EINVAL, "st_embedding_tc: temporal positions without MLP parameters");
+    if (t && (!workspace || workspace_bytes < de::st_embed_tc_workspace_bytes(n_tokens, dim, false)))
+        return fail(DE_EINVAL, "st_embedding_tc: workspace of %zu bytes, %zu needed", workspace_bytes, de::st_embed_tc_workspace_bytes(n_tokens, dim, false));
+    if (t && (reinterpret_cast<uintptr_t>(workspace) % 256 || reinterpret_cast<uintptr_t>(tokens) % 16 || reinterpret_cast<uintptr_t>(out) % 16))
+        return fail(DE_EALIGN, "st_embedding_tc: workspace must be 256-byte, tokens / out 16-byte aligned");
+    if (n_tokens > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "st_embedding_tc: n_tokens too large");
+    de::StEmbedParams P{};
+    P.tokens = tokens; P.pos = pos; P.t = t; P.ex = embed_x; P.ey = embed_y; P.w1 = t_w1; P.b1 = t_b1; P.w2 = t_w2; P.b2 = t_b2;
+    P.mod = modality; P.out = out; P.err = error_flag; P.n = n_tokens; P.pos_stride = pos_stride; P.D = dim; P.R = resolution;
+    cudaError_t e = de::launch_st_embed_forward_tc(P, workspace, device_sms(), static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "st_embedding_tc forward launch");
+}
+
+DE_API int de_st_embedding_backward_tc(const float* grad_out, int64_t n_tokens, int dim, const float* pos, int64_t pos_stride,
+                                const float* t, int resolution, const float* t_w1, const float* t_b1, const float* t_w2,
+                                float* grad_embed_x, float* grad_embed_y, float* grad_t_w1, float* grad_t_b1,
+                                float* grad_t_w2, float* grad_t_b2, float* grad_modality, void* workspace, size_t workspace_bytes,
+                                void* stream) {
+    if (n_tokens < 0) return fail(DE_EINVAL, "n_tokens < 0");
+    if (n_tokens == 0) return DE_OK;
+    if (!grad_out) return fail(DE_EINVAL, "st_embedding_backward_tc: grad_out is NULL");
+    if (!de::st_embed_tc_supported(dim)) return fail(DE_EUNSUPPORTED, "st_embedding_backward_tc: dim=%d must be a multiple of 128", dim);
+    if (pos && pos_stride < 2) return fail(DE_EINVAL, "st_embedding_backward_tc: pos_stride=%lld < 2", (long long)pos_stride);
+    if (pos && resolution < 1) return fail(DE_EINVAL, "st_embedding_backward_tc: resolution=%d", resolution);
+    if (pos && static_cast<size_t>(resolution) * 32 * sizeof(float) > 48 * 1024)
+        return fail(DE_EUNSUPPORTED, "st_embedding_backward_tc: resolution=%d > 384 table rows", resolution);
+    if (t && (!t_w1 || !t_b1 || !t_w2 || !grad_t_w1 || !grad_t_b1 || !grad_t_w2))
+        return fail(DE_EINVAL, "st_embedding_backward_tc: temporal branch needs w1, b1, w2 and the three weight gradients");
+    if (t && (!workspace || workspace_bytes < de::st_embed_tc_workspace_bytes(n_tokens, dim, true)))
+        return fail(DE_EINVAL, "st_embedding_backward_tc: workspace of %zu bytes, %zu needed", workspace_bytes, de::st_embed_tc_workspace_bytes(n_tokens, dim, true));
+    if (t && (reinterpret_cast<uintptr_t>(workspace) % 256 || reinterpret_cast<uintptr_t>(grad_t_w2) % 16))
+        return fail(DE_EALIGN, "st_embedding_backward_tc: workspace must be 256-byte, grad_t_w2 16-byte aligned");
+    if (n_tokens > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "st_embedding_backward_tc: n_tokens too large");
+    de::StEmbedBwdParams P{};
+    P.g = grad_out; P.pos = pos; P.t = t; P.w1 = t_w1; P.b1 = t_b1; P.w2 = t_w2; P.dpre = nullptr;
+    P.d_ex = grad_embed_x; P.d_ey = grad_embed_y; P.d_w1 = grad_t_w1; P.d_b1 = grad_t_b1; P.d_w2 = grad_t_w2; P.d_b2 = grad_t_b2;
+    P.d_mod = grad_modality; P.n = n_tokens; P.pos_stride = pos_stride; P.D = dim; P.R = resolution;
+    cudaError_t e = de::launch_st_embed_backward_tc(P, workspace, device_sms(), static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? DE_OK : cuda_fail(e, "st_embedding_tc backward launch");
+}
+
 DE_API int de_gemm_bf16(const void* a_bf16, int64_t lda, const void* b_bf16, int64_t ldb, int64_t m, int n, int64_t k,
                  const float* bias, void* c, int64_t ldc, int out_dtype, int transposed, int accumulate, void* stream) {
     if (m < 0 || n < 1 || k < 1) return fail(DE_EINVAL, "gemm_bf16: m=%lld n=%d k=%lld", (long long)m, n, (long long)k);

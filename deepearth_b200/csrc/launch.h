@@ -146,6 +146,17 @@ struct GemmParams {
     int bias_vec;                 // filled by the launcher: bias is 16-byte aligned
     int tma_store;                // filled by the launcher: fp32 C leaves through shared memory and TMA tensor stores
     int full_n;                   // filled by the launcher: DE_GEMM_FULL_N=1 keeps every MMA 256 columns wide (A/B switch)
+    // optional: C = acc + bias + residual (fp32 store only; rows ldr floats apart)
+    const float* residual;
+    long long ldr;
+    // optional operand segments (split-precision products, st_embed_tc): the contraction runs over `n_seg` segments of
+    // seg_blocks 64-element k-blocks each (K = n_seg * seg_blocks * 64); segment s multiplies operand part seg_a[s] of A
+    // with part seg_b[s] of B.  Parts lie side by side in the operands' COLUMNS, seg_stride_a / _b elements apart: along K
+    // for K-major operands (transposed = 0), along M / N for row-contracted ones (transposed = 1).  0 segments = off.
+    int n_seg, seg_blocks;
+    long long seg_stride_a, seg_stride_b;
+    unsigned char seg_a[8], seg_b[8];
+    long long a_rows, a_cols, b_rows, b_cols;     // true extents of the operand matrices when segments are used (tensor maps)
 };
 struct ProjDpreParams {
     const float* x;               // (n, in_dim) fp32 features (forward input)
@@ -235,6 +246,13 @@ struct StEmbedBwdParams {
 };
 cudaError_t launch_st_embed_forward(const StEmbedParams& P, cudaStream_t s);
 cudaError_t launch_st_embed_backward(const StEmbedBwdParams& P, cudaStream_t s);
+cudaError_t launch_st_embed_spatial(const StEmbedParams& P, int c_end, cudaStream_t s);
+cudaError_t launch_st_embed_backward_common(const StEmbedBwdParams& P, cudaStream_t s);
+// temporal MLP on the tensor cores (st_embed_tc.cu): dim / 2 a multiple of 64
+bool st_embed_tc_supported(int D);
+size_t st_embed_tc_workspace_bytes(long long n, int D, bool backward);
+cudaError_t launch_st_embed_forward_tc(const StEmbedParams& P, void* ws, int n_sms, cudaStream_t s);
+cudaError_t launch_st_embed_backward_tc(const StEmbedBwdParams& P, void* ws, int n_sms, cudaStream_t s);
 
 cudaError_t launch_geo2xyzt(const void* geo, bool geo_f64, const void* t, bool t_f64, const double* bbox_min,
                             const double* bbox_span, const double* t_range, float* xyzt, double* ecef,

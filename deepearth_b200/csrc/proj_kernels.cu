@@ -384,37 +384,46 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 mbar_wait(&s_empty[stage], phase ^ 1u);
                 unsigned char* sa = smem + stage * kGemmStageBytes;
                 unsigned char* sb = sa + kGemmBM * kGemmBK * 2;
+                // coordinates of this k-block in the operands (operand segments: see GemmParams)
+                int ka = kb * kGemmBK, kbb = kb * kGemmBK, am0 = m0, bn0 = n0;
+                if (P.n_seg) {
+                    const int sg = kb / P.seg_blocks, within = (kb - sg * P.seg_blocks) * kGemmBK;
+                    if constexpr (A_MN) { ka = within; am0 = m0 + static_cast<int>(P.seg_a[sg] * P.seg_stride_a); }
+                    else ka = static_cast<int>(P.seg_a[sg] * P.seg_stride_a) + within;
+                    if constexpr (B_MN) { kbb = within; bn0 = n0 + static_cast<int>(P.seg_b[sg] * P.seg_stride_b); }
+                    else kbb = static_cast<int>(P.seg_b[sg] * P.seg_stride_b) + within;
+                }
                 if constexpr (MC == 2) {
                     // both CTAs' boxes report to the LEADER's full barrier, which the leader arms for the pair's bytes
                     if (rank == 0) mbar_expect_tx(&s_full[stage], 2 * kGemmStageBytes);
                     const uint32_t full = mapa_u32(smem_u32(&s_full[stage]), 0);
                     // this CTA's half of the B tile: the MMA reads the first n_eff / 2 rows of each CTA's B buffer
-                    const int nb = n0 + static_cast<int>(rank) * (gemm_n_eff<MC>(P.full_n ? kGemmBN : P.N - n0) / 2);
+                    const int nb = bn0 + static_cast<int>(rank) * (gemm_n_eff<MC>(P.full_n ? kGemmBN : P.N - n0) / 2);
                     if constexpr (A_MN) {
 #pragma unroll
-                        for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d_pair(sa + i * 8192, &map_a, m0 + 64 * i, kb * kGemmBK, full);
+                        for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d_pair(sa + i * 8192, &map_a, am0 + 64 * i, ka, full);
                     } else {
-                        tma_load_2d_pair(sa, &map_a, kb * kGemmBK, m0, full);
+                        tma_load_2d_pair(sa, &map_a, ka, m0, full);
                     }
                     if constexpr (B_MN) {
 #pragma unroll
-                        for (int i = 0; i < kGemmBN / 128; ++i) tma_load_2d_pair(sb + i * 8192, &map_b, nb + 64 * i, kb * kGemmBK, full);
+                        for (int i = 0; i < kGemmBN / 128; ++i) tma_load_2d_pair(sb + i * 8192, &map_b, nb + 64 * i, kbb, full);
                     } else {
-                        tma_load_2d_pair(sb, &map_b, kb * kGemmBK, nb, full);
+                        tma_load_2d_pair(sb, &map_b, kbb, nb, full);
                     }
                 } else {
                     mbar_expect_tx(&s_full[stage], kGemmStageBytes);
                     if constexpr (A_MN) {
 #pragma unroll
-                        for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d(sa + i * 8192, &map_a, m0 + 64 * i, kb * kGemmBK, &s_full[stage]);
+                        for (int i = 0; i < kGemmBM / 64; ++i) tma_load_2d(sa + i * 8192, &map_a, am0 + 64 * i, ka, &s_full[stage]);
                     } else {
-                        tma_load_2d(sa, &map_a, kb * kGemmBK, m0, &s_full[stage]);
+                        tma_load_2d(sa, &map_a, ka, m0, &s_full[stage]);
                     }
                     if constexpr (B_MN) {
 #pragma unroll
-                        for (int i = 0; i < kGemmBN / 64; ++i) tma_load_2d(sb + i * 8192, &map_b, n0 + 64 * i, kb * kGemmBK, &s_full[stage]);
+                        for (int i = 0; i < kGemmBN / 64; ++i) tma_load_2d(sb + i * 8192, &map_b, bn0 + 64 * i, kbb, &s_full[stage]);
                     } else {
-                        tma_load_2d(sb, &map_b, kb * kGemmBK, n0, &s_full[stage]);
+                        tma_load_2d(sb, &map_b, kbb, n0, &s_full[stage]);
                     }
                 }
                 if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
@@ -495,6 +504,19 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldg(P.bias + col0 + j) : 0.0f;
+                    }
+                }
+                if (EPI == 0 && P.residual && r < P.M) {
+                    const float* rp = P.residual + r * P.ldr + col0;
+                    if (col0 + 32 <= P.N && ((reinterpret_cast<uintptr_t>(rp) & 15) == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 q4 = __ldcs(reinterpret_cast<const float4*>(rp) + j);
+                            v[4 * j] += q4.x; v[4 * j + 1] += q4.y; v[4 * j + 2] += q4.z; v[4 * j + 3] += q4.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldcs(rp + j) : 0.0f;
                     }
                 }
                 if (EPI == 0 && P.tma_store) {
@@ -723,8 +745,12 @@ cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long l
     const int mc = (gemm_pair() && tiles_m >= 2) ? 2 : 1;
     CUtensorMap map_a, map_b;
     bool ok;
-    if (transposed) ok = make_map_bf16(&map_a, a, P.K, P.M, lda, 64) && make_map_bf16(&map_b, b, P.K, P.N, ldb, 64);
-    else ok = make_map_bf16(&map_a, a, P.M, P.K, lda, kGemmBM) && make_map_bf16(&map_b, b, P.N, P.K, ldb, kGemmBN / mc);
+    // (rows, cols) of the operand matrices as stored; with operand segments the caller states them (K is the segmented total)
+    const long long ar = P.n_seg ? P.a_rows : (transposed ? P.K : P.M), ac = P.n_seg ? P.a_cols : (transposed ? P.M : P.K);
+    const long long br = P.n_seg ? P.b_rows : (transposed ? P.K : static_cast<long long>(P.N));
+    const long long bc = P.n_seg ? P.b_cols : (transposed ? static_cast<long long>(P.N) : P.K);
+    if (transposed) ok = make_map_bf16(&map_a, a, ar, ac, lda, 64) && make_map_bf16(&map_b, b, br, bc, ldb, 64);
+    else ok = make_map_bf16(&map_a, a, ar, ac, lda, kGemmBM) && make_map_bf16(&map_b, b, br, bc, ldb, kGemmBN / mc);
     if (!ok) return cudaErrorInvalidValue;
     const long long units = ((tiles_m + mc - 1) / mc) * tiles_n;           // scheduling units: tiles or vertical tile pairs
     const long long max_units = n_sms / mc;
@@ -753,7 +779,7 @@ cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long l
     static const int tma_store = []() { const char* e = getenv("DE_GEMM_TMA_STORE"); return (e && *e) ? (atoi(e) != 0) : 1; }();
     CUtensorMap map_c = map_a;                             // placeholder when unused
     P.tma_store = 0;
-    if (epi == 0 && tma_store && reinterpret_cast<uintptr_t>(P.c) % 16 == 0 && (P.ldc * 4) % 16 == 0 &&
+    if (epi == 0 && tma_store && !P.residual && reinterpret_cast<uintptr_t>(P.c) % 16 == 0 && (P.ldc * 4) % 16 == 0 &&
         make_map_f32_store(&map_c, P.c, P.M, P.N, P.ldc))
         P.tma_store = 1;
     if (mc == 2)

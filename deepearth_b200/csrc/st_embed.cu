@@ -19,6 +19,7 @@
 #include <stdint.h>
 
 #include "launch.h"
+#include "st_embed_common.cuh"
 
 namespace de {
 
@@ -27,12 +28,6 @@ namespace {
 constexpr int kTile = 64;   // tokens x outputs per CTA
 constexpr int kTk = 16;     // contraction chunk
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
-__device__ __forceinline__ float gelu_erf_grad(float x) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
-    const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
-    return cdf + x * pdf;
-}
 
 // (pos * R).long() with PyTorch's negative-index wrap; -1 = outside [-R, R) or not finite
 __device__ __forceinline__ int table_row(float p, int R) {
@@ -238,14 +233,19 @@ long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
 
 }  // namespace
 
-cudaError_t launch_st_embed_forward(const StEmbedParams& P, cudaStream_t s) {
-    const int Dh = P.D / 2;
-    const int c_end = P.t ? Dh : P.D;                 // columns the streaming kernel owns
+// the streaming kernel alone over columns [0, c_end) (st_embed_tc.cu runs the temporal half on the tensor cores)
+cudaError_t launch_st_embed_spatial(const StEmbedParams& P, int c_end, cudaStream_t s) {
     long long blocks = ceil_div(P.n * c_end, 256 * 4);
     if (blocks > 148 * 16) blocks = 148 * 16;
     if (blocks < 1) blocks = 1;
     st_embed_spatial_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(P, c_end);
-    cudaError_t e = cudaGetLastError();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_st_embed_forward(const StEmbedParams& P, cudaStream_t s) {
+    const int Dh = P.D / 2;
+    const int c_end = P.t ? Dh : P.D;                 // columns the streaming kernel owns
+    cudaError_t e = launch_st_embed_spatial(P, c_end, s);
     if (e != cudaSuccess || !P.t) return e;
     dim3 grid(static_cast<unsigned>(ceil_div(P.n, kTile)), static_cast<unsigned>(ceil_div(Dh, kTile)), 1);
     st_tile_gemm_kernel<<<grid, 256, 0, s>>>(P.n, Dh, static_cast<long long>(Dh), static_cast<long long>(Dh),
@@ -254,7 +254,8 @@ cudaError_t launch_st_embed_forward(const StEmbedParams& P, cudaStream_t s) {
     return cudaGetLastError();
 }
 
-cudaError_t launch_st_embed_backward(const StEmbedBwdParams& P, cudaStream_t s) {
+// everything but the temporal MLP: d(modality), d(spatial tables), d(b2)
+cudaError_t launch_st_embed_backward_common(const StEmbedBwdParams& P, cudaStream_t s) {
     const int Dh = P.D / 2, Dq = P.D / 4;
     cudaError_t e = cudaSuccess;
     if (P.d_mod) {          // d(modality)[c] = sum_m g[m, c]
@@ -270,13 +271,21 @@ cudaError_t launch_st_embed_backward(const StEmbedBwdParams& P, cudaStream_t s) 
             P.g, P.pos, P.pos_stride, P.n, P.D, P.R, P.d_ex, P.d_ey, rows);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
+    if (P.t && P.d_b2) {    // d(b2)[j] = sum_m g[m, D/2 + j]
+        const long long rows = 4096;
+        dim3 grid(static_cast<unsigned>(ceil_div(Dh, 32)), static_cast<unsigned>(ceil_div(P.n, rows)));
+        st_colsum_kernel<<<grid, 256, 0, s>>>(P.g, P.n, Dh, P.D, Dh, nullptr, nullptr, P.d_b2, rows);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_st_embed_backward(const StEmbedBwdParams& P, cudaStream_t s) {
+    const int Dh = P.D / 2;
+    cudaError_t e = launch_st_embed_backward_common(P, s);
+    if (e != cudaSuccess) return e;
     if (P.t) {
         const long long rows = 4096;
-        if (P.d_b2) {       // d(b2)[j] = sum_m g[m, D/2 + j]
-            dim3 grid(static_cast<unsigned>(ceil_div(Dh, 32)), static_cast<unsigned>(ceil_div(P.n, rows)));
-            st_colsum_kernel<<<grid, 256, 0, s>>>(P.g, P.n, Dh, P.D, Dh, nullptr, nullptr, P.d_b2, rows);
-            if ((e = cudaGetLastError()) != cudaSuccess) return e;
-        }
         {                   // dpre = (g_t . W2) * GELU'(pre)
             dim3 grid(static_cast<unsigned>(ceil_div(P.n, kTile)), static_cast<unsigned>(ceil_div(Dh, kTile)), 1);
             st_tile_gemm_kernel<<<grid, 256, 0, s>>>(P.n, Dh, static_cast<long long>(Dh), static_cast<long long>(Dh),

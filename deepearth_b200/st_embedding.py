@@ -32,7 +32,7 @@ def _rows(x: torch.Tensor, n: int, min_cols: int, name: str) -> torch.Tensor:
 
 class _StEmbedFunction(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, tokens, pos, t, ex, ey, w1, b1, w2, b2, mod, check):
+    def forward(ctx, tokens, pos, t, ex, ey, w1, b1, w2, b2, mod, check, use_tc=True):
         D = tokens.shape[-1]
         tok2 = tokens.reshape(-1, D)
         if not tok2.is_contiguous():
@@ -44,19 +44,28 @@ class _StEmbedFunction(torch.autograd.Function):
         R = ex.shape[1]
         err = torch.zeros(1, dtype=torch.int32, device=tokens.device) if pos is not None else None
         w1v = w1.reshape(-1).contiguous()
+        lib = _lib.load() if n else None
+        # temporal MLP on the tensor cores (split-bf16 products, fp32 accuracy) when the width allows it
+        tc = bool(n) and use_tc and t1 is not None and bool(lib.de_st_embedding_tc_supported(D))
         if n:
-            with torch.cuda.device(tokens.device):
-                rc = _lib.load().de_st_embedding_forward(
-                    _ptr(tok2), n, D, _ptr(pos2), pos2.stride(0) if pos2 is not None and n > 1 else (pos2.shape[1] if pos2 is not None else 0),
+            args = (_ptr(tok2), n, D, _ptr(pos2), pos2.stride(0) if pos2 is not None and n > 1 else (pos2.shape[1] if pos2 is not None else 0),
                     _ptr(t1), _ptr(ex.contiguous()), _ptr(ey.contiguous()), R, _ptr(w1v), _ptr(b1.contiguous()),
                     _ptr(w2.contiguous()), _ptr(b2.contiguous()), _ptr(mod.reshape(-1).contiguous() if mod is not None else None),
-                    _ptr(out), _ptr(err), _stream_ptr(tokens.device))
-            _lib.check(rc, "de_st_embedding_forward")
+                    _ptr(out), _ptr(err))
+            with torch.cuda.device(tokens.device):
+                if tc:
+                    ws_bytes = int(lib.de_st_embedding_tc_workspace_bytes(n, D, 0))
+                    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=tokens.device)
+                    rc = lib.de_st_embedding_forward_tc(*args, _ptr(ws), ws_bytes, _stream_ptr(tokens.device))
+                else:
+                    rc = lib.de_st_embedding_forward(*args, _stream_ptr(tokens.device))
+            _lib.check(rc, "de_st_embedding_forward_tc" if tc else "de_st_embedding_forward")
             if check and err is not None and int(err.item()):
                 raise IndexError(f"SpatialTemporalEmbedding: a spatial index (position * {R}).long() is out of range for "
                                  f"{R} table rows (models/cross_modal_fusion.py:145-149 raises here too)")
         ctx.save_for_backward(pos2, t1, w1v, b1, w2)
         ctx.meta = (tuple(tokens.shape), R, ex.shape, w1.shape, mod.shape if mod is not None else None)
+        ctx.use_tc = use_tc
         return out.view(tokens.shape)
 
     @staticmethod
@@ -79,27 +88,38 @@ class _StEmbedFunction(torch.autograd.Function):
         d_w2 = z(D // 2, D // 2) if temporal else None
         d_b2 = z(D // 2) if temporal else None
         d_mod = z(*mod_shape) if mod_shape is not None and need[9] else None
-        scratch = torch.empty((n, D // 2), dtype=torch.float32, device=dev) if temporal else None
         if n:
-            with torch.cuda.device(dev):
-                rc = _lib.load().de_st_embedding_backward(
-                    _ptr(g2), n, D, _ptr(pos2 if d_ex is not None else None),
+            lib = _lib.load()
+            tc = temporal and ctx.use_tc and bool(lib.de_st_embedding_tc_supported(D))
+            args = (_ptr(g2), n, D, _ptr(pos2 if d_ex is not None else None),
                     (pos2.stride(0) if n > 1 else pos2.shape[1]) if pos2 is not None else 0,
-                    _ptr(t1 if temporal else None), R, _ptr(w1v), _ptr(b1), _ptr(w2), _ptr(d_ex), _ptr(d_ey), _ptr(d_w1),
-                    _ptr(d_b1), _ptr(d_w2), _ptr(d_b2), _ptr(d_mod), _ptr(scratch), _stream_ptr(dev))
-            _lib.check(rc, "de_st_embedding_backward")
-        return (g if need[0] else None, None, None, d_ex, d_ey, d_w1, d_b1, d_w2, d_b2, d_mod, None)
+                    _ptr(t1 if temporal else None), R, _ptr(w1v), _ptr(b1), _ptr(w2.contiguous()), _ptr(d_ex), _ptr(d_ey), _ptr(d_w1),
+                    _ptr(d_b1), _ptr(d_w2), _ptr(d_b2), _ptr(d_mod))
+            with torch.cuda.device(dev):
+                if tc:
+                    ws_bytes = int(lib.de_st_embedding_tc_workspace_bytes(n, D, 1))
+                    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+                    rc = lib.de_st_embedding_backward_tc(*args, _ptr(ws), ws_bytes, _stream_ptr(dev))
+                else:
+                    scratch = torch.empty((n, D // 2), dtype=torch.float32, device=dev) if temporal else None
+                    rc = lib.de_st_embedding_backward(*args, _ptr(scratch), _stream_ptr(dev))
+            _lib.check(rc, "de_st_embedding_backward_tc" if tc else "de_st_embedding_backward")
+        return (g if need[0] else None, None, None, d_ex, d_ey, d_w1, d_b1, d_w2, d_b2, d_mod, None, None)
 
 
 class SpatialTemporalEmbedding(nn.Module):
     """Learnable spatial-temporal(-modal) embeddings added to universal tokens (cross_modal_fusion.py:99-165)."""
 
-    def __init__(self, universal_dim: int, max_spatial_resolution: int = 64, check_indices: bool = True):
+    def __init__(self, universal_dim: int, max_spatial_resolution: int = 64, check_indices: bool = True,
+                 tensor_core_mlp: bool = True):
         super().__init__()
         if universal_dim % 4:
             raise ValueError(f"universal_dim={universal_dim} must be a multiple of 4")
         self.universal_dim = universal_dim
         self.check_indices = bool(check_indices)   # True: raise IndexError like the reference (one device->host read)
+        # True: the temporal MLP's second Linear runs on the tensor cores as a split-bf16 product at fp32 accuracy
+        # (csrc/st_embed_tc.cu; universal_dim % 128 == 0), False: the fp32 SIMT tile GEMM of csrc/st_embed.cu
+        self.tensor_core_mlp = bool(tensor_core_mlp)
         # construction order = the reference's, so a shared seed gives identical parameters (:107-123)
         self.spatial_embed_x = nn.Parameter(torch.randn(1, max_spatial_resolution, universal_dim // 4) * 0.02)
         self.spatial_embed_y = nn.Parameter(torch.randn(1, max_spatial_resolution, universal_dim // 4) * 0.02)
@@ -131,4 +151,4 @@ class SpatialTemporalEmbedding(nn.Module):
         lin1, lin2 = self.temporal_embed[0], self.temporal_embed[2]
         return _StEmbedFunction.apply(tokens, spatial_positions, temporal_positions, self.spatial_embed_x,
                                       self.spatial_embed_y, lin1.weight, lin1.bias, lin2.weight, lin2.bias, mod,
-                                      self.check_indices)
+                                      self.check_indices, self.tensor_core_mlp)

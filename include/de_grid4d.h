@@ -418,6 +418,30 @@ DE_API int de_st_embedding_backward(const float* grad_out, int64_t n_tokens, int
                              float* grad_t_w2, float* grad_t_b2, float* grad_modality,
                              float* scratch, void* stream);
 
+/*
+ * The same two calls with the temporal MLP's second Linear (2 (dim/2)^2 flop per token) on the tensor cores at fp32 accuracy:
+ * every fp32 operand is split into three bf16 parts (8 + 8 + 8 mantissa bits) and the six significant part products are
+ * accumulated in fp32 in tensor memory by ONE TMA + tcgen05 GEMM over six operand segments (csrc/st_embed_tc.cu) -- the
+ * reference runs this layer as an fp32 cuBLAS SGEMM.  dim must be a multiple of 128 (de_st_embedding_tc_supported); results
+ * agree with the fp32 entry points to fp32 rounding (same tolerances in tests/test_st_embed.py).  workspace:
+ * de_st_embedding_tc_workspace_bytes(n_tokens, dim, backward) bytes, 256-byte aligned (split operands of one slab of tokens;
+ * bounded: <= ~1.1 GiB at dim 2048); the backward needs no (n, dim/2) scratch.
+ */
+DE_API int de_st_embedding_tc_supported(int dim);
+DE_API size_t de_st_embedding_tc_workspace_bytes(int64_t n_tokens, int dim, int backward);
+DE_API int de_st_embedding_forward_tc(const float* tokens, int64_t n_tokens, int dim,
+                               const float* pos, int64_t pos_stride, const float* t,
+                               const float* embed_x, const float* embed_y, int resolution,
+                               const float* t_w1, const float* t_b1, const float* t_w2, const float* t_b2,
+                               const float* modality, float* out, int* error_flag,
+                               void* workspace, size_t workspace_bytes, void* stream);
+DE_API int de_st_embedding_backward_tc(const float* grad_out, int64_t n_tokens, int dim,
+                                const float* pos, int64_t pos_stride, const float* t, int resolution,
+                                const float* t_w1, const float* t_b1, const float* t_w2,
+                                float* grad_embed_x, float* grad_embed_y, float* grad_t_w1, float* grad_t_b1,
+                                float* grad_t_w2, float* grad_t_b2, float* grad_modality,
+                                void* workspace, size_t workspace_bytes, void* stream);
+
 /* fp64 sum of an fp32 buffer into *result (device, caller-zeroed): bench/e2e checksum. */
 DE_API int de_sum_f32(const float* x, int64_t n, double* result, void* stream);
 

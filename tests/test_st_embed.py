@@ -149,3 +149,60 @@ def test_cuda_module_large_vs_torch_eager(gold):
     want = tok + emb
     assert torch.equal(out[..., :D // 2], want[..., :D // 2])
     assert float((out - want).abs().max()) <= FWD_TOL * float(want.abs().max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,n,with_mod", [(128, 1000, True), (256, 64 * 7 + 3, False), (512, 70001, True), (2048, 3000, True)])
+def test_tensor_core_mlp_matches_fp32_path_and_fp64(D, n, with_mod):
+    """The temporal MLP on the tensor cores (split-bf16 products, csrc/st_embed_tc.cu; the default when D % 128 == 0) against the
+    fp32 SIMT path (tensor_core_mlp=False) and against an fp64 evaluation: forward and every parameter gradient, ragged token
+    counts (slab tails, k-blocks of the token contraction that are not full), with and without a modality embedding.  Both
+    paths must sit at fp32 rounding distance from fp64 -- the split product is not a reduced-precision mode."""
+    import deepearth_b200 as de
+    dev = torch.device("cuda:0")
+    torch.manual_seed(D + n)
+    m_tc = de.SpatialTemporalEmbedding(D).to(dev)
+    if with_mod:
+        m_tc.add_modality("x")
+    m_32 = de.SpatialTemporalEmbedding(D, tensor_core_mlp=False).to(dev)
+    if with_mod:
+        m_32.add_modality("x")
+    m_32.load_state_dict(m_tc.state_dict())
+    g = torch.Generator(device=dev).manual_seed(n)
+    tok = torch.randn((1, n, D), device=dev, generator=g)
+    pos = torch.rand((1, n, 2), device=dev, generator=g) * 0.999
+    t = torch.rand((1, n, 1), device=dev, generator=g)
+    gout = torch.randn((1, n, D), device=dev, generator=g)
+    name = "x" if with_mod else None
+    outs, grads = [], []
+    for m in (m_tc, m_32):
+        out = m(tok, pos, t, name)
+        out.backward(gout)
+        outs.append(out.detach())
+        grads.append({k: p.grad.clone() for k, p in m.named_parameters()})
+    # fp64 evaluation of the temporal half and its gradients
+    lin1, lin2 = m_tc.temporal_embed[0], m_tc.temporal_embed[2]
+    w1, b1, w2, b2 = (p.detach().double().requires_grad_(True) for p in (lin1.weight, lin1.bias, lin2.weight, lin2.bias))
+    h = torch.nn.functional.gelu(t.double() @ w1.t() + b1)
+    emb_t = h @ w2.t() + b2
+    if with_mod:
+        emb_t = emb_t + m_tc.modality_embeds["x"].detach().double().reshape(-1)[D // 2:]
+    want_t = tok.double()[..., D // 2:] + emb_t
+    emb_t.backward(gout.double()[..., D // 2:])
+    ref = {"temporal_embed.0.weight": w1.grad, "temporal_embed.0.bias": b1.grad, "temporal_embed.2.weight": w2.grad,
+           "temporal_embed.2.bias": b2.grad}
+    scale = float(want_t.abs().max())
+    e_tc = float((outs[0][..., D // 2:].double() - want_t).abs().max()) / scale
+    e_32 = float((outs[1][..., D // 2:].double() - want_t).abs().max()) / scale
+    assert torch.equal(outs[0][..., :D // 2], outs[1][..., :D // 2])                    # the gather half is the same kernel
+    assert e_tc <= 1e-6 and e_32 <= 1e-6, (e_tc, e_32)             # B200: tensor-core 5e-8 .. 2.7e-7, SIMT 7e-8 .. 2.9e-7
+    worst = {}
+    for k, r in ref.items():
+        s = float(r.abs().max())
+        worst[k] = (float((grads[0][k].double() - r).abs().max()) / s, float((grads[1][k].double() - r).abs().max()) / s)
+        assert worst[k][0] <= GRAD_TOL and worst[k][1] <= GRAD_TOL, (k, worst[k])
+    for k in grads[0]:
+        if k not in ref:                                                               # tables, modality: shared kernels
+            assert float((grads[0][k] - grads[1][k]).abs().max()) <= 1e-6 * max(float(grads[1][k].abs().max()), 1e-30), k
+    print(f"st_embed D={D} n={n}: forward vs fp64 tensor-core {e_tc:.1e} / SIMT {e_32:.1e}; gradients (tc, simt):",
+          {k.replace('temporal_embed.', ''): (f"{a:.1e}", f"{b:.1e}") for k, (a, b) in worst.items()})
