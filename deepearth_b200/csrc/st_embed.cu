@@ -65,6 +65,38 @@ __global__ void __launch_bounds__(256) st_embed_spatial_kernel(const StEmbedPara
     }
 }
 
+// Same, four columns per thread (16-byte loads and stores): D a multiple of 16 -- a float4 never straddles the x / y / temporal
+// column ranges -- and 16-byte aligned buffers.  The additions per element are the scalar kernel's, in its order.
+__global__ void __launch_bounds__(256) st_embed_spatial_vec4_kernel(const StEmbedParams P, int c_end) {
+    const int Dq = P.D / 4, c4_end = c_end / 4;
+    const long long total = P.n * c4_end;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const long long m = e / c4_end;
+        const int c = static_cast<int>(e - m * c4_end) * 4;
+        float4 emb = make_float4(0.f, 0.f, 0.f, 0.f);
+        bool has = false;
+        if (P.pos && c < 2 * Dq) {
+            const int which = c >= Dq;
+            const int row = table_row(__ldg(P.pos + m * P.pos_stride + which), P.R);
+            if (row < 0) {
+                if (P.err && (c == 0 || c == Dq)) atomicOr(P.err, 1);
+                emb = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F);
+            } else {
+                emb = __ldg(reinterpret_cast<const float4*>((which ? P.ey : P.ex) + static_cast<long long>(row) * Dq + (c - which * Dq)));
+            }
+            has = true;
+        }
+        if (P.mod) {
+            const float4 md = __ldg(reinterpret_cast<const float4*>(P.mod + c));
+            emb = has ? make_float4(__fadd_rn(emb.x, md.x), __fadd_rn(emb.y, md.y), __fadd_rn(emb.z, md.z), __fadd_rn(emb.w, md.w)) : md;
+        }
+        const float4 tok = __ldcs(reinterpret_cast<const float4*>(P.tokens + m * P.D + c));
+        __stcs(reinterpret_cast<float4*>(P.out + m * P.D + c),
+               make_float4(__fadd_rn(tok.x, emb.x), __fadd_rn(tok.y, emb.y), __fadd_rn(tok.z, emb.z), __fadd_rn(tok.w, emb.w)));
+    }
+}
+
 // ---- 64 x 64 fp32 tile GEMM with functor operands:  C(m, n) = sum_k A(m, k) * B(k, n)  over k in this CTA's split ------
 template <class ALoad, class BLoad, class Epi>
 __global__ void __launch_bounds__(256) st_tile_gemm_kernel(long long M, int N, long long K, long long k_per_split,
@@ -235,10 +267,13 @@ long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
 
 // the streaming kernel alone over columns [0, c_end) (st_embed_tc.cu runs the temporal half on the tensor cores)
 cudaError_t launch_st_embed_spatial(const StEmbedParams& P, int c_end, cudaStream_t s) {
-    long long blocks = ceil_div(P.n * c_end, 256 * 4);
+    const auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    const bool vec = P.D % 16 == 0 && c_end % 4 == 0 && al16(P.tokens) && al16(P.out) && al16(P.ex) && al16(P.ey) && al16(P.mod);
+    long long blocks = ceil_div(P.n * (vec ? c_end / 4 : c_end), 256 * 4);
     if (blocks > 148 * 16) blocks = 148 * 16;
     if (blocks < 1) blocks = 1;
-    st_embed_spatial_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(P, c_end);
+    if (vec) st_embed_spatial_vec4_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(P, c_end);
+    else st_embed_spatial_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(P, c_end);
     return cudaGetLastError();
 }
 
