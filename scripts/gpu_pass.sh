@@ -1,7 +1,7 @@
 #!/bin/bash
 # round-2 GPU pass: tests + smoke, then the bench lines of the reworked kernels and a launch list of the projection
 mkdir -p gpurun_out
-T=${1:-r02v}
+T=${1:-r02x}
 timeout 1200 python -m pytest tests -m gpu -q -s 2>&1 | tail -30 > gpurun_out/${T}_pytest.txt
 tail -3 gpurun_out/${T}_pytest.txt
 timeout 300 python __graft_entry__.py smoke 2>&1 | tail -3
