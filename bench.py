@@ -448,6 +448,49 @@ def eager_cuda_baseline(wl, n, device, steps=3, warmup=2):
             "what": what + "; fwd+bwd, CUDA events, same B200", "peak_mem_gib": round(peak_gib, 1)}
 
 
+def encoder_default_ab(device, log2_points=20):
+    """The whole module a user of the reference calls -- Grid4DEncoder(DeepEarthConfig()) with every default (reference
+    geometry: 16 x 3-D + 8 x 1-D nearest-cell levels, projection at hidden_dim 768) -- forward + backward over 2^20 points: the
+    UNMODIFIED reference classes (oracle/_ref) in PyTorch-CUDA eager against ours with the same state dict, in fp32 and under
+    torch.autocast(bfloat16) (the reference's training mode, hpc/train_distrbuted.py:284)."""
+    import deepearth_b200 as de
+    from oracle.ref_loader import load_reference_models
+    ref = load_reference_models()
+    if ref is None:
+        return {"unavailable": "oracle/_ref not built"}
+    n = 2 ** log2_points
+    torch.manual_seed(1234)
+    enc_ref = ref.Grid4DEncoder(ref.DeepEarthConfig()).to(device)
+    enc = de.Grid4DEncoder(de.DeepEarthConfig()).to(device)
+    enc.load_state_dict(enc_ref.state_dict())
+    g = torch.Generator(device=device).manual_seed(5)
+    xyzt = torch.rand((n, 4), device=device, generator=g)
+    gout = torch.randn((n, enc.projection[-1].out_features), device=device, generator=g)
+    with torch.no_grad():
+        a, b = enc_ref(xyzt[:65536]), enc(xyzt[:65536])
+        rel = float((a - b).abs().max()) / float(a.abs().max())
+
+    def step(m, amp):
+        def run():
+            m.zero_grad(set_to_none=True)
+            if amp:
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    y = m(xyzt)
+                y.backward(gout.to(y.dtype))
+            else:
+                m(xyzt).backward(gout)
+        return run
+    out = {"points": n, "hidden_dim": int(enc.projection[0].out_features), "forward_max_rel_diff_vs_reference_fp32": rel}
+    for tag, amp in (("fp32", False), ("autocast_bf16", True)):
+        ms_ref = _time_cuda(step(enc_ref, amp), steps=3, warmup=1)
+        ms_ours = _time_cuda(step(enc, amp), steps=5, warmup=2)
+        out[tag] = {"reference_eager_ms": ms_ref, "ours_ms": ms_ours, "speedup": ms_ref / ms_ours,
+                    "ours_mpoints_per_s": n / ms_ours / 1e3, "reference_mpoints_per_s": n / ms_ref / 1e3}
+    out["what"] = ("Grid4DEncoder(DeepEarthConfig()) forward + backward, same state dict, same batch, same B200: unmodified reference "
+                   "classes (oracle/_ref) in eager PyTorch vs deepearth_b200 (hash grids + the 768-wide projection on tcgen05 / TMA)")
+    return out
+
+
 def _time_cuda(fn, steps=5, warmup=2):
     for _ in range(warmup):
         fn()
@@ -1084,6 +1127,8 @@ def run_extra_only(args):
         out = {"c2": eager_cuda_baseline(dict(WORKLOADS["c2"]), 2 ** 22, ctx.device)}
         torch.cuda.empty_cache()
         out["c1r"] = eager_cuda_baseline(dict(WORKLOADS["c1r"]), 2 ** 22, ctx.device)
+        torch.cuda.empty_cache()
+        out["encoder_default"] = encoder_default_ab(ctx.device)
     else:
         raise SystemExit(f"unknown extra {name!r}")
     print(json.dumps(out), flush=True)
