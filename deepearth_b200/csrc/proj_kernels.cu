@@ -6,18 +6,22 @@
 // Two kernels, because a 128-row tile's hidden row (H >= 768 fp32 accumulators) does not fit tensor memory (512 columns)
 // next to the output accumulators, and the LayerNorm statistics need the whole row before any of it can be normalised:
 //
-//   proj_hidden_kernel<K1>   x (n, K1) fp32  ->  a = GELU(LN(W1 x + b1)) (n, H) bf16.   The first Linear is small (K1 = 48
-//       or 128), so it is simply run TWICE per tile in 128-column chunks: pass 1 reads the chunks back from TMEM only to
-//       accumulate the row statistics (chunk-wise mean / M2, merged with Chan's formula -- no E[h^2] - mean^2 cancellation),
-//       pass 2 recomputes each chunk, normalises, applies GELU and writes bf16.  The pre-activation never exists in
-//       memory; the tile's features are read once, the hidden row is written once.  W1 chunks are staged through a
-//       double buffer while the previous chunk's epilogue runs.
+//   proj_hidden_kernel<K1, NT>   x (n, K1) fp32  ->  a = GELU(LN(W1 x + b1)) (n, H) bf16.   The first Linear is small
+//       (K1 = 48 or 128), so it is simply run TWICE per tile in 128-column chunks: pass 1 reads the chunks back from TMEM only
+//       to accumulate the row statistics (chunk-wise mean / M2, merged with Chan's formula -- no E[h^2] - mean^2
+//       cancellation), pass 2 recomputes each chunk, normalises, applies GELU and writes bf16.  The pre-activation never
+//       exists in memory; the tile's features are read once, the hidden row is written once.  W1 chunks arrive by TMA as a
+//       continuous stream through a double buffer, one epilogue ahead; two threads per row; the epilogue runs on packed fp32
+//       pairs (FFMA2 / FADD2 / FMUL2), software-pipelined 16-column TMEM pieces and one 32-byte store per piece.
 //
-//   gemm_bf16_tma_kernel     C (M, N) = A (M, K) . B (N, K)^T [+ bias]: the second Linear (and, with other operands, the
-//       GEMMs of the backward pass).  Persistent, warp specialised: warp 0 issues TMA loads (cp.async.bulk.tensor, 128 B
-//       swizzle) into a 4-stage shared-memory ring, warp 1 issues tcgen05.mma (M = 128, N = 256, K = 16) into one of two
-//       256-column TMEM accumulators, warps 4..7 drain the other accumulator (tcgen05.ld, bias, 32-byte stores), so the
-//       epilogue of tile i overlaps the mainloop of tile i + 1.
+//   gemm_bf16_tma_kernel<A_MN, B_MN, EPI, MC>   C (M, N) = A (M, K) . B (N, K)^T [+ bias] [+ residual]: the second Linear
+//       (and, with other operands, the GEMMs of the backward pass and of st_embed_tc.cu).  Persistent, warp specialised: warp
+//       0 issues TMA loads (cp.async.bulk.tensor, 128 B swizzle) into the operand ring, warp 1 issues tcgen05.mma into one of
+//       two 256-column TMEM accumulators, warps 4..11 drain the other one, so the epilogue of tile i overlaps the mainloop of
+//       tile i + 1.  MC = 2 (default): CTA pairs -- cta_group::2 MMAs with M = 256, each CTA stages its 128 rows of A and
+//       half of B (6-stage ring of 32 KB); MC = 1: single CTAs, M = 128 (4 stages of 48 KB).  fp32 output leaves through
+//       swizzled shared memory and TMA tensor stores; split-K partial sums by red.global.add.v4.f32; the contraction may run
+//       over operand segments (GemmParams::n_seg: split-precision products).
 //
 // Operand layouts follow cute::UMMA (CUTLASS 4.x, cute/atom/mma_traits_sm100.hpp): K-major SWIZZLE_128B tiles are 8-row x
 // 128-byte atoms (stride byte offset 1024), exactly what a TMA box {64 bf16, rows} with CU_TENSOR_MAP_SWIZZLE_128B writes.
