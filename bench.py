@@ -668,7 +668,7 @@ def projection_bench(device, log2_points=20, in_dim=128, hidden=768):
                       "hbm_gbs_fp32_out": gemm_bytes / ms_gemm / 1e6, "hbm_frac_fp32_out": gemm_bytes / ms_gemm / 1e6 / hbm,
                       "ms_bf16_out": ms_gemm16, "tflops_bf16_out": tf16, "frac_of_bf16_burst_bf16_out": tf16 / burst,
                       "peak_source": "MEASURED_PEAKS.json bf16_tflops / bf16_tflops_sustained" if peaks else "fallback 1590 / 1400",
-                      "what": "y (n, H) = a (n, H) bf16 . W2^T + b2: persistent TMA + tcgen05 kernel, 128 x 256 tiles; with fp32 output the "
+                      "what": "y (n, H) = a (n, H) bf16 . W2^T + b2: persistent TMA + tcgen05 kernel, CTA pairs (256 x 256 tiles); with fp32 output the "
                               "kernel writes 4 B per 2 H flop (H = 768: 3 KB per 1.18 MFLOP), so HBM binds before the tensor cores do"},
             "torch_cublas_fp32_fwd_bwd_ms": ms_t32, "torch_cublas_bf16_autocast_fwd_bwd_ms": ms_amp,
             "speedup_vs_cublas_fp32": ms_t32 / ms_step, "speedup_vs_cublas_bf16_autocast": ms_amp / ms_step,

@@ -284,8 +284,9 @@ DE_API int de_mlp_head_backward(const float* x, const float* grad_y, int64_t n_p
  *   a = GELU( LN( W1 x + b1 ) )   one tcgen05 kernel: x (n, in_dim) fp32 read once, a (n, hidden) bf16 written once; the
  *                                 first Linear runs twice per 128-row tile in 128-column TMEM chunks (pass 1 = LayerNorm
  *                                 statistics, pass 2 = normalise + GELU), so the pre-activation never exists in memory;
- *   y = W2 a + b2                 persistent TMA (cp.async.bulk.tensor, 128 B swizzle) + tcgen05.mma GEMM, 128 x 256 tiles,
- *                                 double-buffered TMEM accumulators, fp32 output.
+ *   y = W2 a + b2                 persistent TMA (cp.async.bulk.tensor, 128 B swizzle) + tcgen05.mma GEMM: CTA pairs
+ *                                 (cta_group::2, 256 x 256 tiles), double-buffered TMEM accumulators, fp32 output through
+ *                                 TMA tensor stores.
  * in_dim in {32, 48, 64, 96, 128}; out_dim a multiple of 8.  w1_bf16 (hidden, in_dim), w2_bf16 (out_dim, hidden): bf16 in
  * nn.Linear.weight layout.  hidden_bf16: (n, hidden) bf16 device buffer (the activations the backward needs);
  * row_stats: optional (n, 2) fp32 {mean, rstd} of the pre-LayerNorm rows.
