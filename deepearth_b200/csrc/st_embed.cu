@@ -209,7 +209,8 @@ struct Dw2Epi {
 // ---- column sums over tokens:  o1[c] += sum_m f[m, c] (* s[m]),  o2[c] += sum_m f[m, c] ------------------------------
 __global__ void __launch_bounds__(256) st_colsum_kernel(const float* __restrict__ f, long long n, int n_cols, long long stride,
                                                         int col0, const float* __restrict__ scale, float* o_scaled,
-                                                        float* o_plain, long long rows_per_cta) {
+                                                        float* o_plain, long long rows_per_cta, float* o_plain_hi = nullptr,
+                                                        int hi_col0 = 0) {
     __shared__ float s1[8][33], s2[8][33];
     const int c = blockIdx.x * 32 + (threadIdx.x & 31);
     const int r = threadIdx.x >> 5;
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(256) st_colsum_kernel(const float* __restrict_
         for (int i = 1; i < 8; ++i) { a1 += s1[i][threadIdx.x]; a2 += s2[i][threadIdx.x]; }
         if (o_scaled) atomicAdd(o_scaled + c, a1);
         if (o_plain) atomicAdd(o_plain + c, a2);
+        if (o_plain_hi && c >= hi_col0) atomicAdd(o_plain_hi + (c - hi_col0), a2);      // a second consumer of the upper columns
     }
 }
 
@@ -293,10 +295,11 @@ cudaError_t launch_st_embed_forward(const StEmbedParams& P, cudaStream_t s) {
 cudaError_t launch_st_embed_backward_common(const StEmbedBwdParams& P, cudaStream_t s) {
     const int Dh = P.D / 2, Dq = P.D / 4;
     cudaError_t e = cudaSuccess;
+    const bool b2_with_mod = P.d_mod && P.t && P.d_b2;      // d(b2)[j] = sum_m g[m, D/2 + j]: the upper half of the same column sums
     if (P.d_mod) {          // d(modality)[c] = sum_m g[m, c]
         const long long rows = 4096;
         dim3 grid(static_cast<unsigned>(ceil_div(P.D, 32)), static_cast<unsigned>(ceil_div(P.n, rows)));
-        st_colsum_kernel<<<grid, 256, 0, s>>>(P.g, P.n, P.D, P.D, 0, nullptr, nullptr, P.d_mod, rows);
+        st_colsum_kernel<<<grid, 256, 0, s>>>(P.g, P.n, P.D, P.D, 0, nullptr, nullptr, P.d_mod, rows, b2_with_mod ? P.d_b2 : nullptr, Dh);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     if (P.pos && P.d_ex && P.d_ey) {
@@ -306,7 +309,7 @@ cudaError_t launch_st_embed_backward_common(const StEmbedBwdParams& P, cudaStrea
             P.g, P.pos, P.pos_stride, P.n, P.D, P.R, P.d_ex, P.d_ey, rows);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
-    if (P.t && P.d_b2) {    // d(b2)[j] = sum_m g[m, D/2 + j]
+    if (P.t && P.d_b2 && !b2_with_mod) {
         const long long rows = 4096;
         dim3 grid(static_cast<unsigned>(ceil_div(Dh, 32)), static_cast<unsigned>(ceil_div(P.n, rows)));
         st_colsum_kernel<<<grid, 256, 0, s>>>(P.g, P.n, Dh, P.D, Dh, nullptr, nullptr, P.d_b2, rows);
