@@ -314,8 +314,12 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_n = (P.N + kGemmBN - 1) / kGemmBN;
     const long long tiles_m = (P.M + kGemmBM - 1) / kGemmBM;
-    const int k_blocks_all = static_cast<int>((P.K + kGemmBK - 1) / kGemmBK);
+    // With operand segments a split is a range of k-blocks INSIDE a segment, walked once per segment (small-term segments
+    // first): every work item then ends with its own share of the large a0 b0 products instead of some items holding nothing
+    // else -- the tensor core truncates the accumulator once per MMA, so what counts is how many MMAs run at full magnitude.
+    const int k_blocks_all = P.n_seg ? P.seg_blocks : static_cast<int>((P.K + kGemmBK - 1) / kGemmBK);
     const int kb_per = (k_blocks_all + P.k_splits - 1) / P.k_splits;          // host guarantees every split is non-empty
+    const int seg_rep = P.n_seg ? P.n_seg : 1;
     const long long tiles_mc = (tiles_m + MC - 1) / MC;                        // MC vertically adjacent tiles per cluster
     const long long n_tiles = tiles_mc * tiles_n * P.k_splits;                 // work items: (output tile [pair], K split)
     const uint32_t rank = MC > 1 ? cluster_rank() : 0u;
@@ -382,8 +386,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             const long long tile = work / P.k_splits;
             const int split = static_cast<int>(work - tile * P.k_splits);
             const int m0 = static_cast<int>((tile / tiles_n) * MC + rank) * kGemmBM, n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
-            const int kb_end = min(k_blocks_all, (split + 1) * kb_per);
-            for (int kb = split * kb_per; kb < kb_end; ++kb) {
+            const int kb_begin = split * kb_per, kb_len = min(k_blocks_all, (split + 1) * kb_per) - kb_begin;
+            for (int it = 0; it < seg_rep * kb_len; ++it) {
+                const int sg = it / kb_len, kb = kb_begin + (it - sg * kb_len);
                 pf_step();
                 mbar_wait(&s_empty[stage], phase ^ 1u);
                 unsigned char* sa = smem + stage * kGemmStageBytes;
@@ -391,7 +396,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 // coordinates of this k-block in the operands (operand segments: see GemmParams)
                 int ka = kb * kGemmBK, kbb = kb * kGemmBK, am0 = m0, bn0 = n0;
                 if (P.n_seg) {
-                    const int sg = kb / P.seg_blocks, within = (kb - sg * P.seg_blocks) * kGemmBK;
+                    const int within = kb * kGemmBK;
                     if constexpr (A_MN) { ka = within; am0 = m0 + static_cast<int>(P.seg_a[sg] * P.seg_stride_a); }
                     else ka = static_cast<int>(P.seg_a[sg] * P.seg_stride_a) + within;
                     if constexpr (B_MN) { kbb = within; bn0 = n0 + static_cast<int>(P.seg_b[sg] * P.seg_stride_b); }
@@ -448,7 +453,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             const uint32_t kIdesc = idesc_bf16(kGemmBM * MC, gemm_n_eff<MC>(P.full_n ? kGemmBN : n_left), A_MN != 0, B_MN != 0);
             mbar_wait(&s_tempty[as], aphase ^ 1u);                  // epilogue has drained this accumulator
             tc_fence_after();
-            for (int kb = kb_begin; kb < kb_end; ++kb) {
+            const int n_it = seg_rep * (kb_end - kb_begin);
+            for (int it = 0; it < n_it; ++it) {
                 mbar_wait(&s_full[stage], phase);
                 tc_fence_after();
                 const uint32_t a0 = smem_u32(smem + stage * kGemmStageBytes);
@@ -459,15 +465,15 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                     // 1024 B atoms further (LBO = 8192 B between 64-wide MN blocks, SBO = 1024 B between 8-row K groups)
                     const uint64_t da = A_MN ? umma_desc_sw128(a0 + k * 2048, 8192, 1024) : umma_desc_sw128(a0 + k * 32, 16, 1024);
                     const uint64_t db = B_MN ? umma_desc_sw128(b0 + k * 2048, 8192, 1024) : umma_desc_sw128(b0 + k * 32, 16, 1024);
-                    if constexpr (MC == 2) umma_bf16_pair(tmem + as * kGemmBN, da, db, kIdesc, (kb > kb_begin || k) ? 1u : 0u);
-                    else umma_bf16(tmem + as * kGemmBN, da, db, kIdesc, (kb > kb_begin || k) ? 1u : 0u);
+                    if constexpr (MC == 2) umma_bf16_pair(tmem + as * kGemmBN, da, db, kIdesc, (it > 0 || k) ? 1u : 0u);
+                    else umma_bf16(tmem + as * kGemmBN, da, db, kIdesc, (it > 0 || k) ? 1u : 0u);
                 }
                 if constexpr (MC == 2) {
                     umma_commit_pair(&s_empty[stage], 3);            // the slot is refilled by BOTH producers: tell both
-                    if (kb == kb_end - 1) umma_commit_pair(&s_tfull[as], 3);       // each CTA drains its own half
+                    if (it == n_it - 1) umma_commit_pair(&s_tfull[as], 3);         // each CTA drains its own half
                 } else {
                     umma_commit(&s_empty[stage]);                    // frees the slot when these MMAs have read it
-                    if (kb == kb_end - 1) umma_commit(&s_tfull[as]); // accumulator complete
+                    if (it == n_it - 1) umma_commit(&s_tfull[as]);   // accumulator complete
                 }
                 if (++stage == kGemmStages) { stage = 0; phase ^= 1u; }
             }
@@ -758,7 +764,7 @@ cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long l
     if (!ok) return cudaErrorInvalidValue;
     const long long units = ((tiles_m + mc - 1) / mc) * tiles_n;           // scheduling units: tiles or vertical tile pairs
     const long long max_units = n_sms / mc;
-    const long long k_blocks = (P.K + kGemmBK - 1) / kGemmBK;
+    const long long k_blocks = P.n_seg ? P.seg_blocks : (P.K + kGemmBK - 1) / kGemmBK;      // what the splits cut (see the kernel)
     long long splits = 1;
     if (epi == 2) {
         // fill the machine ONCE: units * splits <= the resident CTAs (pairs).  Rounding up instead (9 splits of 9 tile pairs
@@ -771,7 +777,7 @@ cudaError_t launch_gemm_bf16(const void* a, long long lda, const void* b, long l
     }
     P.k_splits = static_cast<int>(splits);
     static const int prefetch = []() { const char* e = getenv("DE_GEMM_PREFETCH"); return (e && *e) ? (atoi(e) != 0) : 0; }();   // B200 r02g: 13.7 ms with, 11.9 ms without
-    P.prefetch = prefetch;
+    P.prefetch = prefetch && !P.n_seg;
     static const int full_n = []() { const char* e = getenv("DE_GEMM_FULL_N"); return (e && *e) ? (atoi(e) != 0) : 0; }();
     P.full_n = full_n;
     const long long work = units * splits;

@@ -152,7 +152,8 @@ def test_cuda_module_large_vs_torch_eager(gold):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("D,n,with_mod", [(128, 1000, True), (256, 64 * 7 + 3, False), (512, 70001, True), (2048, 3000, True)])
+@pytest.mark.parametrize("D,n,with_mod", [(128, 1000, True), (256, 64 * 7 + 3, False), (512, 70001, True), (2048, 3000, True),
+                                          (1024, 2 * 65536 + 777, True)])      # the last one: three token slabs, ragged tail
 def test_tensor_core_mlp_matches_fp32_path_and_fp64(D, n, with_mod):
     """The temporal MLP on the tensor cores (split-bf16 products, csrc/st_embed_tc.cu; the default when D % 128 == 0) against the
     fp32 SIMT path (tensor_core_mlp=False) and against an fp64 evaluation: forward and every parameter gradient, ragged token
@@ -200,7 +201,7 @@ def test_tensor_core_mlp_matches_fp32_path_and_fp64(D, n, with_mod):
     for k, r in ref.items():
         s = float(r.abs().max())
         worst[k] = (float((grads[0][k].double() - r).abs().max()) / s, float((grads[1][k].double() - r).abs().max()) / s)
-        assert worst[k][0] <= GRAD_TOL and worst[k][1] <= GRAD_TOL, (k, worst[k])
+        assert worst[k][0] <= 1e-5 and worst[k][1] <= 1e-5, (k, worst[k])       # B200: both paths <= 3e-6 of max
     for k in grads[0]:
         if k not in ref:                                                               # tables, modality: shared kernels
             assert float((grads[0][k] - grads[1][k]).abs().max()) <= 1e-6 * max(float(grads[1][k].abs().max()), 1e-30), k
