@@ -387,8 +387,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             const int split = static_cast<int>(work - tile * P.k_splits);
             const int m0 = static_cast<int>((tile / tiles_n) * MC + rank) * kGemmBM, n0 = static_cast<int>(tile % tiles_n) * kGemmBN;
             const int kb_begin = split * kb_per, kb_len = min(k_blocks_all, (split + 1) * kb_per) - kb_begin;
-            for (int it = 0; it < seg_rep * kb_len; ++it) {
-                const int sg = it / kb_len, kb = kb_begin + (it - sg * kb_len);
+            for (int sg = 0, kb = kb_begin, it = 0; it < seg_rep * kb_len; ++it, ++kb) {
+                if (kb == kb_begin + kb_len) { kb = kb_begin; ++sg; }          // next segment over the same k-block range
                 pf_step();
                 mbar_wait(&s_empty[stage], phase ^ 1u);
                 unsigned char* sa = smem + stage * kGemmStageBytes;
