@@ -1088,8 +1088,9 @@ DE_API int de_st_embedding_forward_tc(const float* tokens, int64_t n_tokens, int
     if (t && (!t_w1 || !t_b1 || !t_w2 || !t_b2)) return fail(DE_EINVAL, "st_embedding_tc: temporal positions without MLP parameters");
     if (t && (!workspace || workspace_bytes < de::st_embed_tc_workspace_bytes(n_tokens, dim, false)))
         return fail(DE_EINVAL, "st_embedding_tc: workspace of %zu bytes, %zu needed", workspace_bytes, de::st_embed_tc_workspace_bytes(n_tokens, dim, false));
-    if (t && (reinterpret_cast<uintptr_t>(workspace) % 256 || reinterpret_cast<uintptr_t>(tokens) % 16 || reinterpret_cast<uintptr_t>(out) % 16))
-        return fail(DE_EALIGN, "st_embedding_tc: workspace must be 256-byte, tokens / out 16-byte aligned");
+    if (t && (reinterpret_cast<uintptr_t>(workspace) % 256 || reinterpret_cast<uintptr_t>(tokens) % 16 || reinterpret_cast<uintptr_t>(out) % 16 ||
+              reinterpret_cast<uintptr_t>(t_w1) % 16 || reinterpret_cast<uintptr_t>(t_b1) % 16))
+        return fail(DE_EALIGN, "st_embedding_tc: workspace must be 256-byte, tokens / out / t_w1 / t_b1 16-byte aligned");
     if (n_tokens > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "st_embedding_tc: n_tokens too large");
     de::StEmbedParams P{};
     P.tokens = tokens; P.pos = pos; P.t = t; P.ex = embed_x; P.ey = embed_y; P.w1 = t_w1; P.b1 = t_b1; P.w2 = t_w2; P.b2 = t_b2;
@@ -1115,8 +1116,9 @@ DE_API int de_st_embedding_backward_tc(const float* grad_out, int64_t n_tokens, 
         return fail(DE_EINVAL, "st_embedding_backward_tc: temporal branch needs w1, b1, w2 and the three weight gradients");
     if (t && (!workspace || workspace_bytes < de::st_embed_tc_workspace_bytes(n_tokens, dim, true)))
         return fail(DE_EINVAL, "st_embedding_backward_tc: workspace of %zu bytes, %zu needed", workspace_bytes, de::st_embed_tc_workspace_bytes(n_tokens, dim, true));
-    if (t && (reinterpret_cast<uintptr_t>(workspace) % 256 || reinterpret_cast<uintptr_t>(grad_t_w2) % 16))
-        return fail(DE_EALIGN, "st_embedding_backward_tc: workspace must be 256-byte, grad_t_w2 16-byte aligned");
+    if (t && (reinterpret_cast<uintptr_t>(workspace) % 256 || reinterpret_cast<uintptr_t>(grad_t_w2) % 16 ||
+              reinterpret_cast<uintptr_t>(t_w1) % 16 || reinterpret_cast<uintptr_t>(t_b1) % 16))
+        return fail(DE_EALIGN, "st_embedding_backward_tc: workspace must be 256-byte, grad_t_w2 / t_w1 / t_b1 16-byte aligned");
     if (n_tokens > 0x7fffffffll) return fail(DE_EUNSUPPORTED, "st_embedding_backward_tc: n_tokens too large");
     de::StEmbedBwdParams P{};
     P.g = grad_out; P.pos = pos; P.t = t; P.w1 = t_w1; P.b1 = t_b1; P.w2 = t_w2; P.dpre = nullptr;

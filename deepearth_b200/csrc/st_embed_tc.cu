@@ -30,6 +30,15 @@ __device__ __forceinline__ void split3(float x, __nv_bfloat16& p0, __nv_bfloat16
     p2 = __float2bfloat16_rn(__fsub_rn(r1, __bfloat162float(p1)));
 }
 
+// eight values -> their three parts, each as one 16-byte store
+__device__ __forceinline__ void split3_store8(const float (&x)[8], __nv_bfloat16* d, long long part_stride) {
+    __align__(16) __nv_bfloat16 p[3][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) split3(x[i], p[0][i], p[1][i], p[2][i]);
+#pragma unroll
+    for (int q = 0; q < 3; ++q) *reinterpret_cast<uint4*>(d + q * part_stride) = *reinterpret_cast<const uint4*>(p[q]);
+}
+
 // dst (rows, 3 cols) bf16 = the three parts of src(r, c) = src[r * ld_r + c * ld_c], side by side
 __global__ void __launch_bounds__(256) split3_kernel(const float* __restrict__ src, long long ld_r, long long ld_c, long long rows,
                                                      int cols, __nv_bfloat16* __restrict__ dst) {
@@ -45,19 +54,39 @@ __global__ void __launch_bounds__(256) split3_kernel(const float* __restrict__ s
     }
 }
 
-// dst (rows, 3 Dh) = split3(GELU(t[r] * w1[k] + b1[k]))
+// same for rows that are contiguous in memory (ld_c = 1), eight columns per thread: cols % 8 == 0, 16-byte aligned rows
+__global__ void __launch_bounds__(256) split3_rows8_kernel(const float* __restrict__ src, long long ld_r, long long rows, int cols,
+                                                           __nv_bfloat16* __restrict__ dst) {
+    const int c8n = cols / 8;
+    const long long total = rows * c8n;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const long long r = e / c8n;
+        const int c = static_cast<int>(e - r * c8n) * 8;
+        const float4 a = __ldcs(reinterpret_cast<const float4*>(src + r * ld_r + c)), b = __ldcs(reinterpret_cast<const float4*>(src + r * ld_r + c) + 1);
+        const float x[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        split3_store8(x, dst + r * 3 * cols + c, cols);
+    }
+}
+
+// dst (rows, 3 Dh) = split3(GELU(t[r] * w1[k] + b1[k])), eight hidden units per thread (Dh % 8 == 0)
 __global__ void __launch_bounds__(256) split3_hidden_kernel(const float* __restrict__ t, const float* __restrict__ w1,
                                                             const float* __restrict__ b1, long long rows, int Dh,
                                                             __nv_bfloat16* __restrict__ dst) {
-    const long long total = rows * Dh;
+    const int k8n = Dh / 8;
+    const long long total = rows * k8n;
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
     for (long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; e < total; e += stride) {
-        const long long r = e / Dh;
-        const int k = static_cast<int>(e - r * Dh);
-        __nv_bfloat16 p0, p1, p2;
-        split3(gelu_erf(__fmaf_rn(__ldg(t + r), __ldg(w1 + k), __ldg(b1 + k))), p0, p1, p2);
-        __nv_bfloat16* d = dst + r * 3 * Dh + k;
-        d[0] = p0; d[Dh] = p1; d[2 * Dh] = p2;
+        const long long r = e / k8n;
+        const int k = static_cast<int>(e - r * k8n) * 8;
+        const float tr = __ldg(t + r);
+        const float4 wa = __ldg(reinterpret_cast<const float4*>(w1 + k)), wb = __ldg(reinterpret_cast<const float4*>(w1 + k) + 1);
+        const float4 ba = __ldg(reinterpret_cast<const float4*>(b1 + k)), bb = __ldg(reinterpret_cast<const float4*>(b1 + k) + 1);
+        const float w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w}, b[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+        float x[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = gelu_erf(__fmaf_rn(tr, w[i], b[i]));
+        split3_store8(x, dst + r * 3 * Dh + k, Dh);
     }
 }
 
@@ -150,7 +179,7 @@ cudaError_t launch_st_embed_forward_tc(const StEmbedParams& P, void* ws, int n_s
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     for (long long m0 = 0; m0 < P.n; m0 += slab) {
         const long long ns = P.n - m0 < slab ? P.n - m0 : slab;
-        split3_hidden_kernel<<<grid_for(ns * Dh), 256, 0, s>>>(P.t + m0, P.w1, P.b1, ns, Dh, hs);
+        split3_hidden_kernel<<<grid_for(ns * Dh / 8), 256, 0, s>>>(P.t + m0, P.w1, P.b1, ns, Dh, hs);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         GemmParams G{};
         G.M = ns; G.N = Dh; G.K = 6LL * Dh;
@@ -179,8 +208,9 @@ cudaError_t launch_st_embed_backward_tc(const StEmbedBwdParams& P, void* ws, int
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     for (long long m0 = 0; m0 < P.n; m0 += slab) {
         const long long ns = P.n - m0 < slab ? P.n - m0 : slab;
-        split3_kernel<<<grid_for(ns * Dh), 256, 0, s>>>(P.g + m0 * P.D + Dh, P.D, 1, ns, Dh, gs);
-        split3_hidden_kernel<<<grid_for(ns * Dh), 256, 0, s>>>(P.t + m0, P.w1, P.b1, ns, Dh, hs);
+        if ((reinterpret_cast<uintptr_t>(P.g) & 15) == 0) split3_rows8_kernel<<<grid_for(ns * Dh / 8), 256, 0, s>>>(P.g + m0 * P.D + Dh, P.D, ns, Dh, gs);
+        else split3_kernel<<<grid_for(ns * Dh), 256, 0, s>>>(P.g + m0 * P.D + Dh, P.D, 1, ns, Dh, gs);
+        split3_hidden_kernel<<<grid_for(ns * Dh / 8), 256, 0, s>>>(P.t + m0, P.w1, P.b1, ns, Dh, hs);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         {       // C1 (ns, Dh) = g_t . W2
             GemmParams G{};
