@@ -149,6 +149,11 @@ struct GemmParams {
     // optional: C = acc + bias + residual (fp32 store only; rows ldr floats apart)
     const float* residual;
     long long ldr;
+    // optional (fp32 store only): C(r, c) *= GELU'(row_t[r] * col_w[c] + col_b[c]) -- the temporal MLP's backward (st_embed_tc.cu);
+    // the erf evaluations run in the epilogue warps, under the next tile's mainloop
+    const float* gg_row_t;
+    const float* gg_col_w;
+    const float* gg_col_b;
     // optional operand segments (split-precision products, st_embed_tc): the contraction runs over `n_seg` segments of
     // seg_blocks 64-element k-blocks each (K = n_seg * seg_blocks * 64); segment s multiplies operand part seg_a[s] of A
     // with part seg_b[s] of B.  Parts lie side by side in the operands' COLUMNS, seg_stride_a / _b elements apart: along K

@@ -32,6 +32,7 @@
 #include "launch.h"
 #include "mlp_common.cuh"
 #include "proj_common.cuh"
+#include "st_embed_common.cuh"
 
 namespace de {
 
@@ -528,6 +529,12 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] += (col0 + j < P.N) ? __ldcs(rp + j) : 0.0f;
                     }
+                }
+                if (EPI == 0 && P.gg_row_t) {
+                    const float tr = r < P.M ? __ldg(P.gg_row_t + r) : 0.0f;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (col0 + j < P.N) v[j] *= gelu_erf_grad(__fmaf_rn(tr, __ldg(P.gg_col_w + col0 + j), __ldg(P.gg_col_b + col0 + j)));
                 }
                 if (EPI == 0 && P.tma_store) {
                     // fp32 rows through shared memory and a tensor store: the 32 lanes' 32 x 128 B leave as one box of whole

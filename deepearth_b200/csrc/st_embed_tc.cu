@@ -12,7 +12,8 @@
 // Tokens are processed in slabs so that the split operands stay a bounded workspace.
 //
 //   forward:   H'' = split3(GELU(t w1 + b1))  (slab, 3 D/2);  out[:, D/2:] = tokens + (H'' . W2''^T + (b2 + mod))   [residual epilogue]
-//   backward:  C1 = split3(g_t) . split3(W2^T)^T;  d w1, d b1 = column sums of C1 * GELU'(pre) (* t);  d W2 += split3(g_t)^T . H''
+//   backward:  dpre = (split3(g_t) . split3(W2^T)^T) * GELU'(pre)  [GELU' in the GEMM epilogue];  d w1, d b1 = column sums of dpre (* t);
+//              d W2 += split3(g_t)^T . H''
 //              (contraction over tokens: row-contracted operands, split over the CTAs, fp32 red.global.add)
 #include <cuda_bf16.h>
 
@@ -96,7 +97,9 @@ __global__ void bias_sum_kernel(const float* __restrict__ b2, const float* __res
     if (j < Dh) out[j] = mod_t ? __fadd_rn(__ldg(b2 + j), __ldg(mod_t + j)) : __ldg(b2 + j);
 }
 
-// d w1[k] += sum_m c1[m, k] * GELU'(t_m w1_k + b1_k) * t_m ;  d b1[k] += sum_m c1[m, k] * GELU'(...)
+// d w1[k] += sum_m dpre[m, k] * t_m ;  d b1[k] += sum_m dpre[m, k], dpre = c1 * GELU'(t_m w1_k + b1_k).  APPLY = false: c1 already
+// carries the GELU' factor (the GEMM epilogue applied it under its mainloop).
+template <bool APPLY>
 __global__ void __launch_bounds__(256) dpre_colsum_kernel(const float* __restrict__ c1, const float* __restrict__ t,
                                                           const float* __restrict__ w1, const float* __restrict__ b1, long long n,
                                                           int Dh, float* d_w1, float* d_b1, long long rows_per_cta) {
@@ -110,7 +113,8 @@ __global__ void __launch_bounds__(256) dpre_colsum_kernel(const float* __restric
         const float w = __ldg(w1 + c), b = __ldg(b1 + c);
         for (long long m = m_begin + r; m < m_end; m += 8) {
             const float tm = __ldg(t + m);
-            const float v = __ldcs(c1 + m * Dh + c) * gelu_erf_grad(__fmaf_rn(tm, w, b));
+            float v = __ldcs(c1 + m * Dh + c);
+            if constexpr (APPLY) v *= gelu_erf_grad(__fmaf_rn(tm, w, b));
             a2 += v;
             a1 = fmaf(v, tm, a1);
         }
@@ -215,6 +219,7 @@ cudaError_t launch_st_embed_backward_tc(const StEmbedBwdParams& P, void* ws, int
         {       // C1 (ns, Dh) = g_t . W2
             GemmParams G{};
             G.M = ns; G.N = Dh; G.K = 6LL * Dh; G.c = c1; G.ldc = Dh;
+            G.gg_row_t = P.t + m0; G.gg_col_w = P.w1; G.gg_col_b = P.b1;         // C1 leaves the GEMM as dpre
             set_segments(G, Dh / 64, Dh);
             G.a_rows = ns; G.a_cols = 3LL * Dh; G.b_rows = Dh; G.b_cols = 3LL * Dh;
             if ((e = launch_gemm_bf16(gs, 3LL * Dh, w2ts, 3LL * Dh, 0, G, 0, n_sms, s)) != cudaSuccess) return e;
@@ -222,7 +227,7 @@ cudaError_t launch_st_embed_backward_tc(const StEmbedBwdParams& P, void* ws, int
         {       // d w1, d b1
             const long long rows = 4096;
             dim3 grid(static_cast<unsigned>((Dh + 31) / 32), static_cast<unsigned>(ceil_div_ll(ns, rows)));
-            dpre_colsum_kernel<<<grid, 256, 0, s>>>(c1, P.t + m0, P.w1, P.b1, ns, Dh, P.d_w1, P.d_b1, rows);
+            dpre_colsum_kernel<false><<<grid, 256, 0, s>>>(c1, P.t + m0, P.w1, P.b1, ns, Dh, P.d_w1, P.d_b1, rows);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
         {       // d W2[j][k] += sum_m g_t[m, j] h[m, k]: the tokens are the contraction (rows of both operands)
