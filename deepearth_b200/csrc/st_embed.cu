@@ -250,11 +250,26 @@ __global__ void __launch_bounds__(256) st_embed_table_grad_kernel(const float* _
     __syncthreads();
     const long long m_begin = static_cast<long long>(blockIdx.y) * rows_per_cta;
     const long long m_end = (m_begin + rows_per_cta < n) ? m_begin + rows_per_cta : n;
-    if (cb + lane < Dq)
-        for (long long m = m_begin + r; m < m_end; m += 8) {
+    if (cb + lane < Dq) {
+        long long m = m_begin + r;
+        for (; m + 24 < m_end; m += 32) {                        // four tokens in flight per thread
+            float pv[4], gv[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                pv[u] = __ldg(pos + (m + 8 * u) * pos_stride + which);
+                gv[u] = __ldcs(g + (m + 8 * u) * D + which * Dq + cb + lane);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int row = table_row(pv[u], R);
+                if (row >= 0) atomicAdd(&slab[row * 32 + lane], gv[u]);
+            }
+        }
+        for (; m < m_end; m += 8) {
             const int row = table_row(__ldg(pos + m * pos_stride + which), R);
             if (row >= 0) atomicAdd(&slab[row * 32 + lane], __ldg(g + m * D + which * Dq + cb + lane));
         }
+    }
     __syncthreads();
     float* dst = which ? d_ey : d_ex;
     for (int i = threadIdx.x; i < R * 32; i += 256) {
